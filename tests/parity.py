@@ -1,0 +1,42 @@
+"""Tolerance helpers shared by the CPU (oracle vs golden) and GPU (CUDA vs oracle) tests.
+
+Stated fp32 tolerances (BASELINE.json north_star):
+  affine family : |a-b| <= 1e-6 + 1e-5*|b|
+  splines       : |a-b| <= 1e-5 + 1e-4*|b|   (log-dets: atol scaled by the number of summed elements)
+"""
+import torch
+
+AFFINE = dict(rtol=1e-5, atol=1e-6)
+SPLINE = dict(rtol=1e-4, atol=1e-5)
+F64 = dict(rtol=1e-9, atol=1e-11)
+
+
+def excess(a, b, rtol, atol):
+    """max over elements of |a-b| / (atol + rtol*|b|); <= 1 passes."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    if a.numel() == 0:
+        return 0.0
+    nan_mismatch = (torch.isnan(a) != torch.isnan(b)).any().item()
+    if nan_mismatch:
+        return float("inf")
+    ok = ~torch.isnan(b)
+    return float(((a - b).abs()[ok] / (atol + rtol * b.abs()[ok])).max()) if ok.any() else 0.0
+
+
+def assert_close(a, b, rtol, atol, what=""):
+    assert tuple(a.shape) == tuple(b.shape), (what, a.shape, b.shape)
+    e = excess(a, b, rtol, atol)
+    assert e <= 1.0, "%s: error is %.3g x tolerance (rtol=%g atol=%g, max|ref|=%.3g)" % (
+        what, e, rtol, atol, float(b.abs().max()) if b.numel() else 0.0)
+
+
+def assert_grads_close(got, ref, rtol, what=""):
+    """Gradient tensors: atol scaled by the tensor's max-abs (SURVEY.md B.1 last bullet)."""
+    for name, r in ref.items():
+        g = got.get(name)
+        if r is None:
+            assert g is None or float(g.abs().max()) == 0.0, (what, name)
+            continue
+        assert g is not None, (what, name, "missing gradient")
+        scale = float(r.abs().max()) if r.numel() else 0.0
+        assert_close(g, r, rtol=rtol, atol=rtol * max(scale, 1e-30), what="%s grad[%s]" % (what, name))
