@@ -1,0 +1,159 @@
+/* libvcnf_b200.so -- C ABI of the B200 (sm_100a) bijector kernels.
+ *
+ * The reference (telegraphroad/VCNF, a `normflow` fork) is pure Python on PyTorch: there is no
+ * FFI to bind to, the "operator interface" of the hot path is the set of ATen op chains listed
+ * in SURVEY.md 2.3 (K1..K11).  Each entry point below replaces one such chain and cites it
+ * (paths relative to the reference root).  Conventions:
+ *   - every pointer is a DEVICE pointer valid on the current device unless named *_host;
+ *   - `dtype`: 0 = float32, 1 = float64 (all floating-point buffers of one call share it);
+ *   - `stream` is a cudaStream_t (NULL = legacy default stream); nothing allocates, nothing
+ *     synchronises, kernels are enqueued on `stream` and the call returns immediately;
+ *   - leading dimensions (`ld*`) are in ELEMENTS; rows are the batch (sample) axis;
+ *   - return value: 0 on success, a positive cudaError_t from the launch, or a negative
+ *     VCNF_E_* for invalid arguments.  Numerical failure is reported like the reference does,
+ *     by NaN propagation, plus the optional device-side `err_flag`.
+ */
+#ifndef VCNF_B200_H_
+#define VCNF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VCNF_F32 0
+#define VCNF_F64 1
+
+#define VCNF_E_BADARG (-1)      /* null pointer / negative size / unknown enum */
+#define VCNF_E_UNSUPPORTED (-2) /* e.g. more bins than the kernels are instantiated for */
+
+/* Column kinds for vcnf_rqs_layer_*: col_map[c] = (kind << 16) | index_within_segment */
+#define VCNF_COL_PASS 0   /* y[:, c] = x[:, c], log-det 0 */
+#define VCNF_COL_COND 1   /* spline with per-sample parameters cond_params[b, index*Pc ...] */
+#define VCNF_COL_SHARED 2 /* spline with batch-shared parameters shared_params[index*Ps ...] */
+
+/* Per-feature derivative layout (tails), see vcnf_b200/csrc/rqs_math.cuh DerivMode */
+#define VCNF_TAIL_LINEAR 0
+#define VCNF_TAIL_CIRCULAR 1
+#define VCNF_TAIL_LIST_LINEAR 2
+#define VCNF_TAIL_LIST_CIRCULAR 3
+
+int vcnf_version(void);
+/* Number of SMs the library sizes persistent grids for (148 on B200); 0 if no device. */
+int vcnf_sm_count(void);
+
+/* ---- K4/K5: rational-quadratic spline layer ------------------------------------------------
+ * Replaces normflow/utils/splines.py:20-193 as called from
+ * flows/neural_spline/coupling.py:70-125,147-159,211-240,309-343 (coupling: conditional
+ * transform on `transform_features` + unconditional CDF on `identity_features`) and
+ * flows/neural_spline/autoregressive.py:92-131 (all features conditional), INCLUDING the
+ * index_select split, the scatter merge and utils.sum_except_batch: one launch transforms
+ * whole rows and reduces the per-sample log|det|.
+ *   x, y          [B, D] (ldx, ldy)             y may not alias x
+ *   logdet        [B]; overwritten, or added to when accumulate != 0
+ *   col_map       [D] int32, see VCNF_COL_*
+ *   cond_params   [B, Tc*Pc] (ld_cond), layout feature-major: [uw(K) | uh(K) | ud(Pc-2K)]
+ *                 (coupling.py:155,310-312); uw, uh are multiplied by wh_scale (=1/sqrt(hidden)
+ *                 on the coupling path, coupling.py:314-316; 1 on the autoregressive path)
+ *   shared_params [Ts, Ps] same layout, not scaled (coupling.py:165-246)
+ *   *_modes       uint8 per segment feature (VCNF_TAIL_*), *_bounds tail bound per feature
+ *   inverse       0: spline forward (splines.py:178-193), 1: inverse (splines.py:152-177)
+ *   outside_zero  1: list tails -> out-of-range inputs give 0 (reference quirk, splines.py:50-57)
+ *   bin_out       optional int8 [B, D]: bin index, -1 out of range, -2 pass-through column
+ *   err_flag      optional device int32, bit 0 set on a negative discriminant (splines.py:164)
+ */
+int vcnf_rqs_layer_fwd(const void* x, int64_t ldx, void* y, int64_t ldy, void* logdet, int accumulate,
+                       int64_t B, int D, int K, const int32_t* col_map,
+                       const void* cond_params, int64_t ld_cond, int Tc, int Pc,
+                       const uint8_t* cond_modes, const void* cond_bounds, double wh_scale,
+                       const void* shared_params, int Ts, int Ps,
+                       const uint8_t* shared_modes, const void* shared_bounds,
+                       int inverse, int outside_zero, int8_t* bin_out, int32_t* err_flag,
+                       int dtype, void* stream);
+
+/* Bytes of scratch vcnf_rqs_layer_bwd needs for the deterministic two-stage reduction of the
+ * shared-parameter gradients (0 when Ts == 0). */
+int64_t vcnf_rqs_layer_bwd_workspace(int Ts, int Ps, int dtype);
+
+/* Backward of vcnf_rqs_layer_fwd (hand-written adjoint): given gy [B, D] and
+ * glogdet [B] writes gx [B, D], g_cond [B, Tc*Pc] (already multiplied by wh_scale where the
+ * forward scaled) and g_shared [Ts, Ps] (summed over the batch; overwritten). */
+int vcnf_rqs_layer_bwd(const void* x, int64_t ldx, const void* gy, int64_t ldgy, const void* glogdet,
+                       void* gx, int64_t ldgx, int64_t B, int D, int K, const int32_t* col_map,
+                       const void* cond_params, int64_t ld_cond, int Tc, int Pc,
+                       const uint8_t* cond_modes, const void* cond_bounds, double wh_scale,
+                       void* g_cond, int64_t ld_gcond,
+                       const void* shared_params, int Ts, int Ps,
+                       const uint8_t* shared_modes, const void* shared_bounds,
+                       void* g_shared, void* workspace,
+                       int inverse, int outside_zero, int dtype, void* stream);
+
+/* dst[b, j] = src[b, cols[j]]  (index_select split, coupling.py:78-79; Permute shuffle,
+ * flows/mixing.py:32-33,44-45).  n <= 1024. */
+int vcnf_gather_cols(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t B, int n,
+                     const int32_t* cols, int dtype, void* stream);
+/* dst[b, cols[j]] (+)= src[b, j]; columns not listed are zero-filled when accumulate == 0 and
+ * D_dst > 0 (adjoint of vcnf_gather_cols). */
+int vcnf_scatter_cols(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t B, int n,
+                      int D_dst, const int32_t* cols, int accumulate, int dtype, void* stream);
+
+/* ---- K1: affine coupling block ---------------------------------------------------------------
+ * Replaces Split -> AffineCoupling -> Merge of normflow/flows/affine/coupling.py:113-168,225-259
+ * (+ flows/reshape.py:25-29,50-55) after the conditioner: copies the conditioning half, applies
+ * the affine map to the other half and reduces the per-sample log|det| in one pass.
+ *   z, out [B, C, S] contiguous (S = H*W, or 1 for tabular data); the transformed channels are
+ *   [c2_start, c2_start + C2); param [B, np*C2, S] with shift = param[:, 0::2], raw scale =
+ *   param[:, 1::2] (coupling.py:122-123), np = 1 when scale_map == 3.
+ *   scale_map: 0 exp, 1 sigmoid, 2 sigmoid_inv, 3 none (shift only), 4 MAF sigmoid(u+2)+1e-3
+ *   (flows/affine/autoregressive.py:76-90, use swap_ts = 1: params are (scale, shift) pairs).
+ *   inverse: 0 = the layer's forward(), 1 = its inverse().  logdet [B] is overwritten. */
+int vcnf_affine_coupling_fwd(const void* z, const void* param, void* out, void* logdet, int64_t B, int C, int S,
+                             int c2_start, int C2, int scale_map, int inverse, int swap_ts, int dtype,
+                             void* stream);
+int vcnf_affine_coupling_bwd(const void* z, const void* param, const void* gout, const void* glogdet, void* gz,
+                             void* gparam, int64_t B, int C, int S, int c2_start, int C2, int scale_map,
+                             int inverse, int swap_ts, int dtype, void* stream);
+
+/* ---- K2: masked affine flow (normflow/flows/affine/coupling.py:202-222) -----------------------
+ * out = b*z + (1-b)*(z*exp(s)+t)  /  b*z + (1-b)*(z-t)*exp(-s); non-finite s, t become NaN
+ * (coupling.py:205-208); logdet[b] = +-sum (1-b)*s.  z, s, t, out [B, n]; mask [n]; s or t may be
+ * NULL (the reference's zero lambdas, coupling.py:192-198). */
+int vcnf_masked_affine_fwd(const void* z, const void* mask, const void* s, const void* t, void* out, void* logdet,
+                           int64_t B, int n, int inverse, int dtype, void* stream);
+int vcnf_masked_affine_bwd(const void* z, const void* mask, const void* s, const void* t, const void* gout,
+                           const void* glogdet, void* gz, void* gs, void* gt, int64_t B, int n, int inverse,
+                           int dtype, void* stream);
+
+/* ---- K3: constant affine / ActNorm (coupling.py:37-53, flows/normalization.py:20-38) ----------
+ * out = z*exp(s)+t / (z-t)*exp(-s) with s, t [Pn] broadcast over z [B, Pn, S].  The scalar
+ * log-det (+-S*sum(s)) is formed on the host side from the parameters.  The backward also
+ * reduces the parameter gradients over batch and spatial positions (two-stage, deterministic). */
+int vcnf_const_affine_fwd(const void* z, const void* s, const void* t, void* out, int64_t B, int Pn, int S,
+                          int inverse, int dtype, void* stream);
+int64_t vcnf_const_affine_bwd_workspace(int Pn, int dtype);
+int vcnf_const_affine_bwd(const void* z, const void* s, const void* t, const void* gout, void* gz, void* gs,
+                          void* gt, void* workspace, int64_t B, int Pn, int S, int inverse, int dtype,
+                          void* stream);
+
+/* dst[b, j, s] = src[b, perm[j], s]  (Permute, normflow/flows/mixing.py:32-54). */
+int vcnf_permute_channels(const void* src, void* dst, int64_t B, int C, int S, const int32_t* perm, int dtype,
+                          void* stream);
+/* Squeeze (normflow/flows/reshape.py:93-117).  inverse == 0: src [B, 4c, h, w] -> dst [B, c, 2h, 2w];
+ * inverse == 1: src [B, c, 2h, 2w] -> dst [B, 4c, h, w]. */
+int vcnf_squeeze(const void* src, void* dst, int64_t B, int c_small, int h_small, int w_small, int inverse,
+                 int dtype, void* stream);
+
+/* ---- K8/K10: small dense per-row linear map ---------------------------------------------------
+ * y[r, out_idx[o]] = sum_i W[o, i] * x[r, in_idx[i]] + bias[o]   (sub_bias_first: W (x - bias))
+ * rows are samples (S == 1, x [rows, D]) or pixels of an NCHW tensor (S = H*W, rows = B*S).
+ * LULinearPermute (normflow/flows/mixing.py:398-429,484-492) and Invertible1x1Conv
+ * (mixing.py:101-128); D <= 64; W [D, D] row-major; in_idx/out_idx/bias may be NULL. */
+int vcnf_small_linear(const void* x, void* y, const void* W, const void* bias, const int32_t* in_idx,
+                      const int32_t* out_idx, int64_t rows, int D, int S, int sub_bias_first, int dtype,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VCNF_B200_H_ */

@@ -1,0 +1,54 @@
+// TEST HARNESS ONLY: compiles the product's __host__ __device__ element math
+// (vcnf_b200/csrc/*_math.cuh) for the CPU so that the formulas can be checked against the oracle
+// in the GPU-less build container.  Never linked into libvcnf_b200.so.
+#include <cstdint>
+#include "../../vcnf_b200/csrc/rqs_math.cuh"
+
+using namespace vcnf;
+
+template <typename T, int KMAX>
+static void run_fwd(const T* prm, const T* v, const T* bound, int64_t n, int P, T scale,
+                    RqsElemCfg c, T* out, T* lad, int32_t* bin, int32_t* flag) {
+  for (int64_t i = 0; i < n; ++i) {
+    int b = -1, f = 0;
+    rqs_element<T, KMAX>(prm + i * P, v[i], bound[i], scale, c, out + i, lad + i, &b, &f);
+    bin[i] = b;
+    *flag |= f;
+  }
+}
+
+template <typename T, int KMAX>
+static void run_bwd(const T* prm, const T* v, const T* bound, int64_t n, int P, T scale,
+                    RqsElemCfg c, const T* gout, const T* glad, T* gv, T* gprm) {
+  for (int64_t i = 0; i < n; ++i)
+    rqs_element_bwd<T, KMAX>(prm + i * P, v[i], bound[i], scale, c, gout[i], glad[i], gv + i, gprm + i * P);
+}
+
+#define DISPATCH(T, call)                                        \
+  if (K <= 8) { call(T, 8); } else if (K <= 16) { call(T, 16); } else { call(T, 32); }
+
+extern "C" {
+
+int hostcheck_rqs_fwd(const void* prm, const void* v, const void* bound, int64_t n, int K, int mode,
+                      int inverse, int outside_zero, double scale, int is_double,
+                      void* out, void* lad, int32_t* bin) {
+  RqsElemCfg c{K, mode, inverse, outside_zero};
+  const int P = 2 * K + rqs_num_derivs(K, mode);
+  int32_t flag = 0;
+#define CALL(T, KM) run_fwd<T, KM>((const T*)prm, (const T*)v, (const T*)bound, n, P, (T)scale, c, (T*)out, (T*)lad, bin, &flag)
+  if (is_double) { DISPATCH(double, CALL) } else { DISPATCH(float, CALL) }
+#undef CALL
+  return flag;
+}
+
+int hostcheck_rqs_bwd(const void* prm, const void* v, const void* bound, int64_t n, int K, int mode,
+                      int inverse, int outside_zero, double scale, int is_double,
+                      const void* gout, const void* glad, void* gv, void* gprm) {
+  RqsElemCfg c{K, mode, inverse, outside_zero};
+  const int P = 2 * K + rqs_num_derivs(K, mode);
+#define CALL(T, KM) run_bwd<T, KM>((const T*)prm, (const T*)v, (const T*)bound, n, P, (T)scale, c, (const T*)gout, (const T*)glad, (T*)gv, (T*)gprm)
+  if (is_double) { DISPATCH(double, CALL) } else { DISPATCH(float, CALL) }
+#undef CALL
+  return 0;
+}
+}

@@ -1,0 +1,80 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports every symbol
+include/vcnf_b200.h declares, the product modules load the reference's state_dicts key for key,
+and the product refuses to compute without CUDA (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+import vcnf_b200 as nf
+from vcnf_b200 import _lib
+from cases import LAYER_CASES, MODEL_CASES
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def built():
+    from vcnf_b200 import build
+    return build.build()
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "vcnf_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(vcnf_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(built):
+    handle = ctypes.CDLL(built)
+    names = _declared()
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(handle, n), n
+    assert sorted(_lib.EXPORTED) == names          # the ctypes table covers the whole header
+    assert handle.vcnf_version() == 100
+
+
+def test_bad_arguments_are_rejected_without_a_gpu(built):
+    lib = _lib.lib()
+    assert lib.vcnf_gather_cols(None, 0, None, 0, 4, 2, None, 0, None) == -1
+    assert lib.vcnf_small_linear(None, None, None, None, None, None, 1, 4, 1, 0, 0, None) == -1
+    assert lib.vcnf_squeeze(None, None, 1, 1, 1, 1, 0, 0, None) == -1
+
+
+@pytest.mark.parametrize("name", sorted(LAYER_CASES))
+def test_layer_state_dict_keys_match_reference(name):
+    gold = torch.load(os.path.join(GOLD, "layers.pt"))[name]
+    torch.manual_seed(0)
+    layer = LAYER_CASES[name]["build"](nf)
+    layer.load_state_dict(gold["state"], strict=True)
+    assert list(layer.state_dict().keys()) == list(gold["state"].keys())
+
+
+@pytest.mark.parametrize("name", sorted(MODEL_CASES))
+def test_model_state_dict_keys_match_reference(name):
+    gold = torch.load(os.path.join(GOLD, "models.pt"))[name]
+    torch.manual_seed(0)
+    model = MODEL_CASES[name]["build"](nf)
+    model.load_state_dict(gold["state"], strict=True)
+    assert list(model.state_dict().keys()) == list(gold["state"].keys())
+
+
+def test_no_cpu_fallback():
+    layer = nf.flows.CoupledRationalQuadraticSpline(4, 1, 8)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        layer.inverse(torch.randn(3, 4))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        nf.flows.AffineCouplingBlock(nf.nets.MLP([1, 4, 2]))(torch.randn(3, 2))
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "vcnf_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f

@@ -1,0 +1,215 @@
+"""GPU parity tests: the CUDA product (through the C ABI) against (a) the golden vectors produced
+by the unmodified reference and (b) the CPU oracle on the same seeded inputs.
+
+Stated tolerances (north_star): affine family 1e-5 rel (+1e-6 abs), splines 1e-4 rel (+1e-5 abs);
+per-sample log-dets get the abs term scaled by the number of summed elements; fp64 models 1e-9.
+Spline bin indices must agree exactly with the oracle on the seeded sets (mismatch count 0)."""
+import copy
+import os
+
+import pytest
+import torch
+
+import oracle
+import vcnf_b200 as nf
+from cases import LAYER_CASES, MODEL_CASES, randomize
+from harness import eval_layer, eval_model
+from parity import assert_close, assert_grads_close, AFFINE, SPLINE
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+_cache = {}
+
+
+def gold(kind):
+    if kind not in _cache:
+        _cache[kind] = torch.load(os.path.join(GOLD, kind + ".pt"))
+    return _cache[kind]
+
+
+SPLINE_CASES = {"crqs_linear", "crqs_linear_k10_rev", "crqs_circular_str", "ccrqs_mixed", "arqs", "carqs_mixed"}
+
+
+def _tol(name, dtype):
+    if dtype == torch.float64:
+        return dict(rtol=1e-9, atol=1e-10), 1e-7
+    if name in SPLINE_CASES:
+        return SPLINE, 1e-3
+    return AFFINE, 2e-4
+
+
+@pytest.mark.parametrize("direction", ["inverse", "forward"])
+@pytest.mark.parametrize("name", sorted(LAYER_CASES))
+def test_layer_matches_reference_golden(name, direction):
+    case, g = LAYER_CASES[name], gold("layers")[name]
+    dtype = case.get("dtype", torch.float32)
+    torch.manual_seed(0)
+    layer = case["build"](nf).to(dtype)
+    layer.load_state_dict(g["state"])
+    layer = layer.cuda()
+    got = eval_layer(layer, g["x"].cuda(), direction, case.get("nograd", False))
+    ref = g[direction]
+    tol, gtol = _tol(name, dtype)
+    n_sum = max(1, g["x"][0].numel())
+    assert_close(got["z"], ref["z"], what=name + ".z", **tol)
+    assert_close(got["log_det"], ref["log_det"], what=name + ".log_det", rtol=tol["rtol"], atol=tol["atol"] * n_sum)
+    if ref["gx"] is not None:
+        assert_grads_close({"x": got["gx"], **got["grads"]}, {"x": ref["gx"], **ref["grads"]}, rtol=gtol, what=name)
+
+
+@pytest.mark.parametrize("name", sorted(MODEL_CASES))
+def test_model_matches_reference_golden(name):
+    case, g = MODEL_CASES[name], gold("models")[name]
+    dtype = case.get("dtype", torch.float32)
+    torch.manual_seed(0)
+    model = case["build"](nf).to(dtype)
+    model.load_state_dict(g["state"])
+    model = model.cuda()
+    y = g["y"].cuda() if g["y"] is not None else None
+    for call in case["calls"]:
+        if name == "cfg4_small":
+            continue            # dequantisation noise comes from the device RNG; see test below
+        got = eval_model(copy.deepcopy(model), g["x"].cuda(), call, y)
+        ref = g[call]
+        assert_close(got["value"], ref["value"], rtol=1e-4, atol=2e-3, what="%s.%s" % (name, call))
+        assert_grads_close(got["grads"], ref["grads"], rtol=2e-3, what="%s.%s" % (name, call))
+
+
+def test_vdeq_model_runs_and_is_finite():
+    """cfg 4 shape: per-column variational dequantisation + masked affine stack, fp64 model."""
+    case = MODEL_CASES["cfg4_small"]
+    torch.manual_seed(0)
+    model = case["build"](nf).double()
+    randomize(model, scale=0.2)
+    model = model.cuda()
+    x = case["x"]().cuda()
+    loss = model.forward_kld(x)
+    loss.backward()
+    assert torch.isfinite(loss)
+    assert all(torch.isfinite(p.grad).all() for p in model.parameters() if p.grad is not None)
+    # dequantised columns are written back into the caller's tensor (core.py:54)
+    assert not torch.equal(x[:, 1], torch.floor(x[:, 1]))
+
+
+def _pair(build, dtype=torch.float32, scale=0.3, seed=0):
+    torch.manual_seed(seed)
+    ref = build(oracle)
+    randomize(ref, scale=scale)
+    ref = ref.to(dtype)
+    torch.manual_seed(seed)
+    prod = build(nf).to(dtype)
+    prod.load_state_dict(ref.state_dict())
+    return ref, prod.cuda()
+
+
+@pytest.mark.parametrize("B", [1, 3, 33, 257, 4099])
+def test_crqs_ragged_batches_and_bins_vs_oracle(B):
+    """Tile raggedness (B not a multiple of the row tile, single row) + exact bin indices."""
+    build = lambda m: m.flows.CoupledRationalQuadraticSpline(29, 2, 32)
+    ref, prod = _pair(build)
+    x = 1.5 * torch.randn(B, 29, generator=torch.Generator().manual_seed(B))
+    x[0, :4] = torch.tensor([3.0, -3.0, 3.0000002, -7.0])          # both ends, just outside, far outside
+    z_ref, ld_ref = ref.inverse(x)
+    z, ld = prod.inverse(x.cuda())
+    assert_close(z, z_ref, what="z", **SPLINE)
+    assert_close(ld, ld_ref, what="ld", rtol=1e-4, atol=29e-5)
+    # bin indices: product kernel vs oracle search on the same parameters
+    p = prod.prqct
+    _, _, bins = p.forward(x.cuda(), want_bins=True)
+    ident = x[:, ref.prqct.identity_features]
+    trans = x[:, ref.prqct.transform_features]
+    prm = ref.prqct.transform_net(ident).reshape(B, trans.shape[1], -1)
+    k, rh = 8, float(torch.sqrt(torch.tensor(32.0)))
+    _, _, b_t = oracle.splines.unconstrained_rqs(trans, prm[..., :k] / rh, prm[..., k:2 * k] / rh, prm[..., 2 * k:],
+                                                 tails="linear", tail_bound=3.0, return_bin=True)
+    got_t = bins.cpu()[:, ref.prqct.transform_features].long()
+    assert int((got_t != b_t).sum()) == 0, "bin mismatches: %d" % int((got_t != b_t).sum())
+
+
+def test_round_trip_full_size_cfg2_layer():
+    """BASELINE cfg 2 layer at full size (B = 65536, d = 29, hidden 128): inverse(forward(x)) = x and
+    the two log-dets cancel (the reference's own test property, splines_test.py:7-56)."""
+    torch.manual_seed(0)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(layer, scale=0.2)
+    lu = nf.flows.LULinearPermute(29, identity_init=False)
+    layer, lu = layer.cuda(), lu.cuda()
+    x = 1.5 * torch.randn(65536, 29, device="cuda")
+    with torch.no_grad():
+        y, ld1 = layer.inverse(x)
+        y2, ld2 = lu.inverse(y)
+        y1, ld3 = lu.forward(y2)
+        x1, ld4 = layer.forward(y1)
+    assert float((y1 - y).abs().max()) < 1e-3
+    assert float((x1 - x).abs().max()) < 2e-3
+    assert float((ld1 + ld4).abs().max()) < 5e-3
+    assert float((ld2 + ld3).abs().max()) < 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_arqs_full_width_vs_oracle(dtype):
+    """cfg 3 layer width (d = 64, hidden 256 -> 1472 params/sample), density direction + grads."""
+    build = lambda m: m.flows.AutoregressiveRationalQuadraticSpline(64, 2, 256)
+    ref, prod = _pair(build, dtype=dtype, scale=0.05)
+    x = (1.5 * torch.randn(777, 64, generator=torch.Generator().manual_seed(5))).to(dtype)
+    r = eval_layer(ref, x, "inverse")
+    g = eval_layer(prod, x.cuda(), "inverse")
+    tol = SPLINE if dtype == torch.float32 else dict(rtol=1e-9, atol=1e-10)
+    assert_close(g["z"], r["z"], what="z", **tol)
+    assert_close(g["log_det"], r["log_det"], what="ld", rtol=tol["rtol"], atol=tol["atol"] * 64)
+    assert_grads_close({"x": g["gx"], **g["grads"]}, {"x": r["gx"], **r["grads"]},
+                       rtol=1e-3 if dtype == torch.float32 else 1e-7, what="arqs")
+
+
+def test_glow_block_full_channels_vs_oracle():
+    """cfg 5 level-2 block (C = 12 @ 16x16, hidden 64 to keep the CPU oracle quick)."""
+    build = lambda m: m.flows.GlowBlock(12, 64)
+    ref, prod = _pair(build, scale=0.05)
+    x = torch.randn(8, 12, 16, 16, generator=torch.Generator().manual_seed(6))
+    for direction in ("inverse", "forward"):
+        r = eval_layer(copy.deepcopy(ref), x, direction)
+        g = eval_layer(copy.deepcopy(prod), x.cuda(), direction)
+        assert_close(g["z"], r["z"], what="z", rtol=1e-4, atol=1e-5)
+        assert_close(g["log_det"], r["log_det"], what="ld", rtol=1e-4, atol=1e-3)
+        assert_grads_close({"x": g["gx"], **g["grads"]}, {"x": r["gx"], **r["grads"]}, rtol=2e-3, what="glow")
+
+
+def test_masked_affine_nan_propagation():
+    """Non-finite conditioner outputs become NaN exactly like coupling.py:205-208."""
+    class Inf(torch.nn.Module):
+        def forward(self, x):
+            out = torch.zeros_like(x)
+            out[0, 1] = float("inf")
+            return out
+    b = torch.tensor([1.0, 0.0, 1.0, 0.0])
+    ref = oracle.flows.MaskedAffineFlow(b, Inf(), Inf())
+    prod = nf.flows.MaskedAffineFlow(b, Inf(), Inf()).cuda()
+    x = torch.randn(4, 4)
+    z_ref, ld_ref = ref.forward(x)
+    z, ld = prod.forward(x.cuda())
+    assert torch.equal(torch.isnan(z.cpu()), torch.isnan(z_ref))
+    assert torch.equal(torch.isnan(ld.cpu()), torch.isnan(ld_ref))
+
+
+def test_empty_batch():
+    layer = nf.flows.AffineCouplingBlock(nf.nets.MLP([1, 8, 2])).cuda()
+    z, ld = layer(torch.zeros(0, 2, device="cuda"))
+    assert z.shape == (0, 2) and ld.shape == (0,)
+    lu = nf.flows.LULinearPermute(5).cuda()
+    z, ld = lu.inverse(torch.zeros(0, 5, device="cuda"))
+    assert z.shape == (0, 5)
+
+
+def test_functional_spline_round_trip():
+    """The reference's own spline test (utils/splines_test.py:33-56) against the kernel."""
+    from vcnf_b200.utils import splines
+    torch.manual_seed(0)
+    shape, K = [2, 3, 4], 10
+    uw, uh = torch.randn(*shape, K).cuda(), torch.randn(*shape, K).cuda()
+    ud = torch.randn(*shape, K - 1).cuda()
+    x = (3 * torch.randn(*shape)).cuda()
+    y, lad = splines.unconstrained_rational_quadratic_spline(x, uw, uh, ud, inverse=False, tail_bound=1.)
+    x1, lad_i = splines.unconstrained_rational_quadratic_spline(y, uw, uh, ud, inverse=True, tail_bound=1.)
+    assert float((x - x1).abs().max()) < 1e-4
+    assert float((lad + lad_i).abs().max()) < 1e-4

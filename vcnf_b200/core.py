@@ -1,0 +1,224 @@
+"""Model containers with the reference's public API (normflow/core.py): the Python layer loops
+stay on the host, every layer call lands in the sm_100a kernels.
+
+Reference behaviours kept on purpose: `forward_kld` accumulates log q in fp32
+whatever the model dtype (A.3), writes the dequantised columns back into the caller's `x`
+(core.py:54) and hands the running accumulator to the dequantisers, which mutate it in place
+(triangular accumulation, A.2).  Single intentional deviation: `categoricals=None` means "no
+dequantisation" (the reference raises AttributeError at core.py:42,157, hazard A.1)."""
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import utils
+
+
+class NormalizingFlow(nn.Module):
+    def __init__(self, q0, flows, p=None, categoricals=None, catlevels=None, catvdeqs=None):
+        super().__init__()
+        self.q0 = q0
+        self.flows = nn.ModuleList(flows)
+        self.p = p
+        self.categoricals = categoricals
+        if categoricals is not None:
+            self.vdeqs = nn.ModuleList(catvdeqs)
+            self.catlevels = catlevels
+
+    def forward_kld(self, x, extended=False):
+        """core.py:33-66."""
+        log_qt = torch.zeros(len(x), device=x.device)
+        log_q = torch.zeros(len(x), device=x.device)
+        z = x
+        zarr, zparr = [], []
+        if self.categoricals is not None:
+            zc = x[:, self.categoricals]
+            for vcn in range(len(self.categoricals)):
+                zct, log_det = self.vdeqs[vcn].forward(z=zc[:, vcn].view([zc.shape[0], 1]), ldj=log_q,
+                                                       reverse=False)
+                zc[:, vcn] = zct.squeeze()
+                if extended:
+                    zarr.append(z.cpu().detach().numpy())
+                    zparr.append(log_det.cpu().detach().numpy())
+                log_qt += log_det
+            z[:, self.categoricals] = zc.float()
+        log_q = log_qt
+        for i in range(len(self.flows) - 1, -1, -1):
+            z, log_det = self.flows[i].inverse(z)
+            if extended:
+                zarr.append(z.cpu().detach().numpy())
+                zparr.append(log_det.cpu().detach().numpy())
+            log_q += log_det
+        log_q += self.q0.log_prob(z)
+        if extended:
+            return -torch.mean(log_q), zarr, zparr, log_q
+        return -torch.mean(log_q)
+
+    def reverse_kld(self, num_samples=1, beta=1., score_fn=True, extended=False):
+        """core.py:68-101."""
+        z, log_q_ = self.q0(num_samples)
+        log_q = torch.zeros_like(log_q_)
+        log_q += log_q_
+        zarr, zparr = [], []
+        for flow in self.flows:
+            z, log_det = flow(z)
+            if extended:
+                zarr.append(z.cpu().detach().numpy())
+                zparr.append(log_det.cpu().detach().numpy())
+            log_q -= log_det
+        if not score_fn:
+            z_ = z
+            log_q = torch.zeros(len(z_), device=z_.device)
+            utils.set_requires_grad(self, False)
+            for i in range(len(self.flows) - 1, -1, -1):
+                z_, log_det = self.flows[i].inverse(z_)
+                log_q += log_det
+            log_q += self.q0.log_prob(z_)
+            utils.set_requires_grad(self, True)
+        log_p = self.p.log_prob(z)
+        if extended:
+            return torch.mean(log_q) - beta * torch.mean(log_p), zarr, zparr, log_p, log_q
+        return torch.mean(log_q) - beta * torch.mean(log_p)
+
+    def reverse_alpha_div(self, num_samples=1, alpha=1, dreg=False, extended=False):
+        """core.py:102-142."""
+        z, log_q = self.q0(num_samples)
+        zarr, zparr = [], []
+        for flow in self.flows:
+            z, log_det = flow(z)
+            if extended:
+                zarr.append(z.cpu().detach().numpy())
+                zparr.append(log_det.cpu().detach().numpy())
+            log_q -= log_det
+        log_p = self.p.log_prob(z)
+        if dreg:
+            w_const = torch.exp(log_p - log_q).detach()
+            z_ = z
+            log_q = torch.zeros(len(z_), device=z_.device)
+            utils.set_requires_grad(self, False)
+            for i in range(len(self.flows) - 1, -1, -1):
+                z_, log_det = self.flows[i].inverse(z_)
+                log_q += log_det
+            log_q += self.q0.log_prob(z_)
+            utils.set_requires_grad(self, True)
+            w = torch.exp(log_p - log_q)
+            w_alpha = w_const ** alpha
+            w_alpha = w_alpha / torch.mean(w_alpha)
+            weights = (1 - alpha) * w_alpha + alpha * w_alpha ** 2
+            loss = -alpha * torch.mean(weights * torch.log(w))
+        else:
+            loss = np.sign(alpha - 1) * torch.logsumexp(alpha * (log_p - log_q), 0)
+        if extended:
+            return loss, zarr, zparr
+        return loss
+
+    def sample(self, num_samples=1):
+        """core.py:144-168."""
+        z, log_q = self.q0(num_samples)
+        for flow in self.flows:
+            z, log_det = flow(z)
+            log_q -= log_det
+        if self.categoricals is not None and len(self.categoricals) > 0:
+            zc = z[:, self.categoricals]
+            for vct in range(len(self.categoricals)):
+                zct, log_det = self.vdeqs[vct].forward(z=zc[:, vct].view([zc.shape[0], 1]), ldj=log_q,
+                                                       reverse=True)
+                zc[:, vct] = zct.squeeze()
+                log_q += log_det
+            z[:, self.categoricals] = zc.to(z.dtype)
+        return z, log_q
+
+    def log_prob(self, x):
+        """core.py:170-183."""
+        log_q = torch.zeros(len(x), dtype=x.dtype, device=x.device)
+        z = x
+        for i in range(len(self.flows) - 1, -1, -1):
+            z, log_det = self.flows[i].inverse(z)
+            log_q += log_det
+        log_q += self.q0.log_prob(z)
+        return log_q
+
+    def save(self, path):
+        torch.save(self.state_dict(), path)
+
+    def load(self, path):
+        self.load_state_dict(torch.load(path))
+
+
+class MultiscaleFlow(nn.Module):
+    """Multiscale (RealNVP / Glow) container, core.py:271-399."""
+
+    def __init__(self, q0, flows, merges, transform=None, class_cond=True):
+        super().__init__()
+        self.q0 = nn.ModuleList(q0)
+        self.num_levels = len(self.q0)
+        self.flows = torch.nn.ModuleList([nn.ModuleList(flow) for flow in flows])
+        self.merges = torch.nn.ModuleList(merges)
+        self.transform = transform
+        self.class_cond = class_cond
+
+    def forward_kld(self, x, y=None):
+        return -torch.mean(self.log_prob(x, y))
+
+    def forward(self, x, y=None):
+        return -self.log_prob(x, y)
+
+    def sample(self, num_samples=1, y=None, temperature=None):
+        if temperature is not None:
+            self.set_temperature(temperature)
+        for i in range(len(self.q0)):
+            if self.class_cond:
+                z_, log_q_ = self.q0[i](num_samples, y)
+            else:
+                z_, log_q_ = self.q0[i](num_samples)
+            if i == 0:
+                log_q, z = log_q_, z_
+            else:
+                log_q += log_q_
+                z, log_det = self.merges[i - 1]([z, z_])
+                log_q -= log_det
+            for flow in self.flows[i]:
+                z, log_det = flow(z)
+                log_q -= log_det
+        if self.transform is not None:
+            z, log_det = self.transform(z)
+            log_q -= log_det
+        if temperature is not None:
+            self.reset_temperature()
+        return z, log_q
+
+    def log_prob(self, x, y):
+        log_q = 0
+        z = x
+        if self.transform is not None:
+            z, log_det = self.transform.inverse(z)
+            log_q += log_det
+        for i in range(len(self.q0) - 1, -1, -1):
+            for j in range(len(self.flows[i]) - 1, -1, -1):
+                z, log_det = self.flows[i][j].inverse(z)
+                log_q += log_det
+            if i > 0:
+                [z, z_], log_det = self.merges[i - 1].inverse(z)
+                log_q += log_det
+            else:
+                z_ = z
+            if self.class_cond:
+                log_q += self.q0[i].log_prob(z_, y)
+            else:
+                log_q += self.q0[i].log_prob(z_)
+        return log_q
+
+    def save(self, path):
+        torch.save(self.state_dict(), path)
+
+    def load(self, path):
+        self.load_state_dict(torch.load(path))
+
+    def set_temperature(self, temperature):
+        for q0 in self.q0:
+            if hasattr(q0, "temperature"):
+                q0.temperature = temperature
+            else:
+                raise NotImplementedError("One base function does not support temperature annealed sampling")
+
+    def reset_temperature(self):
+        self.set_temperature(None)

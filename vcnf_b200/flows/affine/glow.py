@@ -1,0 +1,48 @@
+"""Glow block (reference: normflow/flows/affine/glow.py:12-75)."""
+import torch
+from torch import nn
+
+from ..base import Flow
+from .coupling import AffineCouplingBlock
+from ..mixing import Invertible1x1Conv
+from ..normalization import ActNorm
+from ... import nets
+
+
+class GlowBlock(Flow):
+    """AffineCouplingBlock(ConvNet2d 3x3,1x1,3x3) + Invertible1x1Conv + ActNorm."""
+
+    def __init__(self, channels, hidden_channels, scale=True, scale_map="sigmoid",
+                 split_mode="channel", leaky=0.0, init_zeros=True, use_lu=True,
+                 net_actnorm=False):
+        super().__init__()
+        self.flows = nn.ModuleList([])
+        kernel_size = (3, 1, 3)
+        num_param = 2 if scale else 1
+        if "channel" == split_mode:
+            channels_ = (channels // 2,) + 2 * (hidden_channels,)
+            channels_ += (num_param * ((channels + 1) // 2),)
+        elif "channel_inv" == split_mode:
+            channels_ = ((channels + 1) // 2,) + 2 * (hidden_channels,)
+            channels_ += (num_param * (channels // 2),)
+        else:
+            raise NotImplementedError("Mode " + split_mode + " is not implemented.")
+        param_map = nets.ConvNet2d(channels_, kernel_size, leaky, init_zeros, actnorm=net_actnorm)
+        self.flows += [AffineCouplingBlock(param_map, scale, scale_map, split_mode)]
+        if channels > 1:
+            self.flows += [Invertible1x1Conv(channels, use_lu)]
+        self.flows += [ActNorm((channels,) + (1, 1))]
+
+    def forward(self, z):
+        log_det_tot = torch.zeros(z.shape[0], dtype=z.dtype, device=z.device)
+        for flow in self.flows:
+            z, log_det = flow(z)
+            log_det_tot = log_det_tot + log_det
+        return z, log_det_tot
+
+    def inverse(self, z):
+        log_det_tot = torch.zeros(z.shape[0], dtype=z.dtype, device=z.device)
+        for i in range(len(self.flows) - 1, -1, -1):
+            z, log_det = self.flows[i].inverse(z)
+            log_det_tot = log_det_tot + log_det
+        return z, log_det_tot

@@ -1,0 +1,225 @@
+"""Mixing layers (reference: normflow/flows/mixing.py): Permute, Invertible1x1Conv,
+LULinearPermute.  The per-sample / per-pixel D x D maps run in `vcnf_small_linear`."""
+import numpy as np
+import torch
+from torch import nn
+from torch.nn import functional as F, init
+
+from .base import Flow
+from .. import ops
+
+
+def _i32(t):
+    return t.to(torch.int32).contiguous()
+
+
+class Permute(Flow):
+    """Channel permutation (mixing.py:10-54).  'swap': forward splits at C//2, inverse at
+    (C+1)//2 (hazard A.13); 'shuffle': fixed random permutation (buffers perm, inv_perm)."""
+
+    def __init__(self, num_channels, mode="shuffle"):
+        super().__init__()
+        self.mode = mode
+        self.num_channels = num_channels
+        if self.mode == "shuffle":
+            perm = torch.randperm(self.num_channels)
+            inv_perm = torch.empty_like(perm).scatter_(dim=0, index=perm, src=torch.arange(self.num_channels))
+            self.register_buffer("perm", perm)
+            self.register_buffer("inv_perm", inv_perm)
+        self._idx_cache = {}
+
+    def _swap_index(self, cut, device):
+        key = (cut, str(device))
+        if key not in self._idx_cache:
+            c = self.num_channels
+            fwd = torch.cat([torch.arange(cut, c), torch.arange(0, cut)]).to(torch.int32).to(device)
+            self._idx_cache[key] = (fwd, torch.argsort(fwd.long()).to(torch.int32))
+        return self._idx_cache[key]
+
+    def _apply_perm(self, z, inverse):
+        if self.mode == "shuffle":
+            p, q = (self.inv_perm, self.perm) if inverse else (self.perm, self.inv_perm)
+            return ops.permute_channels(z, _i32(p), _i32(q))
+        if self.mode == "swap":
+            cut = (self.num_channels + 1) // 2 if inverse else self.num_channels // 2
+            p, q = self._swap_index(cut, z.device)
+            return ops.permute_channels(z, p, q)
+        raise NotImplementedError("The mode " + self.mode + " is not implemented.")
+
+    def forward(self, z):
+        return self._apply_perm(z, False), 0
+
+    def inverse(self, z):
+        return self._apply_perm(z, True), 0
+
+
+class Invertible1x1Conv(Flow):
+    """Glow's invertible 1x1 convolution (mixing.py:57-128).  W (or its inverse, with the
+    triangular factors inverted in fp64 as the reference does, :91-96) is assembled from the C x C
+    parameters by a handful of tiny library ops; the per-pixel C x C matvec over the NCHW tensor
+    is the `vcnf_small_linear` kernel."""
+
+    def __init__(self, num_channels, use_lu=False):
+        super().__init__()
+        self.num_channels = num_channels
+        self.use_lu = use_lu
+        Q = torch.linalg.qr(torch.randn(self.num_channels, self.num_channels))[0]
+        if use_lu:
+            P, L, U = torch.linalg.lu(Q)
+            self.register_buffer("P", P)
+            self.L = nn.Parameter(L)
+            S = U.diag()
+            self.register_buffer("sign_S", torch.sign(S))
+            self.log_S = nn.Parameter(torch.log(torch.abs(S)))
+            self.U = nn.Parameter(torch.triu(U, diagonal=1))
+            self.register_buffer("eye", torch.diag(torch.ones(self.num_channels)))
+        else:
+            self.W = nn.Parameter(Q)
+
+    def _assemble_W(self, inverse=False):
+        L = torch.tril(self.L, diagonal=-1) + self.eye
+        U = torch.triu(self.U, diagonal=1) + torch.diag(self.sign_S * torch.exp(self.log_S))
+        if inverse:
+            if self.log_S.dtype == torch.float64:
+                L_inv, U_inv = torch.inverse(L), torch.inverse(U)
+            else:
+                L_inv = torch.inverse(L.double()).type(self.log_S.dtype)
+                U_inv = torch.inverse(U.double()).type(self.log_S.dtype)
+            return U_inv @ L_inv @ self.P.t()
+        return self.P @ L @ U
+
+    def forward(self, z):
+        if self.use_lu:
+            W = self._assemble_W(inverse=True)
+            log_det = -torch.sum(self.log_S)
+        else:
+            W_dtype = self.W.dtype
+            W = torch.inverse(self.W) if W_dtype == torch.float64 else torch.inverse(self.W.double()).type(W_dtype)
+            log_det = -torch.slogdet(self.W)[1]
+        z_ = ops.small_linear(z, W)
+        return z_, log_det * z.size(2) * z.size(3)
+
+    def inverse(self, z):
+        if self.use_lu:
+            W = self._assemble_W()
+            log_det = torch.sum(self.log_S)
+        else:
+            W = self.W
+            log_det = torch.slogdet(self.W)[1]
+        z_ = ops.small_linear(z, W)
+        return z_, log_det * z.size(2) * z.size(3)
+
+
+class _Permutation(Flow):
+    """Fixed feature permutation (mixing.py:203-233); used through LULinearPermute."""
+
+    def __init__(self, permutation, dim=1):
+        if permutation.ndimension() != 1:
+            raise ValueError("Permutation must be a 1D tensor.")
+        super().__init__()
+        self._dim = dim
+        self.register_buffer("_permutation", permutation)
+
+    @property
+    def _inverse_permutation(self):
+        return torch.argsort(self._permutation)
+
+    def forward(self, inputs, context=None):
+        out = ops.permute_channels(inputs, _i32(self._permutation), _i32(self._inverse_permutation))
+        return out, torch.zeros(inputs.shape[0], dtype=inputs.dtype, device=inputs.device)
+
+    def inverse(self, inputs, context=None):
+        out = ops.permute_channels(inputs, _i32(self._inverse_permutation), _i32(self._permutation))
+        return out, torch.zeros(inputs.shape[0], dtype=inputs.dtype, device=inputs.device)
+
+
+class _RandomPermutation(_Permutation):
+    def __init__(self, features, dim=1):
+        super().__init__(torch.randperm(features), dim)
+
+
+class _LULinear(Flow):
+    """W = L U with L unit lower triangular and diag(U) = softplus(d) + eps (mixing.py:352-462).
+    Parameters: bias, lower_entries, upper_entries, unconstrained_upper_diag."""
+
+    def __init__(self, features, using_cache=False, identity_init=True, eps=1e-3):
+        super().__init__()
+        self.features = features
+        self.eps = eps
+        self.bias = nn.Parameter(torch.zeros(features))
+        self.lower_indices = np.tril_indices(features, k=-1)
+        self.upper_indices = np.triu_indices(features, k=1)
+        self.diag_indices = np.diag_indices(features)
+        n_tri = ((features - 1) * features) // 2
+        self.lower_entries = nn.Parameter(torch.zeros(n_tri))
+        self.upper_entries = nn.Parameter(torch.zeros(n_tri))
+        self.unconstrained_upper_diag = nn.Parameter(torch.zeros(features))
+        init.zeros_(self.bias)
+        if identity_init:
+            init.constant_(self.unconstrained_upper_diag, np.log(np.exp(1 - self.eps) - 1))
+        else:
+            stdv = 1.0 / np.sqrt(self.features)
+            init.uniform_(self.lower_entries, -stdv, stdv)
+            init.uniform_(self.upper_entries, -stdv, stdv)
+            init.uniform_(self.unconstrained_upper_diag, -stdv, stdv)
+
+    @property
+    def upper_diag(self):
+        return F.softplus(self.unconstrained_upper_diag) + self.eps
+
+    def _create_lower_upper(self):
+        lower = self.lower_entries.new_zeros(self.features, self.features)
+        lower[self.lower_indices[0], self.lower_indices[1]] = self.lower_entries
+        lower[self.diag_indices[0], self.diag_indices[1]] = 1.
+        upper = self.upper_entries.new_zeros(self.features, self.features)
+        upper[self.upper_indices[0], self.upper_indices[1]] = self.upper_entries
+        upper[self.diag_indices[0], self.diag_indices[1]] = self.upper_diag
+        return lower, upper
+
+    def weight(self):
+        lower, upper = self._create_lower_upper()
+        return lower @ upper
+
+    def weight_inverse(self):
+        """U^-1 L^-1 via two triangular solves against the identity, in fp64 for fp32 models."""
+        lower, upper = self._create_lower_upper()
+        dt = lower.dtype
+        eye = torch.eye(self.features, dtype=torch.float64, device=lower.device)
+        li = torch.linalg.solve_triangular(lower.double(), eye, upper=False, unitriangular=True)
+        wi = torch.linalg.solve_triangular(upper.double(), li, upper=True)
+        return wi.to(dt)
+
+    def logabsdet(self):
+        return torch.sum(torch.log(self.upper_diag))
+
+    def forward(self, inputs, context=None, in_idx=None):
+        out = ops.small_linear(inputs, self.weight(), self.bias, in_idx=in_idx)
+        return out, self.logabsdet() * inputs.new_ones(out.shape[0])
+
+    def inverse(self, inputs, context=None, out_idx=None):
+        out = ops.small_linear(inputs, self.weight_inverse(), self.bias, out_idx=out_idx, sub_bias_first=True)
+        return out, -self.logabsdet() * inputs.new_ones(out.shape[0])
+
+
+class LULinearPermute(Flow):
+    """Permutation + LU-parametrised linear map (mixing.py:465-492), one kernel per direction:
+    inverse (density): y = (L U) x[perm] + bias;  forward (sampling): x = ((L U)^-1 (y - bias))
+    scattered back through the permutation.  The D x D product L U (and its inverse) is formed from
+    the parameters by tiny library ops under autograd; the reference applies U then L (two
+    F.linear calls, :398-410) and two triangular solves (:412-429) -- same map, rounding differs."""
+
+    def __init__(self, num_channels, identity_init=True):
+        super().__init__()
+        self.permutation = _RandomPermutation(num_channels)
+        self.linear = _LULinear(num_channels, identity_init=identity_init)
+
+    def forward(self, z):
+        perm = _i32(self.permutation._permutation)
+        # out[:, perm[o]] = v[o]  ==  v[:, argsort(perm)]
+        z, log_det = self.linear.inverse(z, out_idx=perm)
+        return z, log_det.view(-1)
+
+    def inverse(self, z):
+        perm = _i32(self.permutation._permutation)
+        z, log_det = self.linear(z, in_idx=perm)
+        return z, log_det.view(-1)

@@ -1,0 +1,248 @@
+"""Neural-spline coupling layers (reference: normflow/flows/neural_spline/coupling.py).
+
+`Coupling.forward` / `.inverse` run as: one column gather for the conditioner input, the
+conditioner, then ONE `vcnf_rqs_layer_fwd` launch that does the conditional spline on the
+transform features, the unconditional spline on the identity features, the scatter back to the
+original columns and the per-sample log|det| sum (coupling.py:70-125,147-159,211-240,309-343)."""
+import warnings
+
+import numpy as np
+import torch
+from torch import nn
+
+from ..base import Flow
+from ... import ops
+from ...utils import splines
+
+_TAIL_CODE = {"linear": ops.TAIL_LINEAR, "circular": ops.TAIL_CIRCULAR}
+
+
+def _params_per_feature(tails, num_bins):
+    if tails == "linear":
+        return num_bins * 3 - 1
+    if tails == "circular":
+        return num_bins * 3
+    return num_bins * 3 + 1
+
+
+def _modes_and_bounds(tails, tail_bound, n):
+    """Per-feature (tail mode, bound) lists for a segment of n features."""
+    if isinstance(tails, (list, tuple)):
+        modes = [ops.TAIL_LIST_LINEAR if t == "linear" else ops.TAIL_LIST_CIRCULAR for t in tails]
+    elif tails in _TAIL_CODE:
+        modes = [_TAIL_CODE[tails]] * n
+    else:
+        raise RuntimeError("{} tails are not implemented.".format(tails))
+    if torch.is_tensor(tail_bound):
+        bounds = [float(b) for b in tail_bound.detach().cpu().reshape(-1)]
+        if len(bounds) == 1:
+            bounds = bounds * n
+    else:
+        bounds = [float(tail_bound)] * n
+    return modes, bounds
+
+
+class PiecewiseRationalQuadraticCDF(Flow):
+    """Elementwise spline with parameters shared across the batch (coupling.py:165-246)."""
+
+    def __init__(self, shape, num_bins=10, tails=None, tail_bound=1., identity_init=True,
+                 min_bin_width=splines.DEFAULT_MIN_BIN_WIDTH,
+                 min_bin_height=splines.DEFAULT_MIN_BIN_HEIGHT,
+                 min_derivative=splines.DEFAULT_MIN_DERIVATIVE):
+        super().__init__()
+        splines.check_minimums(num_bins, min_bin_width, min_bin_height, min_derivative)
+        if tails is None:
+            raise NotImplementedError("tails=None (bounded spline) is not on the B200 path")
+        if len(shape) != 1:
+            raise NotImplementedError("image-shaped spline parameters are a SURVEY.md 8(f2) next row")
+        if torch.is_tensor(tail_bound):
+            self.register_buffer("tail_bound", tail_bound)
+        else:
+            self.tail_bound = tail_bound
+        self.tails = tails
+        self.num_bins = num_bins
+        nd = _params_per_feature(tails, num_bins) - 2 * num_bins
+        if identity_init:
+            self.unnormalized_widths = nn.Parameter(torch.zeros(*shape, num_bins))
+            self.unnormalized_heights = nn.Parameter(torch.zeros(*shape, num_bins))
+            constant = np.log(np.exp(1 - min_derivative) - 1)
+            self.unnormalized_derivatives = nn.Parameter(constant * torch.ones(*shape, nd))
+        else:
+            self.unnormalized_widths = nn.Parameter(torch.rand(*shape, num_bins))
+            self.unnormalized_heights = nn.Parameter(torch.rand(*shape, num_bins))
+            self.unnormalized_derivatives = nn.Parameter(torch.rand(*shape, nd))
+        self._spec = None
+
+    def packed_params(self):
+        return torch.cat([self.unnormalized_widths, self.unnormalized_heights,
+                          self.unnormalized_derivatives], dim=-1)
+
+    def segment(self):
+        n = self.unnormalized_widths.shape[0]
+        return _modes_and_bounds(self.tails, self.tail_bound, n)
+
+    def _spline(self, inputs, inverse=False):
+        if self._spec is None:
+            n = self.unnormalized_widths.shape[0]
+            modes, bounds = self.segment()
+            P = _params_per_feature(self.tails, self.num_bins)
+            cmap = [(ops.COL_SHARED << 16) | i for i in range(n)]
+            self._spec = ops.SplineSpec(n, self.num_bins, cmap, [], [], P, 1.0, modes, bounds, P,
+                                        isinstance(self.tails, (list, tuple)))
+        return ops.rqs_layer(inputs, None, self.packed_params(), self._spec, inverse)
+
+    def forward(self, inputs, context=None):
+        return self._spline(inputs, inverse=False)
+
+    def inverse(self, inputs, context=None):
+        return self._spline(inputs, inverse=True)
+
+
+class Coupling(Flow):
+    """Base coupling layer on a binary feature mask (coupling.py:18-137), 2-D inputs."""
+
+    def __init__(self, mask, transform_net_create_fn, unconditional_transform=None):
+        mask = torch.as_tensor(mask)
+        if mask.dim() != 1:
+            raise ValueError("Mask must be a 1-dim tensor.")
+        if mask.numel() <= 0:
+            raise ValueError("Mask can't be empty.")
+        super().__init__()
+        self.features = len(mask)
+        features_vector = torch.arange(self.features)
+        self.register_buffer("identity_features", features_vector.masked_select(mask <= 0))
+        self.register_buffer("transform_features", features_vector.masked_select(mask > 0))
+        assert self.num_identity_features + self.num_transform_features == self.features
+        self.transform_net = transform_net_create_fn(
+            self.num_identity_features,
+            self.num_transform_features * self._transform_dim_multiplier())
+        if unconditional_transform is None:
+            self.unconditional_transform = None
+        else:
+            self.unconditional_transform = unconditional_transform(features=self.num_identity_features)
+
+    @property
+    def num_identity_features(self):
+        return len(self.identity_features)
+
+    @property
+    def num_transform_features(self):
+        return len(self.transform_features)
+
+    def _check(self, inputs):
+        if inputs.dim() not in [2, 4]:
+            raise ValueError("Inputs must be a 2D or a 4D tensor.")
+        if inputs.shape[1] != self.features:
+            raise ValueError("Expected features = {}, got {}.".format(self.features, inputs.shape[1]))
+        if inputs.dim() == 4:
+            raise NotImplementedError("4-D spline coupling is a SURVEY.md 8(f2) next row")
+
+    def _transform_dim_multiplier(self):
+        raise NotImplementedError()
+
+
+class PiecewiseRationalQuadraticCoupling(Coupling):
+    """Rational-quadratic spline coupling (coupling.py:249-343)."""
+
+    def __init__(self, mask, transform_net_create_fn, num_bins=10, tails=None, tail_bound=1.,
+                 apply_unconditional_transform=False, img_shape=None,
+                 min_bin_width=splines.DEFAULT_MIN_BIN_WIDTH,
+                 min_bin_height=splines.DEFAULT_MIN_BIN_HEIGHT,
+                 min_derivative=splines.DEFAULT_MIN_DERIVATIVE):
+        splines.check_minimums(num_bins, min_bin_width, min_bin_height, min_derivative)
+        if tails is None:
+            raise NotImplementedError("tails=None (bounded spline) is not on the B200 path")
+        self.num_bins = num_bins
+        mask = torch.as_tensor(mask)
+        features_vector = torch.arange(len(mask))
+        identity_features = features_vector.masked_select(mask <= 0)
+        transform_features = features_vector.masked_select(mask > 0)
+        if isinstance(tails, (list, tuple)):
+            self.tails = [tails[i] for i in transform_features]
+            tails_ = [tails[i] for i in identity_features]
+        else:
+            self.tails = tails
+            tails_ = tails
+        if torch.is_tensor(tail_bound):
+            tail_bound_ = tail_bound[identity_features]
+        else:
+            self.tail_bound = tail_bound
+            tail_bound_ = tail_bound
+        if apply_unconditional_transform:
+            unconditional_transform = lambda features: PiecewiseRationalQuadraticCDF(
+                shape=[features] + (img_shape if img_shape else []), num_bins=num_bins,
+                tails=tails_, tail_bound=tail_bound_, min_bin_width=min_bin_width,
+                min_bin_height=min_bin_height, min_derivative=min_derivative)
+        else:
+            unconditional_transform = None
+        super().__init__(mask, transform_net_create_fn, unconditional_transform=unconditional_transform)
+        if torch.is_tensor(tail_bound):
+            self.register_buffer("tail_bound", tail_bound[transform_features])
+        self._specs = None
+
+    def _transform_dim_multiplier(self):
+        return _params_per_feature(self.tails, self.num_bins)
+
+    def _wh_scale(self):
+        net = self.transform_net
+        if hasattr(net, "hidden_features"):
+            return 1.0 / np.sqrt(net.hidden_features)           # coupling.py:314-316
+        if hasattr(net, "hidden_channels"):
+            return 1.0 / np.sqrt(net.hidden_channels)
+        warnings.warn("Inputs to the softmax are not scaled down: initialization might be bad.")
+        return 1.0
+
+    def _build_specs(self):
+        D, K = self.features, self.num_bins
+        ident = self.identity_features.tolist()
+        trans = self.transform_features.tolist()
+        Pc = self._transform_dim_multiplier()
+        cmodes, cbounds = _modes_and_bounds(self.tails, self.tail_bound, len(trans))
+        list_mode = isinstance(self.tails, (list, tuple))
+        ut = self.unconditional_transform
+        if ut is not None:
+            smodes, sbounds = ut.segment()
+            Ps = _params_per_feature(ut.tails, K)
+        else:
+            smodes, sbounds, Ps = [], [], Pc
+        wh = self._wh_scale()
+        cond_map, shared_map, both = [0] * D, [0] * D, [0] * D
+        for j, c in enumerate(trans):
+            cond_map[c] = both[c] = (ops.COL_COND << 16) | j
+        if ut is not None:
+            for j, c in enumerate(ident):
+                shared_map[c] = both[c] = (ops.COL_SHARED << 16) | j
+        mk = lambda cmap, cm, cb, sm, sb: ops.SplineSpec(D, K, cmap, cm, cb, Pc, wh, sm, sb, Ps, list_mode)
+        self._specs = {
+            "both": mk(both, cmodes, cbounds, smodes, sbounds),        # density direction: one launch
+            "shared": mk(shared_map, [], [], smodes, sbounds),         # sampling direction, step 1
+            "cond": mk(cond_map, cmodes, cbounds, [], []),             # sampling direction, step 2
+        }
+        self._id_cols = self.identity_features.to(torch.int32)
+
+    def _cols(self, device):
+        if self._id_cols.device != device:
+            self._id_cols = self._id_cols.to(device)
+        return self._id_cols
+
+    def forward(self, inputs, context=None, want_bins=False):
+        self._check(inputs)
+        if self._specs is None:
+            self._build_specs()
+        identity_split = ops.gather_cols(inputs, self._cols(inputs.device))
+        params = self.transform_net(identity_split, context)
+        shared = self.unconditional_transform.packed_params() if self.unconditional_transform is not None else None
+        return ops.rqs_layer(inputs, params, shared, self._specs["both"], False, want_bins)
+
+    def inverse(self, inputs, context=None):
+        self._check(inputs)
+        if self._specs is None:
+            self._build_specs()
+        logabsdet = 0.0
+        if self.unconditional_transform is not None:
+            inputs, logabsdet = ops.rqs_layer(inputs, None, self.unconditional_transform.packed_params(),
+                                              self._specs["shared"], True)
+        identity_split = ops.gather_cols(inputs, self._cols(inputs.device))
+        params = self.transform_net(identity_split, context)
+        outputs, logabsdet_split = ops.rqs_layer(inputs, params, None, self._specs["cond"], True)
+        return outputs, logabsdet + logabsdet_split

@@ -1,0 +1,134 @@
+"""MADE conditioner (reference: normflow/nets/made.py:15-300): masked linear layers with
+sequential degrees, residual blocks, output index = feature*multiplier + m."""
+import torch
+from torch import nn
+from torch.nn import functional as F, init
+
+from ..utils import tile
+
+
+def _get_input_degrees(in_features):
+    return torch.arange(1, in_features + 1)
+
+
+class MaskedLinear(nn.Linear):
+    """Linear layer whose weight is multiplied by a fixed 0/1 degree mask (made.py:20-80)."""
+
+    def __init__(self, in_degrees, out_features, autoregressive_features, random_mask, is_output,
+                 bias=True, out_degrees_=None):
+        super().__init__(in_features=len(in_degrees), out_features=out_features, bias=bias)
+        mask, degrees = self._get_mask_and_degrees(in_degrees, out_features, autoregressive_features,
+                                                   random_mask, is_output, out_degrees_)
+        self.register_buffer("mask", mask)
+        self.register_buffer("degrees", degrees)
+
+    @classmethod
+    def _get_mask_and_degrees(cls, in_degrees, out_features, autoregressive_features, random_mask,
+                              is_output, out_degrees_=None):
+        d = autoregressive_features
+        if is_output:
+            base = _get_input_degrees(d) if out_degrees_ is None else out_degrees_
+            out_degrees = tile(base, out_features // d)
+            return (out_degrees[..., None] > in_degrees).float(), out_degrees     # strict (made.py:60)
+        if random_mask:
+            lo = min(torch.min(in_degrees).item(), d - 1)
+            out_degrees = torch.randint(low=lo, high=d, size=[out_features], dtype=torch.long)
+        else:
+            out_degrees = torch.arange(out_features) % max(1, d - 1) + min(1, d - 1)
+        return (out_degrees[..., None] >= in_degrees).float(), out_degrees
+
+    def forward(self, x):
+        return F.linear(x, self.weight * self.mask, self.bias)
+
+
+class MaskedFeedforwardBlock(nn.Module):
+    def __init__(self, in_degrees, autoregressive_features, context_features=None, random_mask=False,
+                 activation=F.relu, dropout_probability=0., use_batch_norm=False):
+        super().__init__()
+        features = len(in_degrees)
+        self.batch_norm = nn.BatchNorm1d(features, eps=1e-3) if use_batch_norm else None
+        if context_features is not None:
+            raise NotImplementedError()
+        self.linear = MaskedLinear(in_degrees, features, autoregressive_features, random_mask, False)
+        self.degrees = self.linear.degrees
+        self.activation = activation
+        self.dropout = nn.Dropout(p=dropout_probability)
+
+    def forward(self, inputs, context=None):
+        if context is not None:
+            raise NotImplementedError()
+        h = self.batch_norm(inputs) if self.batch_norm else inputs
+        return self.dropout(self.activation(self.linear(h)))
+
+
+class MaskedResidualBlock(nn.Module):
+    def __init__(self, in_degrees, autoregressive_features, context_features=None, random_mask=False,
+                 activation=F.relu, dropout_probability=0., use_batch_norm=False, zero_initialization=True):
+        if random_mask:
+            raise ValueError("Masked residual block can't be used with random masks.")
+        super().__init__()
+        features = len(in_degrees)
+        if context_features is not None:
+            self.context_layer = nn.Linear(context_features, features)
+        self.use_batch_norm = use_batch_norm
+        if use_batch_norm:
+            self.batch_norm_layers = nn.ModuleList([nn.BatchNorm1d(features, eps=1e-3) for _ in range(2)])
+        first = MaskedLinear(in_degrees, features, autoregressive_features, False, False)
+        second = MaskedLinear(first.degrees, features, autoregressive_features, False, False)
+        self.linear_layers = nn.ModuleList([first, second])
+        self.degrees = second.degrees
+        if torch.all(self.degrees >= in_degrees).item() != 1:
+            raise RuntimeError("In a masked residual block, the output degrees can't be"
+                               " less than the corresponding input degrees.")
+        self.activation = activation
+        self.dropout = nn.Dropout(p=dropout_probability)
+        if zero_initialization:
+            init.uniform_(self.linear_layers[-1].weight, a=-1e-3, b=1e-3)
+            init.uniform_(self.linear_layers[-1].bias, a=-1e-3, b=1e-3)
+
+    def forward(self, inputs, context=None):
+        h = inputs
+        if self.use_batch_norm:
+            h = self.batch_norm_layers[0](h)
+        h = self.linear_layers[0](self.activation(h))
+        if self.use_batch_norm:
+            h = self.batch_norm_layers[1](h)
+        h = self.linear_layers[1](self.dropout(self.activation(h)))
+        if context is not None:
+            h = F.glu(torch.cat((h, self.context_layer(context)), dim=1), dim=1)
+        return inputs + h
+
+
+class MADE(nn.Module):
+    def __init__(self, features, hidden_features, context_features=None, num_blocks=2, output_multiplier=1,
+                 use_residual_blocks=True, random_mask=False, permute_mask=False, activation=F.relu,
+                 dropout_probability=0., use_batch_norm=False, preprocessing=None):
+        if use_residual_blocks and random_mask:
+            raise ValueError("Residual blocks can't be used with random masks.")
+        super().__init__()
+        self.preprocessing = (lambda inputs: inputs) if preprocessing is None else preprocessing
+        input_degrees_ = _get_input_degrees(features)
+        if permute_mask:
+            input_degrees_ = input_degrees_[torch.randperm(features)]
+        self.initial_layer = MaskedLinear(input_degrees_, hidden_features, features, random_mask, False)
+        if context_features is not None:
+            self.context_layer = nn.Linear(context_features, hidden_features)
+        block_cls = MaskedResidualBlock if use_residual_blocks else MaskedFeedforwardBlock
+        blocks, prev = [], self.initial_layer.degrees
+        for _ in range(num_blocks):
+            blocks.append(block_cls(in_degrees=prev, autoregressive_features=features,
+                                    context_features=context_features, random_mask=random_mask,
+                                    activation=activation, dropout_probability=dropout_probability,
+                                    use_batch_norm=use_batch_norm))
+            prev = blocks[-1].degrees
+        self.blocks = nn.ModuleList(blocks)
+        self.final_layer = MaskedLinear(prev, features * output_multiplier, features, random_mask, True,
+                                        out_degrees_=input_degrees_)
+
+    def forward(self, inputs, context=None):
+        h = self.initial_layer(self.preprocessing(inputs))
+        if context is not None:
+            h = h + self.context_layer(context)
+        for block in self.blocks:
+            h = block(h, context)
+        return self.final_layer(h)

@@ -1,0 +1,330 @@
+"""Autograd bindings of the C-ABI kernels.  Every function here launches hand-written sm_100a
+kernels on the current CUDA stream; backward passes are hand-written kernels too (no autograd
+tracing through ATen for the bijector math)."""
+import math
+
+import torch
+from torch.autograd.function import once_differentiable
+
+from . import _lib
+from ._lib import call, ptr, stream, dtype_code
+
+# kernel launches issued through this module (read by bench.py for `gpu_launches`)
+LAUNCHES = 0
+
+COL_PASS, COL_COND, COL_SHARED = 0, 1, 2
+TAIL_LINEAR, TAIL_CIRCULAR, TAIL_LIST_LINEAR, TAIL_LIST_CIRCULAR = 0, 1, 2, 3
+SCALE_MAPS = {"exp": 0, "sigmoid": 1, "sigmoid_inv": 2, "none": 3, "maf": 4}
+
+
+def _launch(name, *args, n=1):
+    global LAUNCHES
+    LAUNCHES += n
+    call(name, *args)
+
+
+def _zeros_if_none(g, like_shape, ref):
+    return torch.zeros(like_shape, dtype=ref.dtype, device=ref.device) if g is None else g.contiguous()
+
+
+class SplineSpec:
+    """Per-layer constant metadata of a spline layer, resident on the device."""
+
+    def __init__(self, D, K, col_map, cond_modes, cond_bounds, Pc, wh_scale,
+                 shared_modes, shared_bounds, Ps, outside_zero):
+        self.D, self.K = D, K
+        self.col_map_host = torch.as_tensor(col_map, dtype=torch.int32)
+        self.cond_modes_host = torch.as_tensor(cond_modes, dtype=torch.uint8)
+        self.cond_bounds_host = torch.as_tensor(cond_bounds, dtype=torch.float64)
+        self.shared_modes_host = torch.as_tensor(shared_modes, dtype=torch.uint8)
+        self.shared_bounds_host = torch.as_tensor(shared_bounds, dtype=torch.float64)
+        self.Tc, self.Ts = len(self.cond_modes_host), len(self.shared_modes_host)
+        self.Pc, self.Ps = Pc, Ps
+        self.wh_scale = float(wh_scale)
+        self.outside_zero = int(outside_zero)
+        self._cache = {}
+
+    def on(self, device, dtype):
+        key = (str(device), dtype)
+        if key not in self._cache:
+            self._cache[key] = (
+                self.col_map_host.to(device),
+                self.cond_modes_host.to(device), self.cond_bounds_host.to(device, dtype),
+                self.shared_modes_host.to(device), self.shared_bounds_host.to(device, dtype))
+        return self._cache[key]
+
+
+class _RqsLayer(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cond, shared, spec, inverse, want_bins):
+        x = x.contiguous()
+        B, D = x.shape
+        if D != spec.D:
+            raise ValueError("Expected features = {}, got {}.".format(spec.D, D))
+        cmap, cm, cb, sm, sb = spec.on(x.device, x.dtype)
+        cond = cond.contiguous() if cond is not None else None
+        shared = shared.contiguous() if shared is not None else None
+        y = torch.empty_like(x)
+        logdet = torch.empty(B, dtype=x.dtype, device=x.device)
+        bins = torch.empty((B, D), dtype=torch.int8, device=x.device) if want_bins else None
+        _launch("vcnf_rqs_layer_fwd", ptr(x), D, ptr(y), D, ptr(logdet), 0, B, D, spec.K, ptr(cmap),
+                ptr(cond), spec.Tc * spec.Pc, spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale,
+                ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb), int(inverse), spec.outside_zero,
+                ptr(bins), None, dtype_code(x), stream())
+        ctx.spec, ctx.inverse = spec, int(inverse)
+        ctx.save_for_backward(x, cond, shared)
+        if want_bins:
+            ctx.mark_non_differentiable(bins)
+            return y, logdet, bins
+        return y, logdet
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy, gld, *unused):
+        x, cond, shared = ctx.saved_tensors
+        spec = ctx.spec
+        B, D = x.shape
+        cmap, cm, cb, sm, sb = spec.on(x.device, x.dtype)
+        gy = _zeros_if_none(gy, x.shape, x)
+        gld = _zeros_if_none(gld, (B,), x)
+        gx = torch.empty_like(x)
+        gcond = torch.empty_like(cond) if cond is not None else None
+        gshared = torch.empty_like(shared) if shared is not None else None
+        ws = None
+        if spec.Ts > 0:
+            nbytes = _lib.query("vcnf_rqs_layer_bwd_workspace", spec.Ts, spec.Ps, dtype_code(x))
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+        _launch("vcnf_rqs_layer_bwd", ptr(x), D, ptr(gy), D, ptr(gld), ptr(gx), D, B, D, spec.K, ptr(cmap),
+                ptr(cond), spec.Tc * spec.Pc, spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale,
+                ptr(gcond), spec.Tc * spec.Pc, ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb),
+                ptr(gshared), ptr(ws), ctx.inverse, spec.outside_zero, dtype_code(x), stream(),
+                n=2 if spec.Ts > 0 else 1)
+        return gx, gcond, gshared, None, None, None
+
+
+def rqs_layer(x, cond, shared, spec, inverse, want_bins=False):
+    """Spline layer: returns (y, logdet[, bin_idx])."""
+    return _RqsLayer.apply(x, cond, shared, spec, inverse, want_bins)
+
+
+class _GatherCols(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cols):
+        x = x.contiguous()
+        B, D = x.shape
+        n = cols.numel()
+        out = torch.empty((B, n), dtype=x.dtype, device=x.device)
+        _launch("vcnf_gather_cols", ptr(x), D, ptr(out), n, B, n, ptr(cols), dtype_code(x), stream())
+        ctx.save_for_backward(cols)
+        ctx.D = D
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        (cols,) = ctx.saved_tensors
+        g = g.contiguous()
+        B, n = g.shape
+        gx = torch.empty((B, ctx.D), dtype=g.dtype, device=g.device)
+        _launch("vcnf_scatter_cols", ptr(g), n, ptr(gx), ctx.D, B, n, ctx.D, ptr(cols), 0, dtype_code(g), stream())
+        return gx, None
+
+
+def gather_cols(x, cols_i32):
+    return _GatherCols.apply(x, cols_i32)
+
+
+class _AffineCoupling(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, param, c2_start, C2, scale_map, inverse, swap_ts):
+        z, param = z.contiguous(), param.contiguous()
+        B, C = z.shape[0], z.shape[1]
+        S = math.prod(z.shape[2:])
+        out = torch.empty_like(z)
+        logdet = torch.empty(B, dtype=z.dtype, device=z.device)
+        _launch("vcnf_affine_coupling_fwd", ptr(z), ptr(param), ptr(out), ptr(logdet), B, C, S, c2_start, C2,
+                scale_map, int(inverse), int(swap_ts), dtype_code(z), stream())
+        ctx.cfg = (B, C, S, c2_start, C2, scale_map, int(inverse), int(swap_ts))
+        ctx.save_for_backward(z, param)
+        return out, logdet
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gout, gld):
+        z, param = ctx.saved_tensors
+        B, C, S, c2_start, C2, scale_map, inverse, swap_ts = ctx.cfg
+        gout = _zeros_if_none(gout, z.shape, z)
+        gld = _zeros_if_none(gld, (B,), z)
+        gz, gparam = torch.empty_like(z), torch.empty_like(param)
+        _launch("vcnf_affine_coupling_bwd", ptr(z), ptr(param), ptr(gout), ptr(gld), ptr(gz), ptr(gparam),
+                B, C, S, c2_start, C2, scale_map, inverse, swap_ts, dtype_code(z), stream())
+        return gz, gparam, None, None, None, None, None
+
+
+def affine_coupling(z, param, c2_start, C2, scale_map, inverse, swap_ts=False):
+    return _AffineCoupling.apply(z, param, c2_start, C2, scale_map, inverse, swap_ts)
+
+
+class _MaskedAffine(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, mask, s, t, inverse):
+        z = z.contiguous()
+        B = z.shape[0]
+        n = math.prod(z.shape[1:])
+        s = s.contiguous() if s is not None else None
+        t = t.contiguous() if t is not None else None
+        out = torch.empty_like(z)
+        logdet = torch.empty(B, dtype=z.dtype, device=z.device)
+        _launch("vcnf_masked_affine_fwd", ptr(z), ptr(mask), ptr(s), ptr(t), ptr(out), ptr(logdet), B, n,
+                int(inverse), dtype_code(z), stream())
+        ctx.inverse = int(inverse)
+        ctx.save_for_backward(z, mask, s, t)
+        return out, logdet
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gout, gld):
+        z, mask, s, t = ctx.saved_tensors
+        B, n = z.shape[0], math.prod(z.shape[1:])
+        gout = _zeros_if_none(gout, z.shape, z)
+        gld = _zeros_if_none(gld, (B,), z)
+        gz = torch.empty_like(z)
+        gs = torch.empty_like(z) if s is not None else None
+        gt = torch.empty_like(z) if t is not None else None
+        _launch("vcnf_masked_affine_bwd", ptr(z), ptr(mask), ptr(s), ptr(t), ptr(gout), ptr(gld), ptr(gz),
+                ptr(gs), ptr(gt), B, n, ctx.inverse, dtype_code(z), stream())
+        return gz, None, gs, gt, None
+
+
+def masked_affine(z, mask, s, t, inverse):
+    return _MaskedAffine.apply(z, mask, s, t, inverse)
+
+
+class _ConstAffine(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, s, t, S, inverse):
+        z = z.contiguous()
+        s_, t_ = s.reshape(-1).contiguous(), t.reshape(-1).contiguous()
+        Pn = s_.numel()
+        B = z.numel() // (Pn * S)
+        out = torch.empty_like(z)
+        _launch("vcnf_const_affine_fwd", ptr(z), ptr(s_), ptr(t_), ptr(out), B, Pn, S, int(inverse),
+                dtype_code(z), stream())
+        ctx.cfg = (B, Pn, S, int(inverse), s.shape, t.shape)
+        ctx.save_for_backward(z, s_, t_)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gout):
+        z, s_, t_ = ctx.saved_tensors
+        B, Pn, S, inverse, s_shape, t_shape = ctx.cfg
+        gout = gout.contiguous()
+        gz, gs, gt = torch.empty_like(z), torch.empty_like(s_), torch.empty_like(t_)
+        ws = torch.empty(_lib.query("vcnf_const_affine_bwd_workspace", Pn, dtype_code(z)), dtype=torch.uint8,
+                         device=z.device)
+        _launch("vcnf_const_affine_bwd", ptr(z), ptr(s_), ptr(t_), ptr(gout), ptr(gz), ptr(gs), ptr(gt), ptr(ws),
+                B, Pn, S, inverse, dtype_code(z), stream(), n=2)
+        return gz, gs.view(s_shape), gt.view(t_shape), None, None
+
+
+def const_affine(z, s, t, S, inverse):
+    return _ConstAffine.apply(z, s, t, S, inverse)
+
+
+class _PermuteChannels(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, perm, inv_perm):
+        z = z.contiguous()
+        B, C = z.shape[0], z.shape[1]
+        S = math.prod(z.shape[2:])
+        out = torch.empty_like(z)
+        _launch("vcnf_permute_channels", ptr(z), ptr(out), B, C, S, ptr(perm), dtype_code(z), stream())
+        ctx.save_for_backward(perm, inv_perm)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        perm, inv_perm = ctx.saved_tensors
+        return _PermuteChannels.apply(g, inv_perm, perm), None, None
+
+
+def permute_channels(z, perm_i32, inv_perm_i32):
+    """out[:, j] = z[:, perm[j]]"""
+    return _PermuteChannels.apply(z, perm_i32, inv_perm_i32)
+
+
+class _Squeeze(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, inverse):
+        z = z.contiguous()
+        B, C, H, W = z.shape
+        if not inverse:
+            c, h, w = C // 4, H, W
+            out = torch.empty((B, c, 2 * h, 2 * w), dtype=z.dtype, device=z.device)
+        else:
+            c, h, w = C, H // 2, W // 2
+            out = torch.empty((B, 4 * c, h, w), dtype=z.dtype, device=z.device)
+        _launch("vcnf_squeeze", ptr(z), ptr(out), B, c, h, w, int(inverse), dtype_code(z), stream())
+        ctx.inverse = int(inverse)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        return _Squeeze.apply(g, 1 - ctx.inverse), None
+
+
+def squeeze(z, inverse):
+    return _Squeeze.apply(z, inverse)
+
+
+class _SmallLinear(torch.autograd.Function):
+    """y[r, out_idx[o]] = sum_i W[o, i] x[r, in_idx[i]] + bias[o]  (or W (x - bias))."""
+
+    @staticmethod
+    def forward(ctx, x, W, bias, in_idx, out_idx, sub_bias_first):
+        x, W = x.contiguous(), W.contiguous()
+        D = W.shape[0]
+        S = math.prod(x.shape[2:])
+        rows = x.shape[0] * S
+        y = torch.empty_like(x)
+        _launch("vcnf_small_linear", ptr(x), ptr(y), ptr(W), ptr(bias), ptr(in_idx), ptr(out_idx), rows, D, S,
+                int(sub_bias_first), dtype_code(x), stream())
+        ctx.cfg = (D, S, rows, int(sub_bias_first))
+        ctx.save_for_backward(x, W, bias, in_idx, out_idx)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        x, W, bias, in_idx, out_idx = ctx.saved_tensors
+        D, S, rows, sub = ctx.cfg
+        gy = gy.contiguous()
+        gx = gW = gb = None
+        if ctx.needs_input_grad[0] or (sub and bias is not None and ctx.needs_input_grad[2]):
+            gx = torch.empty_like(x)
+            Wt = W.t().contiguous()
+            _launch("vcnf_small_linear", ptr(gy), ptr(gx), ptr(Wt), None, ptr(out_idx), ptr(in_idx), rows, D, S, 0,
+                    dtype_code(x), stream())
+        # D x D parameter gradients: a plain [D, rows] x [rows, D] library GEMM (not on the hot path's
+        # byte budget; SURVEY.md 8d "LULinearPermute ... + D^2 param grads")
+        if ctx.needs_input_grad[1] or (bias is not None and ctx.needs_input_grad[2]):
+            if S == 1:
+                xg = x if in_idx is None else x.index_select(1, in_idx.long())
+                gg = gy if out_idx is None else gy.index_select(1, out_idx.long())
+            else:
+                xg = (x if in_idx is None else x.index_select(1, in_idx.long())).flatten(2).transpose(1, 2).reshape(-1, D)
+                gg = (gy if out_idx is None else gy.index_select(1, out_idx.long())).flatten(2).transpose(1, 2).reshape(-1, D)
+            if sub and bias is not None:
+                xg = xg - bias
+            if ctx.needs_input_grad[1]:
+                gW = gg.t() @ xg
+            if bias is not None and ctx.needs_input_grad[2]:
+                gb = -(gg @ W).sum(0) if sub else gg.sum(0)
+        return gx, gW, gb, None, None, None
+
+
+def small_linear(x, W, bias=None, in_idx=None, out_idx=None, sub_bias_first=False):
+    return _SmallLinear.apply(x, W, bias, in_idx, out_idx, sub_bias_first)
