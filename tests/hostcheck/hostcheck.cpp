@@ -24,6 +24,32 @@ static void run_bwd(const T* prm, const T* v, const T* bound, int64_t n, int P, 
     rqs_element_bwd<T, KMAX>(prm + i * P, v[i], bound[i], scale, c, gout[i], glad[i], gv + i, gprm + i * P);
 }
 
+
+// batch-shared parameters: one feature's table, n inputs
+template <typename T, int KMAX>
+static void run_table_fwd(const T* prm, const T* v, T bound, int64_t n, RqsElemCfg c, T* out, T* lad,
+                          int32_t* bin, int32_t* flag) {
+  T tab[3 * (KMAX + 1)];
+  rqs_build_table<T, KMAX>(prm, c.K, c.mode, bound, tab);
+  for (int64_t i = 0; i < n; ++i) {
+    int b = -1, f = 0;
+    rqs_table_element<T, KMAX>(tab, v[i], bound, c, out + i, lad + i, &b, &f);
+    bin[i] = b;
+    *flag |= f;
+  }
+}
+
+template <typename T, int KMAX>
+static void run_table_bwd(const T* prm, const T* v, T bound, int64_t n, RqsElemCfg c, const T* gout,
+                          const T* glad, T* gv, T* gprm) {
+  T tab[3 * (KMAX + 1)], gtab[3 * (KMAX + 1)];
+  rqs_build_table<T, KMAX>(prm, c.K, c.mode, bound, tab);
+  for (int i = 0; i < 3 * (KMAX + 1); ++i) gtab[i] = T(0);
+  for (int64_t i = 0; i < n; ++i)
+    rqs_table_element_bwd<T, KMAX>(tab, v[i], bound, c, gout[i], glad[i], gv + i, gtab);
+  rqs_table_to_raw_grad<T, KMAX>(prm, c.K, c.mode, bound, gtab, gprm);
+}
+
 #define DISPATCH(T, call)                                        \
   if (K <= 8) { call(T, 8); } else if (K <= 16) { call(T, 16); } else { call(T, 32); }
 
@@ -47,6 +73,25 @@ int hostcheck_rqs_bwd(const void* prm, const void* v, const void* bound, int64_t
   RqsElemCfg c{K, mode, inverse, outside_zero};
   const int P = 2 * K + rqs_num_derivs(K, mode);
 #define CALL(T, KM) run_bwd<T, KM>((const T*)prm, (const T*)v, (const T*)bound, n, P, (T)scale, c, (const T*)gout, (const T*)glad, (T*)gv, (T*)gprm)
+  if (is_double) { DISPATCH(double, CALL) } else { DISPATCH(float, CALL) }
+#undef CALL
+  return 0;
+}
+int hostcheck_rqs_table_fwd(const void* prm, const void* v, double bound, int64_t n, int K, int mode,
+                            int inverse, int outside_zero, int is_double, void* out, void* lad, int32_t* bin) {
+  RqsElemCfg c{K, mode, inverse, outside_zero};
+  int32_t flag = 0;
+#define CALL(T, KM) run_table_fwd<T, KM>((const T*)prm, (const T*)v, (T)bound, n, c, (T*)out, (T*)lad, bin, &flag)
+  if (is_double) { DISPATCH(double, CALL) } else { DISPATCH(float, CALL) }
+#undef CALL
+  return flag;
+}
+
+int hostcheck_rqs_table_bwd(const void* prm, const void* v, double bound, int64_t n, int K, int mode,
+                            int inverse, int outside_zero, int is_double, const void* gout, const void* glad,
+                            void* gv, void* gprm) {
+  RqsElemCfg c{K, mode, inverse, outside_zero};
+#define CALL(T, KM) run_table_bwd<T, KM>((const T*)prm, (const T*)v, (T)bound, n, c, (const T*)gout, (const T*)glad, (T*)gv, (T*)gprm)
   if (is_double) { DISPATCH(double, CALL) } else { DISPATCH(float, CALL) }
 #undef CALL
   return 0;

@@ -14,7 +14,7 @@ import oracle
 import vcnf_b200 as nf
 from cases import LAYER_CASES, MODEL_CASES, randomize
 from harness import eval_layer, eval_model
-from parity import assert_close, assert_grads_close, AFFINE, SPLINE
+from parity import assert_close, assert_close_tail, assert_grads_close, AFFINE, SPLINE
 
 pytestmark = pytest.mark.gpu
 
@@ -52,8 +52,17 @@ def test_layer_matches_reference_golden(name, direction):
     ref = g[direction]
     tol, gtol = _tol(name, dtype)
     n_sum = max(1, g["x"][0].numel())
-    assert_close(got["z"], ref["z"], what=name + ".z", **tol)
-    assert_close(got["log_det"], ref["log_det"], what=name + ".log_det", rtol=tol["rtol"], atol=tol["atol"] * n_sum)
+    if name in SPLINE_CASES and dtype == torch.float32:
+        # the reference's own fp32 evaluation is ill-conditioned in the tail (its fp32 and
+        # fp64 log-dets of this very case differ by up to 64 x the stated tolerance) -> tail clause
+        r64 = g[direction + "_f64"]
+        assert_close_tail(got["z"], ref["z"], r64["z"], what=name + ".z", **tol)
+        assert_close_tail(got["log_det"], ref["log_det"], r64["log_det"], what=name + ".log_det",
+                          rtol=tol["rtol"], atol=tol["atol"] * n_sum)
+    else:
+        assert_close(got["z"], ref["z"], what=name + ".z", **tol)
+        assert_close(got["log_det"], ref["log_det"], what=name + ".log_det", rtol=tol["rtol"],
+                     atol=tol["atol"] * n_sum)
     if ref["gx"] is not None:
         assert_grads_close({"x": got["gx"], **got["grads"]}, {"x": ref["gx"], **ref["grads"]}, rtol=gtol, what=name)
 

@@ -106,3 +106,51 @@ def test_element_math_matches_oracle(lib, K, mode, inverse, dtype):
         # fp32 gradients vs the fp32 oracle: 99.9 % of elements inside rtol 1e-3 + atol scaled
         e = (gp[m] - gp_ref[m]).abs() / (1e-3 * gp_ref[m].abs() + 1e-4 * gscale)
         assert float((e <= 1).float().mean()) > 0.999
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("inverse", [0, 1])
+@pytest.mark.parametrize("mode", sorted(MODES))
+@pytest.mark.parametrize("K", [8, 10])
+def test_shared_table_path_matches_oracle(lib, K, mode, inverse, dtype):
+    """Batch-shared parameters (PiecewiseRationalQuadraticCDF, coupling.py:165-246): the knot-table
+    path must give the per-element path's values and the batch-summed parameter gradient."""
+    g = torch.Generator().manual_seed(K * 7 + inverse)
+    n, bound = 3000, 3.0
+    nd = {0: K - 1, 1: K}.get(MODES[mode], K + 1)
+    P = 2 * K + nd
+    prm = torch.randn(P, generator=g, dtype=torch.float64).to(dtype)
+    x = (1.4 * torch.randn(n, 1, generator=g, dtype=torch.float64)).to(dtype)
+    x[0], x[1] = bound, -bound
+    gout = torch.randn(n, 1, generator=g, dtype=torch.float64).to(dtype)
+    glad = torch.randn(n, 1, generator=g, dtype=torch.float64).to(dtype)
+
+    xr = x.clone().requires_grad_(True)
+    pr = prm.clone().requires_grad_(True)
+    y_ref, lad_ref, bin_ref = _oracle(xr, pr.expand(n, 1, P), K, mode, bool(inverse), bound, 1.0)
+    loss = (y_ref * gout).sum() + (lad_ref * glad).sum()
+    gx_ref, gp_ref = torch.autograd.grad(loss, [xr, pr])
+
+    out, lad = torch.empty_like(x), torch.empty_like(x)
+    bins = torch.empty(n, dtype=torch.int32)
+    isd = int(dtype == torch.float64)
+    lib.hostcheck_rqs_table_fwd.restype = ctypes.c_int
+    flag = lib.hostcheck_rqs_table_fwd(_ptr(prm), _ptr(x), ctypes.c_double(bound), ctypes.c_int64(n), K,
+                                       MODES[mode], inverse, int(mode.startswith("list")), isd,
+                                       _ptr(out), _ptr(lad), _ptr(bins))
+    assert flag == 0
+    gv, gp = torch.empty_like(x), torch.empty_like(prm)
+    lib.hostcheck_rqs_table_bwd(_ptr(prm), _ptr(x), ctypes.c_double(bound), ctypes.c_int64(n), K, MODES[mode],
+                                inverse, int(mode.startswith("list")), isd, _ptr(gout), _ptr(glad),
+                                _ptr(gv), _ptr(gp))
+    assert int((bins != bin_ref[:, 0].int()).sum()) == 0
+    if dtype == torch.float64:
+        torch.testing.assert_close(out, y_ref.detach(), rtol=1e-9, atol=1e-10)
+        torch.testing.assert_close(lad, lad_ref.detach(), rtol=1e-9, atol=1e-10)
+        torch.testing.assert_close(gv, gx_ref, rtol=1e-7, atol=1e-8 * float(gx_ref.abs().max()))
+        torch.testing.assert_close(gp, gp_ref, rtol=1e-7, atol=1e-8 * float(gp_ref.abs().max()))
+    else:
+        inside = (out - y_ref.detach()).abs() <= 1e-5 + 1e-4 * y_ref.detach().abs()
+        assert float(inside.float().mean()) >= 0.999
+        e = (gp - gp_ref).abs() / (1e-3 * gp_ref.abs() + 1e-3 * float(gp_ref.abs().max()))
+        assert float(e.max()) <= 1.0

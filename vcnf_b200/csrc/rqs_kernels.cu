@@ -6,16 +6,23 @@
 // syncs of normflow/utils/splines.py:20-193 + flows/neural_spline/coupling.py:70-159.
 //
 // Data movement (HBM-bound, SURVEY.md 8d: s*(T*P + 2D + 1) bytes per sample):
-//   * the per-sample parameter block [R rows x Tc*Pc] of a tile is one CONTIGUOUS span in HBM;
-//     it is pulled into shared memory by the TMA engine with a 1-D bulk async copy
-//     (cp.async.bulk ... mbarrier::complete_tx) into a 2-stage ring, so the copy of tile i+1
-//     overlaps the math of tile i and no registers are spent on staging;
-//   * threads then read their element's P parameters from shared memory at stride P (P = 3K-1
-//     is odd -> bank-conflict free), x / y go straight to/from HBM fully coalesced
-//     (consecutive threads = consecutive columns of a row);
+//   * a tile is R consecutive samples.  Its parameter block [R x Tc*Pc], its x rows [R x D] (and
+//     in the backward its gy rows) are CONTIGUOUS spans in HBM; each is pulled into shared memory
+//     by the TMA engine with one 1-D bulk async copy (cp.async.bulk ... mbarrier::complete_tx)
+//     into a 2-stage ring, so the copies of tile i+1 overlap the math of tile i and no registers
+//     are spent on staging;
+//   * the math runs in passes in which EVERY thread does the same kind of work (no divergence):
+//       pass A: conditional elements, index space rows x Tc; thread e reads its P parameters from
+//               shared memory at stride P (P = 3K-1 odd -> bank-conflict free);
+//       pass B: batch-shared / pass-through elements; the knots of batch-shared parameters are
+//               built ONCE per CTA into a shared-memory table (rqs_math.cuh: rqs_build_table);
+//   * outputs (y, per-element log-det terms; gx, parameter gradients) are assembled in shared
+//     memory and leave as full coalesced rows / one bulk store per tile;
+//   * log|det|: half-warp per sample, shuffle tree (fixed order -> deterministic);
 //   * persistent grid: #CTAs = SMs x resident CTAs, each walks tiles blockIdx.x, +gridDim.x, ...
-//   * log|det|: per-element terms go through shared memory and are summed per row in feature
-//     order by one thread (deterministic).
+//   * batch-shared parameter gradients: every thread owns a private accumulator table in shared
+//     memory (no atomics), reduced per CTA in a fixed order, chained back to the raw parameters
+//     once per CTA and finished by rqs_partial_reduce_kernel (deterministic two-stage reduction).
 #include "common.cuh"
 #include "rqs_math.cuh"
 #include "../../include/vcnf_b200.h"
@@ -37,217 +44,389 @@ struct RqsLayerArgs {
   const uint8_t* smodes; const T* sbounds;
   int inverse; int outside_zero;
   int8_t* bin_out; int32_t* err_flag;
-  int R; int bulk_in; int64_t num_tiles;
+  int R; int64_t num_tiles;
+  int bulk_p, bulk_x, bulk_gy, bulk_gp;   // base pointer + leading dimension allow 1-D bulk copies
   // backward only
   const T* gy; int64_t ldgy; const T* gld;
   T* gx; int64_t ldgx;
-  T* gcond; int64_t ld_gcond; int bulk_out;
+  T* gcond; int64_t ld_gcond;
   T* partial;     // [gridDim.x, Ts*Ps]
 };
 
 __host__ __device__ inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 __host__ __device__ inline int64_t imin64(int64_t a, int64_t b) { return a < b ? a : b; }
 
-// Fill one parameter stage for tile `t`.  Full tiles of a contiguous, 16 B-aligned parameter
-// matrix go through the TMA engine; anything else is copied cooperatively.
+// Shared-memory carve-up, computed identically on host (size) and device (pointers).
+struct RqsSmem {
+  size_t bars, pst, pst_stride, xst, xst_stride, gyst, outs, lads, gst, tab, acc, tabg, meta, total;
+};
 template <typename T>
-__device__ __forceinline__ void stage_issue(const RqsLayerArgs<T>& a, int64_t t, T* stage, uint64_t* bar) {
-  const int64_t rows = imin64(a.R, a.B - t * a.R);
-  if (a.Tc > 0 && a.bulk_in && rows == a.R && threadIdx.x == 0) {
-    const uint32_t bytes = static_cast<uint32_t>(static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T));
-    mbar_expect_tx(bar, bytes);
-    bulk_g2s(stage, a.cond + t * a.R * a.ld_cond, bytes, bar);
-  }
+__host__ __device__ inline RqsSmem rqs_smem_layout(int R, int D, int Tc, int Pc, int Ts, int K, bool bwd, int nthreads) {
+  RqsSmem m;
+  size_t o = 0;
+  m.bars = o; o += 128;
+  m.pst_stride = round_up(static_cast<size_t>(R) * Tc * Pc * sizeof(T), 128);
+  m.pst = o; o += 2 * m.pst_stride;
+  m.xst_stride = round_up(static_cast<size_t>(R) * D * sizeof(T), 128);
+  m.xst = o; o += 2 * m.xst_stride;
+  m.gyst = o; if (bwd) o += 2 * m.xst_stride;
+  m.outs = o; o += m.xst_stride;                       // y tile (fwd) / gx tile (bwd)
+  m.lads = o; if (!bwd) o += m.xst_stride;             // per-element log-det terms (fwd)
+  m.gst = o; if (bwd) o += m.pst_stride;               // conditional parameter gradients (bwd)
+  const size_t TK = 3 * (static_cast<size_t>(K) + 1);
+  m.tab = o; o += round_up(Ts * TK * sizeof(T), 128);
+  m.acc = o; if (bwd && Ts > 0) o += round_up(static_cast<size_t>(nthreads / Ts) * Ts * TK * sizeof(T), 128);
+  m.tabg = o; if (bwd) o += round_up(Ts * TK * sizeof(T), 128);
+  // meta: cond_col[Tc] | other_col[D] | other_map[D] | cmode[Tc] | smode[Ts] | shared_col[Ts] (int32),
+  //       cbound[Tc] | sbound[Ts] (T)
+  m.meta = o; o += round_up((2 * static_cast<size_t>(Tc) + 2 * D + 2 * Ts) * sizeof(int32_t), 16) +
+                   round_up((static_cast<size_t>(Tc) + Ts) * sizeof(T), 16);
+  m.total = o;
+  return m;
 }
 
 template <typename T>
-__device__ __forceinline__ void stage_wait(const RqsLayerArgs<T>& a, int64_t t, T* stage, uint64_t* bar,
-                                           uint32_t parity) {
-  if (a.Tc <= 0) return;
+struct RqsMeta {
+  int32_t* cond_col; int32_t* other_col; int32_t* other_map; int32_t* cmode; int32_t* smode;
+  int32_t* shared_col;
+  T* cbound; T* sbound;
+  int n_other;
+};
+
+// Column lists, tail modes and bounds into shared memory; knot tables of the batch-shared features.
+template <typename T, int KMAX>
+__device__ __forceinline__ RqsMeta<T> rqs_setup(const RqsLayerArgs<T>& a, int K, unsigned char* smem,
+                                                const RqsSmem& L, int* n_other_s) {
+  RqsMeta<T> m;
+  int32_t* ip = reinterpret_cast<int32_t*>(smem + L.meta);
+  m.cond_col = ip; ip += a.Tc;
+  m.other_col = ip; ip += a.D;
+  m.other_map = ip; ip += a.D;
+  m.cmode = ip; ip += a.Tc;
+  m.smode = ip; ip += a.Ts;
+  m.shared_col = ip; ip += a.Ts;
+  T* tp = reinterpret_cast<T*>(smem + L.meta + round_up((2 * static_cast<size_t>(a.Tc) + 2 * a.D + 2 * a.Ts) * sizeof(int32_t), 16));
+  m.cbound = tp; tp += a.Tc;
+  m.sbound = tp;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    int n = 0;
+    for (int j = 0; j < a.Ts; ++j) m.shared_col[j] = -1;
+    for (int c = 0; c < a.D; ++c) {
+      const int cm = a.col_map[c];
+      if ((cm >> 16) == VCNF_COL_COND) m.cond_col[cm & 0xffff] = c;
+      else {
+        m.other_col[n] = c; m.other_map[n] = cm; ++n;
+        if ((cm >> 16) == VCNF_COL_SHARED) m.shared_col[cm & 0xffff] = c;
+      }
+    }
+    *n_other_s = n;
+  }
+  for (int j = tid; j < a.Tc; j += blockDim.x) { m.cmode[j] = a.cmodes[j]; m.cbound[j] = a.cbounds[j]; }
+  for (int j = tid; j < a.Ts; j += blockDim.x) { m.smode[j] = a.smodes[j]; m.sbound[j] = a.sbounds[j]; }
+  T* tab = reinterpret_cast<T*>(smem + L.tab);
+  const int TK = 3 * (K + 1);
+  for (int j = tid; j < a.Ts; j += blockDim.x)
+    rqs_build_table<T, KMAX>(a.shared + static_cast<size_t>(j) * a.Ps, K, a.smodes[j], a.sbounds[j], tab + j * TK);
+  __syncthreads();
+  m.n_other = *n_other_s;
+  return m;
+}
+
+// ---- tile staging: TMA bulk copies when the span is contiguous and 16 B granular, else cooperative
+template <typename T>
+__device__ __forceinline__ bool span_bulk(int flag, int64_t elems) {
+  return flag && ((static_cast<size_t>(elems) * sizeof(T)) % 16 == 0);
+}
+
+template <typename T, bool BWD>
+__device__ __forceinline__ void stage_issue(const RqsLayerArgs<T>& a, int64_t t, T* pst, T* xst, T* gyst,
+                                            uint64_t* bar) {
+  if (threadIdx.x != 0) return;
   const int64_t rows = imin64(a.R, a.B - t * a.R);
-  if (a.bulk_in && rows == a.R) {
-    mbar_wait(bar, parity);
-  } else {
+  const int64_t np = rows * a.Tc * a.Pc, nx = rows * a.D;
+  const bool bp = a.Tc > 0 && span_bulk<T>(a.bulk_p, np);
+  const bool bx = span_bulk<T>(a.bulk_x, nx);
+  const bool bg = BWD && span_bulk<T>(a.bulk_gy, nx);
+  const uint32_t bytes = static_cast<uint32_t>(((bp ? np : 0) + (bx ? nx : 0) + (bg ? nx : 0)) * sizeof(T));
+  if (bytes == 0) return;
+  mbar_expect_tx(bar, bytes);
+  if (bp) bulk_g2s(pst, a.cond + t * a.R * a.ld_cond, static_cast<uint32_t>(np * sizeof(T)), bar);
+  if (bx) bulk_g2s(xst, a.x + t * a.R * a.ldx, static_cast<uint32_t>(nx * sizeof(T)), bar);
+  if (bg) bulk_g2s(gyst, a.gy + t * a.R * a.ldgy, static_cast<uint32_t>(nx * sizeof(T)), bar);
+}
+
+// Returns true when the barrier of this stage was used (its phase flipped).
+template <typename T, bool BWD>
+__device__ __forceinline__ bool stage_wait(const RqsLayerArgs<T>& a, int64_t t, T* pst, T* xst, T* gyst,
+                                           uint64_t* bar, uint32_t parity) {
+  const int64_t row0 = t * a.R;
+  const int64_t rows = imin64(a.R, a.B - row0);
+  const int64_t np = rows * a.Tc * a.Pc, nx = rows * a.D;
+  const bool bp = a.Tc > 0 && span_bulk<T>(a.bulk_p, np);
+  const bool bx = span_bulk<T>(a.bulk_x, nx);
+  const bool bg = BWD && span_bulk<T>(a.bulk_gy, nx);
+  if (a.Tc > 0 && !bp) {
     const int n = a.Tc * a.Pc;
-    for (int64_t e = threadIdx.x; e < rows * n; e += blockDim.x) {
+    for (int64_t e = threadIdx.x; e < np; e += blockDim.x) {
       const int64_t r = e / n;
-      stage[e] = a.cond[(t * a.R + r) * a.ld_cond + (e - r * n)];
+      pst[e] = a.cond[(row0 + r) * a.ld_cond + (e - r * n)];
     }
   }
+  if (!bx) {
+    for (int64_t e = threadIdx.x; e < nx; e += blockDim.x) {
+      const int64_t r = e / a.D;
+      xst[e] = a.x[(row0 + r) * a.ldx + (e - r * a.D)];
+    }
+  }
+  if (BWD && !bg) {
+    for (int64_t e = threadIdx.x; e < nx; e += blockDim.x) {
+      const int64_t r = e / a.D;
+      gyst[e] = a.gy[(row0 + r) * a.ldgy + (e - r * a.D)];
+    }
+  }
+  const bool used = bp || bx || bg;
+  if (used) mbar_wait(bar, parity);
+  return used;
 }
 
-template <typename T, int KMAX>
+template <typename T, int KMAX, bool EXACT>
 __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_kernel(const RqsLayerArgs<T> a) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const size_t stage_bytes = round_up(static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T), 128);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
-  T* stage0 = reinterpret_cast<T*>(smem + 128);
-  T* stage1 = reinterpret_cast<T*>(smem + 128 + stage_bytes);
-  T* sh = reinterpret_cast<T*>(smem + 128 + 2 * stage_bytes);
-  T* lad_s = sh + round_up(static_cast<size_t>(a.Ts) * a.Ps, 32);
-
+  __shared__ int n_other_s;
+  const int K = EXACT ? KMAX : a.K;
+  const int TK = 3 * (K + 1);
+  const RqsSmem L = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, K, false, kThreads);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
+  T* ys = reinterpret_cast<T*>(smem + L.outs);
+  T* lads = reinterpret_cast<T*>(smem + L.lads);
+  const T* tab = reinterpret_cast<const T*>(smem + L.tab);
   const int tid = threadIdx.x;
   if (tid == 0) {
     mbar_init(&bars[0], 1);
     mbar_init(&bars[1], 1);
     mbar_init_fence();
   }
-  for (int i = tid; i < a.Ts * a.Ps; i += blockDim.x) sh[i] = a.shared[i];
-  __syncthreads();
+  const RqsMeta<T> M = rqs_setup<T, KMAX>(a, K, smem, L, &n_other_s);   // ends with __syncthreads()
+  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
 
   int flag = 0;
+  uint32_t par0 = 0u, par1 = 0u;
   int64_t tile = blockIdx.x;
-  if (tile < a.num_tiles) stage_issue(a, tile, stage0, &bars[0]);
+  if (tile < a.num_tiles)
+    stage_issue<T, false>(a, tile, reinterpret_cast<T*>(smem + L.pst), reinterpret_cast<T*>(smem + L.xst), nullptr, &bars[0]);
   for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
     const int s = it & 1;
-    T* cur = s ? stage1 : stage0;
+    T* cur = reinterpret_cast<T*>(smem + L.pst + s * L.pst_stride);
+    T* xs = reinterpret_cast<T*>(smem + L.xst + s * L.xst_stride);
     const int64_t next = tile + gridDim.x;
-    if (next < a.num_tiles) stage_issue(a, next, s ? stage0 : stage1, &bars[s ^ 1]);
+    if (next < a.num_tiles)
+      stage_issue<T, false>(a, next, reinterpret_cast<T*>(smem + L.pst + (s ^ 1) * L.pst_stride),
+                            reinterpret_cast<T*>(smem + L.xst + (s ^ 1) * L.xst_stride), nullptr, &bars[s ^ 1]);
     const int64_t row0 = tile * a.R;
     const int rows = static_cast<int>(imin64(a.R, a.B - row0));
-    stage_wait(a, tile, cur, &bars[s], (it >> 1) & 1);
+    if (stage_wait<T, false>(a, tile, cur, xs, nullptr, &bars[s], s ? par1 : par0)) { if (s) par1 ^= 1u; else par0 ^= 1u; }
     __syncthreads();
 
-    const int n_el = rows * a.D;
-    for (int e = tid; e < n_el; e += blockDim.x) {
-      const int r = e / a.D;
-      const int c = e - r * a.D;
-      const int cm = __ldg(a.col_map + c);
-      const int kind = cm >> 16, idx = cm & 0xffff;
-      const T v = a.x[(row0 + r) * a.ldx + c];
+    // pass A: conditional elements (e = r*Tc + j; parameters at cur + e*Pc)
+    const int nA = rows * Tc;
+    for (int e = tid; e < nA; e += kThreads) {
+      const int r = e / Tc;
+      const int j = e - r * Tc;
+      const int c = M.cond_col[j];
+      const T v = xs[r * D + c];
+      RqsElemCfg cfg{K, M.cmode[j], a.inverse, a.outside_zero};
+      T out, lad;
+      int bin;
+      rqs_element<T, KMAX>(cur + static_cast<size_t>(e) * Pc, v, M.cbound[j], a.wh_scale, cfg, &out, &lad, &bin, &flag);
+      ys[r * D + c] = out;
+      lads[r * D + c] = lad;
+      if (a.bin_out) a.bin_out[(row0 + r) * D + c] = static_cast<int8_t>(bin);
+    }
+    // pass B: batch-shared and pass-through elements
+    const int nB = rows * No;
+    for (int e = tid; e < nB; e += kThreads) {
+      const int r = e / No;
+      const int j = e - r * No;
+      const int c = M.other_col[j];
+      const int cm = M.other_map[j];
+      const T v = xs[r * D + c];
       T out = v, lad = T(0);
       int bin = -2;
-      if (kind != VCNF_COL_PASS) {
-        const T* prm;
-        T scale, bound;
-        RqsElemCfg cfg{a.K, 0, a.inverse, a.outside_zero};
-        if (kind == VCNF_COL_COND) {
-          prm = cur + (static_cast<size_t>(r) * a.Tc + idx) * a.Pc;
-          scale = a.wh_scale;
-          cfg.mode = __ldg(a.cmodes + idx);
-          bound = __ldg(a.cbounds + idx);
-        } else {
-          prm = sh + static_cast<size_t>(idx) * a.Ps;
-          scale = T(1);
-          cfg.mode = __ldg(a.smodes + idx);
-          bound = __ldg(a.sbounds + idx);
-        }
-        rqs_element<T, KMAX>(prm, v, bound, scale, cfg, &out, &lad, &bin, &flag);
+      if ((cm >> 16) == VCNF_COL_SHARED) {
+        const int idx = cm & 0xffff;
+        RqsElemCfg cfg{K, M.smode[idx], a.inverse, a.outside_zero};
+        rqs_table_element<T, KMAX>(tab + idx * TK, v, M.sbound[idx], cfg, &out, &lad, &bin, &flag);
       }
-      a.y[(row0 + r) * a.ldy + c] = out;
-      lad_s[e] = lad;
-      if (a.bin_out) a.bin_out[(row0 + r) * a.D + c] = static_cast<int8_t>(bin);
+      ys[r * D + c] = out;
+      lads[r * D + c] = lad;
+      if (a.bin_out) a.bin_out[(row0 + r) * D + c] = static_cast<int8_t>(bin);
     }
     __syncthreads();
-    for (int r = tid; r < rows; r += blockDim.x) {
+
+    // pass C: coalesced row stores + per-sample log|det| (half-warp per sample, shuffle tree)
+    const int nY = rows * D;
+    if (a.ldy == D) {
+      T* dst = a.y + row0 * D;
+      for (int e = tid; e < nY; e += kThreads) dst[e] = ys[e];
+    } else {
+      for (int e = tid; e < nY; e += kThreads) {
+        const int r = e / D;
+        a.y[(row0 + r) * a.ldy + (e - r * D)] = ys[e];
+      }
+    }
+    const int hl = tid & 15;
+    for (int r0 = (tid >> 5) * 2; r0 < rows; r0 += (kThreads >> 5) * 2) {
+      const int r = r0 + ((tid >> 4) & 1);
       T acc = T(0);
-      for (int c = 0; c < a.D; ++c) acc += lad_s[r * a.D + c];
-      if (a.accumulate) acc += a.logdet[row0 + r];
-      a.logdet[row0 + r] = acc;
+      if (r < rows)
+        for (int c = hl; c < D; c += 16) acc += lads[r * D + c];
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (r < rows && hl == 0) {
+        if (a.accumulate) acc += a.logdet[row0 + r];
+        a.logdet[row0 + r] = acc;
+      }
     }
-    __syncthreads();
   }
   if (flag && a.err_flag) atomicOr(a.err_flag, flag);
 }
 
 // Backward: recomputes the bin record from (x, params) and applies the hand-derived adjoint
-// (rqs_math.cuh: rqs_element_bwd).  Parameter gradients of a tile are assembled in shared memory
-// and leave through one bulk store (TMA engine) per tile; batch-shared parameter gradients are
-// reduced per CTA in a fixed order and finished by rqs_partial_reduce_kernel (deterministic).
-template <typename T, int KMAX>
+// (rqs_math.cuh).  Conditional parameter gradients of a tile are assembled in shared memory and
+// leave through one bulk store (TMA engine) per tile.
+template <typename T, int KMAX, bool EXACT>
 __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerArgs<T> a) {
   extern __shared__ __align__(128) unsigned char smem[];
-  const size_t stage_bytes = round_up(static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T), 128);
-  const size_t sgrad_bytes = round_up(static_cast<size_t>(a.R) * a.Ts * a.Ps * sizeof(T), 128);
-  const int n_sh = a.Ts * a.Ps;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
-  T* stage0 = reinterpret_cast<T*>(smem + 128);
-  T* stage1 = reinterpret_cast<T*>(smem + 128 + stage_bytes);
-  T* gstage = reinterpret_cast<T*>(smem + 128 + 2 * stage_bytes);
-  T* sstage = reinterpret_cast<T*>(smem + 128 + 3 * stage_bytes);
-  T* sh = reinterpret_cast<T*>(smem + 128 + 3 * stage_bytes + sgrad_bytes);
-  T* accum = sh + round_up(static_cast<size_t>(n_sh), 32);
-
+  __shared__ int n_other_s;
+  const int K = EXACT ? KMAX : a.K;
+  const int TK = 3 * (K + 1);
+  const RqsSmem L = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, K, true, kThreads);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
+  T* gxs = reinterpret_cast<T*>(smem + L.outs);
+  T* gst = reinterpret_cast<T*>(smem + L.gst);
+  const T* tab = reinterpret_cast<const T*>(smem + L.tab);
+  T* acc = reinterpret_cast<T*>(smem + L.acc);
+  T* tabg = reinterpret_cast<T*>(smem + L.tabg);
   const int tid = threadIdx.x;
   if (tid == 0) {
     mbar_init(&bars[0], 1);
     mbar_init(&bars[1], 1);
     mbar_init_fence();
   }
-  for (int i = tid; i < n_sh; i += blockDim.x) { sh[i] = a.shared[i]; accum[i] = T(0); }
-  __syncthreads();
+  const int G = a.Ts > 0 ? kThreads / a.Ts : 0;          // thread groups of pass B2 (one feature per thread)
+  for (int i = tid; i < G * a.Ts * TK; i += kThreads) acc[i] = T(0);
+  const RqsMeta<T> M = rqs_setup<T, KMAX>(a, K, smem, L, &n_other_s);   // ends with __syncthreads()
+  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other, Ts = a.Ts;
 
+  uint32_t par0 = 0u, par1 = 0u;
   int64_t tile = blockIdx.x;
-  if (tile < a.num_tiles) stage_issue(a, tile, stage0, &bars[0]);
+  if (tile < a.num_tiles)
+    stage_issue<T, true>(a, tile, reinterpret_cast<T*>(smem + L.pst), reinterpret_cast<T*>(smem + L.xst),
+                         reinterpret_cast<T*>(smem + L.gyst), &bars[0]);
   for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
     const int s = it & 1;
-    T* cur = s ? stage1 : stage0;
+    T* cur = reinterpret_cast<T*>(smem + L.pst + s * L.pst_stride);
+    T* xs = reinterpret_cast<T*>(smem + L.xst + s * L.xst_stride);
+    T* gys = reinterpret_cast<T*>(smem + L.gyst + s * L.xst_stride);
     const int64_t next = tile + gridDim.x;
-    if (next < a.num_tiles) stage_issue(a, next, s ? stage0 : stage1, &bars[s ^ 1]);
+    if (next < a.num_tiles)
+      stage_issue<T, true>(a, next, reinterpret_cast<T*>(smem + L.pst + (s ^ 1) * L.pst_stride),
+                           reinterpret_cast<T*>(smem + L.xst + (s ^ 1) * L.xst_stride),
+                           reinterpret_cast<T*>(smem + L.gyst + (s ^ 1) * L.xst_stride), &bars[s ^ 1]);
     const int64_t row0 = tile * a.R;
     const int rows = static_cast<int>(imin64(a.R, a.B - row0));
-    stage_wait(a, tile, cur, &bars[s], (it >> 1) & 1);
+    if (stage_wait<T, true>(a, tile, cur, xs, gys, &bars[s], s ? par1 : par0)) { if (s) par1 ^= 1u; else par0 ^= 1u; }
     __syncthreads();
 
-    const int n_el = rows * a.D;
-    for (int e = tid; e < n_el; e += blockDim.x) {
-      const int r = e / a.D;
-      const int c = e - r * a.D;
-      const int cm = __ldg(a.col_map + c);
-      const int kind = cm >> 16, idx = cm & 0xffff;
-      const T g_out = a.gy[(row0 + r) * a.ldgy + c];
-      T gv = g_out;
-      if (kind != VCNF_COL_PASS) {
-        const T v = a.x[(row0 + r) * a.ldx + c];
-        const T g_lad = a.gld[row0 + r];
-        const T* prm;
-        T* gprm;
-        T scale, bound;
-        RqsElemCfg cfg{a.K, 0, a.inverse, a.outside_zero};
-        if (kind == VCNF_COL_COND) {
-          const size_t off = (static_cast<size_t>(r) * a.Tc + idx) * a.Pc;
-          prm = cur + off;
-          gprm = gstage + off;
-          scale = a.wh_scale;
-          cfg.mode = __ldg(a.cmodes + idx);
-          bound = __ldg(a.cbounds + idx);
-        } else {
-          prm = sh + static_cast<size_t>(idx) * a.Ps;
-          gprm = sstage + (static_cast<size_t>(r) * a.Ts + idx) * a.Ps;
-          scale = T(1);
-          cfg.mode = __ldg(a.smodes + idx);
-          bound = __ldg(a.sbounds + idx);
-        }
-        rqs_element_bwd<T, KMAX>(prm, v, bound, scale, cfg, g_out, g_lad, &gv, gprm);
-      }
-      a.gx[(row0 + r) * a.ldgx + c] = gv;
+    // pass A: conditional elements
+    const int nA = rows * Tc;
+    for (int e = tid; e < nA; e += kThreads) {
+      const int r = e / Tc;
+      const int j = e - r * Tc;
+      const int c = M.cond_col[j];
+      RqsElemCfg cfg{K, M.cmode[j], a.inverse, a.outside_zero};
+      T gv;
+      rqs_element_bwd<T, KMAX>(cur + static_cast<size_t>(e) * Pc, xs[r * D + c], M.cbound[j], a.wh_scale, cfg,
+                               gys[r * D + c], a.gld[row0 + r], &gv, gst + static_cast<size_t>(e) * Pc);
+      gxs[r * D + c] = gv;
     }
-    const bool bulk_store = a.Tc > 0 && a.bulk_out && rows == a.R;
+    // pass B1: pass-through columns;  pass B2: batch-shared columns, thread <-> feature fixed so that
+    // the thread-private accumulator table needs no atomics
+    if (Ts == 0) {
+      const int nB = rows * No;
+      for (int e = tid; e < nB; e += kThreads) {
+        const int r = e / No;
+        const int c = M.other_col[e - r * No];
+        gxs[r * D + c] = gys[r * D + c];
+      }
+    } else {
+      for (int j = 0; j < No; ++j) {
+        if ((M.other_map[j] >> 16) == VCNF_COL_SHARED) continue;
+        const int c = M.other_col[j];
+        for (int r = tid; r < rows; r += kThreads) gxs[r * D + c] = gys[r * D + c];
+      }
+      if (tid < G * Ts) {
+        const int g = tid / Ts;
+        const int jo = tid - g * Ts;                       // this thread's batch-shared feature
+        const int c = M.shared_col[jo];
+        if (c >= 0) {
+          RqsElemCfg cfg{K, M.smode[jo], a.inverse, a.outside_zero};
+          for (int r = g; r < rows; r += G) {
+            T gv;
+            rqs_table_element_bwd<T, KMAX>(tab + jo * TK, xs[r * D + c], M.sbound[jo], cfg, gys[r * D + c],
+                                           a.gld[row0 + r], &gv, acc + static_cast<size_t>(tid) * TK);
+            gxs[r * D + c] = gv;
+          }
+        }
+      }
+    }
+    const int64_t np = static_cast<int64_t>(rows) * Tc * Pc;
+    const bool bulk_store = Tc > 0 && span_bulk<T>(a.bulk_gp, np);
     if (bulk_store) fence_async_smem();
     __syncthreads();
-    if (a.Tc > 0) {
-      const int n = a.Tc * a.Pc;
+
+    // pass C: coalesced gx rows, parameter-gradient tile
+    const int nY = rows * D;
+    if (a.ldgx == D) {
+      T* dst = a.gx + row0 * D;
+      for (int e = tid; e < nY; e += kThreads) dst[e] = gxs[e];
+    } else {
+      for (int e = tid; e < nY; e += kThreads) {
+        const int r = e / D;
+        a.gx[(row0 + r) * a.ldgx + (e - r * D)] = gxs[e];
+      }
+    }
+    if (Tc > 0) {
       if (bulk_store) {
         if (tid == 0) {
-          bulk_s2g(a.gcond + row0 * a.ld_gcond, gstage, static_cast<uint32_t>(static_cast<size_t>(a.R) * n * sizeof(T)));
+          bulk_s2g(a.gcond + row0 * a.ld_gcond, gst, static_cast<uint32_t>(np * sizeof(T)));
           bulk_commit();
+          bulk_wait_read0();                 // gst is rewritten by the next tile's pass A
         }
       } else {
-        for (int e = tid; e < rows * n; e += blockDim.x) {
-          const int r = e / n;
-          a.gcond[(row0 + r) * a.ld_gcond + (e - r * n)] = gstage[e];
+        const int n = Tc * Pc;
+        for (int64_t e = tid; e < np; e += kThreads) {
+          const int64_t r = e / n;
+          a.gcond[(row0 + r) * a.ld_gcond + (e - r * n)] = gst[e];
         }
       }
     }
-    for (int j = tid; j < n_sh; j += blockDim.x) {
-      T acc = accum[j];
-      for (int r = 0; r < rows; ++r) acc += sstage[static_cast<size_t>(r) * n_sh + j];
-      accum[j] = acc;
-    }
-    if (bulk_store && tid == 0) bulk_wait_read0();
-    __syncthreads();
+    // (the __syncthreads() after the next stage_wait orders these reads before the next tile's writes)
   }
-  for (int j = tid; j < n_sh; j += blockDim.x) a.partial[static_cast<size_t>(blockIdx.x) * n_sh + j] = accum[j];
+  if (Ts > 0) {
+    __syncthreads();
+    for (int q = tid; q < Ts * TK; q += kThreads) {
+      const int j = q / TK, i = q - j * TK;
+      T sum = T(0);
+      for (int g = 0; g < G; ++g) sum += acc[(static_cast<size_t>(g) * Ts + j) * TK + i];
+      tabg[q] = sum;
+    }
+    __syncthreads();
+    for (int j = tid; j < Ts; j += kThreads)
+      rqs_table_to_raw_grad<T, KMAX>(a.shared + static_cast<size_t>(j) * a.Ps, K, M.smode[j], M.sbound[j],
+                                     tabg + j * TK, a.partial + (static_cast<size_t>(blockIdx.x) * Ts + j) * a.Ps);
+  }
 }
 
 template <typename T>
@@ -298,31 +477,48 @@ __global__ void scatter_cols_kernel(const T* src, int64_t lds, T* dst, int64_t l
 
 // ------------------------------------------------------------------------------------------- host
 constexpr size_t kSmemMax = 227 * 1024;
+constexpr int kMaxBwdGrid = 148 * 2;
 
-static int pick_rows(int Tc, int Pc, int Ts, int Ps, size_t elt, bool bwd, int D) {
-  const size_t per_row = static_cast<size_t>(bwd ? (Tc * Pc > Ts * Ps ? Tc * Pc : Ts * Ps) : Tc * Pc) * elt;
-  const size_t budget = bwd ? 20 * 1024 : 40 * 1024;
-  int R = per_row ? static_cast<int>(budget / per_row) : 64;
-  if (R > 64) R = 64;
-  R = R / 4 * 4;
-  if (R < 4) R = 4;
-  (void)D;
-  return R;
+// Rows per tile: a multiple of 4 (keeps every tile start 16 B aligned for the bulk copies) whose
+// parameter block fits the per-stage budget and whose rows*Tc fills whole passes of kThreads best.
+static int pick_rows(int Tc, int Pc, int D, size_t elt) {
+  const size_t per_row = static_cast<size_t>(Tc > 0 ? Tc * Pc : D) * elt;
+  const size_t budget = 20 * 1024;
+  int rmax = static_cast<int>(budget / per_row) / 4 * 4;
+  if (rmax > 64) rmax = 64;
+  if (rmax < 4) rmax = 4;
+  const int width = Tc > 0 ? Tc : D;
+  int best = 4;
+  double best_u = -1.0;
+  for (int R = 4; R <= rmax; R += 4) {
+    const int n = R * width;
+    const double u = static_cast<double>(n) / (static_cast<double>((n + kThreads - 1) / kThreads) * kThreads);
+    if (u >= best_u - 1e-9) { best_u = u > best_u ? u : best_u; best = R; }
+  }
+  return best;
 }
 
-template <typename T, int KMAX>
+template <typename T>
+static void set_bulk_flags(RqsLayerArgs<T>& a, bool bwd) {
+  auto al16 = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  const size_t prow = static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T);
+  const size_t xrow = static_cast<size_t>(a.R) * a.D * sizeof(T);
+  a.bulk_p = a.Tc > 0 && a.ld_cond == static_cast<int64_t>(a.Tc) * a.Pc && prow % 16 == 0 && al16(a.cond);
+  a.bulk_x = a.ldx == a.D && xrow % 16 == 0 && al16(a.x);
+  a.bulk_gy = bwd && a.ldgy == a.D && xrow % 16 == 0 && al16(a.gy);
+  a.bulk_gp = bwd && a.Tc > 0 && a.ld_gcond == static_cast<int64_t>(a.Tc) * a.Pc && prow % 16 == 0 && al16(a.gcond);
+}
+
+template <typename T, int KMAX, bool EXACT>
 static int launch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
   const int sms = sm_count();
   if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
-  a.R = pick_rows(a.Tc, a.Pc, a.Ts, a.Ps, sizeof(T), false, a.D);
+  a.R = pick_rows(a.Tc, a.Pc, a.D, sizeof(T));
   a.num_tiles = (a.B + a.R - 1) / a.R;
-  const size_t tile_bytes = static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T);
-  a.bulk_in = a.Tc > 0 && a.ld_cond == static_cast<int64_t>(a.Tc) * a.Pc && tile_bytes % 16 == 0 &&
-              reinterpret_cast<uintptr_t>(a.cond) % 16 == 0;
-  const size_t smem = 128 + 2 * round_up(tile_bytes, 128) +
-                      (round_up(static_cast<size_t>(a.Ts) * a.Ps, 32) + static_cast<size_t>(a.R) * a.D) * sizeof(T);
+  set_bulk_flags(a, false);
+  const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, false, kThreads).total;
   if (smem > kSmemMax) return VCNF_E_UNSUPPORTED;
-  auto kern = rqs_layer_fwd_kernel<T, KMAX>;
+  auto kern = rqs_layer_fwd_kernel<T, KMAX, EXACT>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   int per_sm = static_cast<int>(kSmemMax / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
@@ -331,24 +527,17 @@ static int launch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
   return launch_status();
 }
 
-constexpr int kMaxBwdGrid = 148 * 2;
-
-template <typename T, int KMAX>
+template <typename T, int KMAX, bool EXACT>
 static int launch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
   const int sms = sm_count();
   if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
-  a.R = pick_rows(a.Tc, a.Pc, a.Ts, a.Ps, sizeof(T), true, a.D);
+  if (a.Ts > kThreads) return VCNF_E_UNSUPPORTED;
+  a.R = pick_rows(a.Tc, a.Pc, a.D, sizeof(T));
   a.num_tiles = (a.B + a.R - 1) / a.R;
-  const size_t tile_bytes = static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T);
-  a.bulk_in = a.Tc > 0 && a.ld_cond == static_cast<int64_t>(a.Tc) * a.Pc && tile_bytes % 16 == 0 &&
-              reinterpret_cast<uintptr_t>(a.cond) % 16 == 0;
-  a.bulk_out = a.Tc > 0 && a.ld_gcond == static_cast<int64_t>(a.Tc) * a.Pc && tile_bytes % 16 == 0 &&
-               reinterpret_cast<uintptr_t>(a.gcond) % 16 == 0;
-  const size_t smem = 128 + 3 * round_up(tile_bytes, 128) +
-                      round_up(static_cast<size_t>(a.R) * a.Ts * a.Ps * sizeof(T), 128) +
-                      2 * round_up(static_cast<size_t>(a.Ts) * a.Ps, 32) * sizeof(T);
+  set_bulk_flags(a, true);
+  const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, true, kThreads).total;
   if (smem > kSmemMax) return VCNF_E_UNSUPPORTED;
-  auto kern = rqs_layer_bwd_kernel<T, KMAX>;
+  auto kern = rqs_layer_bwd_kernel<T, KMAX, EXACT>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   int per_sm = static_cast<int>(kSmemMax / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);
@@ -365,18 +554,22 @@ static int launch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
   return rc;
 }
 
+// K == 8 (the default of every spline wrapper, neural_spline/wrapper.py:20-31) gets a fully unrolled
+// instantiation; other bin counts run the bounded-loop instantiation of the same code.
 template <typename T>
 static int dispatch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
-  if (a.K <= 8) return launch_fwd<T, 8>(a, st);
-  if (a.K <= 16) return launch_fwd<T, 16>(a, st);
-  if (a.K <= 32) return launch_fwd<T, 32>(a, st);
+  if (a.K == 8) return launch_fwd<T, 8, true>(a, st);
+  if (a.K < 8) return launch_fwd<T, 8, false>(a, st);
+  if (a.K <= 16) return launch_fwd<T, 16, false>(a, st);
+  if (a.K <= 32) return launch_fwd<T, 32, false>(a, st);
   return VCNF_E_UNSUPPORTED;
 }
 template <typename T>
 static int dispatch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
-  if (a.K <= 8) return launch_bwd<T, 8>(a, g_shared, st);
-  if (a.K <= 16) return launch_bwd<T, 16>(a, g_shared, st);
-  if (a.K <= 32) return launch_bwd<T, 32>(a, g_shared, st);
+  if (a.K == 8) return launch_bwd<T, 8, true>(a, g_shared, st);
+  if (a.K < 8) return launch_bwd<T, 8, false>(a, g_shared, st);
+  if (a.K <= 16) return launch_bwd<T, 16, false>(a, g_shared, st);
+  if (a.K <= 32) return launch_bwd<T, 32, false>(a, g_shared, st);
   return VCNF_E_UNSUPPORTED;
 }
 

@@ -294,6 +294,31 @@ VCNF_HD void rqs_axis_adjoint(const T* p, int K, T bound, T scale, int i, T g_lo
   }
 }
 
+// Adjoint of one located element wrt its input and the six bin quantities (either direction).
+// gout = dLoss/d out, glad = dLoss/d lad.
+template <typename T>
+VCNF_HD void rqs_bin_adjoint(T v, const RqsBin<T>& b, int inverse, T gout, T glad, T* gv, RqsBinGrad<T>* g) {
+  if (!inverse) {
+    rq_forward_adjoint(v, b, gout, glad, gv, g);
+    return;
+  }
+  // v = f(x; phi) solved for x; lad_inv = -lad_fwd(x, phi).  Implicit differentiation:
+  //   pass 1: adjoint of (-glad * lad_fwd) wrt x and phi
+  //   pass 2: dx/dv = 1/f', dx/dphi = -(df/dphi)/f'  weighted by the total adjoint of x
+  T x, li; int ok;
+  rq_inverse(v, b, &x, &li, &ok);
+  const T fprime = vexp(-li);                        // f'(x) = exp(lad_fwd) = exp(-lad_inv)
+  T gx1; RqsBinGrad<T> g1;
+  rq_forward_adjoint(x, b, T(0), -glad, &gx1, &g1);
+  const T xb = gout + gx1;
+  const T lam = -xb / fprime;
+  T gx2; RqsBinGrad<T> g2;
+  rq_forward_adjoint(x, b, lam, T(0), &gx2, &g2);
+  *gv = xb / fprime;
+  g->x0 = g1.x0 + g2.x0; g->w = g1.w + g2.w; g->y0 = g1.y0 + g2.y0;
+  g->h = g1.h + g2.h; g->d0 = g1.d0 + g2.d0; g->d1 = g1.d1 + g2.d1;
+}
+
 // Backward of rqs_element.  gout = dLoss/d out, glad = dLoss/d lad.  Writes gv (dLoss/d v) and
 // the full parameter-vector gradient gprm[0 .. 2K+ND) (zeros where nothing flows).
 template <typename T, int KMAX>
@@ -309,33 +334,129 @@ VCNF_HD void rqs_element_bwd(const T* prm, T v, T bound, T wh_scale, const RqsEl
     return;
   }
   RqsBinGrad<T> g;
-  if (!c.inverse) {
-    T gx;
-    rq_forward_adjoint(v, b, gout, glad, &gx, &g);
-    *gv = gx;
-  } else {
-    // v = f(x; phi) solved for x; lad_inv = -lad_fwd(x, phi).  Implicit differentiation:
-    //   pass 1: adjoint of (-glad * lad_fwd) wrt x and phi
-    //   pass 2: dx/dv = 1/f', dx/dphi = -(df/dphi)/f'  weighted by the total adjoint of x
-    T x, li; int ok;
-    rq_inverse(v, b, &x, &li, &ok);
-    const T fprime = vexp(-li);                        // f'(x) = exp(lad_fwd) = exp(-lad_inv)
-    T gx1; RqsBinGrad<T> g1;
-    rq_forward_adjoint(x, b, T(0), -glad, &gx1, &g1);
-    const T xb = gout + gx1;
-    const T lam = -xb / fprime;
-    T gx2; RqsBinGrad<T> g2;
-    rq_forward_adjoint(x, b, lam, T(0), &gx2, &g2);
-    *gv = xb / fprime;
-    g.x0 = g1.x0 + g2.x0; g.w = g1.w + g2.w; g.y0 = g1.y0 + g2.y0;
-    g.h = g1.h + g2.h; g.d0 = g1.d0 + g2.d0; g.d1 = g1.d1 + g2.d1;
-  }
+  rqs_bin_adjoint(v, b, c.inverse, gout, glad, gv, &g);
   // knots: x0 = X[i], w = X[i+1]-X[i]  ->  adj X[i] = g.x0 - g.w, adj X[i+1] = g.w  (same for Y)
   rqs_axis_adjoint<T, KMAX>(pw, K, bound, wh_scale, b.idx, g.x0 - g.w, g.w, gprm);
   rqs_axis_adjoint<T, KMAX>(ph, K, bound, wh_scale, b.idx, g.y0 - g.h, g.h, gprm + K);
   for (int j = 0; j < nd; ++j) gprm[2 * K + j] = T(0);
   if (b.s0 >= 0) gprm[2 * K + b.s0] += g.d0 * softplus20_grad(b.r0);
   if (b.s1 >= 0) gprm[2 * K + b.s1] += g.d1 * softplus20_grad(b.r1);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Knot tables for BATCH-SHARED parameters (PiecewiseRationalQuadraticCDF,
+// neural_spline/coupling.py:165-246): the knots of a feature are the same for every sample, so
+// they are built once per CTA instead of once per element.  Table layout, stride KT = K+1:
+//   tab[0 .. K]       X knots        tab[KT .. KT+K]   Y knots        tab[2KT .. 2KT+K]  derivatives
+// The arithmetic is the very same rqs_axis / softplus20 sequence as the per-element path, so both
+// give identical values for identical parameters.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int KMAX>
+VCNF_HD void rqs_build_table(const T* prm, int K, int mode, T bound, T* tab) {
+  T p[KMAX], kn[KMAX + 1];
+  const int KT = K + 1;
+  rqs_axis<T, KMAX>(prm, T(1), K, bound, p, kn);
+  for (int k = 0; k <= K; ++k) tab[k] = kn[k];
+  rqs_axis<T, KMAX>(prm + K, T(1), K, bound, p, kn);
+  for (int k = 0; k <= K; ++k) tab[KT + k] = kn[k];
+  const T edge = RqsConst<T>::edge();
+  for (int k = 0; k <= K; ++k) {
+    int s;
+    const T r = rqs_raw_deriv(prm + 2 * K, k, K, mode, edge, &s);
+    tab[2 * KT + k] = RqsConst<T>::min_deriv() + softplus20(r);
+  }
+}
+
+template <typename T, int KMAX>
+VCNF_HD bool rqs_table_locate(const T* tab, int K, T v, T bound, int inverse, RqsBin<T>* b) {
+  if (!(v >= -bound && v <= bound)) return false;
+  const int KT = K + 1;
+  const T* X = tab;
+  const T* Y = tab + KT;
+  const T* Dv = tab + 2 * KT;
+  const int i = rqs_search<T, KMAX>(inverse ? Y : X, K, v);
+  b->idx = i;
+  b->x0 = X[i];
+  b->w = X[i + 1] - b->x0;
+  b->y0 = Y[i];
+  b->h = Y[i + 1] - b->y0;
+  b->d0 = Dv[i];
+  b->d1 = Dv[i + 1];
+  b->r0 = b->r1 = T(0);
+  b->s0 = b->s1 = -1;
+  return true;
+}
+
+template <typename T, int KMAX>
+VCNF_HD void rqs_table_element(const T* tab, T v, T bound, const RqsElemCfg& c, T* out, T* lad, int* bin,
+                               int* flag) {
+  RqsBin<T> b;
+  if (!rqs_table_locate<T, KMAX>(tab, c.K, v, bound, c.inverse, &b)) {
+    *out = c.outside_zero ? T(0) : v;
+    *lad = T(0);
+    *bin = -1;
+    return;
+  }
+  *bin = b.idx;
+  if (c.inverse) {
+    int ok;
+    rq_inverse(v, b, out, lad, &ok);
+    if (!ok) *flag |= 1;
+  } else {
+    rq_forward(v, b, out, lad);
+  }
+}
+
+// Backward of rqs_table_element: accumulates the adjoints of the touched table entries into gtab
+// (same layout as tab; the caller owns it exclusively, plain +=).
+template <typename T, int KMAX>
+VCNF_HD void rqs_table_element_bwd(const T* tab, T v, T bound, const RqsElemCfg& c, T gout, T glad, T* gv,
+                                   T* gtab) {
+  RqsBin<T> b;
+  if (!rqs_table_locate<T, KMAX>(tab, c.K, v, bound, c.inverse, &b)) {
+    *gv = c.outside_zero ? T(0) : gout;
+    return;
+  }
+  RqsBinGrad<T> g;
+  rqs_bin_adjoint(v, b, c.inverse, gout, glad, gv, &g);
+  const int KT = c.K + 1, i = b.idx;
+  gtab[i] += g.x0 - g.w;
+  gtab[i + 1] += g.w;
+  gtab[KT + i] += g.y0 - g.h;
+  gtab[KT + i + 1] += g.h;
+  gtab[2 * KT + i] += g.d0;
+  gtab[2 * KT + i + 1] += g.d1;
+}
+
+// Chain rule from table adjoints back to the raw parameter vector of one feature
+// (softmax / running-sum / softplus; the pinned end knots carry no gradient, B.2 item 1).
+template <typename T, int KMAX>
+VCNF_HD void rqs_table_to_raw_grad(const T* prm, int K, int mode, T bound, const T* gtab, T* gprm) {
+  const int KT = K + 1;
+  const int nd = rqs_num_derivs(K, mode);
+  const T span = T(1) - RqsConst<T>::min_size() * T(K);
+  const T kk = (bound - (-bound)) * span;
+  T p[KMAX], kn[KMAX + 1];
+  for (int axis = 0; axis < 2; ++axis) {
+    rqs_axis<T, KMAX>(prm + axis * K, T(1), K, bound, p, kn);
+    const T* gk = gtab + axis * KT;
+    // knot_k (1 <= k <= K-1) depends on p_j for j < k
+    T suffix = T(0), dot = T(0);
+    T a[KMAX];
+    for (int j = K - 1; j >= 0; --j) {
+      if (j + 1 <= K - 1) suffix += gk[j + 1];
+      a[j] = suffix * kk;
+    }
+    for (int j = 0; j < K; ++j) dot += p[j] * a[j];
+    for (int j = 0; j < K; ++j) gprm[axis * K + j] = p[j] * (a[j] - dot);
+  }
+  for (int j = 0; j < nd; ++j) gprm[2 * K + j] = T(0);
+  const T edge = RqsConst<T>::edge();
+  for (int k = 0; k <= K; ++k) {
+    int s;
+    const T r = rqs_raw_deriv(prm + 2 * K, k, K, mode, edge, &s);
+    if (s >= 0) gprm[2 * K + s] += gtab[2 * KT + k] * softplus20_grad(r);
+  }
 }
 
 }  // namespace vcnf
