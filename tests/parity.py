@@ -60,3 +60,30 @@ def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.999):
     assert share >= frac, "%s: only %.4f%% of elements inside rtol=%g atol=%g (worst %.3g x tol)" % (
         what, 100 * share, rtol, atol, float((err / (atol + rtol * r32.abs()[ok])).max()))
     assert e64 <= 2 * ref_e + 10 * atol, "%s: max error vs fp64 reference %.3g > 2 x %.3g + 10 atol" % (what, e64, ref_e)
+
+
+def assert_grads_close_tail(got, ref32, ref64, rtol, what=""):
+    """Gradients of an fp32 spline layer: an element passes when it is inside the stated tolerance
+    of the fp32 reference, OR no further from the fp64 reference than twice the fp32 reference's own
+    error there (+ the same tolerance).  The second clause exists because the reference's fp32
+    gradient is itself wrong (even in sign) on ill-conditioned samples -- measured on the golden
+    case crqs_linear/forward row 45: reference fp32 -227.5, reference fp64 +135.3."""
+    for name, r32 in ref32.items():
+        g = got.get(name)
+        if r32 is None:
+            assert g is None or float(g.abs().max()) == 0.0, (what, name)
+            continue
+        assert g is not None, (what, name, "missing gradient")
+        g_, r32_, r64_ = g.detach().double().cpu(), r32.detach().double().cpu(), ref64[name].detach().double().cpu()
+        scale = float(r32_.abs().max()) if r32_.numel() else 0.0
+        tol = rtol * max(scale, 1e-30) + rtol * r32_.abs()
+        ok = ((g_ - r32_).abs() <= tol) | ((g_ - r64_).abs() <= 2 * (r32_ - r64_).abs() + tol)
+        # population clause (rounding errors are independent per element, amplified by 1/f' on the
+        # ill-conditioned ones): >= 99.9 % inside, and the worst error against fp64 no larger than
+        # twice the fp32 reference's own worst error against fp64
+        share = float(ok.double().mean()) if ok.numel() else 1.0
+        e64 = float((g_ - r64_).abs().max()) if ok.numel() else 0.0
+        ref_e = float((r32_ - r64_).abs().max()) if ok.numel() else 0.0
+        assert share >= 0.999 and e64 <= 2 * ref_e + float(tol.max()), (
+            "%s grad[%s]: %d of %d elements outside both clauses; worst vs fp64 %.3g (reference fp32: %.3g)" % (
+                what, name, int((~ok).sum()), ok.numel(), e64, ref_e))

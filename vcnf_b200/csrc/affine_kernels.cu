@@ -303,6 +303,7 @@ extern "C" {
 int vcnf_affine_coupling_fwd(const void* z, const void* param, void* out, void* logdet, int64_t B, int C, int S,
                              int c2_start, int C2, int scale_map, int inverse, int swap_ts, int dtype,
                              void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!z || !param || !out || !logdet || B < 0 || C <= 0 || S <= 0 || C2 < 0 || c2_start < 0 ||
       c2_start + C2 > C || scale_map < 0 || scale_map > 4 || VCNF_BAD_DTYPE(dtype))
     return VCNF_E_BADARG;
@@ -322,6 +323,7 @@ int vcnf_affine_coupling_fwd(const void* z, const void* param, void* out, void* 
 int vcnf_affine_coupling_bwd(const void* z, const void* param, const void* gout, const void* glogdet, void* gz,
                              void* gparam, int64_t B, int C, int S, int c2_start, int C2, int scale_map,
                              int inverse, int swap_ts, int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!z || !param || !gout || !glogdet || !gz || !gparam || B < 0 || C <= 0 || S <= 0 || C2 < 0 ||
       c2_start < 0 || c2_start + C2 > C || scale_map < 0 || scale_map > 4 || VCNF_BAD_DTYPE(dtype))
     return VCNF_E_BADARG;
@@ -341,6 +343,7 @@ int vcnf_affine_coupling_bwd(const void* z, const void* param, const void* gout,
 
 int vcnf_masked_affine_fwd(const void* z, const void* mask, const void* s, const void* t, void* out, void* logdet,
                            int64_t B, int n, int inverse, int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!z || !mask || !out || !logdet || B < 0 || n <= 0 || VCNF_BAD_DTYPE(dtype)) return VCNF_E_BADARG;
   if (B == 0) return 0;
 #define GO(T)                                                                                         \
@@ -357,6 +360,7 @@ int vcnf_masked_affine_fwd(const void* z, const void* mask, const void* s, const
 int vcnf_masked_affine_bwd(const void* z, const void* mask, const void* s, const void* t, const void* gout,
                            const void* glogdet, void* gz, void* gs, void* gt, int64_t B, int n, int inverse,
                            int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!z || !mask || !gout || !glogdet || !gz || B < 0 || n <= 0 || VCNF_BAD_DTYPE(dtype)) return VCNF_E_BADARG;
   if (B == 0) return 0;
 #define GO(T)                                                                                         \
@@ -373,6 +377,7 @@ int vcnf_masked_affine_bwd(const void* z, const void* mask, const void* s, const
 
 int vcnf_const_affine_fwd(const void* z, const void* s, const void* t, void* out, int64_t B, int Pn, int S,
                           int inverse, int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!z || !s || !t || !out || B < 0 || Pn <= 0 || S <= 0 || VCNF_BAD_DTYPE(dtype)) return VCNF_E_BADARG;
   const int64_t total = B * Pn * S;
   if (total == 0) return 0;
@@ -393,6 +398,7 @@ int64_t vcnf_const_affine_bwd_workspace(int Pn, int dtype) {
 int vcnf_const_affine_bwd(const void* z, const void* s, const void* t, const void* gout, void* gz, void* gs,
                           void* gt, void* workspace, int64_t B, int Pn, int S, int inverse, int dtype,
                           void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!z || !s || !t || !gout || !gz || !gs || !gt || !workspace || B < 0 || Pn <= 0 || S <= 0 ||
       (S == 1 && Pn > kAffThreads) || (S > 1 && Pn > 65535) || VCNF_BAD_DTYPE(dtype))
     return VCNF_E_BADARG;
@@ -422,6 +428,7 @@ int vcnf_const_affine_bwd(const void* z, const void* s, const void* t, const voi
 
 int vcnf_permute_channels(const void* src, void* dst, int64_t B, int C, int S, const int32_t* perm, int dtype,
                           void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!src || !dst || !perm || B < 0 || C <= 0 || S <= 0 || src == dst || VCNF_BAD_DTYPE(dtype)) return VCNF_E_BADARG;
   const int64_t total = B * C * S;
   if (total == 0) return 0;
@@ -435,6 +442,7 @@ int vcnf_permute_channels(const void* src, void* dst, int64_t B, int C, int S, c
 
 int vcnf_squeeze(const void* src, void* dst, int64_t B, int c_small, int h_small, int w_small, int inverse,
                  int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!src || !dst || B < 0 || c_small <= 0 || h_small <= 0 || w_small <= 0 || src == dst || VCNF_BAD_DTYPE(dtype))
     return VCNF_E_BADARG;
   const int64_t total = B * 4 * c_small * h_small * w_small;

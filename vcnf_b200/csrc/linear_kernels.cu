@@ -120,6 +120,7 @@ using namespace vcnf;
 extern "C" int vcnf_small_linear(const void* x, void* y, const void* W, const void* bias, const int32_t* in_idx,
                                  const int32_t* out_idx, int64_t rows, int D, int S, int sub_bias_first,
                                  int dtype, void* stream) {
+  if (rows == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!x || !y || !W || rows < 0 || D <= 0 || S <= 0 || x == y || (dtype != VCNF_F32 && dtype != VCNF_F64))
     return VCNF_E_BADARG;
   if (rows == 0) return 0;

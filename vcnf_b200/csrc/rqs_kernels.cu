@@ -483,7 +483,7 @@ constexpr int kMaxBwdGrid = 148 * 2;
 // parameter block fits the per-stage budget and whose rows*Tc fills whole passes of kThreads best.
 static int pick_rows(int Tc, int Pc, int D, size_t elt) {
   const size_t per_row = static_cast<size_t>(Tc > 0 ? Tc * Pc : D) * elt;
-  const size_t budget = 20 * 1024;
+  const size_t budget = 24 * 1024;
   int rmax = static_cast<int>(budget / per_row) / 4 * 4;
   if (rmax > 64) rmax = 64;
   if (rmax < 4) rmax = 4;
@@ -612,6 +612,7 @@ int vcnf_rqs_layer_fwd(const void* x, int64_t ldx, void* y, int64_t ldy, void* l
                        double wh_scale, const void* shared_params, int Ts, int Ps,
                        const uint8_t* shared_modes, const void* shared_bounds, int inverse, int outside_zero,
                        int8_t* bin_out, int32_t* err_flag, int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (bad_layer_args(x, B, D, K, col_map, cond_params, Tc, Pc, cond_modes, cond_bounds, shared_params, Ts, Ps,
                      shared_modes, shared_bounds, dtype) || !y || !logdet || x == y)
     return VCNF_E_BADARG;
@@ -641,15 +642,15 @@ int vcnf_rqs_layer_bwd(const void* x, int64_t ldx, const void* gy, int64_t ldgy,
                        double wh_scale, void* g_cond, int64_t ld_gcond, const void* shared_params, int Ts,
                        int Ps, const uint8_t* shared_modes, const void* shared_bounds, void* g_shared,
                        void* workspace, int inverse, int outside_zero, int dtype, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (B == 0) {   /* empty batch: batch pointers may be NULL; shared-parameter gradients are zero */
+    if (Ts > 0 && g_shared) cudaMemsetAsync(g_shared, 0, static_cast<size_t>(Ts) * Ps * (dtype == VCNF_F64 ? 8 : 4), st);
+    return launch_status();
+  }
   if (bad_layer_args(x, B, D, K, col_map, cond_params, Tc, Pc, cond_modes, cond_bounds, shared_params, Ts, Ps,
                      shared_modes, shared_bounds, dtype) || !gy || !glogdet || !gx || (Tc > 0 && !g_cond) ||
       (Ts > 0 && (!g_shared || !workspace)))
     return VCNF_E_BADARG;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (B == 0) {
-    if (Ts > 0) cudaMemsetAsync(g_shared, 0, static_cast<size_t>(Ts) * Ps * (dtype == VCNF_F64 ? 8 : 4), st);
-    return launch_status();
-  }
 #define VCNF_BWD(T)                                                                                      \
   {                                                                                                      \
     RqsLayerArgs<T> a;                                                                                   \
@@ -666,6 +667,7 @@ int vcnf_rqs_layer_bwd(const void* x, int64_t ldx, const void* gy, int64_t ldgy,
 
 int vcnf_gather_cols(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t B, int n, const int32_t* cols,
                      int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!src || !dst || !cols || B < 0 || n <= 0 || n > 1024 || (dtype != VCNF_F32 && dtype != VCNF_F64))
     return VCNF_E_BADARG;
   if (B == 0) return 0;
@@ -685,6 +687,7 @@ int vcnf_gather_cols(const void* src, int64_t lds, void* dst, int64_t ldd, int64
 
 int vcnf_scatter_cols(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t B, int n, int D_dst,
                       const int32_t* cols, int accumulate, int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
   if (!src || !dst || !cols || B < 0 || n <= 0 || D_dst < n || D_dst > 1024 ||
       (dtype != VCNF_F32 && dtype != VCNF_F64))
     return VCNF_E_BADARG;

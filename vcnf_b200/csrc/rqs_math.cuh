@@ -54,6 +54,16 @@ VCNF_HD float vlog(float x) { return logf(x); }
 VCNF_HD double vlog(double x) { return log(x); }
 VCNF_HD float vlog1p(float x) { return log1pf(x); }
 VCNF_HD double vlog1p(double x) { return log1p(x); }
+// Division inside the closed forms (NOT on the knot / bin-search path, which stays IEEE so that bin
+// indices keep agreeing with the reference): on the device in fp32 this is the 2-ulp fast divide.
+VCNF_HD float vdiv(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return __fdividef(a, b);
+#else
+  return a / b;
+#endif
+}
+VCNF_HD double vdiv(double a, double b) { return a / b; }
 VCNF_HD float vsqrt(float x) { return sqrtf(x); }
 VCNF_HD double vsqrt(double x) { return sqrt(x); }
 
@@ -131,12 +141,12 @@ VCNF_HD T rqs_pick(const T* a, int n, int i) {
 // Forward closed form (splines.py:178-193).
 template <typename T>
 VCNF_HD void rq_forward(T x, const RqsBin<T>& b, T* y, T* lad) {
-  const T s = b.h / b.w;
-  const T th = (x - b.x0) / b.w;
+  const T s = vdiv(b.h, b.w);
+  const T th = vdiv(x - b.x0, b.w);
   const T t1 = th * (T(1) - th);
   const T num = b.h * (s * th * th + b.d0 * t1);
   const T den = s + (b.d0 + b.d1 - T(2) * s) * t1;
-  *y = b.y0 + num / den;
+  *y = b.y0 + vdiv(num, den);
   const T dn = s * s * (b.d1 * th * th + T(2) * s * t1 + b.d0 * (T(1) - th) * (T(1) - th));
   *lad = vlog(dn) - T(2) * vlog(den);
 }
@@ -145,7 +155,7 @@ VCNF_HD void rq_forward(T x, const RqsBin<T>& b, T* y, T* lad) {
 // discriminant is negative (the reference asserts, splines.py:164); the result is then NaN.
 template <typename T>
 VCNF_HD void rq_inverse(T v, const RqsBin<T>& b, T* x, T* lad, int* ok) {
-  const T s = b.h / b.w;
+  const T s = vdiv(b.h, b.w);
   const T dv = v - b.y0;
   const T q = b.d0 + b.d1 - T(2) * s;
   const T qa = dv * q + b.h * (s - b.d0);
@@ -153,7 +163,7 @@ VCNF_HD void rq_inverse(T v, const RqsBin<T>& b, T* x, T* lad, int* ok) {
   const T qc = -s * dv;
   const T disc = qb * qb - T(4) * qa * qc;
   *ok = disc >= T(0) ? 1 : 0;
-  const T root = (T(2) * qc) / (-qb - vsqrt(disc));
+  const T root = vdiv(T(2) * qc, -qb - vsqrt(disc));
   *x = root * b.w + b.x0;
   const T t1 = root * (T(1) - root);
   const T den = s + q * t1;

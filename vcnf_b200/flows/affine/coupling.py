@@ -98,7 +98,8 @@ class MaskedAffineFlow(Flow):
             self.add_module("t", t)
 
     def _run(self, z, inverse):
-        mask = self.b.to(z.dtype) if self.b.dtype != z.dtype else self.b
+        dt = torch.promote_types(self.b.dtype, z.dtype)      # `self.b * z` promotes (coupling.py:203)
+        mask, z = self.b.to(dt), z.to(dt)
         z_masked = mask * z
         scale = self.s(z_masked) if self._has_s else None
         trans = self.t(z_masked) if self._has_t else None

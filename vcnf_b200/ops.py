@@ -23,6 +23,16 @@ def _launch(name, *args, n=1):
     call(name, *args)
 
 
+def _promote(*tensors):
+    """Type promotion of the floating-point operands like the reference's ATen ops do (an fp32 batch
+    fed to an `nfm.double()` model computes in fp64, runadultvdeq.py:172,183)."""
+    dt = None
+    for t in tensors:
+        if t is not None:
+            dt = t.dtype if dt is None else torch.promote_types(dt, t.dtype)
+    return tuple(t if t is None or t.dtype == dt else t.to(dt) for t in tensors)
+
+
 def _zeros_if_none(g, like_shape, ref):
     return torch.zeros(like_shape, dtype=ref.dtype, device=ref.device) if g is None else g.contiguous()
 
@@ -104,6 +114,7 @@ class _RqsLayer(torch.autograd.Function):
 
 def rqs_layer(x, cond, shared, spec, inverse, want_bins=False):
     """Spline layer: returns (y, logdet[, bin_idx])."""
+    x, cond, shared = _promote(x, cond, shared)
     return _RqsLayer.apply(x, cond, shared, spec, inverse, want_bins)
 
 
@@ -162,6 +173,7 @@ class _AffineCoupling(torch.autograd.Function):
 
 
 def affine_coupling(z, param, c2_start, C2, scale_map, inverse, swap_ts=False):
+    z, param = _promote(z, param)
     return _AffineCoupling.apply(z, param, c2_start, C2, scale_map, inverse, swap_ts)
 
 
@@ -197,6 +209,7 @@ class _MaskedAffine(torch.autograd.Function):
 
 
 def masked_affine(z, mask, s, t, inverse):
+    z, mask, s, t = _promote(z, mask, s, t)
     return _MaskedAffine.apply(z, mask, s, t, inverse)
 
 
@@ -229,6 +242,7 @@ class _ConstAffine(torch.autograd.Function):
 
 
 def const_affine(z, s, t, S, inverse):
+    z, s, t = _promote(z, s, t)
     return _ConstAffine.apply(z, s, t, S, inverse)
 
 
@@ -327,4 +341,5 @@ class _SmallLinear(torch.autograd.Function):
 
 
 def small_linear(x, W, bias=None, in_idx=None, out_idx=None, sub_bias_first=False):
+    x, W, bias = _promote(x, W, bias)
     return _SmallLinear.apply(x, W, bias, in_idx, out_idx, sub_bias_first)
