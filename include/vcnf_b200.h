@@ -153,6 +153,19 @@ int vcnf_small_linear(const void* x, void* y, const void* W, const void* bias, c
                       const int32_t* out_idx, int64_t rows, int D, int S, int sub_bias_first, int dtype,
                       void* stream);
 
+/* ---- K6/K7: conditioner dense layer on tcgen05 tensor cores, fp32-faithful (3xTF32) -------------
+ * Replaces F.linear (+ ReLU / residual add / ReLU-backward mask) of the conditioner nets:
+ * normflow/nets/resnet.py:38-58,76-106 (ResidualBlock / ResidualNet), nets/mlp.py:7-58,
+ * nets/made.py:79-80 (after pre-masking the weight), forward and input-gradient direction.
+ *   C[m, n] = [mask[m, n] > 0] * ( sum_k act(A[m, k]) * W[n*sw_n + k*sw_k] + bias[n] ) + residual[m, n]
+ * A [M, K] (lda), C [M, N] (ldc), float32 only; act = ReLU when relu_in != 0 (pre-activation blocks,
+ * resnet.py:49-55); bias / residual / mask may be NULL.  Forward: W = weight [N, K], sw_n = K, sw_k = 1.
+ * Input gradient: A = grad-output [M, out], W = weight [out, in] read as [n = in, k = out]:
+ * sw_n = 1, sw_k = in; mask = the saved pre-activation input.  K <= 128.  C must not alias A. */
+int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int64_t sw_n, int64_t sw_k,
+                       const void* bias, const void* residual, int64_t ldr, const void* mask, int64_t ldm,
+                       void* C, int64_t ldc, int64_t M, int N, int K, int relu_in, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

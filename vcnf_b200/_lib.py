@@ -34,6 +34,7 @@ _SIGNATURES = {
     "vcnf_const_affine_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
     "vcnf_permute_channels": [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _vp],
     "vcnf_squeeze": [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
+    "vcnf_linear_tf32x3": [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp],
     "vcnf_small_linear": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
 }
 _I64_RETURN = {

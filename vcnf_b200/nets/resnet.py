@@ -4,6 +4,8 @@ import torch
 from torch import nn
 from torch.nn import functional as F, init
 
+from .. import ops
+
 
 class ResidualBlock(nn.Module):
     """x + W1 act(W0 act(x)) (pre-activation; resnet.py:38-58)."""
@@ -23,7 +25,18 @@ class ResidualBlock(nn.Module):
             init.uniform_(self.linear_layers[-1].weight, -1e-3, 1e-3)
             init.uniform_(self.linear_layers[-1].bias, -1e-3, 1e-3)
 
+    def _fast(self, inputs, context):
+        """Both dense layers on the tcgen05 kernel with ReLU / bias / residual fused."""
+        is_relu = self.activation is F.relu or self.activation is torch.relu or isinstance(self.activation, nn.ReLU)
+        return (context is None and not self.use_batch_norm and is_relu
+                and (self.dropout.p == 0. or not self.training)
+                and ops.linear_supported(inputs, self.linear_layers[0].weight))
+
     def forward(self, inputs, context=None):
+        if self._fast(inputs, context):
+            l0, l1 = self.linear_layers
+            t = ops.linear(inputs, l0.weight, l0.bias, relu_in=True)
+            return ops.linear(t, l1.weight, l1.bias, residual=inputs, relu_in=True)
         h = inputs
         if self.use_batch_norm:
             h = self.batch_norm_layers[0](h)
@@ -53,7 +66,11 @@ class ResidualNet(nn.Module):
 
     def forward(self, inputs, context=None):
         h = inputs if self.preprocessing is None else self.preprocessing(inputs)
-        h = self.initial_layer(h if context is None else torch.cat((h, context), dim=1))
+        h = h if context is None else torch.cat((h, context), dim=1)
+        fast = ops.linear_supported(h, self.initial_layer.weight) and self.hidden_features <= 128
+        h = ops.linear(h, self.initial_layer.weight, self.initial_layer.bias) if fast else self.initial_layer(h)
         for block in self.blocks:
             h = block(h, context=context)
+        if fast:
+            return ops.linear(h, self.final_layer.weight, self.final_layer.bias)
         return self.final_layer(h)

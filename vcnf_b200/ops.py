@@ -343,3 +343,70 @@ class _SmallLinear(torch.autograd.Function):
 def small_linear(x, W, bias=None, in_idx=None, out_idx=None, sub_bias_first=False):
     x, W, bias = _promote(x, W, bias)
     return _SmallLinear.apply(x, W, bias, in_idx, out_idx, sub_bias_first)
+
+
+# ------------------------------------------------------------------ conditioner dense layers
+def linear_supported(x, weight):
+    """The tcgen05 3xTF32 kernel covers fp32 CUDA tensors with in_features <= 128."""
+    return (x.is_cuda and x.dtype == torch.float32 and weight.dtype == torch.float32 and x.dim() == 2
+            and weight.shape[1] <= 128)
+
+
+class _Linear(torch.autograd.Function):
+    """y = act(x) W^T + b (+ residual), act = ReLU when relu_in (pre-activation residual blocks,
+    nets/resnet.py:49-55).  Forward and input-gradient run `vcnf_linear_tf32x3` (tcgen05, fp32-faithful);
+    the ReLU, the bias, the residual add and the ReLU-backward mask are fused into the kernels."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, relu_in):
+        x, weight = x.contiguous(), weight.contiguous()
+        M, K = x.shape
+        N = weight.shape[0]
+        bias_ = bias.contiguous() if bias is not None else None
+        res_ = residual.contiguous() if residual is not None else None
+        y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+        _launch("vcnf_linear_tf32x3", ptr(x), K, ptr(weight), K, 1, ptr(bias_), ptr(res_), N, None, 0,
+                ptr(y), N, M, N, K, int(relu_in), stream())
+        ctx.relu_in = bool(relu_in)
+        ctx.has_bias, ctx.has_res = bias is not None, residual is not None
+        ctx.save_for_backward(x, weight)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        gy = gy.contiguous()
+        M, K = x.shape
+        N = weight.shape[0]
+        gx = gw = gb = gres = None
+        if ctx.needs_input_grad[0]:
+            gx = torch.empty_like(x)
+            # gx[m, k] = [x > 0] * sum_n gy[m, n] W[n, k]  : W read as [n' = k, k' = n] -> sw_n = 1, sw_k = K
+            if N <= 128:
+                _launch("vcnf_linear_tf32x3", ptr(gy), N, ptr(weight), 1, K, None, None, 0,
+                        ptr(x) if ctx.relu_in else None, K, ptr(gx), K, M, K, N, 0, stream())
+            else:
+                # out_features > 128 (the 3K-1 wide head): reduce over column slices of <= 128
+                first = True
+                for n0 in range(0, N, 128):
+                    n1 = min(N, n0 + 128)
+                    last = n1 == N
+                    _launch("vcnf_linear_tf32x3", ptr(gy) + 4 * n0, N, ptr(weight) + 4 * n0 * K, 1, K, None,
+                            None if first else ptr(gx), K, ptr(x) if (ctx.relu_in and last and first) else None, K,
+                            ptr(gx), K, M, K, n1 - n0, 0, stream())
+                    first = False
+                if ctx.relu_in and N > 128:
+                    gx = gx * (x > 0)
+        if ctx.needs_input_grad[1]:
+            xa = torch.relu(x) if ctx.relu_in else x
+            gw = gy.t() @ xa
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = gy.sum(0)
+        if ctx.has_res and ctx.needs_input_grad[3]:
+            gres = gy
+        return gx, gw, gb, gres, None
+
+
+def linear(x, weight, bias=None, residual=None, relu_in=False):
+    return _Linear.apply(x, weight, bias, residual, relu_in)
