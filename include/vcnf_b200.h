@@ -166,6 +166,15 @@ int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int64_t sw_n, 
                        const void* bias, const void* residual, int64_t ldr, const void* mask, int64_t ldm,
                        void* C, int64_t ldc, int64_t M, int N, int K, int relu_in, void* stream);
 
+/* Weight / bias gradient of the same dense layer (autograd of F.linear, the "nt" sgemm + column-sum):
+ *   gW[o, i] = sum_b gY[b, o] * act(X[b, i])      gb[o] = sum_b gY[b, o]   (gb may be NULL)
+ * gY [B, N] (ldg), X [B, K] (ldx), gW [N, K] contiguous, float32, K <= 128.  Split over the batch
+ * across the SMs, partials summed in a fixed order (deterministic).  `workspace` must hold
+ * vcnf_linear_wgrad_workspace(B, N, K) bytes. */
+int64_t vcnf_linear_wgrad_workspace(int64_t B, int N, int K);
+int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void* X, int64_t ldx, void* gW, void* gb,
+                             void* workspace, int64_t B, int N, int K, int relu_in, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

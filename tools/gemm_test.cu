@@ -71,7 +71,93 @@ static int run(int64_t M, int N, int K, int64_t lda, bool transposed_w, bool rel
   return bad != 0;
 }
 
+static int run_wgrad(int64_t B, int N, int K, bool relu, int reps) {
+  std::vector<float> G(B * N), X(B * K), gW((size_t)N * K, -3.f), gb(N, -3.f);
+  for (auto& v : G) v = frand();
+  for (auto& v : X) v = frand();
+  float *dG, *dX, *dW, *db, *ws;
+  int64_t wsb = vcnf_linear_wgrad_workspace(B, N, K);
+  cudaMalloc(&dG, G.size() * 4); cudaMalloc(&dX, X.size() * 4); cudaMalloc(&dW, gW.size() * 4);
+  cudaMalloc(&db, N * 4); cudaMalloc(&ws, wsb);
+  cudaMemcpy(dG, G.data(), G.size() * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(dX, X.data(), X.size() * 4, cudaMemcpyHostToDevice);
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  int rc = 0; float ms = 0;
+  for (int r = 0; r < reps; ++r) {
+    if (r == reps - 1) cudaEventRecord(e0);
+    rc = vcnf_linear_wgrad_tf32x3(dG, N, dX, K, dW, db, ws, B, N, K, relu, nullptr);
+    if (r == reps - 1) cudaEventRecord(e1);
+  }
+  cudaError_t err = cudaDeviceSynchronize();
+  cudaEventElapsedTime(&ms, e0, e1);
+  printf("WGRAD B=%lld N=%d K=%d relu=%d ws=%lld KB: rc=%d sync=%s %.3f ms", (long long)B, N, K, relu, (long long)wsb / 1024, rc,
+         cudaGetErrorString(err), ms);
+  if (rc || err != cudaSuccess) { printf("\n"); return 1; }
+  cudaMemcpy(gW.data(), dW, gW.size() * 4, cudaMemcpyDeviceToHost);
+  cudaMemcpy(gb.data(), db, N * 4, cudaMemcpyDeviceToHost);
+  double worst = 0; int bad = 0;
+  const int ostep = N > 64 ? 7 : 1, istep = K > 64 ? 5 : 1;
+  for (int o = 0; o < N; o += ostep) {
+    double sb = 0, sbm = 0;
+    for (int64_t b = 0; b < B; ++b) { sb += G[b * N + o]; sbm += fabs(G[b * N + o]); }
+    double eb = fabs(sb - gb[o]) / (sbm + 1e-6);
+    if (eb > worst) worst = eb;
+    if (eb > 2e-6) ++bad;
+    for (int i = 0; i < K; i += istep) {
+      double acc = 0, mag = 0;
+      for (int64_t b = 0; b < B; ++b) {
+        double xv = X[b * K + i]; if (relu && xv < 0) xv = 0;
+        acc += (double)G[b * N + o] * xv; mag += fabs((double)G[b * N + o] * xv);
+      }
+      double e = fabs(acc - gW[(size_t)o * K + i]) / (mag + 1e-6);
+      if (e > worst) worst = e;
+      if (e > 2e-6) ++bad;
+    }
+  }
+  printf("  max err/sum|terms|=%.3g bad=%d %s\n", worst, bad, bad ? "FAIL" : "ok");
+  cudaFree(dG); cudaFree(dX); cudaFree(dW); cudaFree(db); cudaFree(ws);
+  return bad != 0;
+}
+
+static void wgrad_probe(int mode) {
+  const int64_t B = 32; const int N = 128, K = 16;
+  std::vector<float> G(B * N, 0.f), X(B * K, 0.f), gW((size_t)N * K, -3.f), gb(N, -3.f);
+  for (int64_t b = 0; b < 8; ++b) {
+    for (int o = 0; o < N; ++o) G[b * N + o] = mode == 0 ? (float)((o + 1) * (1 << b)) : 1.f;
+    for (int i = 0; i < K; ++i) X[b * K + i] = mode == 0 ? 1.f : (float)((i + 1) * (1 << b));
+  }
+  float *dG, *dX, *dW, *db, *ws;
+  cudaMalloc(&dG, G.size() * 4); cudaMalloc(&dX, X.size() * 4); cudaMalloc(&dW, gW.size() * 4);
+  cudaMalloc(&db, N * 4); cudaMalloc(&ws, vcnf_linear_wgrad_workspace(B, N, K));
+  cudaMemcpy(dG, G.data(), G.size() * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(dX, X.data(), X.size() * 4, cudaMemcpyHostToDevice);
+  vcnf_linear_wgrad_tf32x3(dG, N, dX, K, dW, db, ws, B, N, K, 0, nullptr);
+  cudaDeviceSynchronize();
+  cudaMemcpy(gW.data(), dW, gW.size() * 4, cudaMemcpyDeviceToHost);
+  cudaMemcpy(gb.data(), db, N * 4, cudaMemcpyDeviceToHost);
+  printf("PROBE mode %d: expect gW[o,i] = %s, gb[o] = %s\n", mode, mode == 0 ? "255*(o+1)" : "255*(i+1)",
+         mode == 0 ? "255*(o+1)" : "8");
+  for (int o = 0; o < 20; ++o) {
+    printf("  o=%3d gb=%g :", o, gb[o]);
+    for (int i = 0; i < K; ++i) printf(" %g", gW[o * K + i]);
+    printf("\n");
+  }
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && atoi(argv[1]) == 5) { wgrad_probe(0); wgrad_probe(1); return 0; }
+  if (argc > 1 && atoi(argv[1]) == 4) {
+    int f = 0;
+    f += run_wgrad(32, 128, 128, false, 1);
+    f += run_wgrad(1000, 128, 128, true, 1);
+    f += run_wgrad(777, 128, 15, false, 1);
+    f += run_wgrad(5000, 322, 128, false, 1);
+    f += run_wgrad(65536, 128, 128, true, 3);
+    f += run_wgrad(65536, 322, 128, false, 3);
+    f += run_wgrad(65536, 128, 15, false, 3);
+    printf("%s (%d failing)\n", f ? "WGRAD TEST FAILED" : "WGRAD TEST PASSED", f);
+    return f;
+  }
   int fails = 0;
   fails += run(128, 128, 32, 32, false, false, false, false, false, 1);      // one tile, one k-chunk
   if (argc > 1 && atoi(argv[1]) == 1) return fails;

@@ -35,11 +35,13 @@ _SIGNATURES = {
     "vcnf_permute_channels": [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _vp],
     "vcnf_squeeze": [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
     "vcnf_linear_tf32x3": [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp],
+    "vcnf_linear_wgrad_tf32x3": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
     "vcnf_small_linear": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
 }
 _I64_RETURN = {
     "vcnf_rqs_layer_bwd_workspace": [_i32, _i32, _i32],
     "vcnf_const_affine_bwd_workspace": [_i32, _i32],
+    "vcnf_linear_wgrad_workspace": [_i64, _i32, _i32],
 }
 EXPORTED = sorted(list(_SIGNATURES) + list(_I64_RETURN))
 

@@ -402,6 +402,240 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
 }
 
+
+// =================================================================================================
+// Weight gradient:  gW[o, i] = sum_b gY[b, o] * act(X[b, i]),   gb[o] = sum_b gY[b, o]
+// (autograd of F.linear in the conditioners: the cuBLAS "nt" sgemm + the bias-gradient reduce_kernel,
+// 25 ms of the first measured 60 ms training step of cfg 2).
+//
+// The reduction runs over the BATCH, which is the slow index of both operands in HBM, while the
+// tensor core wants K(= batch)-major operands (tf32 MN-major no-swizzle operands returned zeros on
+// B200, tools/gemm_test.cu probe).  So every loader thread transposes in registers: it loads a 4
+// samples x 4 features block with four coalesced 128-bit loads (a warp reads 512 contiguous bytes of
+// one sample row per instruction) and stores four 16 B chunks "feature row x 4 consecutive samples" of
+// the canonical K-major layout.  The 8-row-group stride (SBO) is skewed by 16 B (1040 instead of 1024)
+// so that the 8 lanes of a store phase hit 8 different 16 B bank groups.
+// UMMA M = output features (<= 128 per CTA), N = input features + a ones column (-> gb for free), K =
+// samples.  Split-K over the batch: every CTA accumulates its share in TMEM and writes one partial;
+// wgrad_reduce_kernel sums the partials in a fixed order (deterministic).
+// =================================================================================================
+constexpr int kWStages = 3;
+constexpr int kWBK = 32;             // samples per stage (4 MMA k-steps of 8)
+constexpr uint32_t kWSbo = 1024 + 16;
+
+struct WArgs {
+  const float* gY; int64_t ldg;      // [B, N]
+  const float* X; int64_t ldx;       // [B, K]
+  float* partial;                    // [splits, o_tiles * 128, K + 1]
+  int64_t B; int N; int K;
+  int relu_in;
+  int o_tiles, splits;
+  int NX;                            // K + 1 rounded up to 16 = UMMA N
+  int64_t chunks;                    // ceil(B / kWBK)
+};
+
+// Thread item: feature chunk c = tid & 31 (features 4c .. 4c+3), sample group sg = tid >> 5 (samples
+// 4sg .. 4sg+3 of the stage).  v[j] = the four features of sample 4sg + j.
+__device__ __forceinline__ void wload(float4 (&v)[4], const float* src, int64_t ld, int f0, int n_valid, int n_chunks,
+                                      int64_t b0, int64_t B, bool vec_ok, int tid) {
+  const int c = tid & 31, sg = tid >> 5;
+  const int f = c * 4;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int64_t b = b0 + sg * 4 + j;
+    if (c < n_chunks && b < B) {
+      const float* p = src + b * ld + f0 + f;
+      if (vec_ok && f + 3 < n_valid) {
+        t = __ldg(reinterpret_cast<const float4*>(p));
+      } else {
+        if (f + 0 < n_valid) t.x = __ldg(p + 0);
+        if (f + 1 < n_valid) t.y = __ldg(p + 1);
+        if (f + 2 < n_valid) t.z = __ldg(p + 2);
+        if (f + 3 < n_valid) t.w = __ldg(p + 3);
+      }
+    }
+    v[j] = t;
+  }
+}
+
+// Transpose the 4x4 block and store the hi / lo planes.  ones_at: feature index that must read 1.0
+// (bias-gradient column) when it falls inside this thread's chunk, -1 otherwise.
+__device__ __forceinline__ void wstore(const float4 (&v)[4], unsigned char* hi, unsigned char* lo, int n_chunks, bool relu,
+                                       int ones_at, int tid) {
+  const int c = tid & 31, sg = tid >> 5;
+  if (c >= n_chunks) return;
+  const float in[4][4] = {{v[0].x, v[0].y, v[0].z, v[0].w}, {v[1].x, v[1].y, v[1].z, v[1].w},
+                          {v[2].x, v[2].y, v[2].z, v[2].w}, {v[3].x, v[3].y, v[3].z, v[3].w}};
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {                           // feature row 4c + r: samples 4sg .. 4sg+3
+    const int row = c * 4 + r;
+    float e[4], h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      e[j] = in[j][r];
+      if (relu) e[j] = fmaxf(e[j], 0.f);
+      if (row == ones_at) e[j] = 1.f;
+      split_tf32(e[j], h[j], l[j]);
+    }
+    const uint32_t off = static_cast<uint32_t>(row >> 3) * kWSbo + static_cast<uint32_t>(sg) * 128 + (row & 7) * 16;
+    *reinterpret_cast<float4*>(hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const WArgs a) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);            // [kWStages]
+  uint64_t* empty = full + kWStages;                             // [kWStages]
+  uint64_t* acc_full = empty + kWStages;                         // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  const int NX = a.NX;
+  const uint32_t a_half = (128 / 8) * kWSbo;                     // gY operand plane (hi or lo)
+  const uint32_t b_half = static_cast<uint32_t>(NX / 8) * kWSbo; // X operand plane
+  const uint32_t stage_bytes = 2 * a_half + 2 * b_half;
+  unsigned char* st0 = smem + 1024;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ot = blockIdx.x % a.o_tiles;
+  const int split = blockIdx.x / a.o_tiles;
+  const int o0 = ot * 128;
+  const int o_valid = (a.N - o0) < 128 ? (a.N - o0) : 128;
+  const int64_t per = (a.chunks + a.splits - 1) / a.splits;
+  const int64_t c_begin = split * per;
+  const int64_t c_end = (c_begin + per) < a.chunks ? (c_begin + per) : a.chunks;
+  const int64_t G = c_end > c_begin ? c_end - c_begin : 0;
+  const int x_chunks = (a.K + 3) / 4;                            // feature chunks of X that hold data
+  const int ones_in_data = (a.K % 4 != 0) ? a.K : -1;            // ones column shares a chunk with data
+
+  if (tid == 0) {
+    for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], kLoaderWarps * 32); mbar_init(&empty[s], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init_fence();
+  }
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
+  // constant rows of the X operand (features >= 4 * x_chunks): ones column (if not inside a data chunk)
+  // and zero padding up to NX, written once for every stage
+  for (int idx = tid; idx < kWStages * (NX - 4 * x_chunks) * (kWBK / 4); idx += kThreads) {
+    const int per_stage = (NX - 4 * x_chunks) * (kWBK / 4);
+    const int s = idx / per_stage, rem = idx - s * per_stage;
+    const int row = 4 * x_chunks + rem / (kWBK / 4), sg = rem % (kWBK / 4);
+    const float val = (row == a.K) ? 1.f : 0.f;
+    unsigned char* bh = st0 + static_cast<uint32_t>(s) * stage_bytes + 2 * a_half;
+    const uint32_t off = static_cast<uint32_t>(row >> 3) * kWSbo + static_cast<uint32_t>(sg) * 128 + (row & 7) * 16;
+    *reinterpret_cast<float4*>(bh + off) = make_float4(val, val, val, val);
+    *reinterpret_cast<float4*>(bh + b_half + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < kLoaderWarps) {
+    // ------------------------------ loaders: chunk i+1 in registers while chunk i is stored
+    const bool vec_g = (a.ldg % 4 == 0) && (reinterpret_cast<uintptr_t>(a.gY) % 16 == 0) && (o0 % 4 == 0);
+    const bool vec_x = (a.ldx % 4 == 0) && (reinterpret_cast<uintptr_t>(a.X) % 16 == 0);
+    float4 ga[4], xa[4], gb[4], xb[4];
+    auto load = [&](float4 (&g)[4], float4 (&x)[4], int64_t i) {
+      if (i >= G) return;
+      const int64_t b0 = (c_begin + i) * kWBK;
+      wload(g, a.gY, a.ldg, o0, o_valid, 32, b0, a.B, vec_g, tid);
+      wload(x, a.X, a.ldx, 0, a.K, x_chunks, b0, a.B, vec_x, tid);
+    };
+    auto store = [&](const float4 (&g)[4], const float4 (&x)[4], int64_t i) {
+      if (i >= G) return;
+      const uint32_t it = static_cast<uint32_t>(i);
+      const int s = it % kWStages;
+      mbar_wait(&empty[s], ((it / kWStages) & 1u) ^ 1u);
+      unsigned char* st = st0 + static_cast<uint32_t>(s) * stage_bytes;
+      wstore(g, st, st + a_half, 32, false, -1, tid);
+      wstore(x, st + 2 * a_half, st + 2 * a_half + b_half, x_chunks, a.relu_in != 0, ones_in_data, tid);
+      fence_async_smem();
+      mbar_arrive(&full[s]);
+    };
+    load(ga, xa, 0);
+    for (int64_t i = 0; i < G; i += 2) {
+      load(gb, xb, i + 1);
+      store(ga, xa, i);
+      load(ga, xa, i + 2);
+      store(gb, xb, i + 1);
+    }
+  } else if (warp == kMmaWarp) {
+    // ------------------------------ MMA issuer
+    const uint32_t idesc = instr_desc_tf32(128, NX);
+    const uint32_t d_main = tmem_base, d_small = tmem_base + 256;
+    for (int64_t i = 0; i < G; ++i) {
+      const uint32_t it = static_cast<uint32_t>(i);
+      const int s = it % kWStages;
+      mbar_wait(&full[s], (it / kWStages) & 1u);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t a_hi = smem_u32(st0 + static_cast<uint32_t>(s) * stage_bytes);
+        const uint32_t a_lo = a_hi + a_half;
+        const uint32_t b_hi = a_hi + 2 * a_half;
+        const uint32_t b_lo = b_hi + b_half;
+#pragma unroll
+        for (int combo = 0; combo < 3; ++combo) {
+          const uint32_t ab = combo == 0 ? a_lo : a_hi;
+          const uint32_t bb = combo == 1 ? b_lo : b_hi;
+#pragma unroll
+          for (int kk = 0; kk < kWBK / 8; ++kk) {
+            const uint64_t ad = smem_desc(ab + kk * 256, 128, kWSbo);
+            const uint64_t bd = smem_desc(bb + kk * 256, 128, kWSbo);
+            if (combo == 2) mma_tf32(d_main, ad, bd, idesc, (i > 0 || kk > 0) ? 1u : 0u);
+            else mma_tf32(d_small, ad, bd, idesc, (i > 0 || combo > 0 || kk > 0) ? 1u : 0u);
+          }
+        }
+        tc_commit(&empty[s]);
+        if (i == G - 1) tc_commit(acc_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------ epilogue: one partial [128, K + 1] per CTA
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int W1 = a.K + 1;
+    float* dst = a.partial + (static_cast<int64_t>(split) * a.o_tiles * 128 + o0 + row) * W1;
+    if (G > 0) {
+      mbar_wait(acc_full, 0);
+      tc_fence_after();
+    }
+    for (int cb = 0; cb * 32 < W1; ++cb) {
+      uint32_t r[32], r2[32];
+      if (G > 0) {
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cb * 32;
+        tmem_ld32(taddr, r);
+        tmem_ld32(taddr + 256, r2);
+        tmem_ld_wait();
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = cb * 32 + j;
+        if (col < W1) dst[col] = G > 0 ? __uint_as_float(r[j]) + __uint_as_float(r2[j]) : 0.f;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// gW[o, i] = sum_s partial[s][o][i], gb[o] = sum_s partial[s][o][K]   (fixed order)
+__global__ void wgrad_reduce_kernel(const float* partial, int splits, int rows_pad, int N, int K, float* gW, float* gb) {
+  const int W1 = K + 1;
+  const int64_t total = static_cast<int64_t>(N) * W1;
+  for (int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int o = static_cast<int>(e / W1), i = static_cast<int>(e - static_cast<int64_t>(o) * W1);
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += partial[(static_cast<int64_t>(s) * rows_pad + o) * W1 + i];
+    if (i < K) gW[static_cast<int64_t>(o) * K + i] = acc;
+    else if (gb) gb[o] = acc;
+  }
+}
+
 }  // namespace gemm
 }  // namespace vcnf
 
@@ -441,5 +675,59 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
   }
   gemm::linear_tf32x3_kernel<<<static_cast<unsigned>(a.n_tiles * cpt), gemm::kThreads, smem,
                                static_cast<cudaStream_t>(stream)>>>(a);
+  return launch_status();
+}
+
+
+static int wgrad_splits(int64_t B, int N) {
+  const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
+  const int o_tiles = (N + 127) / 128;
+  const int64_t chunks = (B + gemm::kWBK - 1) / gemm::kWBK;
+  int64_t s = sms / o_tiles;
+  if (s < 1) s = 1;
+  if (s > chunks) s = chunks;
+  return static_cast<int>(s);
+}
+
+extern "C" int64_t vcnf_linear_wgrad_workspace(int64_t B, int N, int K) {
+  if (B <= 0 || N <= 0 || K <= 0) return 0;
+  const int o_tiles = (N + 127) / 128;
+  return static_cast<int64_t>(wgrad_splits(B, N)) * o_tiles * 128 * (K + 1) * 4;
+}
+
+extern "C" int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void* X, int64_t ldx, void* gW, void* gb,
+                                        void* workspace, int64_t B, int N, int K, int relu_in, void* stream) {
+  if (!gW || N <= 0 || K <= 0 || B < 0) return VCNF_E_BADARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (B == 0) {   /* empty batch: gradients are zero */
+    cudaMemsetAsync(gW, 0, static_cast<size_t>(N) * K * 4, st);
+    if (gb) cudaMemsetAsync(gb, 0, static_cast<size_t>(N) * 4, st);
+    return launch_status();
+  }
+  if (!gY || !X || !workspace || ldg < N || ldx < K) return VCNF_E_BADARG;
+  if (K > gemm::kMaxK) return VCNF_E_UNSUPPORTED;
+  gemm::WArgs a{};
+  a.gY = static_cast<const float*>(gY); a.ldg = ldg;
+  a.X = static_cast<const float*>(X); a.ldx = ldx;
+  a.partial = static_cast<float*>(workspace);
+  a.B = B; a.N = N; a.K = K; a.relu_in = relu_in;
+  a.o_tiles = (N + 127) / 128;
+  a.splits = wgrad_splits(B, N);
+  a.NX = (K + 1 + 15) / 16 * 16;
+  a.chunks = (B + gemm::kWBK - 1) / gemm::kWBK;
+  const size_t smem = 1024 + static_cast<size_t>(gemm::kWStages) * 2 * (128 / 8 + static_cast<size_t>(a.NX) / 8) * gemm::kWSbo;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(gemm::linear_wgrad_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    attr_set = true;
+  }
+  gemm::linear_wgrad_tf32x3_kernel<<<static_cast<unsigned>(a.o_tiles * a.splits), gemm::kThreads, smem, st>>>(a);
+  int rc = launch_status();
+  if (rc) return rc;
+  const int64_t total = static_cast<int64_t>(N) * (K + 1);
+  int grid = static_cast<int>((total + 255) / 256);
+  if (grid > 1184) grid = 1184;
+  gemm::wgrad_reduce_kernel<<<grid, 256, 0, st>>>(a.partial, a.splits, a.o_tiles * 128, N, K, static_cast<float*>(gW),
+                                                   static_cast<float*>(gb));
   return launch_status();
 }

@@ -398,11 +398,17 @@ class _Linear(torch.autograd.Function):
                     first = False
                 if ctx.relu_in and N > 128:
                     gx = gx * (x > 0)
-        if ctx.needs_input_grad[1]:
-            xa = torch.relu(x) if ctx.relu_in else x
-            gw = gy.t() @ xa
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = gy.sum(0)
+        want_w = ctx.needs_input_grad[1]
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        if want_w or want_b:
+            # gW = gy^T act(x), gb = column sums of gy: one split-K tcgen05 kernel + a fixed-order reduce
+            gw = torch.empty_like(weight)
+            gb = torch.empty(N, dtype=x.dtype, device=x.device) if want_b else None
+            ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", M, N, K), dtype=torch.uint8, device=x.device)
+            _launch("vcnf_linear_wgrad_tf32x3", ptr(gy), N, ptr(x), K, ptr(gw), ptr(gb), ptr(ws), M, N, K,
+                    int(ctx.relu_in), stream(), n=2)
+            if not want_w:
+                gw = None
         if ctx.has_res and ctx.needs_input_grad[3]:
             gres = gy
         return gx, gw, gb, gres, None
