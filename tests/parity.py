@@ -53,7 +53,12 @@ def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.999):
     if not ok.any():
         return
     err = (a_ - r32).abs()[ok]
-    inside = err <= atol + rtol * r32.abs()[ok]
+    tol = atol + rtol * r32.abs()[ok]
+    # elements on which the reference's OWN fp32 rounding already uses a quarter of the tolerance are
+    # ill-conditioned: a different (equally valid) fp32 evaluation order cannot be held to `tol` there;
+    # they are covered by the worst-error clause below instead
+    excused = (r32 - r64).abs()[ok] > 0.25 * tol
+    inside = (err <= tol) | excused
     share = float(inside.double().mean())
     e64 = float((a_ - r64).abs()[ok].max())
     ref_e = float((r32 - r64).abs()[ok].max())

@@ -8,9 +8,10 @@
 // and input-gradient (A = grad-output, W = weight^T through strides, mask = relu'(saved input)).
 //
 // Why 3xTF32: the stated parity tolerance (1e-4 rel on spline outputs) rules out plain TF32/BF16
-// products (2^-11).  Every fp32 operand is split a = hi + lo with hi = a & 0xffffe000 (exact TF32)
-// and lo = a - hi (exact in fp32, |lo| <= 2^-10 |a|), and three tcgen05.mma.kind::tf32 chains
-// lo*hi + hi*lo + hi*hi accumulate in one fp32 TMEM accumulator: relative error ~2^-21 per product.
+// products (2^-11).  Every fp32 operand is split a = hi + lo with hi = rn_tf32(a) and lo =
+// rn_tf32(a - hi) (|lo| <= 2^-11 |a|), and three tcgen05.mma.kind::tf32 chains lo*hi + hi*lo + hi*hi
+// accumulate in fp32 TMEM accumulators (hi*hi and the cross terms separately, summed in the
+// epilogue): relative error ~2^-22 per product, the level of an fp32 FMA chain.
 //
 // Structure (one CTA per SM, persistent over 128-row tiles of a fixed <=128-column slice of W):
 //   warps 0-7  loaders : ld.global (128-bit, 8 rows x 64 B per warp request, three k-chunks in flight
@@ -23,6 +24,7 @@
 //                        global stores; double-buffered accumulators (2 x 128 TMEM columns) let the
 //                        epilogue of tile i overlap the MMAs of tile i+1
 // W (hi and lo, <= 2 x 64 KB) stays resident in shared memory for the CTA's lifetime.
+#include <cstdlib>
 #include "common.cuh"
 #include "../../include/vcnf_b200.h"
 
@@ -114,6 +116,7 @@ struct Args {
   float* C; int64_t ldc;
   int64_t M; int N; int K;
   int relu_in;
+  int dbg;            // timing experiments only (VCNF_GEMM_DEBUG): 1 no global loads, 2 no MMA, 4 no stores
   int n_tiles;        // ceil(N / kBN)
   int ctas_per_ntile; // persistent CTAs sharing one column slice
   int KP;             // K rounded up to a multiple of kBK
@@ -124,9 +127,17 @@ __device__ __forceinline__ uint32_t canon_off(int row, int k, int KP) {
   return static_cast<uint32_t>((row >> 3) * (KP * 32) + (k >> 2) * 128 + (row & 7) * 16 + (k & 3) * 4);
 }
 
+// a = hi + lo with BOTH parts rounded to nearest TF32 (10 explicit mantissa bits).  The tensor core
+// truncates whatever low bits it is given; with a truncating split the dropped part of lo is up to
+// 2^-20 |a| (measured: max error / sum|terms| 5e-7 even for K = 15), with round-to-nearest it is
+// <= 2^-23 |a|.  Integer rounding (add half an ulp of TF32, clear the low 13 bits) = cvt.rna.tf32.f32
+// without its lower issue rate.
+__device__ __forceinline__ float rn_tf32(float a) {
+  return __uint_as_float((__float_as_uint(a) + 0x1000u) & 0xffffe000u);
+}
 __device__ __forceinline__ void split_tf32(float a, float& hi, float& lo) {
-  hi = __uint_as_float(__float_as_uint(a) & 0xffffe000u);
-  lo = a - hi;
+  hi = rn_tf32(a);
+  lo = rn_tf32(a - hi);
 }
 
 __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a) {
@@ -155,8 +166,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
   const int nk8 = (a.K + 7) >> 3;                                // 8-wide MMA steps that carry data
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], kLoaderWarps * 32); mbar_init(&empty[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps * 32); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], kLoaderWarps); mbar_init(&empty[s], 1); }   // one arrival per WARP:
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps); }      // 256 same-word arrivals serialise
     mbar_init_fence();
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
@@ -259,7 +270,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
         const int64_t gr = m0 + row;
         const int gk = k0 + chunk * 4;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gr < a.M) {
+        if (gr < a.M && !(a.dbg & 1)) {
           const float* src = a.A + gr * a.lda + gk;
           if (vec_ok && gk + 3 < a.K) {
             v = __ldg(reinterpret_cast<const float4*>(src));
@@ -296,7 +307,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
         *reinterpret_cast<float4*>(lo_base + off) = lo4;
       }
       fence_async_smem();
-      mbar_arrive(&full[s]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
     };
     float4 b0[kLoadsPerChunk], b1[kLoadsPerChunk], b2[kLoadsPerChunk];
     load_chunk(b0, 0);
@@ -341,6 +353,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
             for (int kk = 0; kk < steps; ++kk) {
               const uint64_t ad = smem_desc(ab + kk * 256, 128, 1024);
               const uint64_t bd = smem_desc(bb + kk * 256, 128, w_sbo);
+              if (a.dbg & 2) continue;
               if (combo == 2) mma_tf32(d_main, ad, bd, idesc, (kc > 0 || kk > 0) ? 1u : 0u);
               else mma_tf32(d_small, ad, bd, idesc, (kc > 0 || combo > 0 || kk > 0) ? 1u : 0u);
             }
@@ -377,7 +390,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
         for (int j = 0; j < 32; ++j) tbuf[lane * 33 + j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]);
         __syncwarp();
         const int col = n0 + cb * 32 + lane;
-        if (col < a.N) {
+        if (col < a.N && !(a.dbg & 4)) {
           const float bv = a.bias ? __ldg(a.bias + col) : 0.f;
           float* cp = a.C + row0 * a.ldc + col;
           const float* rp = a.residual ? a.residual + row0 * a.ldr + col : nullptr;
@@ -393,7 +406,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
         __syncwarp();
       }
       tc_fence_before();
-      mbar_arrive(&acc_empty[buf]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
 
@@ -509,7 +523,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const 
   const int ones_in_data = (a.K % 4 != 0) ? a.K : -1;            // ones column shares a chunk with data
 
   if (tid == 0) {
-    for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], kLoaderWarps * 32); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], kLoaderWarps); mbar_init(&empty[s], 1); }
     mbar_init(acc_full, 1);
     mbar_init_fence();
   }
@@ -552,7 +566,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const 
       wstore(g, st, st + a_half, 32, false, -1, tid);
       wstore(x, st + 2 * a_half, st + 2 * a_half + b_half, x_chunks, a.relu_in != 0, ones_in_data, tid);
       fence_async_smem();
-      mbar_arrive(&full[s]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
     };
     load(ga, xa, 0);
     for (int64_t i = 0; i < G; i += 2) {
@@ -658,6 +673,7 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
   a.mask = static_cast<const float*>(mask); a.ldm = ldm;
   a.C = static_cast<float*>(C); a.ldc = ldc;
   a.M = M; a.N = N; a.K = K; a.relu_in = relu_in;
+  { const char* e = getenv("VCNF_GEMM_DEBUG"); a.dbg = e ? atoi(e) : 0; }
   a.n_tiles = (N + gemm::kBN - 1) / gemm::kBN;
   a.KP = (K + gemm::kBK - 1) / gemm::kBK * gemm::kBK;
   const int64_t m_tiles = (M + gemm::kBM - 1) / gemm::kBM;
