@@ -125,7 +125,8 @@ def _time_launches(fn, flush, reps=20):
     torch.cuda.synchronize()
     tot = 0.0
     for _ in range(reps):
-        flush.zero_()
+        flush.zero_()      # L2 flush; two passes also keep the GPU busy while the host enqueues
+        flush.zero_()      # e0 / fn / e1, so the event pair brackets the kernel(s) without a launch gap
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn()
@@ -163,23 +164,51 @@ def kernel_roofline(model, dev, flush):
         torch.autograd.grad([y, ld], [x_g, cond_g, sh_g], [gy, gld], retain_graph=True)
 
     P = spec.Tc * spec.Pc
-    for name, fn, bytes_per_sample in (("rqs_layer_fwd", fwd, 4 * (P + 2 * D + 1)),
-                                       ("rqs_layer_bwd", bwd, 4 * (2 * P + 3 * D + 1))):
+    # conditioner dense layer at the hidden shape (64 of the 96 forward GEMMs of a step, and the same
+    # kernel runs the 96 input-gradient GEMMs): y = relu(h) W^T + b + h
+    h = torch.randn(B, HIDDEN, device=dev)
+    W = torch.randn(HIDDEN, HIDDEN, device=dev) * 0.05
+    bvec = torch.randn(HIDDEN, device=dev)
+    gh = torch.randn(B, HIDDEN, device=dev)
+
+    def lin_fwd():
+        with torch.no_grad():
+            ops.linear(h, W, bvec, residual=h, relu_in=True)
+
+    from vcnf_b200 import _lib
+    gW, gbv = torch.empty_like(W), torch.empty_like(bvec)
+    ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", B, HIDDEN, HIDDEN), dtype=torch.uint8, device=dev)
+
+    def lin_wgrad():        # straight through the C ABI (no autograd bookkeeping between the events)
+        _lib.call("vcnf_linear_wgrad_tf32x3", gh.data_ptr(), HIDDEN, h.data_ptr(), HIDDEN, gW.data_ptr(),
+                  gbv.data_ptr(), ws.data_ptr(), B, HIDDEN, HIDDEN, 1, torch.cuda.current_stream().cuda_stream)
+
+    kernels = (("linear_tf32x3 (fwd/dgrad, hidden 128x128, relu+bias+residual fused)", lin_fwd,
+                4 * (3 * HIDDEN), 224),                       # read h (A and residual), write y
+               ("linear_wgrad_tf32x3 (+ reduce)", lin_wgrad, 4 * (2 * HIDDEN), 96),
+               ("rqs_layer_fwd", fwd, 4 * (P + 2 * D + 1), 16),
+               ("rqs_layer_bwd (+ shared-grad reduce)", bwd, 4 * (2 * P + 3 * D + 1), 16))
+    for name, fn, bytes_per_sample, per_step in kernels:
         ms = _time_launches(fn, flush)
         ach = bytes_per_sample * B / (ms * 1e-3) / 1e9
-        out[name] = {"ms": ms, "achieved": ach, "frac": ach / peak, "bytes_per_sample": bytes_per_sample}
+        out[name] = {"ms": ms, "achieved": ach, "frac": ach / peak, "bytes_per_sample": bytes_per_sample,
+                     "launches_per_step": per_step, "step_share_ms": ms * per_step}
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    dom_name = max(out, key=lambda k: out[k]["step_share_ms"])
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("rqs_layer_bwd")
+            traffic = json.load(open(tpath)).get(dom_name.split(" ")[0])
         except Exception:
             traffic = None
-    dom = out["rqs_layer_bwd"]
-    return {"bound": "hbm", "kernel": "rqs_layer_bwd_kernel<float,8> (+ shared-grad reduce)",
+    dom = out[dom_name]
+    return {"bound": "hbm", "kernel": dom_name,
             "achieved": dom["achieved"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
             "frac": dom["frac"], "traffic": traffic, "algorithmic_bytes_per_launch": dom["bytes_per_sample"] * B,
-            "launch_ms": dom["ms"], "other_kernels": {"rqs_layer_fwd": out["rqs_layer_fwd"]}}
+            "launch_ms": dom["ms"],
+            "note": "dominant = largest (launch time x launches per step); the fp32-faithful GEMM moves "
+                    "activations once in / once out, so its roofline is HBM (SURVEY.md 8d)",
+            "other_kernels": {k: v for k, v in out.items() if k != dom_name}}
 
 
 def gpu_run(args):
@@ -195,18 +224,25 @@ def gpu_run(args):
     torch.manual_seed(0)
     model = build_model(nf).to(dev)
     bucket = parallel.GradBucket(model.parameters())
-    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True, capturable=not args.no_graph)
     x_host = synth_batch(BATCH, 1234 + rank).pin_memory()
     x_dev = x_host.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
-    def step(x):
-        bucket.zero()
-        loss = model.forward_kld(x)
-        loss.backward()
-        bucket.allreduce_mean(world)
-        opt.step()
-        return loss
+    if args.no_graph:
+        def step(x):
+            bucket.zero()
+            loss = model.forward_kld(x)
+            loss.backward()
+            bucket.allreduce_mean(world)
+            opt.step()
+            return loss
+        graphed = False
+    else:
+        # the whole step (~1600 launches) captured once into a CUDA graph and replayed (parallel.py)
+        step = parallel.GraphedTrainStep(model, opt, bucket, x_dev, world=world)
+        graphed = step.graph is not None
+    launches_per_step = None
 
     def barrier():
         if world > 1:
@@ -218,7 +254,14 @@ def gpu_run(args):
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    launches0 = ops.LAUNCHES
+    if not graphed:
+        launches0 = ops.LAUNCHES
+    else:
+        # kernels inside one replay = kernels the eager step launches (counted on one eager run)
+        launches0 = ops.LAUNCHES
+        step._eager()
+        launches_per_step = ops.LAUNCHES - launches0
+        barrier()
     evs = []
     barrier()
     for _ in range(args.steps):
@@ -229,7 +272,7 @@ def gpu_run(args):
         e1.record()
         evs.append((e0, e1))
     barrier()
-    launches = ops.LAUNCHES - launches0
+    launches = (ops.LAUNCHES - launches0) if not graphed else launches_per_step * args.steps
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
     clocks = sampler.summary()
     t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
@@ -276,7 +319,8 @@ def gpu_run(args):
         "config": {"workload": WORKLOAD, "global_batch": world * BATCH, "features": D, "layers": LAYERS,
                    "hidden": HIDDEN, "bins": BINS, "parallelism": "dp%d" % world,
                    "l2": "256 MiB buffer written between timed steps (L2 flush)",
-                   "conditioner_gemms": "library (cuBLAS fp32) in round 1", "optimizer": "Adam(fused)"},
+                   "conditioner_gemms": "tcgen05 3xTF32 (vcnf_linear_tf32x3 fwd/dgrad, vcnf_linear_wgrad_tf32x3)", "optimizer": "Adam(fused)", "cuda_graph": graphed,
+                   "cuda_graph_error": getattr(step, "capture_error", None) if not args.no_graph else None},
         "clocks": clocks, "gpu_launches": launches,
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * D * 4,
                 "d2h_bytes_per_step": 4},
@@ -314,6 +358,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_run(args)

@@ -517,9 +517,13 @@ static int launch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
   a.num_tiles = (a.B + a.R - 1) / a.R;
   set_bulk_flags(a, false);
   const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, false, kThreads).total;
-  if (smem > kSmemMax) return VCNF_E_UNSUPPORTED;
+  if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
   auto kern = rqs_layer_fwd_kernel<T, KMAX, EXACT>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  static bool attr_set = false;     // once per instantiation (not a stream operation: keep it out of graph capture)
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax - 2048));   // static __shared__ of the kernel counts too
+    attr_set = true;
+  }
   int per_sm = static_cast<int>(kSmemMax / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
   const int64_t grid = a.num_tiles < static_cast<int64_t>(sms) * per_sm ? a.num_tiles : static_cast<int64_t>(sms) * per_sm;
@@ -536,9 +540,13 @@ static int launch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
   a.num_tiles = (a.B + a.R - 1) / a.R;
   set_bulk_flags(a, true);
   const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, true, kThreads).total;
-  if (smem > kSmemMax) return VCNF_E_UNSUPPORTED;
+  if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
   auto kern = rqs_layer_bwd_kernel<T, KMAX, EXACT>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax - 2048));   // static __shared__ of the kernel counts too
+    attr_set = true;
+  }
   int per_sm = static_cast<int>(kSmemMax / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);
   int64_t grid = static_cast<int64_t>(sms) * per_sm;

@@ -167,13 +167,26 @@ class _LULinear(Flow):
     def upper_diag(self):
         return F.softplus(self.unconstrained_upper_diag) + self.eps
 
+    def _index_tensors(self, device):
+        """Triangular index sets as DEVICE tensors, built once per device: indexing with the numpy arrays
+        would stage a host->device copy on every call (and is illegal inside CUDA-graph capture)."""
+        cache = getattr(self, "_idx_cache", None)
+        if cache is None or cache[0] != device:
+            mk = lambda a: torch.as_tensor(np.asarray(a), dtype=torch.long, device=device)
+            cache = (device, tuple(mk(a) for a in (self.lower_indices[0], self.lower_indices[1],
+                                                    self.upper_indices[0], self.upper_indices[1],
+                                                    self.diag_indices[0])))
+            self._idx_cache = cache
+        return cache[1]
+
     def _create_lower_upper(self):
+        li, lj, ui, uj, di = self._index_tensors(self.lower_entries.device)
         lower = self.lower_entries.new_zeros(self.features, self.features)
-        lower[self.lower_indices[0], self.lower_indices[1]] = self.lower_entries
-        lower[self.diag_indices[0], self.diag_indices[1]] = 1.
+        lower = lower.index_put((li, lj), self.lower_entries)
+        lower = lower.index_put((di, di), self.lower_entries.new_ones(self.features))
         upper = self.upper_entries.new_zeros(self.features, self.features)
-        upper[self.upper_indices[0], self.upper_indices[1]] = self.upper_entries
-        upper[self.diag_indices[0], self.diag_indices[1]] = self.upper_diag
+        upper = upper.index_put((ui, uj), self.upper_entries)
+        upper = upper.index_put((di, di), self.upper_diag)
         return lower, upper
 
     def weight(self):

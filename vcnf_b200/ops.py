@@ -333,6 +333,20 @@ class _SmallLinear(torch.autograd.Function):
                 gg = (gy if out_idx is None else gy.index_select(1, out_idx.long())).flatten(2).transpose(1, 2).reshape(-1, D)
             if sub and bias is not None:
                 xg = xg - bias
+            if x.dtype == torch.float32 and not sub and rows > 0:
+                # [D, rows] x [rows, D] with rows = batch: the split-K tcgen05 weight-gradient kernel
+                # (cuBLAS picks a 64x64 SIMT tile here: 2.6 ms per cfg-2 step for sixteen 29 x 29 results)
+                xg, gg = xg.contiguous(), gg.contiguous()
+                gW = torch.empty((D, D), dtype=x.dtype, device=x.device)
+                gb_ = torch.empty(D, dtype=x.dtype, device=x.device)
+                ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", rows, D, D), dtype=torch.uint8,
+                                 device=x.device)
+                _launch("vcnf_linear_wgrad_tf32x3", ptr(gg), D, ptr(xg), D, ptr(gW), ptr(gb_), ptr(ws), rows, D, D,
+                        0, stream(), n=2)
+                gb = gb_ if (bias is not None and ctx.needs_input_grad[2]) else None
+                if not ctx.needs_input_grad[1]:
+                    gW = None
+                return gx, gW, gb, None, None, None
             if ctx.needs_input_grad[1]:
                 gW = gg.t() @ xg
             if bias is not None and ctx.needs_input_grad[2]:

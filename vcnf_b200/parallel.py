@@ -75,3 +75,56 @@ def sync_actnorm_init(model, src=0):
         if hasattr(m, "data_dep_init_done") and hasattr(m, "s") and hasattr(m, "t"):
             dist.broadcast(m.s.data, src)
             dist.broadcast(m.t.data, src)
+
+
+class GraphedTrainStep:
+    """One `forward_kld` training step (zero grads -> loss -> backward -> [gradient all-reduce] -> optimizer
+    step) captured ONCE into a CUDA graph and replayed.  A cfg-2 step is ~1600 kernel launches from a
+    Python loop (core.py:55-61 keeps the per-layer loop on the host); measured on B200 the host needs
+    ~29 ms to issue them while the kernels take less, so the launch stream -- not the GPU -- bounds the
+    step.  Replaying the captured graph removes the host from the loop; the arithmetic is identical.
+
+        step = GraphedTrainStep(model, opt, bucket, example_batch)      # warms up 3 eager steps, captures
+        loss = step(batch)          # copies `batch` into the static input, replays, returns the 0-dim loss
+
+    The optimizer must be graph-capturable (e.g. torch.optim.Adam(..., capturable=True)).  If capture is
+    not possible (a layer with a host-side branch such as ActNorm's first-call init), `.graph` stays None
+    and the step runs eagerly -- same results, launch-bound."""
+
+    def __init__(self, model, optimizer, bucket, example, world=None, warmup=3, loss_fn=None):
+        self.model, self.opt, self.bucket = model, optimizer, bucket
+        self.world = world
+        self.loss_fn = loss_fn if loss_fn is not None else (lambda m, x: m.forward_kld(x))
+        self.x = example.clone()
+        self.graph, self.loss = None, None
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._eager()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.loss = self._eager()
+            self.graph = g
+        except Exception as exc:            # noqa: BLE001 -- report and run eagerly
+            self.capture_error = repr(exc)
+            torch.cuda.synchronize()
+            self.graph = None
+
+    def _eager(self):
+        self.bucket.zero()
+        loss = self.loss_fn(self.model, self.x)
+        loss.backward()
+        self.bucket.allreduce_mean(self.world)
+        self.opt.step()
+        return loss
+
+    def __call__(self, x):
+        self.x.copy_(x, non_blocking=True)
+        if self.graph is None:
+            return self._eager()
+        self.graph.replay()
+        return self.loss
