@@ -169,6 +169,7 @@ int main(int argc, char** argv) {
     run(262144, 128, 128, 128, false, false, true, false, false, 4);
     return 0;
   }
+  if (argc > 1 && atoi(argv[1]) == 6) { run(262144, 128, 128, 128, false, false, true, false, false, 2); return 0; }
   if (argc > 1 && atoi(argv[1]) == 3) { run(65536, 128, 128, 128, false, true, true, true, false, 3); return 0; }
   fails += run(128, 128, 128, 128, false, false, true, false, false, 1);
   fails += run(300, 128, 128, 128, false, true, true, true, false, 1);       // ragged M, relu, residual

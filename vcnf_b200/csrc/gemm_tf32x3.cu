@@ -34,11 +34,13 @@ namespace gemm {
 constexpr int kLoaderWarps = 8, kEpiWarps = 4;
 constexpr int kThreads = (kLoaderWarps + kEpiWarps + 1) * 32;     // 416
 constexpr int kMmaWarp = kLoaderWarps + kEpiWarps;                // 12
-constexpr int kLoadsPerChunk = (128 * 32 / 4) / (kLoaderWarps * 32);   // float4 per loader thread per k-chunk = 4
 constexpr int kBM = 128;          // rows per tile = UMMA M
 constexpr int kBN = 128;          // max columns per CTA slice = max UMMA N used
-constexpr int kBK = 32;           // fp32 elements per k-chunk (one stage)
-constexpr int kStages = 2;
+constexpr int kBK = 16;           // fp32 elements per k-chunk (one stage)
+constexpr int kStages = 4;        // handshake latency (arrive -> MMA -> commit -> refill) is hidden by depth, not size
+constexpr int kLoadsPerChunk = (kBM * kBK / 4) / (kLoaderWarps * 32);   // float4 per loader thread per k-chunk
+constexpr int kBlkPerGroup = kBK / 16;                                  // warp-loads (8 rows x 4 chunks) per 8-row group
+constexpr uint32_t kASbo = (kBK / 4) * 128;                             // byte stride between 8-row groups of an A stage
 constexpr int kMaxK = 128;        // W slice resident in smem
 constexpr uint32_t kTmemCols = 512;   // 2 buffers x (hi*hi accumulator + cross-term accumulator) x 128 columns
 
@@ -153,7 +155,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
   unsigned char* w_lo = w_hi + w_bytes;
   unsigned char* a_st = w_lo + w_bytes;                          // stage s: [hi 16 KB | lo 16 KB]
   constexpr uint32_t kAHalf = kBM * kBK * 4;
-  unsigned char* epi_st = a_st + kStages * 2 * kAHalf;           // 4 x [32][33] fp32 transpose tiles
+  unsigned char* epi_st = a_st + kStages * 2 * kAHalf;           // 4 x [32][36] fp32 transpose tiles
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nt = blockIdx.x % a.n_tiles;
@@ -265,8 +267,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
       for (int i = 0; i < kLoadsPerChunk; ++i) {
         const int q = i * (kLoaderWarps * 32) + tid;
         const int blk = q >> 5, l = q & 31;
-        const int row = (blk >> 1) * 8 + (l & 7);
-        const int chunk = (blk & 1) * 4 + (l >> 3);
+        const int row = (blk / kBlkPerGroup) * 8 + (l & 7);
+        const int chunk = (blk % kBlkPerGroup) * 4 + (l >> 3);
         const int64_t gr = m0 + row;
         const int gk = k0 + chunk * 4;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -295,14 +297,14 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
       for (int i = 0; i < kLoadsPerChunk; ++i) {
         const int q = i * (kLoaderWarps * 32) + tid;
         const int blk = q >> 5, l = q & 31;
-        const int row = (blk >> 1) * 8 + (l & 7);
-        const int chunk = (blk & 1) * 4 + (l >> 3);
+        const int row = (blk / kBlkPerGroup) * 8 + (l & 7);
+        const int chunk = (blk % kBlkPerGroup) * 4 + (l >> 3);
         float4 v = b[i];
         if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
         float4 h, lo4;
         split_tf32(v.x, h.x, lo4.x); split_tf32(v.y, h.y, lo4.y);
         split_tf32(v.z, h.z, lo4.z); split_tf32(v.w, h.w, lo4.w);
-        const uint32_t off = static_cast<uint32_t>((row >> 3) * 1024 + chunk * 128 + (row & 7) * 16);
+        const uint32_t off = static_cast<uint32_t>(row >> 3) * kASbo + chunk * 128 + (row & 7) * 16;
         *reinterpret_cast<float4*>(hi_base + off) = h;
         *reinterpret_cast<float4*>(lo_base + off) = lo4;
       }
@@ -351,7 +353,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
             const uint32_t ab = combo == 0 ? a_lo : a_hi;
             const uint32_t bb = combo == 1 ? b_lo : b_hi;
             for (int kk = 0; kk < steps; ++kk) {
-              const uint64_t ad = smem_desc(ab + kk * 256, 128, 1024);
+              const uint64_t ad = smem_desc(ab + kk * 256, 128, kASbo);
               const uint64_t bd = smem_desc(bb + kk * 256, 128, w_sbo);
               if (a.dbg & 2) continue;
               if (combo == 2) mma_tf32(d_main, ad, bd, idesc, (kc > 0 || kk > 0) ? 1u : 0u);
@@ -371,7 +373,12 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
     // peak).  Each warp therefore transposes its 32 x 32 block through a padded shared-memory tile so
     // that one instruction reads / writes one full 128 B line of a row (lane = column).
     const int q = warp & 3;                                   // TMEM lane quarter this warp may read
-    float* tbuf = reinterpret_cast<float*>(epi_st) + (warp - kLoaderWarps) * (32 * 33);
+    constexpr int kTS = 36;                                   // tile row stride (floats): 16 B aligned, conflict-free
+    float* tbuf = reinterpret_cast<float*>(epi_st) + (warp - kLoaderWarps) * (32 * kTS);
+    const bool vec_out = (a.ldc % 4 == 0) && (a.N % 4 == 0) && (reinterpret_cast<uintptr_t>(a.C) % 16 == 0) &&
+                         (!a.bias || reinterpret_cast<uintptr_t>(a.bias) % 16 == 0) &&
+                         (!a.residual || (a.ldr % 4 == 0 && reinterpret_cast<uintptr_t>(a.residual) % 16 == 0)) &&
+                         (!a.mask || (a.ldm % 4 == 0 && reinterpret_cast<uintptr_t>(a.mask) % 16 == 0));
     uint32_t tc = 0;
     for (int64_t mt = mt0; mt < m_tiles; mt += a.ctas_per_ntile, ++tc) {
       const uint32_t buf = tc & 1u;
@@ -387,20 +394,58 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
         tmem_ld32(taddr + kBN, r2);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) tbuf[lane * 33 + j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]);
+        for (int j = 0; j < 32; j += 4)                        // lane = row: 8 x 16 B, conflict-free
+          *reinterpret_cast<float4*>(tbuf + lane * kTS + j) =
+              make_float4(__uint_as_float(r[j]) + __uint_as_float(r2[j]), __uint_as_float(r[j + 1]) + __uint_as_float(r2[j + 1]),
+                          __uint_as_float(r[j + 2]) + __uint_as_float(r2[j + 2]), __uint_as_float(r[j + 3]) + __uint_as_float(r2[j + 3]));
         __syncwarp();
-        const int col = n0 + cb * 32 + lane;
-        if (col < a.N && !(a.dbg & 4)) {
-          const float bv = a.bias ? __ldg(a.bias + col) : 0.f;
-          float* cp = a.C + row0 * a.ldc + col;
-          const float* rp = a.residual ? a.residual + row0 * a.ldr + col : nullptr;
-          const float* mp = a.mask ? a.mask + row0 * a.ldm + col : nullptr;
+        if (a.dbg & 4) {
+        } else if (vec_out) {
+          // read back with lane = (row group of 4, 16 B column chunk): one instruction moves 4 rows x 128 B.
+          // All residual / mask loads of the block are issued before the first store (the compiler cannot
+          // move loads across stores through possibly-aliasing pointers itself).
+          const int cc = (lane & 7) * 4;                        // column offset inside the 32-column block
+          const int col = n0 + cb * 32 + cc;
+          const bool col_ok = col + 3 < a.N;                    // N % 4 == 0 on this path
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (a.bias && col_ok) bv = __ldg(reinterpret_cast<const float4*>(a.bias + col));
+          float4 rv[8], mv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = i * 4 + (lane >> 3);
+            const bool ok = rr < rows && col_ok;
+            rv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            mv[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+            if (a.residual && ok) rv[i] = __ldg(reinterpret_cast<const float4*>(a.residual + (row0 + rr) * a.ldr + col));
+            if (a.mask && ok) mv[i] = __ldg(reinterpret_cast<const float4*>(a.mask + (row0 + rr) * a.ldm + col));
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = i * 4 + (lane >> 3);
+            if (!(rr < rows && col_ok)) continue;
+            float4 t = *reinterpret_cast<const float4*>(tbuf + rr * kTS + cc);
+            t.x = (mv[i].x > 0.f ? t.x + bv.x : 0.f) + rv[i].x;
+            t.y = (mv[i].y > 0.f ? t.y + bv.y : 0.f) + rv[i].y;
+            t.z = (mv[i].z > 0.f ? t.z + bv.z : 0.f) + rv[i].z;
+            t.w = (mv[i].w > 0.f ? t.w + bv.w : 0.f) + rv[i].w;
+            *reinterpret_cast<float4*>(a.C + (row0 + rr) * a.ldc + col) = t;
+          }
+        } else {
+          // unaligned leading dimensions (e.g. the 322-wide head): lane = column, one 128 B row segment
+          // per instruction
+          const int col = n0 + cb * 32 + lane;
+          if (col < a.N) {
+            const float bv = a.bias ? __ldg(a.bias + col) : 0.f;
+            float* cp = a.C + row0 * a.ldc + col;
+            const float* rp = a.residual ? a.residual + row0 * a.ldr + col : nullptr;
+            const float* mp = a.mask ? a.mask + row0 * a.ldm + col : nullptr;
 #pragma unroll 8
-          for (int rr = 0; rr < rows; ++rr) {
-            float t = tbuf[rr * 33 + lane] + bv;
-            if (mp && !(__ldg(mp + rr * a.ldm) > 0.f)) t = 0.f;
-            if (rp) t += __ldg(rp + rr * a.ldr);
-            cp[rr * a.ldc] = t;
+            for (int rr = 0; rr < rows; ++rr) {
+              float t = tbuf[rr * kTS + lane] + bv;
+              if (mp && !(__ldg(mp + rr * a.ldm) > 0.f)) t = 0.f;
+              if (rp) t += __ldg(rp + rr * a.ldr);
+              cp[rr * a.ldc] = t;
+            }
           }
         }
         __syncwarp();
@@ -683,7 +728,7 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
   a.ctas_per_ntile = cpt;
   const size_t smem = 1024 + 2 * static_cast<size_t>(gemm::kBN) * a.KP * 4 +
                       static_cast<size_t>(gemm::kStages) * 2 * gemm::kBM * gemm::kBK * 4 +
-                      static_cast<size_t>(gemm::kEpiWarps) * 32 * 33 * 4;
+                      static_cast<size_t>(gemm::kEpiWarps) * 32 * 36 * 4;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(gemm::linear_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
