@@ -328,7 +328,7 @@ def gpu_run(args):
         "sample": {"value": sample_rate, "unit": "samples/s", "batch": BATCH},
         "loss": float(loss_val),
     }
-    print(json.dumps(line))
+    _emit(line)
 
 
 def reference_run(args):
@@ -349,10 +349,32 @@ def reference_run(args):
         "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _emit(line)
+
+
+_JSON_FD = None
+
+
+def _guard_stdout():
+    """Keep stdout for the ONE JSON line: everything else written to fd 1 by libraries (NCCL prints its
+    version banner there) is routed to stderr."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    _guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
