@@ -25,6 +25,7 @@
 //                        epilogue of tile i overlap the MMAs of tile i+1
 // W (hi and lo, <= 2 x 64 KB) stays resident in shared memory for the CTA's lifetime.
 #include <cstdlib>
+#include <cuda.h>
 #include "common.cuh"
 #include "../../include/vcnf_b200.h"
 
@@ -463,6 +464,532 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tf32x3_kernel(const Args a
 
 
 // =================================================================================================
+// v2: weights resident in TENSOR MEMORY, activations streamed by cp.async.
+//
+// The contraction is evaluated transposed,  D^T[o, b] = sum_k W[o, k] * act(A[b, k]):
+//   UMMA "A" operand = W  (M = 128 output features), read from TMEM (tcgen05.mma [d], [a_tmem], b_desc):
+//                      hi plane in columns [0, 128), lo plane in [128, 256), written once per CTA with
+//                      tcgen05.st -- no shared memory is spent on the weights;
+//   UMMA "B" operand = activations, N = 64 batch rows per tile, K-major in shared memory;
+//   accumulators     = 2 buffers x (64 columns hi*hi + 64 columns cross terms) in columns [256, 512).
+// What this buys over v1 (W in smem, register-staged A):
+//   * all 221 KB of shared memory is the activation ring (12 stages of 64 rows x 32 k, hi + lo planes);
+//     producers issue 16 B cp.async copies 8 stages ahead (64 KB in flight per SM, no registers held),
+//     then convert their OWN chunks in place (ReLU, round-to-nearest TF32 hi, lo) -- per-thread
+//     cp.async.wait_group is the only synchronisation between copy and convert;
+//   * each MMA reads only the 2 KB activation operand from shared memory (v1: 8 KB per MMA);
+//   * the accumulator comes out feature-major: lane = output feature, register j = batch row j, so one
+//     warp instruction stores 32 consecutive floats of one output row -- coalesced without the
+//     shared-memory transpose, and the residual row segment is prefetched before the accumulator is
+//     even complete.
+// =================================================================================================
+namespace v2 {
+#ifdef VCNF_GEMM_TRACE
+__device__ long long g_trace[160][16];
+#define VTRACE(i) g_trace[blockIdx.x][i] = clock64()
+#else
+#define VTRACE(i)
+#endif
+constexpr int kProdWarps = 4, kEpiWarps = 8;
+constexpr int kThreads = (kProdWarps + kEpiWarps + 1) * 32;          // 416
+constexpr int kMmaWarp = kProdWarps + kEpiWarps;                     // 12
+constexpr int kProd = kProdWarps * 32;
+constexpr int kTN = 64;                    // batch rows per tile = UMMA N
+constexpr int kCK = 32;                    // fp32 per k-chunk = one ring stage
+// Stage plane = 64 rows x 128 B in the SWIZZLE_128B K-major UMMA layout: row r at r * 128, its 16 B chunk c
+// at ((c ^ (r & 7)) * 16); 8-row atoms of 1024 B (SBO).  (The no-swizzle "interleave" layout of v1 is
+// fetched at ~16 B/clk by the tensor core: measured 155 clk per M128 N64 K8 MMA against a 32 clk floor.)
+constexpr uint32_t kSbo = 1024;
+constexpr uint32_t kPlane = kTN * 128;                    // one hi (or lo) plane of a stage (8 KB)
+constexpr int kStages = 8;
+constexpr int kAhead = 6;                  // stages requested ahead of the one being converted
+constexpr int kChunksPerThread = (kTN * kCK / 4) / kProd;            // 16 B chunks per producer thread per stage (4)
+constexpr uint32_t kColWlo = 128, kColAcc = 256;
+constexpr int kEBufs = 3;
+constexpr uint32_t kETile = kTN * 128 * 4;                // one 64 x 128 fp32 epilogue tile (32 KB)
+constexpr size_t kSmemBytes = 1024 + static_cast<size_t>(kStages) * 2 * kPlane + kEBufs * kETile;
+
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 registers of this thread -> 32 consecutive TMEM columns of its lane
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// K-major SWIZZLE_128B operand: LBO unused (1), SBO = 8-row atom stride, layout_type 2 at bits 61-63; the
+// k-step inside the 128 B swizzle row is taken by advancing the start address (32 B per K = 8 tf32).
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+
+// One 64-row x 32-float box of A -> shared memory in the 128 B swizzled layout (rows / k beyond the tensor
+// read as zeros), completion in bytes on `bar`.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, uint32_t src) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(c0), "r"(c1), "r"(src)
+               : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t leader;
+  asm volatile("{.reg .b32 rx; .reg .pred px; elect.sync rx|px, 0xffffffff; selp.b32 %0, 1, 0, px;}" : "=r"(leader));
+  return leader != 0;
+}
+// One k-step (K = 8) of the split product: Wlo*Ahi and Whi*Alo into d_small, Whi*Ahi into d_main.
+// `acc` = 0 starts both accumulators (first k-step of a tile).
+#define VCNF_MMA_TS "tcgen05.mma.cta_group::1.kind::tf32 "
+__device__ __forceinline__ void mma_step(uint32_t d_main, uint32_t d_small, uint32_t w_hi, uint32_t w_lo, uint64_t b_hi,
+                                         uint64_t b_lo, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred pa, pt;\n\t"
+      "setp.ne.b32 pa, %7, 0;\n\t"
+      "setp.eq.b32 pt, %6, %6;\n\t"
+      VCNF_MMA_TS "[%1], [%3], %4, %6, pa;\n\t"
+      VCNF_MMA_TS "[%1], [%2], %5, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [%2], %4, %6, pa;\n\t"
+      "}\n" ::"r"(d_main), "r"(d_small), "r"(w_hi), "r"(w_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// A full 32-wide k-chunk: 4 k-steps x 3 products = 12 MMAs issued back to back (descriptor start address
+// advances 32 B = 2 units, the W columns by 8 per k-step).
+__device__ __forceinline__ void mma_stage4(uint32_t d_main, uint32_t d_small, uint32_t w_hi, uint32_t w_lo, uint64_t b_hi,
+                                           uint64_t b_lo, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred pa, pt;\n\t"
+      ".reg .b32 wh1, wl1, wh2, wl2, wh3, wl3;\n\t"
+      ".reg .b64 bh1, bl1, bh2, bl2, bh3, bl3;\n\t"
+      "setp.ne.b32 pa, %7, 0;\n\t"
+      "setp.eq.b32 pt, %6, %6;\n\t"
+      "add.u32 wh1, %2, 8;\n\t add.u32 wl1, %3, 8;\n\t add.u64 bh1, %4, 2;\n\t add.u64 bl1, %5, 2;\n\t"
+      "add.u32 wh2, %2, 16;\n\t add.u32 wl2, %3, 16;\n\t add.u64 bh2, %4, 4;\n\t add.u64 bl2, %5, 4;\n\t"
+      "add.u32 wh3, %2, 24;\n\t add.u32 wl3, %3, 24;\n\t add.u64 bh3, %4, 6;\n\t add.u64 bl3, %5, 6;\n\t"
+      VCNF_MMA_TS "[%1], [%3], %4, %6, pa;\n\t"
+      VCNF_MMA_TS "[%1], [%2], %5, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [%2], %4, %6, pa;\n\t"
+      VCNF_MMA_TS "[%1], [wl1], bh1, %6, pt;\n\t"
+      VCNF_MMA_TS "[%1], [wh1], bl1, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [wh1], bh1, %6, pt;\n\t"
+      VCNF_MMA_TS "[%1], [wl2], bh2, %6, pt;\n\t"
+      VCNF_MMA_TS "[%1], [wh2], bl2, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [wh2], bh2, %6, pt;\n\t"
+      VCNF_MMA_TS "[%1], [wl3], bh3, %6, pt;\n\t"
+      VCNF_MMA_TS "[%1], [wh3], bl3, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [wh3], bh3, %6, pt;\n\t"
+      "}\n" ::"r"(d_main), "r"(d_small), "r"(w_hi), "r"(w_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
+      : "memory");
+}
+
+struct Args2 {
+  const float* A; int64_t lda;
+  const float* W; int64_t sw_n, sw_k;
+  const float* bias;
+  const float* residual; int64_t ldr;
+  const float* mask; int64_t ldm;
+  float* C; int64_t ldc;
+  int64_t M; int N; int K;
+  int relu_in;
+  int n_tiles;        // ceil(N / 128) column slices
+  int ctas_per_ntile; // persistent CTAs sharing one column slice
+  int use_tma;        // A is 16 B aligned with a 16 B multiple row pitch: stages arrive by tensor-map TMA
+  int e_mode;         // elementwise operand staged by TMA: 0 none, 1 residual, 2 mask
+  int c_tma;          // output leaves by TMA tensor stores
+};
+
+__global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, const __grid_constant__ CUtensorMap tm_a,
+                                                                 const __grid_constant__ CUtensorMap tm_e,
+                                                                 const __grid_constant__ CUtensorMap tm_c) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  uint64_t* ready = reinterpret_cast<uint64_t*>(smem);           // [kStages] producers -> MMA (converted)
+  uint64_t* empty = ready + kStages;                             // [kStages] MMA -> producers
+  uint64_t* acc_full = empty + kStages;                          // [2] MMA -> epilogue
+  uint64_t* acc_empty = acc_full + 2;                            // [2] epilogue -> MMA
+  uint64_t* w_ready = acc_empty + 2;                             // [1] W planes written to TMEM
+  uint64_t* full = w_ready + 1;                                  // [kStages] TMA -> producers (raw fp32 landed)
+  uint64_t* e_full = full + kStages;                             // [kEBufs] epilogue tile ready (E landed / buffer free)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(e_full + kEBufs);
+  unsigned char* ring = smem + 1024;                             // stage s: [hi plane | lo plane]
+  unsigned char* ebuf = ring + kStages * 2 * kPlane;             // kEBufs epilogue tiles
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nt = blockIdx.x % a.n_tiles;
+  const int n0 = nt * 128;
+  const int NT = (a.N - n0) < 128 ? (a.N - n0) : 128;            // valid output features of this slice
+  const int64_t m_tiles = (a.M + kTN - 1) / kTN;
+  const int64_t mt0 = blockIdx.x / a.n_tiles;
+  const int nk = (a.K + kCK - 1) / kCK;                          // ring stages per tile
+  const int nk8 = (a.K + 7) >> 3;                                // 8-wide MMA steps that carry data
+  const int64_t my_tiles = mt0 < m_tiles ? (m_tiles - mt0 + a.ctas_per_ntile - 1) / a.ctas_per_ntile : 0;
+
+  if (tid == 0) {
+    VTRACE(0);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&ready[s], kProdWarps); mbar_init(&empty[s], 1); mbar_init(&full[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps); }
+    mbar_init(w_ready, kEpiWarps);
+    for (int b = 0; b < kEBufs; ++b) mbar_init(&e_full[b], 1);
+    mbar_init_fence();
+  }
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) VTRACE(1);
+
+  if (warp < kProdWarps) {
+    // ===================================== producers =====================================
+    // Stage g of this CTA's stream = (tile g / nk, k-chunk g % nk): 64 rows x 32 fp32.  Thread item i:
+    // 16 B chunk c = tid & 7 of row r = (tid >> 3) + 16 i -- 8 consecutive lanes read one 128 B line,
+    // and land in 8 different 16 B bank groups (128 B swizzle).
+    const int64_t G = my_tiles * nk;
+    if (a.use_tma) {
+      // The raw fp32 box lands by TMA in the swizzled layout (= the hi operand once rounded); the 128
+      // producer threads then make one elementwise pass over the 8 KB plane: ReLU, round-to-nearest TF32
+      // hi in place, lo into the second plane.  Layout-agnostic, so a linear 16 B / thread sweep.
+      auto issue_tma = [&](int64_t g) {                          // thread 0 only
+        if (g >= G) return;
+        const uint32_t it = static_cast<uint32_t>(g);
+        const int s = it % kStages;
+        mbar_wait(&empty[s], ((it / kStages) & 1u) ^ 1u);
+        mbar_expect_tx(&full[s], kPlane);
+        const int64_t m0 = (mt0 + (g / nk) * a.ctas_per_ntile) * kTN;
+        tma_load_2d(smem_u32(ring) + static_cast<uint32_t>(s) * 2 * kPlane, &tm_a, static_cast<int>(g % nk) * kCK,
+                    static_cast<int>(m0), &full[s]);
+      };
+      if (tid == 0) {
+        for (int g = 0; g < kAhead; ++g) issue_tma(g);
+        VTRACE(11);
+      }
+      for (int64_t g = 0; g < G; ++g) {
+        const uint32_t it = static_cast<uint32_t>(g);
+        const int s = it % kStages;
+        mbar_wait(&full[s], (it / kStages) & 1u);
+        unsigned char* hi_p = ring + static_cast<uint32_t>(s) * 2 * kPlane + tid * 16;
+#pragma unroll
+        for (int i = 0; i < kChunksPerThread; ++i) {
+          float4 v = *reinterpret_cast<const float4*>(hi_p + i * (kProd * 16));
+          if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+          float4 h, l;
+          split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
+          split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+          *reinterpret_cast<float4*>(hi_p + i * (kProd * 16)) = h;
+          *reinterpret_cast<float4*>(hi_p + kPlane + i * (kProd * 16)) = l;
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ready[s]);
+        if (tid == 0) {
+          if (g == 0) { VTRACE(3); }
+          issue_tma(g + kAhead);
+        }
+      }
+      if (tid == 0) { VTRACE(7); }
+    } else {
+    const bool vec_ok = (a.lda % 4 == 0) && (a.K % 4 == 0) && (reinterpret_cast<uintptr_t>(a.A) % 16 == 0);
+    const int c = tid & 7, r0 = tid >> 3;
+    const uint32_t ring_u32 = smem_u32(ring);
+    uint32_t off[kChunksPerThread];
+#pragma unroll
+    for (int i = 0; i < kChunksPerThread; ++i) {
+      const int r = r0 + 16 * i;
+      off[i] = static_cast<uint32_t>(r) * 128 + static_cast<uint32_t>((c ^ (r & 7)) << 4);
+    }
+    auto issue = [&](int64_t g) {
+      if (g < G) {
+        const uint32_t it = static_cast<uint32_t>(g);
+        const int s = it % kStages;
+        mbar_wait(&empty[s], ((it / kStages) & 1u) ^ 1u);
+        const int64_t m0 = (mt0 + (g / nk) * a.ctas_per_ntile) * kTN;
+        const int gk = static_cast<int>(g % nk) * kCK + c * 4;
+        const uint32_t base = static_cast<uint32_t>(s) * 2 * kPlane;
+#pragma unroll
+        for (int i = 0; i < kChunksPerThread; ++i) {
+          const int64_t gr = m0 + r0 + 16 * i;
+          const bool ok = gr < a.M && gk < a.K;
+          if (vec_ok) {
+            cp_async16(ring_u32 + base + off[i], ok ? a.A + gr * a.lda + gk : a.A, ok ? 16u : 0u);
+          } else {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok) {
+              const float* src = a.A + gr * a.lda + gk;
+              v.x = __ldg(src);
+              if (gk + 1 < a.K) v.y = __ldg(src + 1);
+              if (gk + 2 < a.K) v.z = __ldg(src + 2);
+              if (gk + 3 < a.K) v.w = __ldg(src + 3);
+            }
+            *reinterpret_cast<float4*>(ring + base + off[i]) = v;
+          }
+        }
+      }
+      cp_async_commit();                                         // one group per stage, empty past the end
+    };
+    for (int g = 0; g < kAhead; ++g) issue(g);
+    for (int64_t g = 0; g < G; ++g) {
+      cp_async_wait<kAhead - 1>();                               // this thread's copies of stage g have landed
+      const int s = static_cast<uint32_t>(g) % kStages;
+      unsigned char* hi_p = ring + static_cast<uint32_t>(s) * 2 * kPlane;
+#pragma unroll
+      for (int i = 0; i < kChunksPerThread; ++i) {
+        float4 v = *reinterpret_cast<const float4*>(hi_p + off[i]);
+        if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
+        split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        *reinterpret_cast<float4*>(hi_p + off[i]) = h;
+        *reinterpret_cast<float4*>(hi_p + kPlane + off[i]) = l;
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ready[s]);
+      if (tid == 0 && g == 0) VTRACE(3);
+      issue(g + kAhead);
+    }
+    cp_async_wait<0>();
+    if (tid == 0) { VTRACE(7); }
+    }
+  } else if (warp == kMmaWarp) {
+    // ===================================== MMA issuer =====================================
+    const uint32_t idesc = instr_desc_tf32(128, kTN);
+    mbar_wait(w_ready, 0);
+    tc_fence_after();
+    const uint32_t ring_u32 = smem_u32(ring);
+    uint32_t it = 0;
+    for (int64_t tc = 0; tc < my_tiles; ++tc) {
+      const uint32_t buf = static_cast<uint32_t>(tc) & 1u;
+      mbar_wait(&acc_empty[buf], ((static_cast<uint32_t>(tc) >> 1) & 1u) ^ 1u);
+      tc_fence_after();
+      const uint32_t d_main = tmem_base + kColAcc + buf * (2 * kTN);
+      const uint32_t d_small = d_main + kTN;
+      for (int kc = 0; kc < nk; ++kc, ++it) {
+        const int s = it % kStages;
+        mbar_wait(&ready[s], (it / kStages) & 1u);
+        tc_fence_after();
+        if (lane == 0 && it == 0) { VTRACE(4); }
+        // Everything up to the issue is computed by the WHOLE warp in convergent code, and the MMAs of a
+        // k-step go out back to back from one asm block: operands computed inside a divergent `if (lane == 0)`
+        // make the compiler wrap every UTCHMMA in an ELECT / R2UR.BROADCAST waterfall loop (measured 230
+        // clk per MMA against the 32 clk this shape needs, tools/mma_rate.cu).
+        const uint32_t w_hi_col = tmem_base + static_cast<uint32_t>(kc) * kCK;
+        const uint32_t w_lo_col = w_hi_col + kColWlo;
+        const uint64_t bd_hi = smem_desc_sw128(ring_u32 + static_cast<uint32_t>(s) * 2 * kPlane, kSbo);
+        const uint64_t bd_lo = smem_desc_sw128(ring_u32 + static_cast<uint32_t>(s) * 2 * kPlane + kPlane, kSbo);
+        const int steps = (nk8 - kc * 4) < 4 ? (nk8 - kc * 4) : 4;
+        const uint32_t acc0 = kc > 0 ? 1u : 0u;
+        const bool last = kc == nk - 1;
+        if (elect_one()) {
+          if (steps == 4) {
+            mma_stage4(d_main, d_small, w_hi_col, w_lo_col, bd_hi, bd_lo, idesc, acc0);
+          } else {
+            for (int kk = 0; kk < steps; ++kk)
+              mma_step(d_main, d_small, w_hi_col + kk * 8, w_lo_col + kk * 8, bd_hi + kk * 2, bd_lo + kk * 2, idesc,
+                       (kc > 0 || kk > 0) ? 1u : 0u);
+          }
+          tc_commit(&empty[s]);
+          if (last) tc_commit(&acc_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) VTRACE(8);
+  } else {
+    // ===================================== epilogue (8 warps) =====================================
+    // warp = (TMEM lane quarter q = warp % 4 -> output features n0 + 32 q + lane, half h -> batch rows
+    // 32 h .. 32 h + 31 of the tile).  First job: put this warp's share of W into tensor memory.
+    const int q = warp & 3, h = (warp - kProdWarps) >> 2;
+    const int o_loc = q * 32 + lane;
+    const bool o_ok = o_loc < NT;
+    const int o = n0 + o_loc;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    {
+      const float* wrow = a.W + static_cast<int64_t>(o_ok ? o : n0) * a.sw_n;
+      // 32 x 32 transpose tile per warp, xor-swizzled; aliases epilogue tile 2, which is first requested
+      // after every epilogue warp has passed the named barrier of tile 0
+      float* tb = reinterpret_cast<float*>(ebuf + 2 * kETile) + (warp - kProdWarps) * (32 * 32);
+      for (int cc = 0; cc < 2; ++cc) {
+        const int k0 = h * 64 + cc * 32;
+        if (k0 >= nk8 * 8) continue;                              // warp-uniform: columns no MMA reads
+        uint32_t whi[32], wlo[32];
+        float w[32];
+        if (a.sw_k == 1) {
+          // row-major W: a warp instruction reads 128 contiguous bytes of ONE row (lane = k), and the 32 x 32
+          // block is transposed through a padded smem tile so that lane = output feature afterwards.  (Per-lane
+          // row reads are 32 sectors per request; with all 148 CTAs hitting the same 64 KB at once they took
+          // 10 us of every launch.)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int oi = q * 32 + i, k = k0 + lane;
+            w[i] = (oi < NT && k < a.K) ? __ldg(a.W + static_cast<int64_t>(n0 + oi) * a.sw_n + k) : 0.f;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) tb[i * 32 + (lane ^ i)] = w[i];
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) w[j] = tb[lane * 32 + (j ^ lane)];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int k = k0 + j;
+            w[j] = (o_ok && k < a.K) ? __ldg(wrow + static_cast<int64_t>(k) * a.sw_k) : 0.f;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float hi, lo;
+          split_tf32(w[j], hi, lo);
+          whi[j] = __float_as_uint(hi);
+          wlo[j] = __float_as_uint(lo);
+        }
+        tmem_st32(lane_base + k0, whi);
+        tmem_st32(lane_base + kColWlo + k0, wlo);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(w_ready);
+      if (warp == kProdWarps && lane == 0) VTRACE(2);
+    }
+    const float bv = (a.bias && o_ok) ? __ldg(a.bias + o) : 0.f;
+    // Elementwise operand E (the residual, or the ReLU mask of the input-gradient call) and the output
+    // tile travel by TMA through three 64 x 128 fp32 tiles in shared memory: E for tile t+2 is requested
+    // while tile t is finished, the result overwrites E in place and leaves with one bulk tensor store.
+    // In-flight bytes live in shared memory, not in registers of 8 warps (the register version topped
+    // out at ~20 KB/us per SM: one memory latency per tile).  Operands whose pitch / alignment rules out
+    // a tensor map fall back to direct, still row-coalesced, accesses.
+    const bool staged = a.e_mode != 0 || a.c_tma != 0;
+    const bool elead = warp == kProdWarps && lane == 0;
+    const float* res_reg = (a.residual && a.e_mode != 1) ? a.residual : nullptr;
+    const float* mask_reg = (a.mask && a.e_mode != 2) ? a.mask : nullptr;
+    auto request_e = [&](int64_t t) {                              // elead only: arm e_full[t % 3]
+      if (t >= my_tiles) return;
+      uint64_t* bar = &e_full[t % kEBufs];
+      if (a.e_mode != 0) {
+        mbar_expect_tx(bar, kETile);
+        tma_load_2d(smem_u32(ebuf) + static_cast<uint32_t>(t % kEBufs) * kETile, &tm_e, n0,
+                    static_cast<int>((mt0 + t * a.ctas_per_ntile) * kTN), bar);
+      } else {
+        mbar_arrive(bar);                                          // buffer free, nothing to load
+      }
+    };
+    if (staged && elead) { request_e(0); request_e(1); }
+    for (int64_t tc = 0; tc < my_tiles; ++tc) {
+      const uint32_t buf = static_cast<uint32_t>(tc) & 1u;
+      const int64_t row0 = (mt0 + tc * a.ctas_per_ntile) * kTN + h * 32;
+      int rows = static_cast<int>(a.M - row0 < 32 ? a.M - row0 : 32);
+      if (rows < 0 || !o_ok) rows = 0;
+      float* et = reinterpret_cast<float*>(ebuf + static_cast<uint32_t>(tc % kEBufs) * kETile) + (h * 32) * 128 + o_loc;
+      float res[32];
+      if (res_reg) {                                              // independent of the MMAs: fetch early
+#pragma unroll
+        for (int j = 0; j < 32; ++j) res[j] = (j < rows) ? __ldg(res_reg + (row0 + j) * a.ldr + o) : 0.f;
+      }
+      mbar_wait(&acc_full[buf], (static_cast<uint32_t>(tc) >> 1) & 1u);
+      tc_fence_after();
+      if (warp == kProdWarps && lane == 0 && tc == 0) VTRACE(5);
+      uint32_t r[32], r2[32];
+      const uint32_t taddr = lane_base + kColAcc + buf * (2 * kTN) + h * 32;
+      tmem_ld32(taddr, r);
+      tmem_ld32(taddr + kTN, r2);
+      tmem_ld_wait();
+      tc_fence_before();                                          // values are in registers: hand the
+      __syncwarp();                                               // accumulator back before the stores
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      float acc[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]) + bv;
+      if (staged) mbar_wait(&e_full[tc % kEBufs], static_cast<uint32_t>(tc / kEBufs) & 1u);
+      if (a.e_mode == 2) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] = et[j * 128] > 0.f ? acc[j] : 0.f;
+      }
+      if (mask_reg) {
+        float mk[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) mk[j] = (j < rows) ? __ldg(mask_reg + (row0 + j) * a.ldm + o) : 1.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] = mk[j] > 0.f ? acc[j] : 0.f;
+      }
+      if (a.e_mode == 1) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] += et[j * 128];
+      }
+      if (res_reg) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] += res[j];
+      }
+      if (a.c_tma) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) et[j * 128] = acc[j];        // lane = column: conflict-free rows
+        fence_async_smem();
+      } else {
+        float* cp = a.C + row0 * a.ldc + o;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < rows) cp[j * a.ldc] = acc[j];                   // one 128 B row segment per warp instruction
+      }
+      if (staged) {
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");   // tile complete / E consumed by all 8 warps
+        if (elead) {
+          if (a.c_tma) {
+            tma_store_2d(&tm_c, n0, static_cast<int>((mt0 + tc * a.ctas_per_ntile) * kTN),
+                         smem_u32(ebuf) + static_cast<uint32_t>(tc % kEBufs) * kETile);
+            bulk_commit();
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // store of tile tc-1 has left its buffer
+          }
+          request_e(tc + 2);                                      // (tc + 2) % 3 == (tc - 1) % 3
+        }
+      }
+      if (warp == kProdWarps && lane == 0 && tc == 0) VTRACE(6);
+    }
+    if (elead && a.c_tma) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (warp == kProdWarps && lane == 0) VTRACE(9);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+  if (tid == 0) VTRACE(10);
+}
+}  // namespace v2
+
+// =================================================================================================
 // Weight gradient:  gW[o, i] = sum_b gY[b, o] * act(X[b, i]),   gb[o] = sum_b gY[b, o]
 // (autograd of F.linear in the conditioners: the cuBLAS "nt" sgemm + the bias-gradient reduce_kernel,
 // 25 ms of the first measured 60 ms training step of cfg 2).
@@ -701,6 +1228,19 @@ __global__ void wgrad_reduce_kernel(const float* partial, int splits, int rows_p
 
 using namespace vcnf;
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// cuTensorMapEncodeTiled through the runtime's driver entry point (the library does not link libcuda).
+static EncodeTiledFn tensor_map_encoder() {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  return reinterpret_cast<EncodeTiledFn>(fn);
+}
+
 extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int64_t sw_n, int64_t sw_k,
                                   const void* bias, const void* residual, int64_t ldr, const void* mask,
                                   int64_t ldm, void* C, int64_t ldc, int64_t M, int N, int K, int relu_in,
@@ -710,6 +1250,51 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
   if (K > gemm::kMaxK) return VCNF_E_UNSUPPORTED;
   const int sms = sm_count();
   if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
+  static const bool use_v1 = [] { const char* e = getenv("VCNF_GEMM_V1"); return e && atoi(e) != 0; }();
+  if (!use_v1) {
+    gemm::v2::Args2 b{};
+    b.A = static_cast<const float*>(A); b.lda = lda;
+    b.W = static_cast<const float*>(W); b.sw_n = sw_n; b.sw_k = sw_k;
+    b.bias = static_cast<const float*>(bias);
+    b.residual = static_cast<const float*>(residual); b.ldr = ldr;
+    b.mask = static_cast<const float*>(mask); b.ldm = ldm;
+    b.C = static_cast<float*>(C); b.ldc = ldc;
+    b.M = M; b.N = N; b.K = K; b.relu_in = relu_in;
+    b.n_tiles = (N + 127) / 128;
+    const int64_t m_tiles2 = (M + gemm::v2::kTN - 1) / gemm::v2::kTN;
+    int cpt2 = sms / b.n_tiles;
+    if (cpt2 < 1) cpt2 = 1;
+    if (cpt2 > m_tiles2) cpt2 = static_cast<int>(m_tiles2);
+    b.ctas_per_ntile = cpt2;
+    CUtensorMap tm{}, tm_e{}, tm_c{};
+    b.use_tma = b.e_mode = b.c_tma = 0;
+    static EncodeTiledFn encode = tensor_map_encoder();
+    // 2-D fp32 view [rows, cols] of pitch ld; eligible when 16 B aligned with a 16 B multiple pitch
+    auto make_map = [&](CUtensorMap* out, const void* ptr, int64_t cols, int64_t ld, uint32_t box_c, uint32_t box_r,
+                        CUtensorMapSwizzle swz) {
+      if (!encode || !ptr || ld % 4 != 0 || reinterpret_cast<uintptr_t>(ptr) % 16 != 0 || M >= (1ll << 31)) return false;
+      const cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(M)};
+      const cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 4};
+      const cuuint32_t box[2] = {box_c, box_r};
+      const cuuint32_t estr[2] = {1, 1};
+      return encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    };
+    if (make_map(&tm, A, K, lda, gemm::v2::kCK, gemm::v2::kTN, CU_TENSOR_MAP_SWIZZLE_128B)) b.use_tma = 1;
+    if (mask && make_map(&tm_e, mask, N, ldm, 128, gemm::v2::kTN, CU_TENSOR_MAP_SWIZZLE_NONE)) b.e_mode = 2;
+    else if (residual && make_map(&tm_e, residual, N, ldr, 128, gemm::v2::kTN, CU_TENSOR_MAP_SWIZZLE_NONE)) b.e_mode = 1;
+    if (make_map(&tm_c, C, N, ldc, 128, gemm::v2::kTN, CU_TENSOR_MAP_SWIZZLE_NONE)) b.c_tma = 1;
+    static bool attr2 = false;
+    if (!attr2) {
+      cudaFuncSetAttribute(gemm::v2::linear_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(gemm::v2::kSmemBytes));
+      attr2 = true;
+    }
+    gemm::v2::linear_ts_kernel<<<static_cast<unsigned>(b.n_tiles * cpt2), gemm::v2::kThreads, gemm::v2::kSmemBytes,
+                                 static_cast<cudaStream_t>(stream)>>>(b, tm, tm_e, tm_c);
+    return launch_status();
+  }
   gemm::Args a{};
   a.A = static_cast<const float*>(A); a.lda = lda;
   a.W = static_cast<const float*>(W); a.sw_n = sw_n; a.sw_k = sw_k;
