@@ -1009,6 +1009,37 @@ constexpr int kWStages = 3;
 constexpr int kWBK = 32;             // samples per stage (4 MMA k-steps of 8)
 constexpr uint32_t kWSbo = 1024 + 16;
 
+// One 32-sample stage of the split product with BOTH operands in shared memory (no-swizzle K-major, 256 B per
+// k-step): 4 k-steps x {lo*hi, hi*lo -> d_small; hi*hi -> d_main}, issued back to back by the elected lane of a
+// CONVERGENT warp (see v2::mma_stage4 for why).
+__device__ __forceinline__ void mma_stage4_ss(uint32_t d_main, uint32_t d_small, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi,
+                                              uint64_t b_lo, uint32_t idesc, uint32_t acc) {
+#define VCNF_MMA_SS "tcgen05.mma.cta_group::1.kind::tf32 "
+  asm volatile(
+      "{\n\t"
+      ".reg .pred pa, pt;\n\t"
+      ".reg .b64 ah1, al1, bh1, bl1, ah2, al2, bh2, bl2, ah3, al3, bh3, bl3;\n\t"
+      "setp.ne.b32 pa, %7, 0;\n\t"
+      "setp.eq.b32 pt, %6, %6;\n\t"
+      "add.u64 ah1, %2, 16;\n\t add.u64 al1, %3, 16;\n\t add.u64 bh1, %4, 16;\n\t add.u64 bl1, %5, 16;\n\t"
+      "add.u64 ah2, %2, 32;\n\t add.u64 al2, %3, 32;\n\t add.u64 bh2, %4, 32;\n\t add.u64 bl2, %5, 32;\n\t"
+      "add.u64 ah3, %2, 48;\n\t add.u64 al3, %3, 48;\n\t add.u64 bh3, %4, 48;\n\t add.u64 bl3, %5, 48;\n\t"
+      VCNF_MMA_SS "[%1], %3, %4, %6, pa;\n\t"
+      VCNF_MMA_SS "[%1], %2, %5, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], %2, %4, %6, pa;\n\t"
+      VCNF_MMA_SS "[%1], al1, bh1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], ah1, bl1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], ah1, bh1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], al2, bh2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], ah2, bl2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], ah2, bh2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], al3, bh3, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], ah3, bl3, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], ah3, bh3, %6, pt;\n\t"
+      "}\n" ::"r"(d_main), "r"(d_small), "l"(a_hi), "l"(a_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
+      : "memory");
+}
+
 struct WArgs {
   const float* gY; int64_t ldg;      // [B, N]
   const float* X; int64_t ldx;       // [B, K]
@@ -1157,34 +1188,30 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const 
       const int s = it % kWStages;
       mbar_wait(&full[s], (it / kWStages) & 1u);
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t a_hi = smem_u32(st0 + static_cast<uint32_t>(s) * stage_bytes);
-        const uint32_t a_lo = a_hi + a_half;
-        const uint32_t b_hi = a_hi + 2 * a_half;
-        const uint32_t b_lo = b_hi + b_half;
-#pragma unroll
-        for (int combo = 0; combo < 3; ++combo) {
-          const uint32_t ab = combo == 0 ? a_lo : a_hi;
-          const uint32_t bb = combo == 1 ? b_lo : b_hi;
-#pragma unroll
-          for (int kk = 0; kk < kWBK / 8; ++kk) {
-            const uint64_t ad = smem_desc(ab + kk * 256, 128, kWSbo);
-            const uint64_t bd = smem_desc(bb + kk * 256, 128, kWSbo);
-            if (combo == 2) mma_tf32(d_main, ad, bd, idesc, (i > 0 || kk > 0) ? 1u : 0u);
-            else mma_tf32(d_small, ad, bd, idesc, (i > 0 || combo > 0 || kk > 0) ? 1u : 0u);
-          }
-        }
+      const uint32_t a_hi = smem_u32(st0 + static_cast<uint32_t>(s) * stage_bytes);
+      const uint32_t a_lo = a_hi + a_half;
+      const uint32_t b_hi = a_hi + 2 * a_half;
+      const uint32_t b_lo = b_hi + b_half;
+      const uint64_t ad_hi = smem_desc(a_hi, 128, kWSbo), ad_lo = smem_desc(a_lo, 128, kWSbo);
+      const uint64_t bd_hi = smem_desc(b_hi, 128, kWSbo), bd_lo = smem_desc(b_lo, 128, kWSbo);
+      const uint32_t acc0 = i > 0 ? 1u : 0u;
+      const bool last = i == G - 1;
+      if (v2::elect_one()) {
+        mma_stage4_ss(d_main, d_small, ad_hi, ad_lo, bd_hi, bd_lo, idesc, acc0);
         tc_commit(&empty[s]);
-        if (i == G - 1) tc_commit(acc_full);
+        if (last) tc_commit(acc_full);
       }
       __syncwarp();
     }
   } else {
     // ------------------------------ epilogue: one partial [128, K + 1] per CTA
+    // TMEM hands every lane one ROW of the partial; each 32 x 32 block is transposed through a padded tile
+    // in the (now idle) stage memory so that a warp instruction writes 128 contiguous bytes of one row
+    // (lane = row stores were 32 sectors per request: 78 MB of L2 write traffic for a 9.8 MB partial).
     const int q = warp & 3;
-    const int row = q * 32 + lane;
     const int W1 = a.K + 1;
-    float* dst = a.partial + (static_cast<int64_t>(split) * a.o_tiles * 128 + o0 + row) * W1;
+    float* dst = a.partial + (static_cast<int64_t>(split) * a.o_tiles * 128 + o0 + q * 32) * W1;
+    float* tb = reinterpret_cast<float*>(st0) + (warp - kLoaderWarps) * (32 * 33);
     if (G > 0) {
       mbar_wait(acc_full, 0);
       tc_fence_after();
@@ -1197,10 +1224,14 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const 
         tmem_ld32(taddr + 256, r2);
         tmem_ld_wait();
       }
+      __syncwarp();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int col = cb * 32 + j;
-        if (col < W1) dst[col] = G > 0 ? __uint_as_float(r[j]) + __uint_as_float(r2[j]) : 0.f;
+      for (int j = 0; j < 32; ++j) tb[lane * 33 + j] = G > 0 ? __uint_as_float(r[j]) + __uint_as_float(r2[j]) : 0.f;
+      __syncwarp();
+      const int col = cb * 32 + lane;
+      if (col < W1) {
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) dst[static_cast<int64_t>(i) * W1 + col] = tb[i * 33 + lane];
       }
     }
   }
@@ -1209,17 +1240,37 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const 
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
 }
 
-// gW[o, i] = sum_s partial[s][o][i], gb[o] = sum_s partial[s][o][K]   (fixed order)
-__global__ void wgrad_reduce_kernel(const float* partial, int splits, int rows_pad, int N, int K, float* gW, float* gb) {
+// Sum of the split-K partials in a FIXED order (bit-reproducible): 8 warps of a block share 32 output
+// elements, warp g adds splits g, g + 8, ... (independent loads, unrolled), then the 8 sub-sums are added
+// in order 0..7.  (One thread per element walked 148 dependent L2 round trips: 10 us per call.)
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* partial, int splits, int rows_pad, int N, int K,
+                                                           float* gW, float* gb) {
+  __shared__ float sub[8][33];
   const int W1 = K + 1;
   const int64_t total = static_cast<int64_t>(N) * W1;
-  for (int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; e < total;
-       e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int o = static_cast<int>(e / W1), i = static_cast<int>(e - static_cast<int64_t>(o) * W1);
+  const int ex = threadIdx.x & 31, g = threadIdx.x >> 5;
+  for (int64_t base = static_cast<int64_t>(blockIdx.x) * 32; base < total; base += static_cast<int64_t>(gridDim.x) * 32) {
+    const int64_t e = base + ex;
     float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += partial[(static_cast<int64_t>(s) * rows_pad + o) * W1 + i];
-    if (i < K) gW[static_cast<int64_t>(o) * K + i] = acc;
-    else if (gb) gb[o] = acc;
+    int o = 0, i = 0;
+    if (e < total) {
+      o = static_cast<int>(e / W1);
+      i = static_cast<int>(e - static_cast<int64_t>(o) * W1);
+      const float* p = partial + static_cast<int64_t>(o) * W1 + i;
+      const int64_t stride = static_cast<int64_t>(rows_pad) * W1;
+#pragma unroll 8
+      for (int s = g; s < splits; s += 8) acc += p[s * stride];
+    }
+    sub[g][ex] = acc;
+    __syncthreads();
+    if (g == 0 && e < total) {
+      float t = sub[0][ex];
+#pragma unroll
+      for (int k = 1; k < 8; ++k) t += sub[k][ex];
+      if (i < K) gW[static_cast<int64_t>(o) * K + i] = t;
+      else if (gb) gb[o] = t;
+    }
+    __syncthreads();
   }
 }
 
@@ -1371,7 +1422,7 @@ extern "C" int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void*
   int rc = launch_status();
   if (rc) return rc;
   const int64_t total = static_cast<int64_t>(N) * (K + 1);
-  int grid = static_cast<int>((total + 255) / 256);
+  int grid = static_cast<int>((total + 31) / 32);
   if (grid > 1184) grid = 1184;
   gemm::wgrad_reduce_kernel<<<grid, 256, 0, st>>>(a.partial, a.splits, a.o_tiles * 128, N, K, static_cast<float*>(gW),
                                                    static_cast<float*>(gb));

@@ -46,6 +46,8 @@ struct RqsLayerArgs {
   int8_t* bin_out; int32_t* err_flag;
   int R; int64_t num_tiles;
   int bulk_p, bulk_x, bulk_gy, bulk_gp;   // base pointer + leading dimension allow 1-D bulk copies
+  int prow, grow;   // row pitch (elements) of the staged parameter / parameter-gradient tiles: Tc*Pc, or the
+                    // caller's padded leading dimension (a 16 B multiple pitch keeps rows TMA-copyable)
   // backward only
   const T* gy; int64_t ldgy; const T* gld;
   T* gx; int64_t ldgx;
@@ -61,18 +63,19 @@ struct RqsSmem {
   size_t bars, pst, pst_stride, xst, xst_stride, gyst, outs, lads, gst, tab, acc, tabg, meta, total;
 };
 template <typename T>
-__host__ __device__ inline RqsSmem rqs_smem_layout(int R, int D, int Tc, int Pc, int Ts, int K, bool bwd, int nthreads) {
+__host__ __device__ inline RqsSmem rqs_smem_layout(int R, int D, int Tc, int Pc, int Ts, int K, bool bwd, int nthreads,
+                                                   int prow, int grow) {
   RqsSmem m;
   size_t o = 0;
   m.bars = o; o += 128;
-  m.pst_stride = round_up(static_cast<size_t>(R) * Tc * Pc * sizeof(T), 128);
+  m.pst_stride = round_up(static_cast<size_t>(R) * prow * sizeof(T), 128);
   m.pst = o; o += 2 * m.pst_stride;
   m.xst_stride = round_up(static_cast<size_t>(R) * D * sizeof(T), 128);
   m.xst = o; o += 2 * m.xst_stride;
   m.gyst = o; if (bwd) o += 2 * m.xst_stride;
   m.outs = o; o += m.xst_stride;                       // y tile (fwd) / gx tile (bwd)
   m.lads = o; if (!bwd) o += m.xst_stride;             // per-element log-det terms (fwd)
-  m.gst = o; if (bwd) o += m.pst_stride;               // conditional parameter gradients (bwd)
+  m.gst = o; if (bwd) o += round_up(static_cast<size_t>(R) * grow * sizeof(T), 128);   // conditional parameter gradients (bwd)
   const size_t TK = 3 * (static_cast<size_t>(K) + 1);
   m.tab = o; o += round_up(Ts * TK * sizeof(T), 128);
   m.acc = o; if (bwd && Ts > 0) o += round_up(static_cast<size_t>(nthreads / Ts) * Ts * TK * sizeof(T), 128);
@@ -144,7 +147,7 @@ __device__ __forceinline__ void stage_issue(const RqsLayerArgs<T>& a, int64_t t,
                                             uint64_t* bar) {
   if (threadIdx.x != 0) return;
   const int64_t rows = imin64(a.R, a.B - t * a.R);
-  const int64_t np = rows * a.Tc * a.Pc, nx = rows * a.D;
+  const int64_t np = rows * a.prow, nx = rows * a.D;
   const bool bp = a.Tc > 0 && span_bulk<T>(a.bulk_p, np);
   const bool bx = span_bulk<T>(a.bulk_x, nx);
   const bool bg = BWD && span_bulk<T>(a.bulk_gy, nx);
@@ -162,15 +165,15 @@ __device__ __forceinline__ bool stage_wait(const RqsLayerArgs<T>& a, int64_t t, 
                                            uint64_t* bar, uint32_t parity) {
   const int64_t row0 = t * a.R;
   const int64_t rows = imin64(a.R, a.B - row0);
-  const int64_t np = rows * a.Tc * a.Pc, nx = rows * a.D;
+  const int64_t np = rows * a.prow, nx = rows * a.D;
   const bool bp = a.Tc > 0 && span_bulk<T>(a.bulk_p, np);
   const bool bx = span_bulk<T>(a.bulk_x, nx);
   const bool bg = BWD && span_bulk<T>(a.bulk_gy, nx);
   if (a.Tc > 0 && !bp) {
     const int n = a.Tc * a.Pc;
-    for (int64_t e = threadIdx.x; e < np; e += blockDim.x) {
+    for (int64_t e = threadIdx.x; e < rows * n; e += blockDim.x) {
       const int64_t r = e / n;
-      pst[e] = a.cond[(row0 + r) * a.ld_cond + (e - r * n)];
+      pst[r * a.prow + (e - r * n)] = a.cond[(row0 + r) * a.ld_cond + (e - r * n)];
     }
   }
   if (!bx) {
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_kernel(const RqsLayerA
   __shared__ int n_other_s;
   const int K = EXACT ? KMAX : a.K;
   const int TK = 3 * (K + 1);
-  const RqsSmem L = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, K, false, kThreads);
+  const RqsSmem L = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, K, false, kThreads, a.prow, a.grow);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
   T* ys = reinterpret_cast<T*>(smem + L.outs);
   T* lads = reinterpret_cast<T*>(smem + L.lads);
@@ -238,7 +241,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_kernel(const RqsLayerA
       RqsElemCfg cfg{K, M.cmode[j], a.inverse, a.outside_zero};
       T out, lad;
       int bin;
-      rqs_element<T, KMAX>(cur + static_cast<size_t>(e) * Pc, v, M.cbound[j], a.wh_scale, cfg, &out, &lad, &bin, &flag);
+      rqs_element<T, KMAX>(cur + static_cast<size_t>(r) * a.prow + j * Pc, v, M.cbound[j], a.wh_scale, cfg, &out, &lad, &bin, &flag);
       ys[r * D + c] = out;
       lads[r * D + c] = lad;
       if (a.bin_out) a.bin_out[(row0 + r) * D + c] = static_cast<int8_t>(bin);
@@ -301,7 +304,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerA
   __shared__ int n_other_s;
   const int K = EXACT ? KMAX : a.K;
   const int TK = 3 * (K + 1);
-  const RqsSmem L = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, K, true, kThreads);
+  const RqsSmem L = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, K, true, kThreads, a.prow, a.grow);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
   T* gxs = reinterpret_cast<T*>(smem + L.outs);
   T* gst = reinterpret_cast<T*>(smem + L.gst);
@@ -347,8 +350,8 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerA
       const int c = M.cond_col[j];
       RqsElemCfg cfg{K, M.cmode[j], a.inverse, a.outside_zero};
       T gv;
-      rqs_element_bwd<T, KMAX>(cur + static_cast<size_t>(e) * Pc, xs[r * D + c], M.cbound[j], a.wh_scale, cfg,
-                               gys[r * D + c], a.gld[row0 + r], &gv, gst + static_cast<size_t>(e) * Pc);
+      rqs_element_bwd<T, KMAX>(cur + static_cast<size_t>(r) * a.prow + j * Pc, xs[r * D + c], M.cbound[j], a.wh_scale, cfg,
+                               gys[r * D + c], a.gld[row0 + r], &gv, gst + static_cast<size_t>(r) * a.grow + j * Pc);
       gxs[r * D + c] = gv;
     }
     // pass B1: pass-through columns;  pass B2: batch-shared columns, thread <-> feature fixed so that
@@ -381,7 +384,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerA
         }
       }
     }
-    const int64_t np = static_cast<int64_t>(rows) * Tc * Pc;
+    const int64_t np = static_cast<int64_t>(rows) * a.grow;
     const bool bulk_store = Tc > 0 && span_bulk<T>(a.bulk_gp, np);
     if (bulk_store) fence_async_smem();
     __syncthreads();
@@ -406,9 +409,9 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerA
         }
       } else {
         const int n = Tc * Pc;
-        for (int64_t e = tid; e < np; e += kThreads) {
+        for (int64_t e = tid; e < static_cast<int64_t>(rows) * n; e += kThreads) {
           const int64_t r = e / n;
-          a.gcond[(row0 + r) * a.ld_gcond + (e - r * n)] = gst[e];
+          a.gcond[(row0 + r) * a.ld_gcond + (e - r * n)] = gst[r * a.grow + (e - r * n)];
         }
       }
     }
@@ -481,8 +484,8 @@ constexpr int kMaxBwdGrid = 148 * 2;
 
 // Rows per tile: a multiple of 4 (keeps every tile start 16 B aligned for the bulk copies) whose
 // parameter block fits the per-stage budget and whose rows*Tc fills whole passes of kThreads best.
-static int pick_rows(int Tc, int Pc, int D, size_t elt) {
-  const size_t per_row = static_cast<size_t>(Tc > 0 ? Tc * Pc : D) * elt;
+static int pick_rows(int Tc, int prow, int D, size_t elt) {
+  const size_t per_row = static_cast<size_t>(Tc > 0 ? prow : D) * elt;
   const size_t budget = 24 * 1024;
   int rmax = static_cast<int>(budget / per_row) / 4 * 4;
   if (rmax > 64) rmax = 64;
@@ -498,25 +501,37 @@ static int pick_rows(int Tc, int Pc, int D, size_t elt) {
   return best;
 }
 
+// Staged row pitch: the natural Tc*Pc, or the caller's leading dimension when that is a slightly padded
+// one (e.g. 324 for 322 = 14 x 23 parameters: the pad makes the pitch a 16 B multiple, which is what
+// lets the producing GEMM store and this kernel load whole tiles with the TMA engine).
+template <typename T>
+static void set_pitches(RqsLayerArgs<T>& a, bool bwd) {
+  const int64_t n = static_cast<int64_t>(a.Tc) * a.Pc;
+  a.prow = static_cast<int>((a.ld_cond > n && a.ld_cond - n < 16) ? a.ld_cond : n);
+  a.grow = static_cast<int>((bwd && a.ld_gcond > n && a.ld_gcond - n < 16) ? a.ld_gcond : n);
+}
+
 template <typename T>
 static void set_bulk_flags(RqsLayerArgs<T>& a, bool bwd) {
   auto al16 = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
-  const size_t prow = static_cast<size_t>(a.R) * a.Tc * a.Pc * sizeof(T);
+  const size_t prow = static_cast<size_t>(a.R) * a.prow * sizeof(T);
+  const size_t grow = static_cast<size_t>(a.R) * a.grow * sizeof(T);
   const size_t xrow = static_cast<size_t>(a.R) * a.D * sizeof(T);
-  a.bulk_p = a.Tc > 0 && a.ld_cond == static_cast<int64_t>(a.Tc) * a.Pc && prow % 16 == 0 && al16(a.cond);
+  a.bulk_p = a.Tc > 0 && a.ld_cond == a.prow && prow % 16 == 0 && al16(a.cond);
   a.bulk_x = a.ldx == a.D && xrow % 16 == 0 && al16(a.x);
   a.bulk_gy = bwd && a.ldgy == a.D && xrow % 16 == 0 && al16(a.gy);
-  a.bulk_gp = bwd && a.Tc > 0 && a.ld_gcond == static_cast<int64_t>(a.Tc) * a.Pc && prow % 16 == 0 && al16(a.gcond);
+  a.bulk_gp = bwd && a.Tc > 0 && a.ld_gcond == a.grow && grow % 16 == 0 && al16(a.gcond);
 }
 
 template <typename T, int KMAX, bool EXACT>
 static int launch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
   const int sms = sm_count();
   if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
-  a.R = pick_rows(a.Tc, a.Pc, a.D, sizeof(T));
+  set_pitches(a, false);
+  a.R = pick_rows(a.Tc, a.prow > a.grow ? a.prow : a.grow, a.D, sizeof(T));
   a.num_tiles = (a.B + a.R - 1) / a.R;
   set_bulk_flags(a, false);
-  const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, false, kThreads).total;
+  const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, false, kThreads, a.prow, a.grow).total;
   if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
   auto kern = rqs_layer_fwd_kernel<T, KMAX, EXACT>;
   static bool attr_set = false;     // once per instantiation (not a stream operation: keep it out of graph capture)
@@ -536,10 +551,11 @@ static int launch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
   const int sms = sm_count();
   if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
   if (a.Ts > kThreads) return VCNF_E_UNSUPPORTED;
-  a.R = pick_rows(a.Tc, a.Pc, a.D, sizeof(T));
+  set_pitches(a, true);
+  a.R = pick_rows(a.Tc, a.prow > a.grow ? a.prow : a.grow, a.D, sizeof(T));
   a.num_tiles = (a.B + a.R - 1) / a.R;
   set_bulk_flags(a, true);
-  const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, true, kThreads).total;
+  const size_t smem = rqs_smem_layout<T>(a.R, a.D, a.Tc, a.Pc, a.Ts, a.K, true, kThreads, a.prow, a.grow).total;
   if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
   auto kern = rqs_layer_bwd_kernel<T, KMAX, EXACT>;
   static bool attr_set = false;

@@ -120,6 +120,11 @@ class Coupling(Flow):
             self.unconditional_transform = None
         else:
             self.unconditional_transform = unconditional_transform(features=self.num_identity_features)
+        # The library's own conditioner takes / returns rows with a padded (16-byte multiple) pitch, which
+        # keeps every tile of the layer TMA-movable; any other user-supplied net sees plain contiguous tensors.
+        self._pad_rows = bool(getattr(self.transform_net, "accepts_padded_rows", False))
+        if self._pad_rows and hasattr(self.transform_net, "padded_out"):
+            self.transform_net.padded_out = True
 
     @property
     def num_identity_features(self):
@@ -229,7 +234,7 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         self._check(inputs)
         if self._specs is None:
             self._build_specs()
-        identity_split = ops.gather_cols(inputs, self._cols(inputs.device))
+        identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
         params = self.transform_net(identity_split, context)
         shared = self.unconditional_transform.packed_params() if self.unconditional_transform is not None else None
         return ops.rqs_layer(inputs, params, shared, self._specs["both"], False, want_bins)
@@ -242,7 +247,7 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         if self.unconditional_transform is not None:
             inputs, logabsdet = ops.rqs_layer(inputs, None, self.unconditional_transform.packed_params(),
                                               self._specs["shared"], True)
-        identity_split = ops.gather_cols(inputs, self._cols(inputs.device))
+        identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
         params = self.transform_net(identity_split, context)
         outputs, logabsdet_split = ops.rqs_layer(inputs, params, None, self._specs["cond"], True)
         return outputs, logabsdet + logabsdet_split

@@ -63,6 +63,12 @@ class ResidualNet(nn.Module):
                           dropout_probability=dropout_probability, use_batch_norm=use_batch_norm)
             for _ in range(num_blocks)])
         self.final_layer = nn.Linear(hidden_features, out_features)
+        # Set by the spline coupling layer that owns this net: its kernels take a leading dimension, so
+        # the (3K-1)*T wide output may be a view with a 16-byte-multiple row pitch (TMA-movable tiles).
+        # Stand-alone the net returns a contiguous tensor like the reference's.
+        self.padded_out = False
+
+    accepts_padded_rows = True   # inputs may be [B, n] views of wider storage (unit column stride)
 
     def forward(self, inputs, context=None):
         h = inputs if self.preprocessing is None else self.preprocessing(inputs)
@@ -72,5 +78,5 @@ class ResidualNet(nn.Module):
         for block in self.blocks:
             h = block(h, context=context)
         if fast:
-            return ops.linear(h, self.final_layer.weight, self.final_layer.bias)
+            return ops.linear(h, self.final_layer.weight, self.final_layer.bias, pad_out=self.padded_out)
         return self.final_layer(h)

@@ -33,6 +33,22 @@ def _promote(*tensors):
     return tuple(t if t is None or t.dtype == dt else t.to(dt) for t in tensors)
 
 
+def _padded_empty(rows, cols, dtype, device):
+    """[rows, cols] tensor whose row pitch is a multiple of 16 bytes (a view of wider storage when
+    `cols` is not): what the TMA engine needs to move row tiles (tensor-map loads / stores in the
+    GEMM, bulk tile copies in the spline kernels).  The pad columns are never read."""
+    q = 16 // torch.empty((), dtype=dtype).element_size()
+    pad = (cols + q - 1) // q * q
+    if pad == cols:
+        return torch.empty((rows, cols), dtype=dtype, device=device)
+    return torch.empty((rows, pad), dtype=dtype, device=device)[:, :cols]
+
+
+def _rows(t):
+    """Row-major 2-D operand with unit column stride (any row pitch); copies only if it is not."""
+    return t if (t.dim() == 2 and t.stride(1) == 1 and t.stride(0) >= t.shape[1]) else t.contiguous()
+
+
 def _zeros_if_none(g, like_shape, ref):
     return torch.zeros(like_shape, dtype=ref.dtype, device=ref.device) if g is None else g.contiguous()
 
@@ -72,13 +88,13 @@ class _RqsLayer(torch.autograd.Function):
         if D != spec.D:
             raise ValueError("Expected features = {}, got {}.".format(spec.D, D))
         cmap, cm, cb, sm, sb = spec.on(x.device, x.dtype)
-        cond = cond.contiguous() if cond is not None else None
+        cond = _rows(cond) if cond is not None else None
         shared = shared.contiguous() if shared is not None else None
         y = torch.empty_like(x)
         logdet = torch.empty(B, dtype=x.dtype, device=x.device)
         bins = torch.empty((B, D), dtype=torch.int8, device=x.device) if want_bins else None
         _launch("vcnf_rqs_layer_fwd", ptr(x), D, ptr(y), D, ptr(logdet), 0, B, D, spec.K, ptr(cmap),
-                ptr(cond), spec.Tc * spec.Pc, spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale,
+                ptr(cond), cond.stride(0) if cond is not None else 0, spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale,
                 ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb), int(inverse), spec.outside_zero,
                 ptr(bins), None, dtype_code(x), stream())
         ctx.spec, ctx.inverse = spec, int(inverse)
@@ -98,15 +114,18 @@ class _RqsLayer(torch.autograd.Function):
         gy = _zeros_if_none(gy, x.shape, x)
         gld = _zeros_if_none(gld, (B,), x)
         gx = torch.empty_like(x)
-        gcond = torch.empty_like(cond) if cond is not None else None
+        gcond = None
+        if cond is not None:   # gradient in the layout the parameters came in (padded pitch stays padded)
+            gcond = (_padded_empty(*cond.shape, cond.dtype, cond.device) if cond.stride(0) != cond.shape[1]
+                     else torch.empty_like(cond))
         gshared = torch.empty_like(shared) if shared is not None else None
         ws = None
         if spec.Ts > 0:
             nbytes = _lib.query("vcnf_rqs_layer_bwd_workspace", spec.Ts, spec.Ps, dtype_code(x))
             ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
         _launch("vcnf_rqs_layer_bwd", ptr(x), D, ptr(gy), D, ptr(gld), ptr(gx), D, B, D, spec.K, ptr(cmap),
-                ptr(cond), spec.Tc * spec.Pc, spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale,
-                ptr(gcond), spec.Tc * spec.Pc, ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb),
+                ptr(cond), cond.stride(0) if cond is not None else 0, spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale,
+                ptr(gcond), gcond.stride(0) if gcond is not None else 0, ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb),
                 ptr(gshared), ptr(ws), ctx.inverse, spec.outside_zero, dtype_code(x), stream(),
                 n=2 if spec.Ts > 0 else 1)
         return gx, gcond, gshared, None, None, None
@@ -120,12 +139,12 @@ def rqs_layer(x, cond, shared, spec, inverse, want_bins=False):
 
 class _GatherCols(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, cols):
+    def forward(ctx, x, cols, pad):
         x = x.contiguous()
         B, D = x.shape
         n = cols.numel()
-        out = torch.empty((B, n), dtype=x.dtype, device=x.device)
-        _launch("vcnf_gather_cols", ptr(x), D, ptr(out), n, B, n, ptr(cols), dtype_code(x), stream())
+        out = _padded_empty(B, n, x.dtype, x.device) if pad else torch.empty((B, n), dtype=x.dtype, device=x.device)
+        _launch("vcnf_gather_cols", ptr(x), D, ptr(out), out.stride(0), B, n, ptr(cols), dtype_code(x), stream())
         ctx.save_for_backward(cols)
         ctx.D = D
         return out
@@ -134,15 +153,17 @@ class _GatherCols(torch.autograd.Function):
     @once_differentiable
     def backward(ctx, g):
         (cols,) = ctx.saved_tensors
-        g = g.contiguous()
+        g = _rows(g)
         B, n = g.shape
         gx = torch.empty((B, ctx.D), dtype=g.dtype, device=g.device)
-        _launch("vcnf_scatter_cols", ptr(g), n, ptr(gx), ctx.D, B, n, ctx.D, ptr(cols), 0, dtype_code(g), stream())
-        return gx, None
+        _launch("vcnf_scatter_cols", ptr(g), g.stride(0), ptr(gx), ctx.D, B, n, ctx.D, ptr(cols), 0, dtype_code(g), stream())
+        return gx, None, None
 
 
-def gather_cols(x, cols_i32):
-    return _GatherCols.apply(x, cols_i32)
+def gather_cols(x, cols_i32, pad=False):
+    """x[:, cols].  pad=True returns a view whose row pitch is a 16-byte multiple (for consumers that
+    take a leading dimension, i.e. ops.linear)."""
+    return _GatherCols.apply(x, cols_i32, pad)
 
 
 class _AffineCoupling(torch.autograd.Function):
@@ -372,15 +393,16 @@ class _Linear(torch.autograd.Function):
     the ReLU, the bias, the residual add and the ReLU-backward mask are fused into the kernels."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, relu_in):
-        x, weight = x.contiguous(), weight.contiguous()
+    def forward(ctx, x, weight, bias, residual, relu_in, pad_out):
+        x, weight = _rows(x), weight.contiguous()
         M, K = x.shape
         N = weight.shape[0]
         bias_ = bias.contiguous() if bias is not None else None
-        res_ = residual.contiguous() if residual is not None else None
-        y = torch.empty((M, N), dtype=x.dtype, device=x.device)
-        _launch("vcnf_linear_tf32x3", ptr(x), K, ptr(weight), K, 1, ptr(bias_), ptr(res_), N, None, 0,
-                ptr(y), N, M, N, K, int(relu_in), stream())
+        res_ = _rows(residual) if residual is not None else None
+        y = _padded_empty(M, N, x.dtype, x.device) if pad_out else torch.empty((M, N), dtype=x.dtype, device=x.device)
+        _launch("vcnf_linear_tf32x3", ptr(x), x.stride(0), ptr(weight), K, 1, ptr(bias_), ptr(res_),
+                res_.stride(0) if res_ is not None else 0, None, 0,
+                ptr(y), y.stride(0), M, N, K, int(relu_in), stream())
         ctx.relu_in = bool(relu_in)
         ctx.has_bias, ctx.has_res = bias is not None, residual is not None
         ctx.save_for_backward(x, weight)
@@ -390,25 +412,27 @@ class _Linear(torch.autograd.Function):
     @once_differentiable
     def backward(ctx, gy):
         x, weight = ctx.saved_tensors
-        gy = gy.contiguous()
+        gy = _rows(gy)
         M, K = x.shape
         N = weight.shape[0]
+        ldg, ldx = gy.stride(0), x.stride(0)
         gx = gw = gb = gres = None
         if ctx.needs_input_grad[0]:
-            gx = torch.empty_like(x)
+            gx = _padded_empty(M, K, x.dtype, x.device) if ldx != K else torch.empty_like(x)
+            ldo = gx.stride(0)
             # gx[m, k] = [x > 0] * sum_n gy[m, n] W[n, k]  : W read as [n' = k, k' = n] -> sw_n = 1, sw_k = K
             if N <= 128:
-                _launch("vcnf_linear_tf32x3", ptr(gy), N, ptr(weight), 1, K, None, None, 0,
-                        ptr(x) if ctx.relu_in else None, K, ptr(gx), K, M, K, N, 0, stream())
+                _launch("vcnf_linear_tf32x3", ptr(gy), ldg, ptr(weight), 1, K, None, None, 0,
+                        ptr(x) if ctx.relu_in else None, ldx, ptr(gx), ldo, M, K, N, 0, stream())
             else:
                 # out_features > 128 (the 3K-1 wide head): reduce over column slices of <= 128
                 first = True
                 for n0 in range(0, N, 128):
                     n1 = min(N, n0 + 128)
                     last = n1 == N
-                    _launch("vcnf_linear_tf32x3", ptr(gy) + 4 * n0, N, ptr(weight) + 4 * n0 * K, 1, K, None,
-                            None if first else ptr(gx), K, ptr(x) if (ctx.relu_in and last and first) else None, K,
-                            ptr(gx), K, M, K, n1 - n0, 0, stream())
+                    _launch("vcnf_linear_tf32x3", ptr(gy) + 4 * n0, ldg, ptr(weight) + 4 * n0 * K, 1, K, None,
+                            None if first else ptr(gx), ldo, ptr(x) if (ctx.relu_in and last and first) else None, ldx,
+                            ptr(gx), ldo, M, K, n1 - n0, 0, stream())
                     first = False
                 if ctx.relu_in and N > 128:
                     gx = gx * (x > 0)
@@ -419,14 +443,15 @@ class _Linear(torch.autograd.Function):
             gw = torch.empty_like(weight)
             gb = torch.empty(N, dtype=x.dtype, device=x.device) if want_b else None
             ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", M, N, K), dtype=torch.uint8, device=x.device)
-            _launch("vcnf_linear_wgrad_tf32x3", ptr(gy), N, ptr(x), K, ptr(gw), ptr(gb), ptr(ws), M, N, K,
+            _launch("vcnf_linear_wgrad_tf32x3", ptr(gy), ldg, ptr(x), ldx, ptr(gw), ptr(gb), ptr(ws), M, N, K,
                     int(ctx.relu_in), stream(), n=2)
             if not want_w:
                 gw = None
         if ctx.has_res and ctx.needs_input_grad[3]:
             gres = gy
-        return gx, gw, gb, gres, None
+        return gx, gw, gb, gres, None, None
 
 
-def linear(x, weight, bias=None, residual=None, relu_in=False):
-    return _Linear.apply(x, weight, bias, residual, relu_in)
+def linear(x, weight, bias=None, residual=None, relu_in=False, pad_out=False):
+    """pad_out=True: the result is a view with a 16-byte-multiple row pitch (see _padded_empty)."""
+    return _Linear.apply(x, weight, bias, residual, relu_in, pad_out)
