@@ -35,8 +35,8 @@ with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     for _ in range(2):
         step()
     torch.cuda.synchronize()
-ev = [e for e in prof.key_averages() if e.device_time_total > 0 and e.self_device_time_total > 0]
+ev = [e for e in prof.key_averages() if e.self_device_time_total > 0 and e.cpu_time_total == 0]   # kernel rows only
 tot = sum(e.self_device_time_total for e in ev)
 print("device busy per step %.2f ms over %d kernel launches per step" % (tot / 2e3, sum(e.count for e in ev) / 2))
-for e in sorted(ev, key=lambda e: -e.self_device_time_total)[:25]:
+for e in sorted(ev, key=lambda e: -e.self_device_time_total)[:45]:
     print("%8.3f ms %5.1f%% n=%4d  %s" % (e.self_device_time_total / 2e3, 100 * e.self_device_time_total / tot, e.count / 2, e.key[:90]))

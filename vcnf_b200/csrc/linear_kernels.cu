@@ -90,8 +90,80 @@ __global__ void __launch_bounds__(kLinRows) small_linear_kernel(const LinArgs<T>
   }
 }
 
+// Row-major [rows, D] fast path (S == 1: LULinearPermute on tabular data).  The tile is one contiguous
+// span in HBM, so it is staged and written back as a flat coalesced copy (no index arithmetic per
+// element); the feature gather / scatter happens on the shared-memory side, where a row pitch of D
+// (odd for the shapes in use) is conflict-free.  Two tiles per CTA iteration share one W load.
+constexpr int kRowThreads = 256;
+
+template <typename T, int DP>
+__global__ void __launch_bounds__(kRowThreads) small_linear_rows_kernel(const LinArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_lin[];
+  const int D = a.D;
+  T* Ws = reinterpret_cast<T*>(smem_lin);              // [D][DP], zero padded
+  T* bs = Ws + static_cast<size_t>(D) * DP;            // [DP]
+  int* iin = reinterpret_cast<int*>(bs + DP);          // [DP]
+  int* iout = iin + DP;                                // [DP]
+  T* xs = reinterpret_cast<T*>(iout + DP);             // [kRowThreads * D]
+  T* ys = xs + static_cast<size_t>(kRowThreads) * D;   // [kRowThreads * D]
+  for (int e = threadIdx.x; e < D * DP; e += kRowThreads) {
+    const int o = e / DP, i = e - o * DP;
+    Ws[e] = i < D ? a.W[o * D + i] : T(0);
+  }
+  for (int e = threadIdx.x; e < DP; e += kRowThreads) {
+    bs[e] = (e < D && a.bias) ? a.bias[e] : T(0);
+    iin[e] = e < D ? (a.in_idx ? a.in_idx[e] : e) : 0;
+    iout[e] = e < D ? (a.out_idx ? a.out_idx[e] : e) : 0;
+  }
+  const int64_t n_tiles = (a.rows + kRowThreads - 1) / kRowThreads;
+  const int r = threadIdx.x;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t r0 = tile * kRowThreads;
+    const int nr = static_cast<int>(a.rows - r0 < kRowThreads ? a.rows - r0 : kRowThreads);
+    const int n = nr * D;
+    const T* src = a.x + r0 * D;
+    for (int e = threadIdx.x; e < n; e += kRowThreads) xs[e] = src[e];
+    __syncthreads();                                   // (also orders the W / index loads on the first tile)
+    if (r < nr) {
+      T xr[DP];
+#pragma unroll
+      for (int i = 0; i < DP; ++i) {
+        T v = i < D ? xs[r * D + iin[i]] : T(0);
+        if (a.sub_bias_first) v -= bs[i];
+        xr[i] = v;
+      }
+      for (int o = 0; o < D; ++o) {
+        T acc0 = a.sub_bias_first ? T(0) : bs[o], acc1 = T(0);
+        const T* w = Ws + o * DP;
+#pragma unroll
+        for (int i = 0; i < DP; i += 2) { acc0 += w[i] * xr[i]; acc1 += w[i + 1] * xr[i + 1]; }
+        ys[r * D + iout[o]] = acc0 + acc1;
+      }
+    }
+    __syncthreads();
+    T* dst = a.y + r0 * D;
+    for (int e = threadIdx.x; e < n; e += kRowThreads) dst[e] = ys[e];
+  }
+}
+
 template <typename T, int DP>
 static int launch_lin(const LinArgs<T>& a, cudaStream_t st) {
+  const size_t smem_rows = (static_cast<size_t>(a.D) * DP + DP) * sizeof(T) + 2 * DP * sizeof(int) +
+                           2 * static_cast<size_t>(kRowThreads) * a.D * sizeof(T);
+  if (a.S == 1 && smem_rows <= 160 * 1024) {
+    const size_t smem = smem_rows;
+    auto kern = small_linear_rows_kernel<T, DP>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+      attr_set = true;
+    }
+    const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
+    const int64_t tiles = (a.rows + kRowThreads - 1) / kRowThreads;
+    const int64_t cap = static_cast<int64_t>(sms) * 2;
+    kern<<<static_cast<unsigned>(tiles < cap ? tiles : cap), kRowThreads, smem, st>>>(a);
+    return launch_status();
+  }
   const size_t smem = (static_cast<size_t>(a.D) * DP + DP + static_cast<size_t>(kLinRows) * (a.D + 1)) * sizeof(T);
   auto kern = small_linear_kernel<T, DP>;
   if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
