@@ -1240,6 +1240,236 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tf32x3_kernel(const 
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
 }
 
+
+// -------------------------------------------------------------------------------------------------
+// Weight gradient, TMA-fed (used whenever both operands have 16-byte-multiple row pitches).
+// The contraction runs over samples, and both operands are stored sample-major with the FEATURE index
+// contiguous -- "MN-major" for the tensor core.  For 32-bit operands UMMA reads MN-major tiles in the
+// SWIZZLE_128B_BASE32B layout (32 features = 128 B per sample row, 32 B chunks xor-ed with (row & 3),
+// 4-row atoms of 512 B), which is exactly what a TMA box {32 features, 32 samples} with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B writes (probed in tools/mn_probe.cu; plain SWIZZLE_128B and the
+// no-swizzle layout return zeros for tf32).  So nothing is transposed any more: raw tiles land by TMA,
+// 8 warps make one elementwise pass (ReLU, round-to-nearest hi in place, lo plane, ones column), and the
+// MMAs read them as they lie.
+// -------------------------------------------------------------------------------------------------
+namespace wg2 {
+#ifdef VCNF_GEMM_TRACE
+__device__ long long g_wtrace[160][16];
+#define WTRACE(i) g_wtrace[blockIdx.x][i] = clock64()
+#else
+#define WTRACE(i)
+#endif
+constexpr int kR = 32;                         // samples per stage
+constexpr uint32_t kGroup = kR * 128;          // one 32-feature group of a stage (4 KB)
+constexpr int kConvWarps = 8;
+constexpr int kStages = 3;
+
+struct Args {
+  float* partial;                              // [splits, o_tiles * 128, K + 1]
+  int64_t B; int N; int K;
+  int relu_in;
+  int o_tiles, splits;
+  int gx;                                      // 32-feature groups of X that hold data: ceil(K / 32)
+  int gb;                                      // groups of the B operand: ceil((K + 1) / 32)  (UMMA N = 32 gb)
+  int64_t chunks;                              // ceil(B / kR)
+};
+
+__device__ __forceinline__ uint64_t desc_mn(uint32_t saddr) {     // MN-major, 128B_BASE32B: LBO = group, SBO = 4-row atom
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>((kGroup >> 4) & 0x3fffu) << 16;
+  d |= static_cast<uint64_t>((512u >> 4) & 0x3fffu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(1) << 61;
+  return d;
+}
+// 4 k-steps (8 samples = 1024 B each) x {lo*hi, hi*lo -> d_small; hi*hi -> d_main}
+__device__ __forceinline__ void mma_stage4_mn(uint32_t d_main, uint32_t d_small, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi,
+                                              uint64_t b_lo, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred pa, pt;\n\t"
+      ".reg .b64 ah1, al1, bh1, bl1, ah2, al2, bh2, bl2, ah3, al3, bh3, bl3;\n\t"
+      "setp.ne.b32 pa, %7, 0;\n\t"
+      "setp.eq.b32 pt, %6, %6;\n\t"
+      "add.u64 ah1, %2, 64;\n\t add.u64 al1, %3, 64;\n\t add.u64 bh1, %4, 64;\n\t add.u64 bl1, %5, 64;\n\t"
+      "add.u64 ah2, %2, 128;\n\t add.u64 al2, %3, 128;\n\t add.u64 bh2, %4, 128;\n\t add.u64 bl2, %5, 128;\n\t"
+      "add.u64 ah3, %2, 192;\n\t add.u64 al3, %3, 192;\n\t add.u64 bh3, %4, 192;\n\t add.u64 bl3, %5, 192;\n\t"
+      VCNF_MMA_SS "[%1], %3, %4, %6, pa;\n\t"
+      VCNF_MMA_SS "[%1], %2, %5, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], %2, %4, %6, pa;\n\t"
+      VCNF_MMA_SS "[%1], al1, bh1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], ah1, bl1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], ah1, bh1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], al2, bh2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], ah2, bl2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], ah2, bh2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], al3, bh3, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], ah3, bl3, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], ah3, bh3, %6, pt;\n\t"
+      "}\n" ::"r"(d_main), "r"(d_small), "l"(a_hi), "l"(a_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Args a, const __grid_constant__ CUtensorMap tm_g,
+                                                                       const __grid_constant__ CUtensorMap tm_x) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);            // [kStages] TMA -> converters
+  uint64_t* ready = full + kStages;                              // [kStages] converters -> MMA
+  uint64_t* empty = ready + kStages;                             // [kStages] MMA -> TMA
+  uint64_t* acc_full = empty + kStages;                          // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  const uint32_t a_plane = 4 * kGroup;                           // gY operand plane (hi or lo): 128 features
+  const uint32_t b_plane = static_cast<uint32_t>(a.gb) * kGroup; // X operand plane
+  const uint32_t stage_bytes = 2 * a_plane + 2 * b_plane;
+  unsigned char* st0 = smem + 1024;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ot = blockIdx.x % a.o_tiles;
+  const int split = blockIdx.x / a.o_tiles;
+  const int o0 = ot * 128;
+  const int64_t per = (a.chunks + a.splits - 1) / a.splits;
+  const int64_t c_begin = split * per;
+  const int64_t c_end = (c_begin + per) < a.chunks ? (c_begin + per) : a.chunks;
+  const int64_t G = c_end > c_begin ? c_end - c_begin : 0;
+
+  if (tid == 0) {
+    WTRACE(0);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&ready[s], kConvWarps); mbar_init(&empty[s], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init_fence();
+  }
+  if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
+  // constant group of the X operand (only when the ones column does not fall inside a data group):
+  // feature 32 gx holds 1.0 for every sample (-> bias gradient), the other 31 features are zero
+  if (a.gb > a.gx) {
+    for (int idx = tid; idx < kStages * (kGroup / 16); idx += kThreads) {
+      const int s = idx / (kGroup / 16), c = idx - s * (kGroup / 16);
+      const int row = c >> 3, p16 = c & 7;
+      const bool first = ((p16 >> 1) ^ (row & 3)) == 0 && (p16 & 1) == 0;     // logical features 0..3 of the group
+      unsigned char* bh = st0 + static_cast<uint32_t>(s) * stage_bytes + 2 * a_plane + static_cast<uint32_t>(a.gx) * kGroup + c * 16;
+      *reinterpret_cast<float4*>(bh) = make_float4(first ? 1.f : 0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(bh + b_plane) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) { WTRACE(1); }
+
+  if (warp < kConvWarps) {
+    // ------------------------------ TMA issue (thread 0) + elementwise conversion (256 threads)
+    const uint32_t tx_bytes = static_cast<uint32_t>(4 + a.gx) * kGroup;
+    auto issue = [&](int64_t i) {
+      if (i >= G) return;
+      const uint32_t it = static_cast<uint32_t>(i);
+      const int s = it % kStages;
+      mbar_wait(&empty[s], ((it / kStages) & 1u) ^ 1u);
+      mbar_expect_tx(&full[s], tx_bytes);
+      const int b0 = static_cast<int>((c_begin + i) * kR);
+      const uint32_t base = smem_u32(st0) + static_cast<uint32_t>(s) * stage_bytes;
+      for (int g = 0; g < 4; ++g) v2::tma_load_2d(base + g * kGroup, &tm_g, o0 + g * 32, b0, &full[s]);
+      for (int g = 0; g < a.gx; ++g) v2::tma_load_2d(base + 2 * a_plane + g * kGroup, &tm_x, g * 32, b0, &full[s]);
+    };
+    if (tid == 0) { issue(0); issue(1); }
+    const int row = tid >> 3, p16 = tid & 7;                       // this thread's 16 B chunk inside every group
+    const int f_in = (((p16 >> 1) ^ (row & 3)) << 3) + ((p16 & 1) << 2);   // its first logical feature in the group
+    for (int64_t i = 0; i < G; ++i) {
+      const uint32_t it = static_cast<uint32_t>(i);
+      const int s = it % kStages;
+      mbar_wait(&full[s], (it / kStages) & 1u);
+      if (tid == 0 && i == 0) { WTRACE(2); }
+      unsigned char* st = st0 + static_cast<uint32_t>(s) * stage_bytes + tid * 16;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {                                // gY: split only
+        float4 v = *reinterpret_cast<const float4*>(st + g * kGroup);
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        *reinterpret_cast<float4*>(st + g * kGroup) = h;
+        *reinterpret_cast<float4*>(st + a_plane + g * kGroup) = l;
+      }
+      for (int g = 0; g < a.gx; ++g) {                             // X: ReLU, ones column, split
+        unsigned char* p = st + 2 * a_plane + g * kGroup;
+        float4 v = *reinterpret_cast<const float4*>(p);
+        if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+        const int f = g * 32 + f_in;
+        if (a.K >= f && a.K < f + 4) {
+          if (a.K == f) v.x = 1.f; else if (a.K == f + 1) v.y = 1.f; else if (a.K == f + 2) v.z = 1.f; else v.w = 1.f;
+        }
+        float4 h, l;
+        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+        *reinterpret_cast<float4*>(p) = h;
+        *reinterpret_cast<float4*>(p + b_plane) = l;
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ready[s]);
+      if (tid == 0 && i == 0) { WTRACE(3); }
+      if (tid == 0) issue(i + 2);
+    }
+    if (tid == 0) { WTRACE(4); }
+  } else if (warp == kMmaWarp) {
+    // ------------------------------ MMA issuer (whole warp convergent, one elected lane issues)
+    const uint32_t idesc = instr_desc_tf32(128, a.gb * 32) | (1u << 15) | (1u << 16);   // both operands MN-major
+    const uint32_t d_main = tmem_base, d_small = tmem_base + 256;
+    for (int64_t i = 0; i < G; ++i) {
+      const uint32_t it = static_cast<uint32_t>(i);
+      const int s = it % kStages;
+      mbar_wait(&ready[s], (it / kStages) & 1u);
+      tc_fence_after();
+      const uint32_t base = smem_u32(st0) + static_cast<uint32_t>(s) * stage_bytes;
+      const uint64_t ad_hi = desc_mn(base), ad_lo = desc_mn(base + a_plane);
+      const uint64_t bd_hi = desc_mn(base + 2 * a_plane), bd_lo = desc_mn(base + 2 * a_plane + b_plane);
+      const uint32_t acc0 = i > 0 ? 1u : 0u;
+      const bool last = i == G - 1;
+      if (v2::elect_one()) {
+        mma_stage4_mn(d_main, d_small, ad_hi, ad_lo, bd_hi, bd_lo, idesc, acc0);
+        tc_commit(&empty[s]);
+        if (last) tc_commit(acc_full);
+      }
+      __syncwarp();
+    }
+    if (lane == 0) { WTRACE(5); }
+  } else {
+    // ------------------------------ epilogue: one partial [128, K + 1] per CTA (coalesced through a smem tile)
+    const int q = warp & 3;
+    const int W1 = a.K + 1;
+    float* dst = a.partial + (static_cast<int64_t>(split) * a.o_tiles * 128 + o0 + q * 32) * W1;
+    float* tb = reinterpret_cast<float*>(st0) + (warp - kConvWarps) * (32 * 33);
+    if (G > 0) {
+      mbar_wait(acc_full, 0);
+      tc_fence_after();
+    }
+    if (warp == kConvWarps && lane == 0) { WTRACE(6); }
+    for (int cb = 0; cb * 32 < W1; ++cb) {
+      uint32_t r[32], r2[32];
+      if (G > 0) {
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cb * 32;
+        tmem_ld32(taddr, r);
+        tmem_ld32(taddr + 256, r2);
+        tmem_ld_wait();
+      }
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) tb[lane * 33 + j] = G > 0 ? __uint_as_float(r[j]) + __uint_as_float(r2[j]) : 0.f;
+      __syncwarp();
+      const int col = cb * 32 + lane;
+      if (col < W1) {
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) dst[static_cast<int64_t>(i) * W1 + col] = tb[i * 33 + lane];
+      }
+    }
+  }
+  if (warp == kConvWarps && lane == 0) { WTRACE(7); }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
+  if (tid == 0) { WTRACE(8); }
+}
+}  // namespace wg2
+
 // Sum of the split-K partials in a FIXED order (bit-reproducible): 8 warps of a block share 32 output
 // elements, warp g adds splits g, g + 8, ... (independent loads, unrolled), then the 8 sub-sums are added
 // in order 0..7.  (One thread per element walked 148 dependent L2 round trips: 10 us per call.)
@@ -1412,14 +1642,44 @@ extern "C" int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void*
   a.splits = wgrad_splits(B, N);
   a.NX = (K + 1 + 15) / 16 * 16;
   a.chunks = (B + gemm::kWBK - 1) / gemm::kWBK;
-  const size_t smem = 1024 + static_cast<size_t>(gemm::kWStages) * 2 * (128 / 8 + static_cast<size_t>(a.NX) / 8) * gemm::kWSbo;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(gemm::linear_wgrad_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr_set = true;
+  int rc;
+  static EncodeTiledFn encode = tensor_map_encoder();
+  static const bool no_tma = [] { const char* e = getenv("VCNF_WGRAD_V1"); return e && atoi(e) != 0; }();
+  CUtensorMap tm_g{}, tm_x{};
+  auto make_map = [&](CUtensorMap* out, const void* ptr, int64_t cols, int64_t ld) {
+    if (!encode || ld % 4 != 0 || reinterpret_cast<uintptr_t>(ptr) % 16 != 0 || B >= (1ll << 31)) return false;
+    const cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(B)};
+    const cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 4};
+    const cuuint32_t box[2] = {32, static_cast<cuuint32_t>(gemm::wg2::kR)};
+    const cuuint32_t estr[2] = {1, 1};
+    return encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  };
+  if (!no_tma && make_map(&tm_g, gY, N, ldg) && make_map(&tm_x, X, K, ldx)) {
+    gemm::wg2::Args w{};
+    w.partial = a.partial; w.B = B; w.N = N; w.K = K; w.relu_in = relu_in;
+    w.o_tiles = a.o_tiles; w.splits = a.splits; w.chunks = a.chunks;
+    w.gx = (K + 31) / 32;
+    w.gb = (K + 1 + 31) / 32;
+    const size_t smem = 1024 + static_cast<size_t>(gemm::wg2::kStages) * 2 * (4 + static_cast<size_t>(w.gb)) * gemm::wg2::kGroup;
+    static bool attr_set2 = false;
+    if (!attr_set2) {
+      cudaFuncSetAttribute(gemm::wg2::linear_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+      attr_set2 = true;
+    }
+    gemm::wg2::linear_wgrad_tma_kernel<<<static_cast<unsigned>(w.o_tiles * w.splits), gemm::kThreads, smem, st>>>(w, tm_g, tm_x);
+    rc = launch_status();
+  } else {
+    const size_t smem = 1024 + static_cast<size_t>(gemm::kWStages) * 2 * (128 / 8 + static_cast<size_t>(a.NX) / 8) * gemm::kWSbo;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(gemm::linear_wgrad_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      attr_set = true;
+    }
+    gemm::linear_wgrad_tf32x3_kernel<<<static_cast<unsigned>(a.o_tiles * a.splits), gemm::kThreads, smem, st>>>(a);
+    rc = launch_status();
   }
-  gemm::linear_wgrad_tf32x3_kernel<<<static_cast<unsigned>(a.o_tiles * a.splits), gemm::kThreads, smem, st>>>(a);
-  int rc = launch_status();
   if (rc) return rc;
   const int64_t total = static_cast<int64_t>(N) * (K + 1);
   int grid = static_cast<int>((total + 31) / 32);
