@@ -183,7 +183,7 @@ def kernel_roofline(model, dev, flush):
         _lib.call("vcnf_linear_wgrad_tf32x3", gh.data_ptr(), HIDDEN, h.data_ptr(), HIDDEN, gW.data_ptr(),
                   gbv.data_ptr(), ws.data_ptr(), B, HIDDEN, HIDDEN, 1, torch.cuda.current_stream().cuda_stream)
 
-    kernels = (("linear_tf32x3 (fwd/dgrad, hidden 128x128, relu+bias+residual fused)", lin_fwd,
+    kernels = (("linear_ts_kernel (vcnf_linear_tf32x3 fwd/dgrad: hidden 128x128, relu+bias+residual fused)", lin_fwd,
                 4 * (3 * HIDDEN), 224),                       # read h (A and residual), write y
                ("linear_wgrad_tf32x3 (+ reduce)", lin_wgrad, 4 * (2 * HIDDEN), 96),
                ("rqs_layer_fwd", fwd, 4 * (P + 2 * D + 1), 16),
