@@ -153,6 +153,20 @@ int vcnf_small_linear(const void* x, void* y, const void* W, const void* bias, c
                       const int32_t* out_idx, int64_t rows, int D, int S, int sub_bias_first, int dtype,
                       void* stream);
 
+/* ---- LU-parametrised weight (normflow/flows/mixing.py:352-396, _create_lower_upper / weight / logabsdet) --
+ * W[D, D] = L U and *logabsdet = sum_i log diag(U)_i from the parameter vectors, one launch:
+ *   lower_entries [D(D-1)/2]  strictly-lower part of L in np.tril_indices(D, -1) order (L has a unit diagonal)
+ *   upper_entries [D(D-1)/2]  strictly-upper part of U in np.triu_indices(D, 1) order
+ *   diag_raw      [D]         diag(U) = softplus(diag_raw) + eps   (mixing.py:382-384)
+ * D <= 64.  Replaces the four index_put calls, softplus, the D x D matmul and the log-sum. */
+int vcnf_lu_compose_fwd(const void* lower_entries, const void* upper_entries, const void* diag_raw, double eps, int D,
+                        void* W, void* logabsdet, int dtype, void* stream);
+/* Adjoint: gW [D, D] (may be NULL = zeros) and glogabsdet [1] (may be NULL) -> gradients of the three
+ * parameter vectors (overwritten). */
+int vcnf_lu_compose_bwd(const void* lower_entries, const void* upper_entries, const void* diag_raw, double eps, int D,
+                        const void* gW, const void* glogabsdet, void* g_lower, void* g_upper, void* g_diag, int dtype,
+                        void* stream);
+
 /* ---- K6/K7: conditioner dense layer on tcgen05 tensor cores, fp32-faithful (3xTF32) -------------
  * Replaces F.linear (+ ReLU / residual add / ReLU-backward mask) of the conditioner nets:
  * normflow/nets/resnet.py:38-58,76-106 (ResidualBlock / ResidualNet), nets/mlp.py:7-58,

@@ -131,3 +131,28 @@ def test_padded_pitch_layer_equals_contiguous_layer():
     layer.prqct._pad_rows, net.padded_out = False, False
     y2, ld2 = layer(x)
     assert torch.equal(y1, y2) and torch.equal(ld1, ld2)
+
+
+@pytest.mark.parametrize("D,dtype", [(29, torch.float32), (29, torch.float64), (2, torch.float32), (64, torch.float64), (1, torch.float32)])
+def test_lu_compose_matches_index_put_route(D, dtype):
+    """Fused W = L U / log|det| kernel (vcnf_lu_compose_*) against the reference's construction
+    (mixing.py:352-396: index_put, softplus, matmul, log-sum) in both directions of autograd."""
+    from vcnf_b200 import ops
+    from vcnf_b200.flows.mixing import _LULinear
+    torch.manual_seed(D)
+    lin = _LULinear(D, identity_init=False).to(DEV, dtype)
+    with torch.no_grad():
+        lin.unconstrained_upper_diag.add_(torch.randn(D, device=DEV, dtype=dtype))
+    gW = torch.randn(D, D, device=DEV, dtype=dtype)
+    gl = torch.randn((), device=DEV, dtype=dtype)
+    params = [lin.lower_entries, lin.upper_entries, lin.unconstrained_upper_diag]
+    W0, l0 = lin.weight(), lin.logabsdet()
+    ref = torch.autograd.grad([W0, l0], params, [gW, gl], allow_unused=True)
+    W1, l1 = ops.lu_compose(*params, lin.eps)
+    got = torch.autograd.grad([W1, l1], params, [gW, gl], allow_unused=True)
+    tol = dict(rtol=1e-5, atol=1e-6) if dtype == torch.float32 else dict(rtol=1e-12, atol=1e-13)
+    torch.testing.assert_close(W1, W0, **tol)
+    torch.testing.assert_close(l1, l0, **tol)
+    for a, b in zip(got, ref):
+        if b is not None and b.numel():
+            torch.testing.assert_close(a, b, **tol)

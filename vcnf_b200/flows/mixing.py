@@ -205,9 +205,18 @@ class _LULinear(Flow):
     def logabsdet(self):
         return torch.sum(torch.log(self.upper_diag))
 
+    def _fused(self):
+        """Parameters on a CUDA device and D <= 64: W and log|det| come from one fused kernel."""
+        return self.lower_entries.is_cuda and self.features <= 64
+
     def forward(self, inputs, context=None, in_idx=None):
-        out = ops.small_linear(inputs, self.weight(), self.bias, in_idx=in_idx)
-        return out, self.logabsdet() * inputs.new_ones(out.shape[0])
+        if self._fused():
+            weight, logabsdet = ops.lu_compose(self.lower_entries, self.upper_entries, self.unconstrained_upper_diag,
+                                               self.eps)
+        else:
+            weight, logabsdet = self.weight(), self.logabsdet()
+        out = ops.small_linear(inputs, weight, self.bias, in_idx=in_idx)
+        return out, logabsdet * inputs.new_ones(out.shape[0])
 
     def inverse(self, inputs, context=None, out_idx=None):
         out = ops.small_linear(inputs, self.weight_inverse(), self.bias, out_idx=out_idx, sub_bias_first=True)

@@ -381,6 +381,41 @@ def small_linear(x, W, bias=None, in_idx=None, out_idx=None, sub_bias_first=Fals
 
 
 # ------------------------------------------------------------------ conditioner dense layers
+class _LuCompose(torch.autograd.Function):
+    """(lower_entries, upper_entries, unconstrained_upper_diag) -> (W = L U, log|det W|): one kernel each
+    way instead of the index_put / softplus / matmul / log / sum chain (mixing.py:352-396)."""
+
+    @staticmethod
+    def forward(ctx, lower, upper, diag_raw, eps):
+        lower, upper, diag_raw = lower.contiguous(), upper.contiguous(), diag_raw.contiguous()
+        D = diag_raw.numel()
+        W = torch.empty((D, D), dtype=diag_raw.dtype, device=diag_raw.device)
+        logabsdet = torch.empty((), dtype=diag_raw.dtype, device=diag_raw.device)
+        _launch("vcnf_lu_compose_fwd", ptr(lower), ptr(upper), ptr(diag_raw), float(eps), D, ptr(W), ptr(logabsdet),
+                dtype_code(diag_raw), stream())
+        ctx.eps = float(eps)
+        ctx.save_for_backward(lower, upper, diag_raw)
+        return W, logabsdet
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gW, gl):
+        lower, upper, diag_raw = ctx.saved_tensors
+        D = diag_raw.numel()
+        gW = gW.contiguous() if gW is not None else None
+        gl = gl.contiguous() if gl is not None else None
+        g_lower, g_upper, g_diag = torch.empty_like(lower), torch.empty_like(upper), torch.empty_like(diag_raw)
+        _launch("vcnf_lu_compose_bwd", ptr(lower), ptr(upper), ptr(diag_raw), ctx.eps, D, ptr(gW), ptr(gl),
+                ptr(g_lower), ptr(g_upper), ptr(g_diag), dtype_code(diag_raw), stream())
+        return g_lower, g_upper, g_diag, None
+
+
+def lu_compose(lower_entries, upper_entries, unconstrained_upper_diag, eps):
+    """W = L U and log|det W| of the LU-parametrised linear flow (D <= 64)."""
+    lower_entries, upper_entries, unconstrained_upper_diag = _promote(lower_entries, upper_entries, unconstrained_upper_diag)
+    return _LuCompose.apply(lower_entries, upper_entries, unconstrained_upper_diag, eps)
+
+
 def linear_supported(x, weight):
     """The tcgen05 3xTF32 kernel covers fp32 CUDA tensors with in_features <= 128."""
     return (x.is_cuda and x.dtype == torch.float32 and weight.dtype == torch.float32 and x.dim() == 2
