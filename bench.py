@@ -231,15 +231,17 @@ def gpu_run(args):
 
     if args.no_graph:
         def step(x):
-            bucket.zero()
+            bucket.begin()
             loss = model.forward_kld(x)
             loss.backward()
-            bucket.allreduce_mean(world)
+            if world > 1:
+                bucket.collect()
+                bucket.allreduce_mean(world)
             opt.step()
             return loss
         graphed = False
     else:
-        # the whole step (~1600 launches) captured once into a CUDA graph and replayed (parallel.py)
+        # the whole step (~1100 launches) captured once into a CUDA graph and replayed (parallel.py)
         step = parallel.GraphedTrainStep(model, opt, bucket, x_dev, world=world)
         graphed = step.graph is not None
     launches_per_step = None

@@ -16,7 +16,7 @@ opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
 x = bench.synth_batch(B, 1234).to(dev)
 
 def step():
-    bucket.zero()
+    bucket.begin()
     loss = model.forward_kld(x)
     loss.backward()
     opt.step()

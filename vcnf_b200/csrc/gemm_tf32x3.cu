@@ -842,38 +842,48 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
       // 32 x 32 transpose tile per warp, xor-swizzled; aliases epilogue tile 2, which is first requested
       // after every epilogue warp has passed the named barrier of tile 0
       float* tb = reinterpret_cast<float*>(ebuf + 2 * kETile) + (warp - kProdWarps) * (32 * 32);
+      // Both 32-column chunks of this warp are requested before the first one is used (one memory latency
+      // instead of two on the critical path to the first MMA).
+      float wv[2][32];
+#pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         const int k0 = h * 64 + cc * 32;
         if (k0 >= nk8 * 8) continue;                              // warp-uniform: columns no MMA reads
-        uint32_t whi[32], wlo[32];
-        float w[32];
         if (a.sw_k == 1) {
-          // row-major W: a warp instruction reads 128 contiguous bytes of ONE row (lane = k), and the 32 x 32
-          // block is transposed through a padded smem tile so that lane = output feature afterwards.  (Per-lane
+          // row-major W: a warp instruction reads 128 contiguous bytes of ONE row (lane = k); the 32 x 32
+          // block is transposed through a smem tile below so that lane = output feature afterwards.  (Per-lane
           // row reads are 32 sectors per request; with all 148 CTAs hitting the same 64 KB at once they took
           // 10 us of every launch.)
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const int oi = q * 32 + i, k = k0 + lane;
-            w[i] = (oi < NT && k < a.K) ? __ldg(a.W + static_cast<int64_t>(n0 + oi) * a.sw_n + k) : 0.f;
+            wv[cc][i] = (oi < NT && k < a.K) ? __ldg(a.W + static_cast<int64_t>(n0 + oi) * a.sw_n + k) : 0.f;
           }
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) tb[i * 32 + (lane ^ i)] = w[i];
-          __syncwarp();
-#pragma unroll
-          for (int j = 0; j < 32; ++j) w[j] = tb[lane * 32 + (j ^ lane)];
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const int k = k0 + j;
-            w[j] = (o_ok && k < a.K) ? __ldg(wrow + static_cast<int64_t>(k) * a.sw_k) : 0.f;
+            wv[cc][j] = (o_ok && k < a.K) ? __ldg(wrow + static_cast<int64_t>(k) * a.sw_k) : 0.f;
           }
+        }
+      }
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int k0 = h * 64 + cc * 32;
+        if (k0 >= nk8 * 8) continue;
+        uint32_t whi[32], wlo[32];
+        if (a.sw_k == 1) {
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) tb[i * 32 + (lane ^ i)] = wv[cc][i];
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) wv[cc][j] = tb[lane * 32 + (j ^ lane)];
         }
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           float hi, lo;
-          split_tf32(w[j], hi, lo);
+          split_tf32(wv[cc][j], hi, lo);
           whi[j] = __float_as_uint(hi);
           wlo[j] = __float_as_uint(lo);
         }
