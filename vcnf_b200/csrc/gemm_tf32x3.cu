@@ -490,7 +490,7 @@ __device__ long long g_trace[160][16];
 #else
 #define VTRACE(i)
 #endif
-constexpr int kProdWarps = 4, kEpiWarps = 8;
+constexpr int kProdWarps = 4, kEpiWarps = 8;   // (8 producer warps = 544 threads: 96 registers, the epilogue spills -- measured slower)
 constexpr int kThreads = (kProdWarps + kEpiWarps + 1) * 32;          // 416
 constexpr int kMmaWarp = kProdWarps + kEpiWarps;                     // 12
 constexpr int kProd = kProdWarps * 32;
@@ -728,7 +728,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
     uint32_t off[kChunksPerThread];
 #pragma unroll
     for (int i = 0; i < kChunksPerThread; ++i) {
-      const int r = r0 + 16 * i;
+      const int r = r0 + (kProd / 8) * i;
       off[i] = static_cast<uint32_t>(r) * 128 + static_cast<uint32_t>((c ^ (r & 7)) << 4);
     }
     auto issue = [&](int64_t g) {
@@ -741,7 +741,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
         const uint32_t base = static_cast<uint32_t>(s) * 2 * kPlane;
 #pragma unroll
         for (int i = 0; i < kChunksPerThread; ++i) {
-          const int64_t gr = m0 + r0 + 16 * i;
+          const int64_t gr = m0 + r0 + (kProd / 8) * i;
           const bool ok = gr < a.M && gk < a.K;
           if (vec_ok) {
             cp_async16(ring_u32 + base + off[i], ok ? a.A + gr * a.lda + gk : a.A, ok ? 16u : 0u);

@@ -35,6 +35,8 @@ class ResidualBlock(nn.Module):
     def forward(self, inputs, context=None):
         if self._fast(inputs, context):
             l0, l1 = self.linear_layers
+            if l0.bias is not None and l1.bias is not None:
+                return ops.residual_block(inputs, l0.weight, l0.bias, l1.weight, l1.bias)
             t = ops.linear(inputs, l0.weight, l0.bias, relu_in=True)
             return ops.linear(t, l1.weight, l1.bias, residual=inputs, relu_in=True)
         h = inputs

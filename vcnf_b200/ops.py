@@ -490,3 +490,60 @@ class _Linear(torch.autograd.Function):
 def linear(x, weight, bias=None, residual=None, relu_in=False, pad_out=False):
     """pad_out=True: the result is a view with a 16-byte-multiple row pitch (see _padded_empty)."""
     return _Linear.apply(x, weight, bias, residual, relu_in, pad_out)
+
+
+class _ResBlock(torch.autograd.Function):
+    """Pre-activation residual block  out = x + W1 relu(W0 relu(x) + b0) + b1  (nets/resnet.py:38-55 with
+    ReLU, no batch norm / dropout / context) as ONE autograd node: two forward GEMM launches, and in the
+    backward the skip-connection gradient rides on the `residual` operand of the second input-gradient
+    GEMM instead of a separate [B, features] add kernel (32 such adds per cfg-2 step)."""
+
+    @staticmethod
+    def forward(ctx, x, w0, b0, w1, b1):
+        x, w0, w1 = _rows(x), w0.contiguous(), w1.contiguous()
+        M, F_ = x.shape
+        t = torch.empty((M, F_), dtype=x.dtype, device=x.device)
+        out = torch.empty((M, F_), dtype=x.dtype, device=x.device)
+        _launch("vcnf_linear_tf32x3", ptr(x), x.stride(0), ptr(w0), F_, 1, ptr(b0), None, 0, None, 0,
+                ptr(t), F_, M, F_, F_, 1, stream())
+        _launch("vcnf_linear_tf32x3", ptr(t), F_, ptr(w1), F_, 1, ptr(b1), ptr(x), x.stride(0), None, 0,
+                ptr(out), F_, M, F_, F_, 1, stream())
+        ctx.save_for_backward(x, t, w0, w1)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        x, t, w0, w1 = ctx.saved_tensors
+        g = _rows(g)
+        M, F_ = x.shape
+        ldg, ldx = g.stride(0), x.stride(0)
+        need_x, need_w0, need_b0, need_w1, need_b1 = ctx.needs_input_grad
+        gx = gw0 = gb0 = gw1 = gb1 = None
+        # g_t = [t > 0] * (g W1)
+        gt = torch.empty((M, F_), dtype=x.dtype, device=x.device)
+        _launch("vcnf_linear_tf32x3", ptr(g), ldg, ptr(w1), 1, F_, None, None, 0, ptr(t), F_, ptr(gt), F_,
+                M, F_, F_, 0, stream())
+        if need_x:   # g_x = [x > 0] * (g_t W0) + g   (skip connection through `residual`)
+            gx = torch.empty((M, F_), dtype=x.dtype, device=x.device)
+            _launch("vcnf_linear_tf32x3", ptr(gt), F_, ptr(w0), 1, F_, None, ptr(g), ldg, ptr(x), ldx, ptr(gx), F_,
+                    M, F_, F_, 0, stream())
+        nbytes = _lib.query("vcnf_linear_wgrad_workspace", M, F_, F_)
+        if need_w1 or need_b1:
+            gw1 = torch.empty_like(w1)
+            gb1 = torch.empty(F_, dtype=x.dtype, device=x.device)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+            _launch("vcnf_linear_wgrad_tf32x3", ptr(g), ldg, ptr(t), F_, ptr(gw1), ptr(gb1), ptr(ws), M, F_, F_, 1,
+                    stream(), n=2)
+        if need_w0 or need_b0:
+            gw0 = torch.empty_like(w0)
+            gb0 = torch.empty(F_, dtype=x.dtype, device=x.device)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+            _launch("vcnf_linear_wgrad_tf32x3", ptr(gt), F_, ptr(x), ldx, ptr(gw0), ptr(gb0), ptr(ws), M, F_, F_, 1,
+                    stream(), n=2)
+        return gx, gw0 if need_w0 else None, gb0 if need_b0 else None, gw1 if need_w1 else None, gb1 if need_b1 else None
+
+
+def residual_block(x, w0, b0, w1, b1):
+    """x + Linear1(relu(Linear0(relu(x)))) with square weights [F, F], F <= 128, biases required."""
+    return _ResBlock.apply(x, w0, b0, w1, b1)
