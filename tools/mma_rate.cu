@@ -41,6 +41,31 @@ __global__ void __launch_bounds__(128, 1) probe(P p) {
       uint32_t leader;
       asm volatile("{.reg .b32 rx; .reg .pred px; elect.sync rx|px, 0xffffffff; selp.b32 %0, 1, 0, px;}" : "=r"(leader));
       if (!leader) continue;
+      if (p.kind == 3 || p.kind == 4) {   // B (kind 3) or both operands (kind 4) MN-major, SWIZZLE_128B_BASE32B
+        const uint32_t idm = idesc | (1u << 16) | (p.kind == 4 ? (1u << 15) : 0u);
+        const uint64_t bm = desc(b_addr, 4096, 512, 1), am = desc(a_addr, 4096, 512, 1);
+        if (p.kind == 3)
+          asm volatile("{.reg .pred q; setp.ne.b32 q, %4, 0;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;}" ::"r"(d), "r"(tm), "l"(bm), "r"(idm), "r"(1));
+        else
+          asm volatile("{.reg .pred q; setp.ne.b32 q, %4, 0;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;\n"
+                       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, q;}" ::"r"(d), "l"(am), "l"(bm), "r"(idm), "r"(1));
+        continue;
+      }
       if (p.kind == 2) {
         asm volatile("{.reg .pred q; setp.ne.b32 q, %4, 0;\n"
                      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, q;\n"
@@ -94,6 +119,14 @@ int main() {
     long long h[2]; cudaMemcpy(h, out, 16, cudaMemcpyDeviceToHost);
     printf("tf32 x8-unrolled N=%3d a_tmem=1: %6.1f  %6.1f clk/MMA\n", N, (double)h[0] / R, (double)h[1] / R);
   }
+  for (int kind : {3, 4}) for (int N : {32, 64, 128, 160}) {
+    P p{kind, N, 1, 1, 1, R / 8, 148, out};
+    probe<<<148, 128, 96 * 1024>>>(p);
+    cudaDeviceSynchronize();
+    long long h[2]; cudaMemcpy(h, out, 16, cudaMemcpyDeviceToHost);
+    printf("tf32 x8-unrolled N=%3d %s MN-major (128B_BASE32B): %6.1f  %6.1f clk/MMA\n", N, kind == 3 ? "A tmem, B" : "A and B", (double)h[0] / R, (double)h[1] / R);
+  }
+  return 0;
   for (int ctas : {148})
     for (int kind : {0})
       for (int N : {64, 128, 256})

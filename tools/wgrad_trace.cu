@@ -30,5 +30,9 @@ int main(int argc, char** argv) {
   printf("B=%lld event time (kernel + reduce) %.1f us; mean over CTAs (us):", (long long)B, ms * 1e3);
   for (int i = 0; i < 9; ++i) printf("  %s=%.2f", names[i], avg[i]);
   printf("\n");
+  const char* n2[7] = {"X conv: wait full begin", "full seen", "converted+arrived", "next TMA issued", "MMA: ready seen", "MMA issued", "gY warp: full seen"};
+  printf("stage 8 of CTA 0/73 (us from entry):");
+  for (int c : {0, 73}) { for (int i = 0; i < 7; ++i) printf("  %s=%.2f", n2[i], (h[c][9 + i] - h[c][0]) / 1965.0); printf(" |"); }
+  printf("\n");
   return 0;
 }

@@ -1271,16 +1271,17 @@ __device__ long long g_wtrace[160][16];
 #endif
 constexpr int kR = 32;                         // samples per stage
 constexpr uint32_t kGroup = kR * 128;          // one 32-feature group of a stage (4 KB)
-constexpr int kConvWarps = 8;
-constexpr int kStages = 3;
+constexpr int kConvWarps = 8;                  // X converters (warps 0-7); warps 8-11 move gY into tensor memory
+constexpr int kStages = 4;                     // raw tiles in flight: [gY raw 16 KB | X raw -> hi, gx groups]
+constexpr int kLoBufs = 2;                     // X lo planes live only from the conversion to the MMAs that read them
+constexpr uint32_t kColSmall = 128, kColA = 256;   // TMEM: d_main [0,128) d_small [128,256) gY stage s at 256 + 64 s: hi | lo
 
 struct Args {
   float* partial;                              // [splits, o_tiles * 128, K + 1]
   int64_t B; int N; int K;
   int relu_in;
   int o_tiles, splits;
-  int gx;                                      // 32-feature groups of X that hold data: ceil(K / 32)
-  int gb;                                      // groups of the B operand: ceil((K + 1) / 32)  (UMMA N = 32 gb)
+  int gx;                                      // 32-feature groups of X: ceil(K / 32)  (UMMA N = 32 gx)
   int64_t chunks;                              // ceil(B / kR)
 };
 
@@ -1293,46 +1294,55 @@ __device__ __forceinline__ uint64_t desc_mn(uint32_t saddr) {     // MN-major, 1
   d |= static_cast<uint64_t>(1) << 61;
   return d;
 }
-// 4 k-steps (8 samples = 1024 B each) x {lo*hi, hi*lo -> d_small; hi*hi -> d_main}
-__device__ __forceinline__ void mma_stage4_mn(uint32_t d_main, uint32_t d_small, uint64_t a_hi, uint64_t a_lo, uint64_t b_hi,
-                                              uint64_t b_lo, uint32_t idesc, uint32_t acc) {
+// 4 k-steps (8 samples: 8 TMEM columns of the A operand, 1024 B of the B operand) x
+// {Alo*Bhi, Ahi*Blo -> d_small; Ahi*Bhi -> d_main}; A = gY^T from tensor memory, B = X MN-major from smem.
+__device__ __forceinline__ void mma_stage4_ts_mn(uint32_t d_main, uint32_t d_small, uint32_t a_hi, uint32_t a_lo, uint64_t b_hi,
+                                                 uint64_t b_lo, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t"
       ".reg .pred pa, pt;\n\t"
-      ".reg .b64 ah1, al1, bh1, bl1, ah2, al2, bh2, bl2, ah3, al3, bh3, bl3;\n\t"
+      ".reg .b32 ah1, al1, ah2, al2, ah3, al3;\n\t"
+      ".reg .b64 bh1, bl1, bh2, bl2, bh3, bl3;\n\t"
       "setp.ne.b32 pa, %7, 0;\n\t"
       "setp.eq.b32 pt, %6, %6;\n\t"
-      "add.u64 ah1, %2, 64;\n\t add.u64 al1, %3, 64;\n\t add.u64 bh1, %4, 64;\n\t add.u64 bl1, %5, 64;\n\t"
-      "add.u64 ah2, %2, 128;\n\t add.u64 al2, %3, 128;\n\t add.u64 bh2, %4, 128;\n\t add.u64 bl2, %5, 128;\n\t"
-      "add.u64 ah3, %2, 192;\n\t add.u64 al3, %3, 192;\n\t add.u64 bh3, %4, 192;\n\t add.u64 bl3, %5, 192;\n\t"
-      VCNF_MMA_SS "[%1], %3, %4, %6, pa;\n\t"
-      VCNF_MMA_SS "[%1], %2, %5, %6, pt;\n\t"
-      VCNF_MMA_SS "[%0], %2, %4, %6, pa;\n\t"
-      VCNF_MMA_SS "[%1], al1, bh1, %6, pt;\n\t"
-      VCNF_MMA_SS "[%1], ah1, bl1, %6, pt;\n\t"
-      VCNF_MMA_SS "[%0], ah1, bh1, %6, pt;\n\t"
-      VCNF_MMA_SS "[%1], al2, bh2, %6, pt;\n\t"
-      VCNF_MMA_SS "[%1], ah2, bl2, %6, pt;\n\t"
-      VCNF_MMA_SS "[%0], ah2, bh2, %6, pt;\n\t"
-      VCNF_MMA_SS "[%1], al3, bh3, %6, pt;\n\t"
-      VCNF_MMA_SS "[%1], ah3, bl3, %6, pt;\n\t"
-      VCNF_MMA_SS "[%0], ah3, bh3, %6, pt;\n\t"
-      "}\n" ::"r"(d_main), "r"(d_small), "l"(a_hi), "l"(a_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
+      "add.u32 ah1, %2, 8;\n\t add.u32 al1, %3, 8;\n\t add.u64 bh1, %4, 64;\n\t add.u64 bl1, %5, 64;\n\t"
+      "add.u32 ah2, %2, 16;\n\t add.u32 al2, %3, 16;\n\t add.u64 bh2, %4, 128;\n\t add.u64 bl2, %5, 128;\n\t"
+      "add.u32 ah3, %2, 24;\n\t add.u32 al3, %3, 24;\n\t add.u64 bh3, %4, 192;\n\t add.u64 bl3, %5, 192;\n\t"
+      VCNF_MMA_SS "[%1], [%3], %4, %6, pa;\n\t"
+      VCNF_MMA_SS "[%1], [%2], %5, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], [%2], %4, %6, pa;\n\t"
+      VCNF_MMA_SS "[%1], [al1], bh1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], [ah1], bl1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], [ah1], bh1, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], [al2], bh2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], [ah2], bl2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], [ah2], bh2, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], [al3], bh3, %6, pt;\n\t"
+      VCNF_MMA_SS "[%1], [ah3], bl3, %6, pt;\n\t"
+      VCNF_MMA_SS "[%0], [ah3], bh3, %6, pt;\n\t"
+      "}\n" ::"r"(d_main), "r"(d_small), "r"(a_hi), "r"(a_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
       : "memory");
 }
 
+// Shared-memory bandwidth, not HBM, bounded the first TMA-fed version (236 KB per 32-sample stage: both
+// operands written as hi + lo planes and read by 12 MMAs).  Here gY goes to TENSOR MEMORY: the 128 threads
+// of warps 8-11 (thread = output feature = TMEM lane) read the raw tile column-wise (conflict-free in the
+// 32 B-atom swizzle), split in registers and tcgen05.st the hi / lo rows, summing the bias gradient on the
+// way -- so there is no ones column, UMMA N is 32 ceil(K/32), and per stage shared memory sees 144 KB.
 __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Args a, const __grid_constant__ CUtensorMap tm_g,
                                                                        const __grid_constant__ CUtensorMap tm_x) {
   extern __shared__ __align__(1024) unsigned char smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);            // [kStages] TMA -> converters
-  uint64_t* ready = full + kStages;                              // [kStages] converters -> MMA
+  uint64_t* ready = full + kStages;                              // [kStages] converters (12 warps) -> MMA
   uint64_t* empty = ready + kStages;                             // [kStages] MMA -> TMA
   uint64_t* acc_full = empty + kStages;                          // [1]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
-  const uint32_t a_plane = 4 * kGroup;                           // gY operand plane (hi or lo): 128 features
-  const uint32_t b_plane = static_cast<uint32_t>(a.gb) * kGroup; // X operand plane
-  const uint32_t stage_bytes = 2 * a_plane + 2 * b_plane;
-  unsigned char* st0 = smem + 1024;
+  uint64_t* lo_free = acc_full + 1;                              // [kLoBufs] MMA -> X converters
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lo_free + kLoBufs);
+  const uint32_t a_plane = 4 * kGroup;                           // raw gY tile: 128 features x 32 samples
+  const uint32_t b_plane = static_cast<uint32_t>(a.gx) * kGroup; // X tile (raw -> hi in place; lo in a lo buffer)
+  const uint32_t stage_bytes = a_plane + b_plane;
+  unsigned char* st0 = smem + 1024;                              // kStages slots [gY raw | X hi]
+  unsigned char* lo0 = st0 + kStages * stage_bytes;              // kLoBufs X lo planes
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ot = blockIdx.x % a.o_tiles;
@@ -1345,24 +1355,12 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Arg
 
   if (tid == 0) {
     WTRACE(0);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&ready[s], kConvWarps); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&ready[s], kConvWarps + 4); mbar_init(&empty[s], 1); }
+    for (int j = 0; j < kLoBufs; ++j) mbar_init(&lo_free[j], 1);
     mbar_init(acc_full, 1);
     mbar_init_fence();
   }
   if (warp == kMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
-  // constant group of the X operand (only when the ones column does not fall inside a data group):
-  // feature 32 gx holds 1.0 for every sample (-> bias gradient), the other 31 features are zero
-  if (a.gb > a.gx) {
-    for (int idx = tid; idx < kStages * (kGroup / 16); idx += kThreads) {
-      const int s = idx / (kGroup / 16), c = idx - s * (kGroup / 16);
-      const int row = c >> 3, p16 = c & 7;
-      const bool first = ((p16 >> 1) ^ (row & 3)) == 0 && (p16 & 1) == 0;     // logical features 0..3 of the group
-      unsigned char* bh = st0 + static_cast<uint32_t>(s) * stage_bytes + 2 * a_plane + static_cast<uint32_t>(a.gx) * kGroup + c * 16;
-      *reinterpret_cast<float4*>(bh) = make_float4(first ? 1.f : 0.f, 0.f, 0.f, 0.f);
-      *reinterpret_cast<float4*>(bh + b_plane) = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  }
-  fence_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -1370,7 +1368,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Arg
   if (tid == 0) { WTRACE(1); }
 
   if (warp < kConvWarps) {
-    // ------------------------------ TMA issue (thread 0) + elementwise conversion (256 threads)
+    // ------------------------------ TMA issue (thread 0) + X conversion (256 threads)
     const uint32_t tx_bytes = static_cast<uint32_t>(4 + a.gx) * kGroup;
     auto issue = [&](int64_t i) {
       if (i >= G) return;
@@ -1381,70 +1379,96 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Arg
       const int b0 = static_cast<int>((c_begin + i) * kR);
       const uint32_t base = smem_u32(st0) + static_cast<uint32_t>(s) * stage_bytes;
       for (int g = 0; g < 4; ++g) v2::tma_load_2d(base + g * kGroup, &tm_g, o0 + g * 32, b0, &full[s]);
-      for (int g = 0; g < a.gx; ++g) v2::tma_load_2d(base + 2 * a_plane + g * kGroup, &tm_x, g * 32, b0, &full[s]);
+      for (int g = 0; g < a.gx; ++g) v2::tma_load_2d(base + a_plane + g * kGroup, &tm_x, g * 32, b0, &full[s]);
     };
-    if (tid == 0) { issue(0); issue(1); }
-    const int row = tid >> 3, p16 = tid & 7;                       // this thread's 16 B chunk inside every group
-    const int f_in = (((p16 >> 1) ^ (row & 3)) << 3) + ((p16 & 1) << 2);   // its first logical feature in the group
+    if (tid == 0) { issue(0); issue(1); issue(2); }
     for (int64_t i = 0; i < G; ++i) {
       const uint32_t it = static_cast<uint32_t>(i);
       const int s = it % kStages;
+      if (tid == 0 && i == 8) { WTRACE(9); }
       mbar_wait(&full[s], (it / kStages) & 1u);
       if (tid == 0 && i == 0) { WTRACE(2); }
-      unsigned char* st = st0 + static_cast<uint32_t>(s) * stage_bytes + tid * 16;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {                                // gY: split only
+      if (tid == 0 && i == 8) { WTRACE(10); }
+      const int j = it % kLoBufs;
+      mbar_wait(&lo_free[j], ((it / kLoBufs) & 1u) ^ 1u);          // MMAs of stage i - 2 have read this lo buffer
+      unsigned char* st = st0 + static_cast<uint32_t>(s) * stage_bytes + a_plane + tid * 16;
+      unsigned char* lo = lo0 + static_cast<uint32_t>(j) * b_plane + tid * 16;
+      for (int g = 0; g < a.gx; ++g) {                             // elementwise: layout-agnostic 16 B sweep
         float4 v = *reinterpret_cast<const float4*>(st + g * kGroup);
+        if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
         float4 h, l;
         split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
         *reinterpret_cast<float4*>(st + g * kGroup) = h;
-        *reinterpret_cast<float4*>(st + a_plane + g * kGroup) = l;
-      }
-      for (int g = 0; g < a.gx; ++g) {                             // X: ReLU, ones column, split
-        unsigned char* p = st + 2 * a_plane + g * kGroup;
-        float4 v = *reinterpret_cast<const float4*>(p);
-        if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-        const int f = g * 32 + f_in;
-        if (a.K >= f && a.K < f + 4) {
-          if (a.K == f) v.x = 1.f; else if (a.K == f + 1) v.y = 1.f; else if (a.K == f + 2) v.z = 1.f; else v.w = 1.f;
-        }
-        float4 h, l;
-        split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
-        *reinterpret_cast<float4*>(p) = h;
-        *reinterpret_cast<float4*>(p + b_plane) = l;
+        *reinterpret_cast<float4*>(lo + g * kGroup) = l;
       }
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ready[s]);
       if (tid == 0 && i == 0) { WTRACE(3); }
-      if (tid == 0) issue(i + 2);
+      if (tid == 0 && i == 8) { WTRACE(11); }
+      if (tid == 0) issue(i + 3);
+      if (tid == 0 && i == 8) { WTRACE(12); }
     }
     if (tid == 0) { WTRACE(4); }
   } else if (warp == kMmaWarp) {
     // ------------------------------ MMA issuer (whole warp convergent, one elected lane issues)
-    const uint32_t idesc = instr_desc_tf32(128, a.gb * 32) | (1u << 15) | (1u << 16);   // both operands MN-major
-    const uint32_t d_main = tmem_base, d_small = tmem_base + 256;
+    const uint32_t idesc = instr_desc_tf32(128, a.gx * 32) | (1u << 16);     // A: TMEM (K-major), B: MN-major smem
+    const uint32_t d_main = tmem_base, d_small = tmem_base + kColSmall;
     for (int64_t i = 0; i < G; ++i) {
       const uint32_t it = static_cast<uint32_t>(i);
       const int s = it % kStages;
       mbar_wait(&ready[s], (it / kStages) & 1u);
       tc_fence_after();
-      const uint32_t base = smem_u32(st0) + static_cast<uint32_t>(s) * stage_bytes;
-      const uint64_t ad_hi = desc_mn(base), ad_lo = desc_mn(base + a_plane);
-      const uint64_t bd_hi = desc_mn(base + 2 * a_plane), bd_lo = desc_mn(base + 2 * a_plane + b_plane);
+      if (lane == 0 && i == 8) { WTRACE(13); }
+      const int j = it % kLoBufs;
+      const uint32_t a_hi = tmem_base + kColA + static_cast<uint32_t>(s) * 64;
+      const uint64_t bd_hi = desc_mn(smem_u32(st0) + static_cast<uint32_t>(s) * stage_bytes + a_plane);
+      const uint64_t bd_lo = desc_mn(smem_u32(lo0) + static_cast<uint32_t>(j) * b_plane);
       const uint32_t acc0 = i > 0 ? 1u : 0u;
       const bool last = i == G - 1;
       if (v2::elect_one()) {
-        mma_stage4_mn(d_main, d_small, ad_hi, ad_lo, bd_hi, bd_lo, idesc, acc0);
+        mma_stage4_ts_mn(d_main, d_small, a_hi, a_hi + 32, bd_hi, bd_lo, idesc, acc0);
         tc_commit(&empty[s]);
+        tc_commit(&lo_free[j]);
         if (last) tc_commit(acc_full);
       }
+      if (lane == 0 && i == 8) { WTRACE(14); }
       __syncwarp();
     }
     if (lane == 0) { WTRACE(5); }
   } else {
-    // ------------------------------ epilogue: one partial [128, K + 1] per CTA (coalesced through a smem tile)
+    // ------------------------------ warps 8-11: gY^T -> tensor memory, bias gradient, then the epilogue
     const int q = warp & 3;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    // element (feature f, sample k) of the raw tile: group f / 32, row k, 32 B chunk ((f % 32) / 8) ^ (k & 3)
+    const uint32_t f_off = static_cast<uint32_t>(q) * kGroup + static_cast<uint32_t>(lane & 7) * 4;
+    const int c32 = lane >> 3;
+    float bsum = 0.f;
+    for (int64_t i = 0; i < G; ++i) {
+      const uint32_t it = static_cast<uint32_t>(i);
+      const int s = it % kStages;
+      mbar_wait(&full[s], (it / kStages) & 1u);
+      if (warp == kConvWarps && lane == 0 && i == 8) { WTRACE(15); }
+      const unsigned char* raw = st0 + static_cast<uint32_t>(s) * stage_bytes + f_off;
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k) {
+        const float v = *reinterpret_cast<const float*>(raw + k * 128 + ((c32 ^ (k & 3)) << 5));
+        bsum += v;
+        float h, l;
+        split_tf32(v, h, l);
+        hi[k] = __float_as_uint(h);
+        lo[k] = __float_as_uint(l);
+      }
+      const uint32_t ta = lane_base + kColA + static_cast<uint32_t>(s) * 64;
+      v2::tmem_st32(ta, hi);
+      v2::tmem_st32(ta + 32, lo);
+      v2::tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ready[s]);
+    }
+    // epilogue: one partial [128, K + 1] per CTA, coalesced through a smem tile (the stage memory is idle now)
     const int W1 = a.K + 1;
     float* dst = a.partial + (static_cast<int64_t>(split) * a.o_tiles * 128 + o0 + q * 32) * W1;
     float* tb = reinterpret_cast<float*>(st0) + (warp - kConvWarps) * (32 * 33);
@@ -1453,26 +1477,27 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Arg
       tc_fence_after();
     }
     if (warp == kConvWarps && lane == 0) { WTRACE(6); }
-    for (int cb = 0; cb * 32 < W1; ++cb) {
+    for (int cb = 0; cb * 32 < a.K; ++cb) {
       uint32_t r[32], r2[32];
       if (G > 0) {
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cb * 32;
+        const uint32_t taddr = lane_base + cb * 32;
         tmem_ld32(taddr, r);
-        tmem_ld32(taddr + 256, r2);
+        tmem_ld32(taddr + kColSmall, r2);
         tmem_ld_wait();
       }
       __syncwarp();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) tb[lane * 33 + j] = G > 0 ? __uint_as_float(r[j]) + __uint_as_float(r2[j]) : 0.f;
+      for (int jj = 0; jj < 32; ++jj) tb[lane * 33 + jj] = G > 0 ? __uint_as_float(r[jj]) + __uint_as_float(r2[jj]) : 0.f;
       __syncwarp();
       const int col = cb * 32 + lane;
-      if (col < W1) {
+      if (col < a.K) {
 #pragma unroll 8
         for (int i = 0; i < 32; ++i) dst[static_cast<int64_t>(i) * W1 + col] = tb[i * 33 + lane];
       }
     }
+    dst[static_cast<int64_t>(lane) * W1 + a.K] = bsum;             // bias-gradient column of this thread's feature
+    if (warp == kConvWarps && lane == 0) { WTRACE(7); }
   }
-  if (warp == kConvWarps && lane == 0) { WTRACE(7); }
   tc_fence_before();
   __syncthreads();
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, kTmemCols);
@@ -1671,8 +1696,8 @@ extern "C" int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void*
     w.partial = a.partial; w.B = B; w.N = N; w.K = K; w.relu_in = relu_in;
     w.o_tiles = a.o_tiles; w.splits = a.splits; w.chunks = a.chunks;
     w.gx = (K + 31) / 32;
-    w.gb = (K + 1 + 31) / 32;
-    const size_t smem = 1024 + static_cast<size_t>(gemm::wg2::kStages) * 2 * (4 + static_cast<size_t>(w.gb)) * gemm::wg2::kGroup;
+    const size_t smem = 1024 + (static_cast<size_t>(gemm::wg2::kStages) * (4 + w.gx) + static_cast<size_t>(gemm::wg2::kLoBufs) * w.gx) *
+                                   gemm::wg2::kGroup;
     static bool attr_set2 = false;
     if (!attr_set2) {
       cudaFuncSetAttribute(gemm::wg2::linear_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
