@@ -43,9 +43,9 @@ def assert_grads_close(got, ref, rtol, what=""):
 
 
 def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.999):
-    """fp32 spline outputs: >= `frac` of the elements inside the stated tolerance of
-    the fp32 reference; the ill-conditioned remainder must be no further from the fp64 reference
-    than 4x the fp32 reference's own worst error against it (+ 10 atol).  (Rounding errors on
+    """fp32 outputs: >= `frac` of the elements inside the stated tolerance of the
+    reference (its fp32 or its fp64 evaluation); the ill-conditioned remainder must be no further from the
+    fp64 reference than 4x the fp32 reference's own worst error against it (+ 10 atol).  (Rounding errors on
     such elements are amplified by the same huge factor for any fp32 evaluation order; which order gets
     the luckier draw on a given element is chance -- golden case crqs_linear: the reference itself is off
     by 0.42 in one per-sample log-det.)"""
@@ -57,16 +57,19 @@ def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.999):
         return
     err = (a_ - r32).abs()[ok]
     tol = atol + rtol * r32.abs()[ok]
+    err64 = (a_ - r64).abs()[ok]
+    # an element agrees when it is inside the stated tolerance of the reference evaluated in fp32 OR in fp64
+    # (the latter is the stronger statement: the reference's fp32 value is itself only an approximation of it)
+    near = (err <= tol) | (err64 <= atol + rtol * r64.abs()[ok])
     # elements on which the reference's OWN fp32 rounding already uses a quarter of the tolerance are
     # ill-conditioned: a different (equally valid) fp32 evaluation order cannot be held to `tol` there;
     # they are covered by the worst-error clause below instead
     excused = (r32 - r64).abs()[ok] > 0.25 * tol
-    inside = (err <= tol) | excused
-    share = float(inside.double().mean())
-    e64 = float((a_ - r64).abs()[ok].max())
+    share = float((near | excused).double().mean())
+    e64 = float(err64[~near].max()) if (~near).any() else 0.0
     ref_e = float((r32 - r64).abs()[ok].max())
     assert share >= frac, "%s: only %.4f%% of elements inside rtol=%g atol=%g (worst %.3g x tol)" % (
-        what, 100 * share, rtol, atol, float((err / (atol + rtol * r32.abs()[ok])).max()))
+        what, 100 * share, rtol, atol, float((err / tol).max()))
     assert e64 <= 4 * ref_e + 10 * atol, "%s: max error vs fp64 reference %.3g > 4 x %.3g + 10 atol" % (what, e64, ref_e)
 
 

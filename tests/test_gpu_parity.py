@@ -71,8 +71,18 @@ def test_layer_matches_reference_golden(name, direction):
         # a dense linear solve: norm-wise relative error (atol scaled by max|ref|; the random L U of this
         # case maps N(0,1) inputs to outputs up to 199)
         tol = dict(rtol=tol["rtol"], atol=tol["rtol"] * float(ref["z"].abs().max()))
-    assert_close(got["z"], ref["z"], what=name + ".z", **tol)
-    assert_close(got["log_det"], ref["log_det"], what=name + ".log_det", rtol=tol["rtol"], atol=tol["atol"] * n_sum)
+    if dtype == torch.float32 and (direction + "_f64") in g and name != "lu_permute":
+        # affine layers whose conditioner output goes through exp(): the reference's own fp32 result is up to
+        # 4 x the stated tolerance away from its fp64 evaluation (masked_affine_f32/inverse; 0.7 x for
+        # affine_block_exp/inverse) -- same tail clause as the splines: elements on which the reference's
+        # fp32-vs-fp64 gap exceeds a quarter of the tolerance are judged against the fp64 evaluation
+        r64 = g[direction + "_f64"]
+        assert_close_tail(got["z"], ref["z"], r64["z"], what=name + ".z", **tol)
+        assert_close_tail(got["log_det"], ref["log_det"], r64["log_det"], what=name + ".log_det",
+                          rtol=tol["rtol"], atol=tol["atol"] * n_sum)
+    else:
+        assert_close(got["z"], ref["z"], what=name + ".z", **tol)
+        assert_close(got["log_det"], ref["log_det"], what=name + ".log_det", rtol=tol["rtol"], atol=tol["atol"] * n_sum)
     if ref["gx"] is not None:
         assert_grads_close({"x": got["gx"], **got["grads"]}, {"x": ref["gx"], **ref["grads"]}, rtol=gtol, what=name)
 

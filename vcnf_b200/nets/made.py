@@ -4,6 +4,7 @@ import torch
 from torch import nn
 from torch.nn import functional as F, init
 
+from .. import ops
 from ..utils import tile
 
 
@@ -37,8 +38,15 @@ class MaskedLinear(nn.Linear):
             out_degrees = torch.arange(out_features) % max(1, d - 1) + min(1, d - 1)
         return (out_degrees[..., None] >= in_degrees).float(), out_degrees
 
-    def forward(self, x):
-        return F.linear(x, self.weight * self.mask, self.bias)
+    def forward(self, x, relu_in=False, residual=None):
+        """F.linear(act(x), W * mask, b) (+ residual) -- made.py:79-80.  fp32 CUDA operands run the tcgen05
+        3xTF32 kernels (ReLU, bias and the residual add fused; hidden widths > 128 as contraction slices);
+        fp64 models (`nfm.double()`) keep the library DGEMM: the tensor cores have no fp64-faithful path."""
+        w = self.weight * self.mask
+        if ops.linear_supported(x, w):
+            return ops.linear(x, w, self.bias, residual=residual, relu_in=relu_in)
+        y = F.linear(F.relu(x) if relu_in else x, w, self.bias)
+        return y if residual is None else residual + y
 
 
 class MaskedFeedforwardBlock(nn.Module):
@@ -87,6 +95,12 @@ class MaskedResidualBlock(nn.Module):
             init.uniform_(self.linear_layers[-1].bias, a=-1e-3, b=1e-3)
 
     def forward(self, inputs, context=None):
+        is_relu = self.activation is F.relu or self.activation is torch.relu or isinstance(self.activation, nn.ReLU)
+        if (context is None and not self.use_batch_norm and is_relu
+                and (self.dropout.p == 0. or not self.training)):
+            # both masked layers with the ReLU, the bias and the skip connection fused into the GEMM launches
+            t = self.linear_layers[0](inputs, relu_in=True)
+            return self.linear_layers[1](t, relu_in=True, residual=inputs)
         h = inputs
         if self.use_batch_norm:
             h = self.batch_norm_layers[0](h)

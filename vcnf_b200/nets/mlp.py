@@ -1,9 +1,11 @@
-"""MLP conditioner (reference: normflow/nets/mlp.py:7-58).  Round-1 status: the dense layers
-are library GEMMs (cuBLAS through nn.Linear); the fused in-kernel conditioner for the tiny nets
-of cfg 1 / cfg 4 and the tcgen05 path for hidden >= 128 are the next kernels."""
+"""MLP conditioner (reference: normflow/nets/mlp.py:7-58).  fp32 CUDA operands with the default
+`leaky=0.0` run every dense layer on the tcgen05 3xTF32 kernel (`ops.linear`), the ReLU fused into the
+load of the following layer; fp64 models (`nfm.double()`) and leaky slopes != 0 keep nn.Linear (library
+GEMM).  Same module tree / state_dict keys (`net.0.weight`, ...) as the reference either way."""
+import torch
 from torch import nn
 
-from .. import utils
+from .. import ops, utils
 
 
 class MLP(nn.Module):
@@ -32,4 +34,20 @@ class MLP(nn.Module):
         self.net = nn.Sequential(*stack)
 
     def forward(self, x):
-        return self.net(x)
+        if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2):
+            return self.net(x)
+        mods = list(self.net)
+        h, pending_relu = x, False
+        for i, m in enumerate(mods):
+            if isinstance(m, nn.Linear) and ops.linear_supported(h, m.weight):
+                h = ops.linear(h, m.weight, m.bias, relu_in=pending_relu)
+                pending_relu = False
+                continue
+            if pending_relu:
+                h, pending_relu = torch.relu(h), False
+            if (isinstance(m, nn.LeakyReLU) and m.negative_slope == 0.0 and i + 1 < len(mods)
+                    and isinstance(mods[i + 1], nn.Linear)):
+                pending_relu = True      # applied by the next layer's operand load
+            else:
+                h = m(h)
+        return torch.relu(h) if pending_relu else h

@@ -35,7 +35,7 @@ class ResidualBlock(nn.Module):
     def forward(self, inputs, context=None):
         if self._fast(inputs, context):
             l0, l1 = self.linear_layers
-            if l0.bias is not None and l1.bias is not None:
+            if l0.bias is not None and l1.bias is not None and ops.resblock_supported(inputs, l0.weight):
                 return ops.residual_block(inputs, l0.weight, l0.bias, l1.weight, l1.bias)
             t = ops.linear(inputs, l0.weight, l0.bias, relu_in=True)
             return ops.linear(t, l1.weight, l1.bias, residual=inputs, relu_in=True)
@@ -75,7 +75,8 @@ class ResidualNet(nn.Module):
     def forward(self, inputs, context=None):
         h = inputs if self.preprocessing is None else self.preprocessing(inputs)
         h = h if context is None else torch.cat((h, context), dim=1)
-        fast = ops.linear_supported(h, self.initial_layer.weight) and self.hidden_features <= 128
+        fast = (ops.linear_supported(h, self.initial_layer.weight)
+                and (self.hidden_features <= ops.KSLICE or self.hidden_features % 4 == 0))
         h = ops.linear(h, self.initial_layer.weight, self.initial_layer.bias) if fast else self.initial_layer(h)
         for block in self.blocks:
             h = block(h, context=context)

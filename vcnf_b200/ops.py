@@ -416,10 +416,19 @@ def lu_compose(lower_entries, upper_entries, unconstrained_upper_diag, eps):
     return _LuCompose.apply(lower_entries, upper_entries, unconstrained_upper_diag, eps)
 
 
+KSLICE = 128   # contraction width of one vcnf_linear_tf32x3 / vcnf_linear_wgrad_tf32x3 launch (W resident in TMEM)
+
+
 def linear_supported(x, weight):
-    """The tcgen05 3xTF32 kernel covers fp32 CUDA tensors with in_features <= 128."""
+    """The tcgen05 3xTF32 kernels cover fp32 CUDA row-major operands; in_features > 128 (MADE, hidden 256)
+    run as column slices of 128 that accumulate in place through the kernel's `residual` operand."""
     return (x.is_cuda and x.dtype == torch.float32 and weight.dtype == torch.float32 and x.dim() == 2
-            and weight.shape[1] <= 128)
+            and weight.dim() == 2 and x.shape[1] == weight.shape[1] and (weight.shape[1] <= KSLICE or weight.shape[1] % 4 == 0))
+
+
+def resblock_supported(x, weight):
+    """`residual_block` (one autograd node, four launches) needs square weights no wider than one slice."""
+    return linear_supported(x, weight) and weight.shape[0] == weight.shape[1] <= KSLICE
 
 
 class _Linear(torch.autograd.Function):
@@ -435,9 +444,13 @@ class _Linear(torch.autograd.Function):
         bias_ = bias.contiguous() if bias is not None else None
         res_ = _rows(residual) if residual is not None else None
         y = _padded_empty(M, N, x.dtype, x.device) if pad_out else torch.empty((M, N), dtype=x.dtype, device=x.device)
-        _launch("vcnf_linear_tf32x3", ptr(x), x.stride(0), ptr(weight), K, 1, ptr(bias_), ptr(res_),
-                res_.stride(0) if res_ is not None else 0, None, 0,
-                ptr(y), y.stride(0), M, N, K, int(relu_in), stream())
+        for k0 in range(0, K, KSLICE):
+            # in_features > 128: slices of the contraction accumulate in place (`residual` = y)
+            first = k0 == 0
+            r_ptr, r_ld = (ptr(res_), res_.stride(0) if res_ is not None else 0) if first else (ptr(y), y.stride(0))
+            _launch("vcnf_linear_tf32x3", ptr(x) + 4 * k0, x.stride(0), ptr(weight) + 4 * k0, K, 1,
+                    ptr(bias_) if first else None, r_ptr, r_ld, None, 0,
+                    ptr(y), y.stride(0), M, N, min(K, k0 + KSLICE) - k0, int(relu_in), stream())
         ctx.relu_in = bool(relu_in)
         ctx.has_bias, ctx.has_res = bias is not None, residual is not None
         ctx.save_for_backward(x, weight)
@@ -475,11 +488,23 @@ class _Linear(torch.autograd.Function):
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         if want_w or want_b:
             # gW = gy^T act(x), gb = column sums of gy: one split-K tcgen05 kernel + a fixed-order reduce
-            gw = torch.empty_like(weight)
             gb = torch.empty(N, dtype=x.dtype, device=x.device) if want_b else None
-            ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", M, N, K), dtype=torch.uint8, device=x.device)
-            _launch("vcnf_linear_wgrad_tf32x3", ptr(gy), ldg, ptr(x), ldx, ptr(gw), ptr(gb), ptr(ws), M, N, K,
-                    int(ctx.relu_in), stream(), n=2)
+            ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", M, N, min(K, KSLICE)), dtype=torch.uint8,
+                             device=x.device)
+            if K <= KSLICE:
+                gw = torch.empty_like(weight)
+                _launch("vcnf_linear_wgrad_tf32x3", ptr(gy), ldg, ptr(x), ldx, ptr(gw), ptr(gb), ptr(ws), M, N, K,
+                        int(ctx.relu_in), stream(), n=2)
+            else:
+                # in_features > 128: one launch per slice of input columns, gW slices joined afterwards
+                parts = []
+                for k0 in range(0, K, KSLICE):
+                    kw = min(K, k0 + KSLICE) - k0
+                    part = torch.empty((N, kw), dtype=x.dtype, device=x.device)
+                    _launch("vcnf_linear_wgrad_tf32x3", ptr(gy), ldg, ptr(x) + 4 * k0, ldx, ptr(part),
+                            ptr(gb) if k0 == 0 else None, ptr(ws), M, N, kw, int(ctx.relu_in), stream(), n=2)
+                    parts.append(part)
+                gw = torch.cat(parts, dim=1)
             if not want_w:
                 gw = None
         if ctx.has_res and ctx.needs_input_grad[3]:
