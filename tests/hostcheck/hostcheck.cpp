@@ -3,6 +3,7 @@
 // in the GPU-less build container.  Never linked into libvcnf_b200.so.
 #include <cstdint>
 #include "../../vcnf_b200/csrc/rqs_math.cuh"
+#include "../../vcnf_b200/csrc/rqs_fast.cuh"
 
 using namespace vcnf;
 
@@ -94,6 +95,59 @@ int hostcheck_rqs_table_bwd(const void* prm, const void* v, double bound, int64_
 #define CALL(T, KM) run_table_bwd<T, KM>((const T*)prm, (const T*)v, (T)bound, n, c, (const T*)gout, (const T*)glad, (T*)gv, (T*)gprm)
   if (is_double) { DISPATCH(double, CALL) } else { DISPATCH(float, CALL) }
 #undef CALL
+  return 0;
+}
+
+// ---- fp32 / K = 8 fast path (rqs_fast.cuh; the MUFU approximations are libm calls on the host) ----
+int hostcheck_rqs_fast_fwd(const float* prm, const float* v, const float* bound, int64_t n, int mode, int inverse,
+                           int outside_zero, double scale, float* out, float* lad, int32_t* bin) {
+  int flag = 0;
+  const int P = 16 + rqs_num_derivs(8, mode);
+  for (int64_t i = 0; i < n; ++i) {
+    int b = -1;
+    if (inverse) fast::element<8, true>(prm + i * P, v[i], bound[i], (float)scale, mode, outside_zero, out + i, lad + i, &b, &flag);
+    else fast::element<8, false>(prm + i * P, v[i], bound[i], (float)scale, mode, outside_zero, out + i, lad + i, &b, &flag);
+    bin[i] = b;
+  }
+  return flag;
+}
+int hostcheck_rqs_fast_bwd(const float* prm, const float* v, const float* bound, int64_t n, int mode, int inverse,
+                           int outside_zero, double scale, const float* gout, const float* glad, float* gv,
+                           float* gprm) {
+  const int P = 16 + rqs_num_derivs(8, mode);
+  for (int64_t i = 0; i < n; ++i) {
+    if (inverse) fast::element_bwd<8, true>(prm + i * P, v[i], bound[i], (float)scale, mode, outside_zero, gout[i], glad[i], gv + i, gprm + i * P);
+    else fast::element_bwd<8, false>(prm + i * P, v[i], bound[i], (float)scale, mode, outside_zero, gout[i], glad[i], gv + i, gprm + i * P);
+  }
+  return 0;
+}
+int hostcheck_rqs_fast_table_fwd(const float* prm, const float* v, double bound, int64_t n, int mode, int inverse,
+                                 int outside_zero, float* out, float* lad, int32_t* bin) {
+  float tab[27];
+  fast::Knot4 rec[9];
+  rqs_build_table<float, 8>(prm, 8, mode, (float)bound, tab);
+  fast::table_to_records<8>(tab, rec);
+  int flag = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    int b = -1;
+    if (inverse) fast::table_element<8, true>(rec, v[i], (float)bound, outside_zero, out + i, lad + i, &b, &flag);
+    else fast::table_element<8, false>(rec, v[i], (float)bound, outside_zero, out + i, lad + i, &b, &flag);
+    bin[i] = b;
+  }
+  return flag;
+}
+int hostcheck_rqs_fast_table_bwd(const float* prm, const float* v, double bound, int64_t n, int mode, int inverse,
+                                 int outside_zero, const float* gout, const float* glad, float* gv, float* gprm) {
+  float tab[27], gtab[27];
+  fast::Knot4 rec[9];
+  rqs_build_table<float, 8>(prm, 8, mode, (float)bound, tab);
+  fast::table_to_records<8>(tab, rec);
+  for (int i = 0; i < 27; ++i) gtab[i] = 0.f;
+  for (int64_t i = 0; i < n; ++i) {
+    if (inverse) fast::table_element_bwd<8, true>(rec, v[i], (float)bound, outside_zero, gout[i], glad[i], gv + i, gtab);
+    else fast::table_element_bwd<8, false>(rec, v[i], (float)bound, outside_zero, gout[i], glad[i], gv + i, gtab);
+  }
+  rqs_table_to_raw_grad<float, 8>(prm, 8, mode, (float)bound, gtab, gprm);
   return 0;
 }
 }

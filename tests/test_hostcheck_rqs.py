@@ -18,8 +18,8 @@ MODES = {"linear": 0, "circular": 1, "list_linear": 2, "list_circular": 3}
 
 @pytest.fixture(scope="module")
 def lib():
-    hdr = os.path.join(HERE, "..", "vcnf_b200", "csrc", "rqs_math.cuh")
-    if not os.path.exists(LIB) or os.path.getmtime(LIB) < max(os.path.getmtime(SRC), os.path.getmtime(hdr)):
+    hdrs = [os.path.join(HERE, "..", "vcnf_b200", "csrc", h) for h in ("rqs_math.cuh", "rqs_fast.cuh")]
+    if not os.path.exists(LIB) or os.path.getmtime(LIB) < max(map(os.path.getmtime, [SRC] + hdrs)):
         subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-o", LIB, SRC])
     return ctypes.CDLL(LIB)
 
@@ -154,3 +154,93 @@ def test_shared_table_path_matches_oracle(lib, K, mode, inverse, dtype):
         assert float(inside.float().mean()) >= 0.999
         e = (gp - gp_ref).abs() / (1e-3 * gp_ref.abs() + 1e-3 * float(gp_ref.abs().max()))
         assert float(e.max()) <= 1.0
+
+
+@pytest.mark.parametrize("inverse", [0, 1])
+@pytest.mark.parametrize("mode", sorted(MODES))
+def test_fast_path_element_math_matches_oracle(lib, mode, inverse):
+    """rqs_fast.cuh (fp32, K = 8: packed two-axis evaluation, reciprocal / series closed forms) against the
+    oracle: bin indices exact, values and gradients under the same fp32 clauses as the generic path."""
+    K, dtype = 8, torch.float32
+    g = torch.Generator().manual_seed(80 + inverse)
+    n, bound, scale = 6000, 3.0, 0.7
+    nd = {0: K - 1, 1: K}.get(MODES[mode], K + 1)
+    P = 2 * K + nd
+    prm = torch.randn(n, 1, P, generator=g, dtype=torch.float64).to(dtype)
+    prm[:, :, 2 * K:] *= 4.0                                  # softplus arguments over [-15, 15]
+    x = (1.4 * torch.randn(n, 1, generator=g, dtype=torch.float64)).to(dtype)
+    x[0], x[1], x[2] = bound, -bound, float("nan")
+    gout = torch.randn(n, 1, generator=g, dtype=torch.float64).to(dtype)
+    glad = torch.randn(n, 1, generator=g, dtype=torch.float64).to(dtype)
+    xr, pr = x.clone().requires_grad_(True), prm.clone().requires_grad_(True)
+    y_ref, lad_ref, bin_ref = _oracle(xr, pr, K, mode, bool(inverse), bound, scale)
+    ok = ~torch.isnan(x)
+    loss = (y_ref * gout)[ok].sum() + (lad_ref * glad)[ok].sum()
+    gx_ref, gp_ref = torch.autograd.grad(loss, [xr, pr])
+    xd, pd = x.double().requires_grad_(True), prm.double().requires_grad_(True)
+    y64, lad64, _ = _oracle(xd, pd, K, mode, bool(inverse), bound, scale)
+    gx64, gp64 = torch.autograd.grad((y64 * gout.double())[ok].sum() + (lad64 * glad.double())[ok].sum(), [xd, pd])
+
+    out, lad = torch.empty_like(x), torch.empty_like(x)
+    bins = torch.empty(n, dtype=torch.int32)
+    bnd = torch.full_like(x, bound)
+    oz = int(mode.startswith("list"))
+    lib.hostcheck_rqs_fast_fwd.restype = ctypes.c_int
+    flag = lib.hostcheck_rqs_fast_fwd(_ptr(prm), _ptr(x), _ptr(bnd), ctypes.c_int64(n), MODES[mode], inverse, oz,
+                                      ctypes.c_double(scale), _ptr(out), _ptr(lad), _ptr(bins))
+    assert flag == 0
+    gv, gp = torch.empty_like(x), torch.empty_like(prm)
+    lib.hostcheck_rqs_fast_bwd(_ptr(prm), _ptr(x), _ptr(bnd), ctypes.c_int64(n), MODES[mode], inverse, oz,
+                               ctypes.c_double(scale), _ptr(gout), _ptr(glad), _ptr(gv), _ptr(gp))
+    m = ok[:, 0]
+    assert torch.isnan(out[2]).all() == torch.isnan(y_ref[2]).all()
+    assert int((bins[m] != bin_ref[:, 0][m].int()).sum()) == 0
+    for got, r32, r64, frac in ((out, y_ref.detach(), y64.detach(), 0.999), (lad, lad_ref.detach(), lad64.detach(), 0.99)):
+        inside = (got[m] - r32[m]).abs() <= 1e-5 + 1e-4 * r32[m].abs()
+        assert float(inside.float().mean()) >= frac
+        e64 = float((got[m].double() - r64[m]).abs().max())
+        ref_e = float((r32[m].double() - r64[m]).abs().max())
+        assert e64 <= 2 * ref_e + 1e-4
+    # gradients against the fp64 oracle, relative to the largest entry (fp32 rounding only)
+    for got, r64 in ((gv, gx64), (gp, gp64)):
+        e = (got[m].double() - r64[m]).abs() / (1e-3 * r64[m].abs() + 1e-4 * float(r64[m].abs().max()))
+        assert float((e <= 1).float().mean()) > 0.999
+
+
+@pytest.mark.parametrize("inverse", [0, 1])
+@pytest.mark.parametrize("mode", sorted(MODES))
+def test_fast_path_shared_table_matches_oracle(lib, mode, inverse):
+    K, dtype = 8, torch.float32
+    g = torch.Generator().manual_seed(90 + inverse)
+    n, bound = 5000, 3.0
+    nd = {0: K - 1, 1: K}.get(MODES[mode], K + 1)
+    P = 2 * K + nd
+    prm = torch.randn(P, generator=g, dtype=torch.float64).to(dtype)
+    x = (1.4 * torch.randn(n, 1, generator=g, dtype=torch.float64)).to(dtype)
+    x[0], x[1] = bound, -bound
+    gout = torch.randn(n, 1, generator=g, dtype=torch.float64).to(dtype)
+    glad = torch.randn(n, 1, generator=g, dtype=torch.float64).to(dtype)
+    xd, pd = x.double().requires_grad_(True), prm.double().requires_grad_(True)
+    y64, lad64, bin_ref = _oracle(xd, pd.expand(n, 1, P), K, mode, bool(inverse), bound, 1.0)
+    gx64, gp64 = torch.autograd.grad((y64 * gout.double()).sum() + (lad64 * glad.double()).sum(), [xd, pd])
+    _, _, bin32 = _oracle(x, prm.expand(n, 1, P), K, mode, bool(inverse), bound, 1.0)
+
+    out, lad = torch.empty_like(x), torch.empty_like(x)
+    bins = torch.empty(n, dtype=torch.int32)
+    oz = int(mode.startswith("list"))
+    lib.hostcheck_rqs_fast_table_fwd.restype = ctypes.c_int
+    flag = lib.hostcheck_rqs_fast_table_fwd(_ptr(prm), _ptr(x), ctypes.c_double(bound), ctypes.c_int64(n),
+                                            MODES[mode], inverse, oz, _ptr(out), _ptr(lad), _ptr(bins))
+    assert flag == 0
+    gv, gp = torch.empty_like(x), torch.empty_like(prm)
+    lib.hostcheck_rqs_fast_table_bwd(_ptr(prm), _ptr(x), ctypes.c_double(bound), ctypes.c_int64(n), MODES[mode],
+                                     inverse, oz, _ptr(gout), _ptr(glad), _ptr(gv), _ptr(gp))
+    assert int((bins != bin32[:, 0].int()).sum()) == 0
+    inside = (out.double() - y64.detach()).abs() <= 1e-5 + 1e-4 * y64.detach().abs()
+    assert float(inside.float().mean()) >= 0.999
+    inside = (lad.double() - lad64.detach()).abs() <= 1e-5 + 1e-4 * lad64.detach().abs()
+    assert float(inside.float().mean()) >= 0.99
+    e = (gp.double() - gp64).abs() / (1e-3 * gp64.abs() + 1e-3 * float(gp64.abs().max()))
+    assert float(e.max()) <= 1.0
+    e = (gv.double() - gx64).abs() / (1e-3 * gx64.abs() + 1e-4 * float(gx64.abs().max()))
+    assert float((e <= 1).float().mean()) > 0.999

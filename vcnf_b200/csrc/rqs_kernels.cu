@@ -23,8 +23,10 @@
 //   * batch-shared parameter gradients: every thread owns a private accumulator table in shared
 //     memory (no atomics), reduced per CTA in a fixed order, chained back to the raw parameters
 //     once per CTA and finished by rqs_partial_reduce_kernel (deterministic two-stage reduction).
+#include <cstdlib>
 #include "common.cuh"
 #include "rqs_math.cuh"
+#include "rqs_fast.cuh"
 #include "../../include/vcnf_b200.h"
 
 namespace vcnf {
@@ -432,6 +434,194 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerA
   }
 }
 
+// =====================================================================================================
+// fp32 / K = 8 fast path (rqs_fast.cuh) -- the default configuration of every spline wrapper.
+//
+// Differences from the generic kernels above:
+//   * WARP-PRIVATE pipelines: a tile is R = 8 * rpw rows and warp w owns rows [w*rpw, (w+1)*rpw) through
+//     all passes (conditional elements, batch-shared elements, row stores + log-det), so the only
+//     synchronisation inside the tile loop is __syncwarp plus two mbarriers per stage: `full` (TMA
+//     transaction bytes) and `empty` (one arrival per warp when its reads of the stage are done; the
+//     producer lane waits on it before re-arming the stage).  No CTA-wide barrier on the fast path.
+//   * element math evaluated as packed f32x2 streams (both spline axes per instruction) with MUFU
+//     approximations; knot records {X, Y, D} for the batch-shared parameters, searched by bisection;
+//   * row / column of an element from a multiply-shift instead of an integer division.
+// =====================================================================================================
+constexpr int kWarps = kThreads / 32;
+
+struct FastSmem {
+  size_t bars, pst, pst_stride, xst, xst_stride, gyst, outs, lads, gst, gst_stride, tab, rec, acc, tabg, meta, total;
+};
+__host__ __device__ inline FastSmem fast_smem_layout(int R, int D, int Tc, int Ts, bool bwd, int prow, int grow,
+                                                     int nst) {
+  FastSmem m;
+  size_t o = 0;
+  m.bars = o; o += 128;
+  m.pst_stride = round_up(static_cast<size_t>(R) * prow * sizeof(float), 128);
+  m.pst = o; o += nst * m.pst_stride;
+  m.xst_stride = round_up(static_cast<size_t>(R) * D * sizeof(float), 128);
+  m.xst = o; o += nst * m.xst_stride;
+  m.gyst = o; if (bwd) o += nst * m.xst_stride;
+  m.outs = o; o += m.xst_stride;
+  m.lads = o; if (!bwd) o += m.xst_stride;
+  m.gst_stride = round_up(static_cast<size_t>(R) * grow * sizeof(float), 128);
+  m.gst = o; if (bwd) o += 2 * m.gst_stride;          // double-buffered: the bulk store of tile i drains during tile i+1
+  const size_t TK = 3 * 9;
+  m.tab = o; o += round_up(Ts * TK * sizeof(float), 128);
+  m.rec = o; o += round_up(static_cast<size_t>(Ts) * 9 * sizeof(fast::Knot4), 128);
+  m.acc = o; if (bwd && Ts > 0) o += round_up(static_cast<size_t>(kThreads / Ts) * Ts * TK * sizeof(float), 128);
+  m.tabg = o; if (bwd) o += round_up(Ts * TK * sizeof(float), 128);
+  m.meta = o; o += round_up((2 * static_cast<size_t>(Tc) + 2 * D + 2 * Ts) * sizeof(int32_t), 16) +
+                   round_up((static_cast<size_t>(Tc) + Ts) * sizeof(float), 16);
+  m.total = o;
+  return m;
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// e / n for 0 <= e < 2^20 / n  (magic = 2^20 / n + 1), or a real division when the host passed magic 0
+__device__ __forceinline__ int fast_div(int e, int n, uint32_t magic) {
+  return magic ? static_cast<int>((static_cast<uint32_t>(e) * magic) >> 20) : e / n;
+}
+
+struct FastExtra { uint32_t magic_tc, magic_no; };
+
+template <bool INV, int NST>
+__global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsLayerArgs<float> a, const FastExtra fx) {
+  constexpr int K = 8, TK = 27;
+  extern __shared__ __align__(128) unsigned char smem[];
+  __shared__ int n_other_s;
+  const FastSmem L = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, false, a.prow, a.grow, NST);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars);
+  uint64_t* empty = full + NST;
+  float* ys = reinterpret_cast<float*>(smem + L.outs);
+  float* lads = reinterpret_cast<float*>(smem + L.lads);
+  fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(smem + L.rec);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kWarps); }
+    mbar_init_fence();
+  }
+  RqsSmem G;                       // the generic setup only needs these two offsets
+  G.meta = L.meta; G.tab = L.tab;
+  const RqsMeta<float> M = rqs_setup<float, K>(a, K, smem, G, &n_other_s);   // ends with __syncthreads()
+  for (int j = tid; j < a.Ts; j += kThreads)
+    fast::table_to_records<K>(reinterpret_cast<const float*>(smem + L.tab) + j * TK, rec + j * (K + 1));
+  __syncthreads();
+  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
+  const int rpw = a.R / kWarps;
+  const int r_lo = warp * rpw;
+
+  int flag = 0;
+  int64_t tile = blockIdx.x;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST - 1; ++s) {
+      const int64_t t = tile + static_cast<int64_t>(s) * gridDim.x;
+      if (t < a.num_tiles)
+        stage_issue<float, false>(a, t, reinterpret_cast<float*>(smem + L.pst + s * L.pst_stride),
+                                  reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride), nullptr, &full[s]);
+    }
+  }
+  for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
+    const int s = it % NST;
+    if (tid == 0) {                                    // producer lane: re-arm the stage read in iteration it-1
+      const int64_t nt = tile + static_cast<int64_t>(NST - 1) * gridDim.x;
+      if (nt < a.num_tiles) {
+        const int ps = (it + NST - 1) % NST;
+        if (it >= 1) mbar_wait(&empty[ps], static_cast<uint32_t>(((it - 1) / NST) & 1));
+        stage_issue<float, false>(a, nt, reinterpret_cast<float*>(smem + L.pst + ps * L.pst_stride),
+                                  reinterpret_cast<float*>(smem + L.xst + ps * L.xst_stride), nullptr, &full[ps]);
+      }
+    }
+    __syncwarp();
+    float* cur = reinterpret_cast<float*>(smem + L.pst + s * L.pst_stride);
+    float* xs = reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride);
+    const int64_t row0 = tile * a.R;
+    const int rows = static_cast<int>(imin64(a.R, a.B - row0));
+    {
+      // spans the TMA engine could not take (ragged last tile, unaligned views) are copied cooperatively;
+      // this is the only CTA-wide synchronisation and it is off the steady-state path
+      const int64_t np = static_cast<int64_t>(rows) * a.prow, nx = static_cast<int64_t>(rows) * D;
+      const bool bp = Tc > 0 && span_bulk<float>(a.bulk_p, np);
+      const bool bx = span_bulk<float>(a.bulk_x, nx);
+      if ((Tc > 0 && !bp) || !bx) __syncthreads();
+      const bool used = stage_wait<float, false>(a, tile, cur, xs, nullptr, &full[s], static_cast<uint32_t>((it / NST) & 1));
+      (void)used;
+      if ((Tc > 0 && !bp) || !bx) __syncthreads();
+    }
+    const int nrow = rows - r_lo < rpw ? rows - r_lo : rpw;       // rows of this warp in this tile (may be <= 0)
+
+    // pass A: conditional elements of this warp's rows
+    const int nA = nrow * Tc;
+    for (int e = lane; e < nA; e += 32) {
+      const int rr = fast_div(e, Tc, fx.magic_tc);
+      const int j = e - rr * Tc;
+      const int r = r_lo + rr;
+      const int c = M.cond_col[j];
+      float out, lad;
+      int bin;
+      fast::element<K, INV>(cur + static_cast<size_t>(r) * a.prow + j * Pc, xs[r * D + c], M.cbound[j], a.wh_scale,
+                            M.cmode[j], a.outside_zero, &out, &lad, &bin, &flag);
+      ys[r * D + c] = out;
+      lads[r * D + c] = lad;
+      if (a.bin_out) a.bin_out[(row0 + r) * D + c] = static_cast<int8_t>(bin);
+    }
+    // pass B: batch-shared and pass-through elements
+    const int nB = nrow * No;
+    for (int e = lane; e < nB; e += 32) {
+      const int rr = fast_div(e, No, fx.magic_no);
+      const int j = e - rr * No;
+      const int r = r_lo + rr;
+      const int c = M.other_col[j];
+      const int cm = M.other_map[j];
+      const float v = xs[r * D + c];
+      float out = v, lad = 0.f;
+      int bin = -2;
+      if ((cm >> 16) == VCNF_COL_SHARED) {
+        const int idx = cm & 0xffff;
+        fast::table_element<K, INV>(rec + idx * (K + 1), v, M.sbound[idx], a.outside_zero, &out, &lad, &bin, &flag);
+      }
+      ys[r * D + c] = out;
+      lads[r * D + c] = lad;
+      if (a.bin_out) a.bin_out[(row0 + r) * D + c] = static_cast<int8_t>(bin);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);             // this warp is done reading the stage
+
+    // pass C: this warp's rows leave as one contiguous span; per-sample log|det| (half-warp per row)
+    if (nrow > 0) {
+      const int n = nrow * D;
+      const float* src = ys + r_lo * D;
+      if (a.ldy == D) {
+        float* dst = a.y + (row0 + r_lo) * D;
+        for (int e = lane; e < n; e += 32) dst[e] = src[e];
+      } else {
+        for (int rr = 0; rr < nrow; ++rr)
+          for (int c = lane; c < D; c += 32) a.y[(row0 + r_lo + rr) * a.ldy + c] = src[rr * D + c];
+      }
+      const int hl = lane & 15;
+      for (int rr0 = 0; rr0 < nrow; rr0 += 2) {
+        const int rr = rr0 + (lane >> 4);
+        float acc = 0.f;
+        if (rr < nrow)
+          for (int c = hl; c < D; c += 16) acc += lads[(r_lo + rr) * D + c];
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (rr < nrow && hl == 0) {
+          const int64_t g = row0 + r_lo + rr;
+          a.logdet[g] = a.accumulate ? acc + a.logdet[g] : acc;
+        }
+      }
+    }
+    __syncwarp();                                      // ys / lads rows are rewritten by other lanes next tile
+  }
+  if (flag && a.err_flag) atomicOr(a.err_flag, flag);
+}
+
 template <typename T>
 __global__ void rqs_partial_reduce_kernel(const T* partial, int nblocks, int n, T* out) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -578,10 +768,74 @@ static int launch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
   return rc;
 }
 
+// Rows per tile of the fast kernels: 8 warps x rpw rows; the parameter block of a stage stays within the
+// budget and rpw*Tc fills whole warp passes best.
+static int pick_rows_fast(int Tc, int prow, int D, size_t budget) {
+  const size_t per_row = static_cast<size_t>(Tc > 0 ? prow : D) * sizeof(float);
+  const int width = Tc > 0 ? Tc : D;
+  int best = 1;
+  double best_u = -1.0;
+  for (int rpw = 1; rpw <= 8; ++rpw) {
+    if (rpw > 1 && static_cast<size_t>(rpw) * kWarps * per_row > budget) break;
+    if ((rpw * kWarps) % 4 != 0) continue;
+    const int n = rpw * width;
+    const double u = static_cast<double>(n) / (static_cast<double>((n + 31) / 32) * 32);
+    if (u > best_u + 1e-9) { best_u = u; best = rpw; }
+  }
+  return best * kWarps;
+}
+
+static uint32_t div_magic(int n, int64_t max_e) {
+  if (n <= 0) return 0;
+  return (max_e * n < (1 << 20)) ? static_cast<uint32_t>((1u << 20) / static_cast<uint32_t>(n) + 1u) : 0u;
+}
+
+constexpr int kFastStages = 2;
+
+// VCNF_RQS_GENERIC=1 routes fp32 / K = 8 layers through the generic kernels (A/B measurements, tests)
+static bool generic_only() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VCNF_RQS_GENERIC"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+
+template <bool INV>
+static int launch_fwd_fast(RqsLayerArgs<float>& a, cudaStream_t st) {
+  const int sms = sm_count();
+  if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
+  set_pitches(a, false);
+  a.R = pick_rows_fast(a.Tc, a.prow, a.D, 24 * 1024);
+  a.num_tiles = (a.B + a.R - 1) / a.R;
+  set_bulk_flags(a, false);
+  const size_t smem = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, false, a.prow, a.grow, kFastStages).total;
+  if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
+  auto kern = rqs_layer_fwd_fast_kernel<INV, kFastStages>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax - 2048));
+    attr_set = true;
+  }
+  int per_sm = static_cast<int>(kSmemMax / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+  const int64_t grid = a.num_tiles < static_cast<int64_t>(sms) * per_sm ? a.num_tiles : static_cast<int64_t>(sms) * per_sm;
+  FastExtra fx;
+  fx.magic_tc = div_magic(a.Tc, static_cast<int64_t>(a.R) * a.Tc);
+  const int n_other = a.D - a.Tc;          // every column is conditional, batch-shared or pass-through
+  fx.magic_no = div_magic(n_other, static_cast<int64_t>(a.R) * n_other);
+  kern<<<static_cast<unsigned>(grid), kThreads, smem, st>>>(a, fx);
+  return launch_status();
+}
+
 // K == 8 (the default of every spline wrapper, neural_spline/wrapper.py:20-31) gets a fully unrolled
 // instantiation; other bin counts run the bounded-loop instantiation of the same code.
 template <typename T>
 static int dispatch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
+  if constexpr (sizeof(T) == 4) {
+    if (a.K == 8 && !generic_only()) {
+      const int rc = a.inverse ? launch_fwd_fast<true>(a, st) : launch_fwd_fast<false>(a, st);
+      if (rc != VCNF_E_UNSUPPORTED) return rc;
+    }
+  }
   if (a.K == 8) return launch_fwd<T, 8, true>(a, st);
   if (a.K < 8) return launch_fwd<T, 8, false>(a, st);
   if (a.K <= 16) return launch_fwd<T, 16, false>(a, st);
