@@ -123,10 +123,8 @@ int hostcheck_rqs_fast_bwd(const float* prm, const float* v, const float* bound,
 }
 int hostcheck_rqs_fast_table_fwd(const float* prm, const float* v, double bound, int64_t n, int mode, int inverse,
                                  int outside_zero, float* out, float* lad, int32_t* bin) {
-  float tab[27];
   fast::Knot4 rec[9];
-  rqs_build_table<float, 8>(prm, 8, mode, (float)bound, tab);
-  fast::table_to_records<8>(tab, rec);
+  fast::build_records<8>(prm, mode, (float)bound, rec);
   int flag = 0;
   for (int64_t i = 0; i < n; ++i) {
     int b = -1;
@@ -138,10 +136,9 @@ int hostcheck_rqs_fast_table_fwd(const float* prm, const float* v, double bound,
 }
 int hostcheck_rqs_fast_table_bwd(const float* prm, const float* v, double bound, int64_t n, int mode, int inverse,
                                  int outside_zero, const float* gout, const float* glad, float* gv, float* gprm) {
-  float tab[27], gtab[27];
+  float gtab[27];
   fast::Knot4 rec[9];
-  rqs_build_table<float, 8>(prm, 8, mode, (float)bound, tab);
-  fast::table_to_records<8>(tab, rec);
+  fast::build_records<8>(prm, mode, (float)bound, rec);
   for (int i = 0; i < 27; ++i) gtab[i] = 0.f;
   for (int64_t i = 0; i < n; ++i) {
     if (inverse) fast::table_element_bwd<8, true>(rec, v[i], (float)bound, outside_zero, gout[i], glad[i], gv + i, gtab);

@@ -212,11 +212,21 @@ VCNF_HD void element(const float* prm, float v, float bound, float scale, int mo
 }
 
 // ---- batch-shared parameters: knot records built once per CTA -------------------------------------
-// rec[k] = {X_k, Y_k, D_k}, k = 0..K, from the generic table of rqs_build_table (same values).
+// rec[k] = {X_k, Y_k, D_k}, k = 0..K (same arithmetic as the per-element path).
 template <int K>
-VCNF_HD void table_to_records(const float* tab, Knot4* rec) {
-  const int KT = K + 1;
-  for (int k = 0; k <= K; ++k) rec[k] = Knot4{tab[k], tab[KT + k], tab[2 * KT + k], 0.f};
+VCNF_HD void build_records(const float* prm, int mode, float bound, Knot4* rec) {
+  P2 p[K], kn[K + 1];
+  axes<K>(prm, 1.f, bound, p, kn);
+  const float edge = RqsConst<float>::edge();
+  for (int k = 0; k <= K; k += 2) {
+    int s;
+    const float ra = rqs_raw_deriv(prm + 2 * K, k, K, mode, edge, &s);
+    const float rb = (k + 1 <= K) ? rqs_raw_deriv(prm + 2 * K, k + 1, K, mode, edge, &s) : edge;
+    P2 e;
+    const P2 sp = softplus2(P2{ra, rb}, &e);
+    rec[k] = Knot4{kn[k].x, kn[k].y, RqsConst<float>::min_deriv() + sp.x, 0.f};
+    if (k + 1 <= K) rec[k + 1] = Knot4{kn[k + 1].x, kn[k + 1].y, RqsConst<float>::min_deriv() + sp.y, 0.f};
+  }
 }
 
 template <int K, bool INV>

@@ -449,6 +449,10 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_kernel(const RqsLayerA
 // =====================================================================================================
 constexpr int kWarps = kThreads / 32;
 
+// Batch-shared features in the backward: lane <-> (row group g, feature jo) is fixed for the whole launch so
+// that every lane owns a private gradient table (no atomics): 32/Ts row groups per warp when Ts <= 32.
+__host__ __device__ inline int fast_slots(int Ts) { return Ts <= 0 ? 0 : (Ts <= 32 ? (32 / Ts) * Ts : Ts); }
+
 struct FastSmem {
   size_t bars, pst, pst_stride, xst, xst_stride, gyst, outs, lads, gst, gst_stride, tab, rec, acc, tabg, meta, total;
 };
@@ -465,11 +469,12 @@ __host__ __device__ inline FastSmem fast_smem_layout(int R, int D, int Tc, int T
   m.outs = o; o += m.xst_stride;
   m.lads = o; if (!bwd) o += m.xst_stride;
   m.gst_stride = round_up(static_cast<size_t>(R) * grow * sizeof(float), 128);
-  m.gst = o; if (bwd) o += 2 * m.gst_stride;          // double-buffered: the bulk store of tile i drains during tile i+1
+  m.gst = o; if (bwd) o += m.gst_stride;
   const size_t TK = 3 * 9;
-  m.tab = o; o += round_up(Ts * TK * sizeof(float), 128);
+  m.tab = o;
   m.rec = o; o += round_up(static_cast<size_t>(Ts) * 9 * sizeof(fast::Knot4), 128);
-  m.acc = o; if (bwd && Ts > 0) o += round_up(static_cast<size_t>(kThreads / Ts) * Ts * TK * sizeof(float), 128);
+  // backward: one private accumulator table per (warp, slot); a slot is a (row group, shared feature) pair
+  m.acc = o; if (bwd && Ts > 0) o += round_up(static_cast<size_t>(kWarps) * fast_slots(Ts) * TK * sizeof(float), 128);
   m.tabg = o; if (bwd) o += round_up(Ts * TK * sizeof(float), 128);
   m.meta = o; o += round_up((2 * static_cast<size_t>(Tc) + 2 * D + 2 * Ts) * sizeof(int32_t), 16) +
                    round_up((static_cast<size_t>(Tc) + Ts) * sizeof(float), 16);
@@ -486,13 +491,56 @@ __device__ __forceinline__ int fast_div(int e, int n, uint32_t magic) {
   return magic ? static_cast<int>((static_cast<uint32_t>(e) * magic) >> 20) : e / n;
 }
 
-struct FastExtra { uint32_t magic_tc, magic_no; };
+// Column lists, tail modes, bounds and the knot records of the batch-shared features, built by all threads
+// in parallel (the generic rqs_setup walks the columns on one thread and runs the libm softmax per feature:
+// 7 us of a 38 us launch under ncu).  The outs tile is free before the tile loop and holds the raw column map.
+template <int K>
+__device__ __forceinline__ RqsMeta<float> fast_setup(const RqsLayerArgs<float>& a, unsigned char* smem,
+                                                     const FastSmem& L, fast::Knot4* rec) {
+  RqsMeta<float> m;
+  int32_t* ip = reinterpret_cast<int32_t*>(smem + L.meta);
+  m.cond_col = ip; ip += a.Tc;
+  m.other_col = ip; ip += a.D;
+  m.other_map = ip; ip += a.D;
+  m.cmode = ip; ip += a.Tc;
+  m.smode = ip; ip += a.Ts;
+  m.shared_col = ip; ip += a.Ts;
+  float* tp = reinterpret_cast<float*>(smem + L.meta + round_up((2 * static_cast<size_t>(a.Tc) + 2 * a.D + 2 * a.Ts) * sizeof(int32_t), 16));
+  m.cbound = tp; tp += a.Tc;
+  m.sbound = tp;
+  int32_t* raw = reinterpret_cast<int32_t*>(smem + L.outs);
+  const int tid = threadIdx.x;
+  for (int c = tid; c < a.D; c += kThreads) raw[c] = a.col_map[c];
+  for (int j = tid; j < a.Tc; j += kThreads) { m.cmode[j] = a.cmodes[j]; m.cbound[j] = a.cbounds[j]; }
+  for (int j = tid; j < a.Ts; j += kThreads) {
+    const int mode = a.smodes[j];
+    const float bound = a.sbounds[j];
+    m.smode[j] = mode; m.sbound[j] = bound; m.shared_col[j] = -1;
+    fast::build_records<K>(a.shared + static_cast<size_t>(j) * a.Ps, mode, bound, rec + j * (K + 1));
+  }
+  __syncthreads();
+  for (int c = tid; c < a.D; c += kThreads) {
+    const int cm = raw[c];
+    if ((cm >> 16) == VCNF_COL_COND) {
+      m.cond_col[cm & 0xffff] = c;
+    } else {
+      int n = 0;
+      for (int q = 0; q < c; ++q) n += ((raw[q] >> 16) != VCNF_COL_COND) ? 1 : 0;
+      m.other_col[n] = c; m.other_map[n] = cm;
+      if ((cm >> 16) == VCNF_COL_SHARED) m.shared_col[cm & 0xffff] = c;
+    }
+  }
+  __syncthreads();
+  m.n_other = a.D - a.Tc;
+  return m;
+}
+
+struct FastExtra { uint32_t magic_tc, magic_no, magic_ts; };
 
 template <bool INV, int NST>
 __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsLayerArgs<float> a, const FastExtra fx) {
-  constexpr int K = 8, TK = 27;
+  constexpr int K = 8;
   extern __shared__ __align__(128) unsigned char smem[];
-  __shared__ int n_other_s;
   const FastSmem L = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, false, a.prow, a.grow, NST);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars);
   uint64_t* empty = full + NST;
@@ -505,15 +553,13 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
     for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kWarps); }
     mbar_init_fence();
   }
-  RqsSmem G;                       // the generic setup only needs these two offsets
-  G.meta = L.meta; G.tab = L.tab;
-  const RqsMeta<float> M = rqs_setup<float, K>(a, K, smem, G, &n_other_s);   // ends with __syncthreads()
-  for (int j = tid; j < a.Ts; j += kThreads)
-    fast::table_to_records<K>(reinterpret_cast<const float*>(smem + L.tab) + j * TK, rec + j * (K + 1));
-  __syncthreads();
+  const RqsMeta<float> M = fast_setup<K>(a, smem, L, rec);   // ends with __syncthreads()
   const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
   const int rpw = a.R / kWarps;
   const int r_lo = warp * rpw;
+  // a full tile whose spans all go through the TMA engine needs nothing but the mbarrier wait
+  const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
+                               span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D);
 
   int flag = 0;
   int64_t tile = blockIdx.x;
@@ -542,16 +588,14 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
     float* xs = reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride);
     const int64_t row0 = tile * a.R;
     const int rows = static_cast<int>(imin64(a.R, a.B - row0));
-    {
+    if (rows == a.R && full_tiles_bulk) {
+      mbar_wait(&full[s], static_cast<uint32_t>((it / NST) & 1));
+    } else {
       // spans the TMA engine could not take (ragged last tile, unaligned views) are copied cooperatively;
       // this is the only CTA-wide synchronisation and it is off the steady-state path
-      const int64_t np = static_cast<int64_t>(rows) * a.prow, nx = static_cast<int64_t>(rows) * D;
-      const bool bp = Tc > 0 && span_bulk<float>(a.bulk_p, np);
-      const bool bx = span_bulk<float>(a.bulk_x, nx);
-      if ((Tc > 0 && !bp) || !bx) __syncthreads();
-      const bool used = stage_wait<float, false>(a, tile, cur, xs, nullptr, &full[s], static_cast<uint32_t>((it / NST) & 1));
-      (void)used;
-      if ((Tc > 0 && !bp) || !bx) __syncthreads();
+      __syncthreads();
+      stage_wait<float, false>(a, tile, cur, xs, nullptr, &full[s], static_cast<uint32_t>((it / NST) & 1));
+      __syncthreads();
     }
     const int nrow = rows - r_lo < rpw ? rows - r_lo : rpw;       // rows of this warp in this tile (may be <= 0)
 
@@ -620,6 +664,183 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
     __syncwarp();                                      // ys / lads rows are rewritten by other lanes next tile
   }
   if (flag && a.err_flag) atomicOr(a.err_flag, flag);
+}
+
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
+// Backward fast path: same warp-private pipeline as the forward.  Each warp owns its rows of the parameter-
+// gradient tile and sends them to HBM with its own bulk store (drains while the warp works on the next tile's
+// batch-shared elements); batch-shared gradients go to lane-private tables, summed in a fixed order at the end.
+template <bool INV, int NST>
+__global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsLayerArgs<float> a, const FastExtra fx) {
+  constexpr int K = 8, TK = 27;
+  extern __shared__ __align__(128) unsigned char smem[];
+  const FastSmem L = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, true, a.prow, a.grow, NST);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bars);
+  uint64_t* empty = full + NST;
+  float* gxs = reinterpret_cast<float*>(smem + L.outs);
+  float* gst = reinterpret_cast<float*>(smem + L.gst);
+  fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(smem + L.rec);
+  float* acc = reinterpret_cast<float*>(smem + L.acc);
+  float* tabg = reinterpret_cast<float*>(smem + L.tabg);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kWarps); }
+    mbar_init_fence();
+  }
+  const int Ts = a.Ts;
+  const int slots = fast_slots(Ts);
+  for (int i = tid; i < kWarps * slots * TK; i += kThreads) acc[i] = 0.f;
+  const RqsMeta<float> M = fast_setup<K>(a, smem, L, rec);   // ends with __syncthreads()
+  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
+  const int rpw = a.R / kWarps;
+  const int r_lo = warp * rpw;
+  const int Gw = Ts > 0 ? (Ts <= 32 ? 32 / Ts : 1) : 0;      // row groups per warp of the batch-shared pass
+  const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
+                               span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D) &&
+                               span_bulk<float>(a.bulk_gy, static_cast<int64_t>(a.R) * D);
+  float* my_gst = gst + static_cast<size_t>(r_lo) * a.grow;
+  bool store_pending = false;                                // lane 0: a bulk store of my_gst may still be reading it
+
+  int64_t tile = blockIdx.x;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST - 1; ++s) {
+      const int64_t t = tile + static_cast<int64_t>(s) * gridDim.x;
+      if (t < a.num_tiles)
+        stage_issue<float, true>(a, t, reinterpret_cast<float*>(smem + L.pst + s * L.pst_stride),
+                                 reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride),
+                                 reinterpret_cast<float*>(smem + L.gyst + s * L.xst_stride), &full[s]);
+    }
+  }
+  for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
+    const int s = it % NST;
+    if (tid == 0) {
+      const int64_t nt = tile + static_cast<int64_t>(NST - 1) * gridDim.x;
+      if (nt < a.num_tiles) {
+        const int ps = (it + NST - 1) % NST;
+        if (it >= 1) mbar_wait(&empty[ps], static_cast<uint32_t>(((it - 1) / NST) & 1));
+        stage_issue<float, true>(a, nt, reinterpret_cast<float*>(smem + L.pst + ps * L.pst_stride),
+                                 reinterpret_cast<float*>(smem + L.xst + ps * L.xst_stride),
+                                 reinterpret_cast<float*>(smem + L.gyst + ps * L.xst_stride), &full[ps]);
+      }
+    }
+    if (lane == 0 && store_pending) { bulk_wait_read_all(); store_pending = false; }
+    __syncwarp();
+    float* cur = reinterpret_cast<float*>(smem + L.pst + s * L.pst_stride);
+    float* xs = reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride);
+    float* gys = reinterpret_cast<float*>(smem + L.gyst + s * L.xst_stride);
+    const int64_t row0 = tile * a.R;
+    const int rows = static_cast<int>(imin64(a.R, a.B - row0));
+    if (rows == a.R && full_tiles_bulk) {
+      mbar_wait(&full[s], static_cast<uint32_t>((it / NST) & 1));
+    } else {
+      __syncthreads();
+      stage_wait<float, true>(a, tile, cur, xs, gys, &full[s], static_cast<uint32_t>((it / NST) & 1));
+      __syncthreads();
+    }
+    const int nrow = rows - r_lo < rpw ? rows - r_lo : rpw;
+
+    // pass A: conditional elements -> input gradient + this element's parameter-gradient vector
+    const int nA = nrow * Tc;
+    for (int e = lane; e < nA; e += 32) {
+      const int rr = fast_div(e, Tc, fx.magic_tc);
+      const int j = e - rr * Tc;
+      const int r = r_lo + rr;
+      const int c = M.cond_col[j];
+      float gv;
+      fast::element_bwd<K, INV>(cur + static_cast<size_t>(r) * a.prow + j * Pc, xs[r * D + c], M.cbound[j], a.wh_scale,
+                                M.cmode[j], a.outside_zero, gys[r * D + c], __ldg(a.gld + row0 + r), &gv,
+                                gst + static_cast<size_t>(r) * a.grow + j * Pc);
+      gxs[r * D + c] = gv;
+    }
+    // this warp's rows of the parameter-gradient tile leave through the TMA engine
+    if (Tc > 0 && nrow > 0) {
+      const size_t bytes = static_cast<size_t>(nrow) * a.grow * sizeof(float);
+      float* dst = a.gcond + (row0 + r_lo) * a.ld_gcond;
+      const bool bulk = a.bulk_gp && bytes % 16 == 0 && (reinterpret_cast<uintptr_t>(dst) % 16 == 0) &&
+                        (smem_u32(my_gst) % 16 == 0);
+      if (bulk) {
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          bulk_s2g(dst, my_gst, static_cast<uint32_t>(bytes));
+          bulk_commit();
+          store_pending = true;
+        }
+      } else {
+        __syncwarp();
+        const int n = Tc * Pc;
+        for (int rr = 0; rr < nrow; ++rr)
+          for (int q = lane; q < n; q += 32) a.gcond[(row0 + r_lo + rr) * a.ld_gcond + q] = my_gst[rr * a.grow + q];
+      }
+    }
+    // pass B: pass-through columns copy the incoming gradient; batch-shared columns accumulate into the
+    // lane-private table of their (row group, feature) slot
+    if (Ts == 0) {
+      const int nB = nrow * No;
+      for (int e = lane; e < nB; e += 32) {
+        const int rr = fast_div(e, No, fx.magic_no);
+        const int c = M.other_col[e - rr * No];
+        gxs[(r_lo + rr) * D + c] = gys[(r_lo + rr) * D + c];
+      }
+    } else {
+      for (int j = 0; j < No; ++j) {
+        if ((M.other_map[j] >> 16) == VCNF_COL_SHARED) continue;
+        const int c = M.other_col[j];
+        for (int rr = lane; rr < nrow; rr += 32) gxs[(r_lo + rr) * D + c] = gys[(r_lo + rr) * D + c];
+      }
+      for (int slot = lane; slot < slots; slot += 32) {
+        const int g = Ts <= 32 ? fast_div(slot, Ts, fx.magic_ts) : 0;
+        const int jo = slot - g * Ts;
+        const int c = M.shared_col[jo];
+        if (c < 0) continue;
+        float* mine = acc + (static_cast<size_t>(warp) * slots + slot) * TK;
+        for (int rr = g; rr < nrow; rr += Gw) {
+          const int r = r_lo + rr;
+          float gv;
+          fast::table_element_bwd<K, INV>(rec + jo * (K + 1), xs[r * D + c], M.sbound[jo], a.outside_zero, gys[r * D + c],
+                                          __ldg(a.gld + row0 + r), &gv, mine);
+          gxs[r * D + c] = gv;
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+
+    // pass C: this warp's input-gradient rows
+    if (nrow > 0) {
+      const int n = nrow * D;
+      const float* src = gxs + r_lo * D;
+      if (a.ldgx == D) {
+        float* dst = a.gx + (row0 + r_lo) * D;
+        for (int e = lane; e < n; e += 32) dst[e] = src[e];
+      } else {
+        for (int rr = 0; rr < nrow; ++rr)
+          for (int c = lane; c < D; c += 32) a.gx[(row0 + r_lo + rr) * a.ldgx + c] = src[rr * D + c];
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0 && store_pending) bulk_wait_read_all();
+  if (Ts > 0) {
+    __syncthreads();
+    const int per_feature = kWarps * Gw;                     // tables per feature, summed in a fixed order
+    for (int q = tid; q < Ts * TK; q += kThreads) {
+      const int j = q / TK, i = q - j * TK;
+      float sum = 0.f;
+      for (int t = 0; t < per_feature; ++t) {
+        const int w = t / Gw, g = t - w * Gw;
+        sum += acc[(static_cast<size_t>(w) * slots + g * Ts + j) * TK + i];
+      }
+      tabg[q] = sum;
+    }
+    __syncthreads();
+    for (int j = tid; j < Ts; j += kThreads)
+      rqs_table_to_raw_grad<float, K>(a.shared + static_cast<size_t>(j) * a.Ps, K, M.smode[j], M.sbound[j],
+                                      tabg + j * TK, a.partial + (static_cast<size_t>(blockIdx.x) * Ts + j) * a.Ps);
+  }
 }
 
 template <typename T>
@@ -822,8 +1043,46 @@ static int launch_fwd_fast(RqsLayerArgs<float>& a, cudaStream_t st) {
   fx.magic_tc = div_magic(a.Tc, static_cast<int64_t>(a.R) * a.Tc);
   const int n_other = a.D - a.Tc;          // every column is conditional, batch-shared or pass-through
   fx.magic_no = div_magic(n_other, static_cast<int64_t>(a.R) * n_other);
+  fx.magic_ts = 0;
   kern<<<static_cast<unsigned>(grid), kThreads, smem, st>>>(a, fx);
   return launch_status();
+}
+
+template <bool INV>
+static int launch_bwd_fast(RqsLayerArgs<float>& a, float* g_shared, cudaStream_t st) {
+  const int sms = sm_count();
+  if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
+  set_pitches(a, true);
+  a.R = pick_rows_fast(a.Tc, a.prow > a.grow ? a.prow : a.grow, a.D, 24 * 1024);
+  a.num_tiles = (a.B + a.R - 1) / a.R;
+  set_bulk_flags(a, true);
+  a.bulk_gp = a.Tc > 0 && a.ld_gcond == a.grow && reinterpret_cast<uintptr_t>(a.gcond) % 16 == 0;   // per-warp spans: checked in the kernel
+  const size_t smem = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, true, a.prow, a.grow, kFastStages).total;
+  if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
+  auto kern = rqs_layer_bwd_fast_kernel<INV, kFastStages>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax - 2048));
+    attr_set = true;
+  }
+  int per_sm = static_cast<int>(kSmemMax / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);
+  int64_t grid = static_cast<int64_t>(sms) * per_sm;
+  if (grid > kMaxBwdGrid) grid = kMaxBwdGrid;
+  if (grid > a.num_tiles) grid = a.num_tiles;
+  FastExtra fx;
+  const int n_other = a.D - a.Tc;
+  fx.magic_tc = div_magic(a.Tc, static_cast<int64_t>(a.R) * a.Tc);
+  fx.magic_no = div_magic(n_other, static_cast<int64_t>(a.R) * n_other);
+  fx.magic_ts = div_magic(a.Ts, 64);
+  kern<<<static_cast<unsigned>(grid), kThreads, smem, st>>>(a, fx);
+  int rc = launch_status();
+  if (rc == 0 && a.Ts > 0) {
+    const int n = a.Ts * a.Ps;
+    rqs_partial_reduce_kernel<float><<<(n + 127) / 128, 128, 0, st>>>(a.partial, static_cast<int>(grid), n, g_shared);
+    rc = launch_status();
+  }
+  return rc;
 }
 
 // K == 8 (the default of every spline wrapper, neural_spline/wrapper.py:20-31) gets a fully unrolled
@@ -844,6 +1103,12 @@ static int dispatch_fwd(RqsLayerArgs<T>& a, cudaStream_t st) {
 }
 template <typename T>
 static int dispatch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
+  if constexpr (sizeof(T) == 4) {
+    if (a.K == 8 && !generic_only()) {
+      const int rc = a.inverse ? launch_bwd_fast<true>(a, g_shared, st) : launch_bwd_fast<false>(a, g_shared, st);
+      if (rc != VCNF_E_UNSUPPORTED) return rc;
+    }
+  }
   if (a.K == 8) return launch_bwd<T, 8, true>(a, g_shared, st);
   if (a.K < 8) return launch_bwd<T, 8, false>(a, g_shared, st);
   if (a.K <= 16) return launch_bwd<T, 16, false>(a, g_shared, st);
