@@ -454,7 +454,7 @@ constexpr int kWarps = kThreads / 32;
 __host__ __device__ inline int fast_slots(int Ts) { return Ts <= 0 ? 0 : (Ts <= 32 ? (32 / Ts) * Ts : Ts); }
 
 struct FastSmem {
-  size_t bars, pst, pst_stride, xst, xst_stride, gyst, outs, lads, gst, gst_stride, tab, rec, acc, tabg, meta, total;
+  size_t bars, pst, pst_stride, xst, xst_stride, gyst, glst, glst_stride, outs, lads, gst, gst_stride, tab, rec, acc, tabg, meta, total;
 };
 __host__ __device__ inline FastSmem fast_smem_layout(int R, int D, int Tc, int Ts, bool bwd, int prow, int grow,
                                                      int nst) {
@@ -466,6 +466,8 @@ __host__ __device__ inline FastSmem fast_smem_layout(int R, int D, int Tc, int T
   m.xst_stride = round_up(static_cast<size_t>(R) * D * sizeof(float), 128);
   m.xst = o; o += nst * m.xst_stride;
   m.gyst = o; if (bwd) o += nst * m.xst_stride;
+  m.glst_stride = round_up(static_cast<size_t>(R) * sizeof(float), 128);      // upstream log-det gradients of the tile
+  m.glst = o; if (bwd) o += nst * m.glst_stride;
   m.outs = o; o += m.xst_stride;
   m.lads = o; if (!bwd) o += m.xst_stride;
   m.gst_stride = round_up(static_cast<size_t>(R) * grow * sizeof(float), 128);
@@ -496,7 +498,7 @@ __device__ __forceinline__ int fast_div(int e, int n, uint32_t magic) {
 // 7 us of a 38 us launch under ncu).  The outs tile is free before the tile loop and holds the raw column map.
 template <int K>
 __device__ __forceinline__ RqsMeta<float> fast_setup(const RqsLayerArgs<float>& a, unsigned char* smem,
-                                                     const FastSmem& L, fast::Knot4* rec) {
+                                                     const FastSmem& L, fast::Knot4* rec, int* n_pass) {
   RqsMeta<float> m;
   int32_t* ip = reinterpret_cast<int32_t*>(smem + L.meta);
   m.cond_col = ip; ip += a.Tc;
@@ -524,14 +526,24 @@ __device__ __forceinline__ RqsMeta<float> fast_setup(const RqsLayerArgs<float>& 
     if ((cm >> 16) == VCNF_COL_COND) {
       m.cond_col[cm & 0xffff] = c;
     } else {
+      // "other" list: pass-through columns first, batch-shared columns after them (each in column order)
+      const bool shared = (cm >> 16) == VCNF_COL_SHARED;
       int n = 0;
-      for (int q = 0; q < c; ++q) n += ((raw[q] >> 16) != VCNF_COL_COND) ? 1 : 0;
+      for (int q = 0; q < a.D; ++q) {
+        const int k = raw[q] >> 16;
+        if (k == VCNF_COL_COND) continue;
+        const bool qs = k == VCNF_COL_SHARED;
+        n += (qs == shared) ? (q < c ? 1 : 0) : (shared ? 1 : 0);
+      }
       m.other_col[n] = c; m.other_map[n] = cm;
-      if ((cm >> 16) == VCNF_COL_SHARED) m.shared_col[cm & 0xffff] = c;
+      if (shared) m.shared_col[cm & 0xffff] = c;
     }
   }
+  int np = 0;
+  for (int q = 0; q < a.D; ++q) np += ((raw[q] >> 16) == VCNF_COL_PASS) ? 1 : 0;
   __syncthreads();
   m.n_other = a.D - a.Tc;
+  *n_pass = np;
   return m;
 }
 
@@ -548,22 +560,12 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
   float* lads = reinterpret_cast<float*>(smem + L.lads);
   fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(smem + L.rec);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  int64_t tile = blockIdx.x;
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kWarps); }
     mbar_init_fence();
-  }
-  const RqsMeta<float> M = fast_setup<K>(a, smem, L, rec);   // ends with __syncthreads()
-  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
-  const int rpw = a.R / kWarps;
-  const int r_lo = warp * rpw;
-  // a full tile whose spans all go through the TMA engine needs nothing but the mbarrier wait
-  const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
-                               span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D);
-
-  int flag = 0;
-  int64_t tile = blockIdx.x;
-  if (tid == 0) {
+    // the first tiles are requested before the setup so that their HBM latency hides behind it
 #pragma unroll
     for (int s = 0; s < NST - 1; ++s) {
       const int64_t t = tile + static_cast<int64_t>(s) * gridDim.x;
@@ -572,6 +574,17 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
                                   reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride), nullptr, &full[s]);
     }
   }
+  int n_pass;
+  const RqsMeta<float> M = fast_setup<K>(a, smem, L, rec, &n_pass);   // ends with __syncthreads()
+  (void)n_pass;
+  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
+  const int rpw = a.R / kWarps;
+  const int r_lo = warp * rpw;
+  // a full tile whose spans all go through the TMA engine needs nothing but the mbarrier wait
+  const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
+                               span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D);
+
+  int flag = 0;
   for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
     const int s = it % NST;
     if (tid == 0) {                                    // producer lane: re-arm the stage read in iteration it-1
@@ -642,17 +655,23 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
       const float* src = ys + r_lo * D;
       if (a.ldy == D) {
         float* dst = a.y + (row0 + r_lo) * D;
+#pragma unroll 1
         for (int e = lane; e < n; e += 32) dst[e] = src[e];
       } else {
         for (int rr = 0; rr < nrow; ++rr)
+#pragma unroll 1
           for (int c = lane; c < D; c += 32) a.y[(row0 + r_lo + rr) * a.ldy + c] = src[rr * D + c];
       }
       const int hl = lane & 15;
+#pragma unroll 1
       for (int rr0 = 0; rr0 < nrow; rr0 += 2) {
         const int rr = rr0 + (lane >> 4);
         float acc = 0.f;
-        if (rr < nrow)
-          for (int c = hl; c < D; c += 16) acc += lads[(r_lo + rr) * D + c];
+        if (rr < nrow) {
+          const float* lrow = lads + (r_lo + rr) * D;
+#pragma unroll 1
+          for (int c = hl; c < D; c += 16) acc += lrow[c];
+        }
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (rr < nrow && hl == 0) {
@@ -684,36 +703,51 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
   float* acc = reinterpret_cast<float*>(smem + L.acc);
   float* tabg = reinterpret_cast<float*>(smem + L.tabg);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int D = a.D, Tc = a.Tc, Pc = a.Pc, Ts = a.Ts;
+  const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
+                               span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D) &&
+                               span_bulk<float>(a.bulk_gy, static_cast<int64_t>(a.R) * D);
+  // the tile's upstream log-det gradients ride along with a fully TMA-staged tile
+  const bool gl_bulk = full_tiles_bulk && (reinterpret_cast<uintptr_t>(a.gld) % 16 == 0) && (a.R % 4 == 0);
+  auto issue = [&](int64_t t, int ps) {
+    float* pd = reinterpret_cast<float*>(smem + L.pst + ps * L.pst_stride);
+    float* xd = reinterpret_cast<float*>(smem + L.xst + ps * L.xst_stride);
+    float* gd = reinterpret_cast<float*>(smem + L.gyst + ps * L.xst_stride);
+    if (full_tiles_bulk && a.B - t * a.R >= a.R) {
+      const uint32_t pb = Tc > 0 ? static_cast<uint32_t>(a.R * a.prow * sizeof(float)) : 0u;
+      const uint32_t xb = static_cast<uint32_t>(a.R * D * sizeof(float));
+      const uint32_t lb = gl_bulk ? static_cast<uint32_t>(a.R * sizeof(float)) : 0u;
+      mbar_expect_tx(&full[ps], pb + 2u * xb + lb);
+      if (pb) bulk_g2s(pd, a.cond + t * a.R * a.ld_cond, pb, &full[ps]);
+      bulk_g2s(xd, a.x + t * a.R * a.ldx, xb, &full[ps]);
+      bulk_g2s(gd, a.gy + t * a.R * a.ldgy, xb, &full[ps]);
+      if (lb) bulk_g2s(smem + L.glst + ps * L.glst_stride, a.gld + t * a.R, lb, &full[ps]);
+    } else {
+      stage_issue<float, true>(a, t, pd, xd, gd, &full[ps]);
+    }
+  };
+  int64_t tile = blockIdx.x;
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kWarps); }
     mbar_init_fence();
-  }
-  const int Ts = a.Ts;
-  const int slots = fast_slots(Ts);
-  for (int i = tid; i < kWarps * slots * TK; i += kThreads) acc[i] = 0.f;
-  const RqsMeta<float> M = fast_setup<K>(a, smem, L, rec);   // ends with __syncthreads()
-  const int D = a.D, Tc = a.Tc, Pc = a.Pc, No = M.n_other;
-  const int rpw = a.R / kWarps;
-  const int r_lo = warp * rpw;
-  const int Gw = Ts > 0 ? (Ts <= 32 ? 32 / Ts : 1) : 0;      // row groups per warp of the batch-shared pass
-  const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
-                               span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D) &&
-                               span_bulk<float>(a.bulk_gy, static_cast<int64_t>(a.R) * D);
-  float* my_gst = gst + static_cast<size_t>(r_lo) * a.grow;
-  bool store_pending = false;                                // lane 0: a bulk store of my_gst may still be reading it
-
-  int64_t tile = blockIdx.x;
-  if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < NST - 1; ++s) {
       const int64_t t = tile + static_cast<int64_t>(s) * gridDim.x;
-      if (t < a.num_tiles)
-        stage_issue<float, true>(a, t, reinterpret_cast<float*>(smem + L.pst + s * L.pst_stride),
-                                 reinterpret_cast<float*>(smem + L.xst + s * L.xst_stride),
-                                 reinterpret_cast<float*>(smem + L.gyst + s * L.xst_stride), &full[s]);
+      if (t < a.num_tiles) issue(t, s);
     }
   }
+  const int slots = fast_slots(Ts);
+  for (int i = tid; i < kWarps * slots * TK; i += kThreads) acc[i] = 0.f;
+  int n_pass;
+  const RqsMeta<float> M = fast_setup<K>(a, smem, L, rec, &n_pass);   // ends with __syncthreads()
+  const int No = M.n_other;
+  const int rpw = a.R / kWarps;
+  const int r_lo = warp * rpw;
+  const int Gw = Ts > 0 ? (Ts <= 32 ? 32 / Ts : 1) : 0;      // row groups per warp of the batch-shared pass
+  float* my_gst = gst + static_cast<size_t>(r_lo) * a.grow;
+  bool store_pending = false;                                // lane 0: a bulk store of my_gst may still be reading it
+
   for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
     const int s = it % NST;
     if (tid == 0) {
@@ -721,9 +755,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
       if (nt < a.num_tiles) {
         const int ps = (it + NST - 1) % NST;
         if (it >= 1) mbar_wait(&empty[ps], static_cast<uint32_t>(((it - 1) / NST) & 1));
-        stage_issue<float, true>(a, nt, reinterpret_cast<float*>(smem + L.pst + ps * L.pst_stride),
-                                 reinterpret_cast<float*>(smem + L.xst + ps * L.xst_stride),
-                                 reinterpret_cast<float*>(smem + L.gyst + ps * L.xst_stride), &full[ps]);
+        issue(nt, ps);
       }
     }
     if (lane == 0 && store_pending) { bulk_wait_read_all(); store_pending = false; }
@@ -741,6 +773,9 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
       __syncthreads();
     }
     const int nrow = rows - r_lo < rpw ? rows - r_lo : rpw;
+    // upstream log-det gradients of this tile: staged with the tile, or straight from HBM on the slow path
+    const float* gl = (rows == a.R && gl_bulk) ? reinterpret_cast<const float*>(smem + L.glst + s * L.glst_stride)
+                                               : a.gld + row0;
 
     // pass A: conditional elements -> input gradient + this element's parameter-gradient vector
     const int nA = nrow * Tc;
@@ -751,7 +786,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
       const int c = M.cond_col[j];
       float gv;
       fast::element_bwd<K, INV>(cur + static_cast<size_t>(r) * a.prow + j * Pc, xs[r * D + c], M.cbound[j], a.wh_scale,
-                                M.cmode[j], a.outside_zero, gys[r * D + c], __ldg(a.gld + row0 + r), &gv,
+                                M.cmode[j], a.outside_zero, gys[r * D + c], gl[r], &gv,
                                 gst + static_cast<size_t>(r) * a.grow + j * Pc);
       gxs[r * D + c] = gv;
     }
@@ -786,11 +821,12 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
         gxs[(r_lo + rr) * D + c] = gys[(r_lo + rr) * D + c];
       }
     } else {
-      for (int j = 0; j < No; ++j) {
-        if ((M.other_map[j] >> 16) == VCNF_COL_SHARED) continue;
-        const int c = M.other_col[j];
-        for (int rr = lane; rr < nrow; rr += 32) gxs[(r_lo + rr) * D + c] = gys[(r_lo + rr) * D + c];
+      for (int e = lane; e < nrow * n_pass; e += 32) {     // pass-through columns lead the "other" list
+        const int rr = e / n_pass;
+        const int c = M.other_col[e - rr * n_pass];
+        gxs[(r_lo + rr) * D + c] = gys[(r_lo + rr) * D + c];
       }
+#pragma unroll 1
       for (int slot = lane; slot < slots; slot += 32) {
         const int g = Ts <= 32 ? fast_div(slot, Ts, fx.magic_ts) : 0;
         const int jo = slot - g * Ts;
@@ -801,7 +837,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
           const int r = r_lo + rr;
           float gv;
           fast::table_element_bwd<K, INV>(rec + jo * (K + 1), xs[r * D + c], M.sbound[jo], a.outside_zero, gys[r * D + c],
-                                          __ldg(a.gld + row0 + r), &gv, mine);
+                                          gl[r], &gv, mine);
           gxs[r * D + c] = gv;
         }
       }
@@ -815,6 +851,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
       const float* src = gxs + r_lo * D;
       if (a.ldgx == D) {
         float* dst = a.gx + (row0 + r_lo) * D;
+#pragma unroll 1
         for (int e = lane; e < n; e += 32) dst[e] = src[e];
       } else {
         for (int rr = 0; rr < nrow; ++rr)
