@@ -488,6 +488,13 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// Consumer-side wait: back off between polls so that a warp waiting for its tile does not take issue slots
+// from the warps that are computing (ncu: 10 % of the executed instructions were polls).
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  while (!mbar_try_wait(bar, parity)) __nanosleep(100);
+}
+
 // e / n for 0 <= e < 2^20 / n  (magic = 2^20 / n + 1), or a real division when the host passed magic 0
 __device__ __forceinline__ int fast_div(int e, int n, uint32_t magic) {
   return magic ? static_cast<int>((static_cast<uint32_t>(e) * magic) >> 20) : e / n;
@@ -514,11 +521,32 @@ __device__ __forceinline__ RqsMeta<float> fast_setup(const RqsLayerArgs<float>& 
   const int tid = threadIdx.x;
   for (int c = tid; c < a.D; c += kThreads) raw[c] = a.col_map[c];
   for (int j = tid; j < a.Tc; j += kThreads) { m.cmode[j] = a.cmodes[j]; m.cbound[j] = a.cbounds[j]; }
-  for (int j = tid; j < a.Ts; j += kThreads) {
+  // knot records of the batch-shared features: one thread per feature for the two softmax axes, and one thread
+  // per pair of knot derivatives (softplus), so that the longest dependent chain is one axes evaluation
+  constexpr int kPairs = (K + 2) / 2;
+  for (int w = tid; w < a.Ts * (1 + kPairs); w += kThreads) {
+    const int j = w / (1 + kPairs), part = w - j * (1 + kPairs);
     const int mode = a.smodes[j];
     const float bound = a.sbounds[j];
-    m.smode[j] = mode; m.sbound[j] = bound; m.shared_col[j] = -1;
-    fast::build_records<K>(a.shared + static_cast<size_t>(j) * a.Ps, mode, bound, rec + j * (K + 1));
+    const float* prm = a.shared + static_cast<size_t>(j) * a.Ps;
+    fast::Knot4* rj = rec + j * (K + 1);
+    if (part == 0) {
+      m.smode[j] = mode; m.sbound[j] = bound; m.shared_col[j] = -1;
+      fast::P2 p[K], kn[K + 1];
+      fast::axes<K>(prm, 1.f, bound, p, kn);
+#pragma unroll
+      for (int k = 0; k <= K; ++k) { rj[k].x = kn[k].x; rj[k].y = kn[k].y; }
+    } else {
+      const int k = 2 * (part - 1);
+      const float edge = RqsConst<float>::edge();
+      int sidx;
+      const float ra = rqs_raw_deriv(prm + 2 * K, k, K, mode, edge, &sidx);
+      const float rb = (k + 1 <= K) ? rqs_raw_deriv(prm + 2 * K, k + 1, K, mode, edge, &sidx) : edge;
+      fast::P2 e;
+      const fast::P2 sp = fast::softplus2(fast::P2{ra, rb}, &e);
+      rj[k].d = RqsConst<float>::min_deriv() + sp.x;
+      if (k + 1 <= K) rj[k + 1].d = RqsConst<float>::min_deriv() + sp.y;
+    }
   }
   __syncthreads();
   for (int c = tid; c < a.D; c += kThreads) {
@@ -602,7 +630,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
     const int64_t row0 = tile * a.R;
     const int rows = static_cast<int>(imin64(a.R, a.B - row0));
     if (rows == a.R && full_tiles_bulk) {
-      mbar_wait(&full[s], static_cast<uint32_t>((it / NST) & 1));
+      mbar_wait_backoff(&full[s], static_cast<uint32_t>((it / NST) & 1));
     } else {
       // spans the TMA engine could not take (ragged last tile, unaligned views) are copied cooperatively;
       // this is the only CTA-wide synchronisation and it is off the steady-state path
@@ -766,7 +794,7 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
     const int64_t row0 = tile * a.R;
     const int rows = static_cast<int>(imin64(a.R, a.B - row0));
     if (rows == a.R && full_tiles_bulk) {
-      mbar_wait(&full[s], static_cast<uint32_t>((it / NST) & 1));
+      mbar_wait_backoff(&full[s], static_cast<uint32_t>((it / NST) & 1));
     } else {
       __syncthreads();
       stage_wait<float, true>(a, tile, cur, xs, gys, &full[s], static_cast<uint32_t>((it / NST) & 1));
@@ -1049,6 +1077,11 @@ static uint32_t div_magic(int n, int64_t max_e) {
 }
 
 constexpr int kFastStages = 2;
+static int fast_stages() {            // VCNF_RQS_STAGES=3: three-stage tile ring (experiments)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VCNF_RQS_STAGES"); v = (e && e[0] == '3') ? 3 : kFastStages; }
+  return v;
+}
 
 // VCNF_RQS_GENERIC=1 routes fp32 / K = 8 layers through the generic kernels (A/B measurements, tests)
 static bool generic_only() {
@@ -1065,9 +1098,10 @@ static int launch_fwd_fast(RqsLayerArgs<float>& a, cudaStream_t st) {
   a.R = pick_rows_fast(a.Tc, a.prow, a.D, 24 * 1024);
   a.num_tiles = (a.B + a.R - 1) / a.R;
   set_bulk_flags(a, false);
-  const size_t smem = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, false, a.prow, a.grow, kFastStages).total;
+  const int nst = fast_stages();
+  const size_t smem = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, false, a.prow, a.grow, nst).total;
   if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
-  auto kern = rqs_layer_fwd_fast_kernel<INV, kFastStages>;
+  auto kern = nst == 3 ? rqs_layer_fwd_fast_kernel<INV, 3> : rqs_layer_fwd_fast_kernel<INV, 2>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax - 2048));
@@ -1094,9 +1128,10 @@ static int launch_bwd_fast(RqsLayerArgs<float>& a, float* g_shared, cudaStream_t
   a.num_tiles = (a.B + a.R - 1) / a.R;
   set_bulk_flags(a, true);
   a.bulk_gp = a.Tc > 0 && a.ld_gcond == a.grow && reinterpret_cast<uintptr_t>(a.gcond) % 16 == 0;   // per-warp spans: checked in the kernel
-  const size_t smem = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, true, a.prow, a.grow, kFastStages).total;
+  const int nst = fast_stages();
+  const size_t smem = fast_smem_layout(a.R, a.D, a.Tc, a.Ts, true, a.prow, a.grow, nst).total;
   if (smem > kSmemMax - 2048) return VCNF_E_UNSUPPORTED;
-  auto kern = rqs_layer_bwd_fast_kernel<INV, kFastStages>;
+  auto kern = nst == 3 ? rqs_layer_bwd_fast_kernel<INV, 3> : rqs_layer_bwd_fast_kernel<INV, 2>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax - 2048));
