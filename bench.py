@@ -144,24 +144,33 @@ def kernel_roofline(model, dev, flush):
         layer._build_specs()
     spec = layer._specs["both"]
     B = BATCH
+    from vcnf_b200 import _lib
+    from vcnf_b200._lib import ptr
+    P = spec.Tc * spec.Pc
     x = 1.5 * torch.randn(B, D, device=dev)
-    cond = 0.5 * torch.randn(B, spec.Tc * spec.Pc, device=dev)
-    shared = layer.unconditional_transform.packed_params().detach()
+    # parameter rows at the 16-byte-multiple pitch the conditioner's final layer writes them with (324 floats)
+    cond = ops._padded_empty(B, P, torch.float32, dev)
+    cond.copy_(0.5 * torch.randn(B, P, device=dev))
+    gcond = ops._padded_empty(B, P, torch.float32, dev)
+    shared = layer.unconditional_transform.packed_params().detach().contiguous()
     gy, gld = torch.randn(B, D, device=dev), torch.randn(B, device=dev)
-    cond_g = cond.clone().requires_grad_(True)
-    x_g = x.clone().requires_grad_(True)
-    sh_g = shared.clone().requires_grad_(True)
+    y, ld, gx = torch.empty_like(x), torch.empty(B, device=dev), torch.empty_like(x)
+    gshared = torch.empty_like(shared)
+    ws = torch.empty(_lib.query("vcnf_rqs_layer_bwd_workspace", spec.Ts, spec.Ps, 0), dtype=torch.uint8, device=dev)
+    cmap, cm, cb, sm, sb = spec.on(dev, torch.float32)
     peak, peak_src = _peak()
     out = {}
 
-    def fwd():
-        with torch.no_grad():
-            ops.rqs_layer(x, cond, shared, spec, False)
+    def fwd():              # straight through the C ABI (no autograd bookkeeping between the events)
+        _lib.call("vcnf_rqs_layer_fwd", ptr(x), D, ptr(y), D, ptr(ld), 0, B, D, spec.K, ptr(cmap), ptr(cond),
+                  cond.stride(0), spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale, ptr(shared), spec.Ts, spec.Ps,
+                  ptr(sm), ptr(sb), 0, spec.outside_zero, None, None, 0, torch.cuda.current_stream().cuda_stream)
 
-    y, ld = ops.rqs_layer(x_g, cond_g, sh_g, spec, False)
-
-    def bwd():
-        torch.autograd.grad([y, ld], [x_g, cond_g, sh_g], [gy, gld], retain_graph=True)
+    def bwd():              # layer backward + the fixed-order reduce of the batch-shared gradients (2 launches)
+        _lib.call("vcnf_rqs_layer_bwd", ptr(x), D, ptr(gy), D, ptr(gld), ptr(gx), D, B, D, spec.K, ptr(cmap), ptr(cond),
+                  cond.stride(0), spec.Tc, spec.Pc, ptr(cm), ptr(cb), spec.wh_scale, ptr(gcond), gcond.stride(0),
+                  ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb), ptr(gshared), ptr(ws), 0, spec.outside_zero, 0,
+                  torch.cuda.current_stream().cuda_stream)
 
     P = spec.Tc * spec.Pc
     # conditioner dense layer at the hidden shape (64 of the 96 forward GEMMs of a step, and the same
@@ -175,33 +184,33 @@ def kernel_roofline(model, dev, flush):
         with torch.no_grad():
             ops.linear(h, W, bvec, residual=h, relu_in=True)
 
-    from vcnf_b200 import _lib
     gW, gbv = torch.empty_like(W), torch.empty_like(bvec)
-    ws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", B, HIDDEN, HIDDEN), dtype=torch.uint8, device=dev)
+    wws = torch.empty(_lib.query("vcnf_linear_wgrad_workspace", B, HIDDEN, HIDDEN), dtype=torch.uint8, device=dev)
 
     def lin_wgrad():        # straight through the C ABI (no autograd bookkeeping between the events)
         _lib.call("vcnf_linear_wgrad_tf32x3", gh.data_ptr(), HIDDEN, h.data_ptr(), HIDDEN, gW.data_ptr(),
-                  gbv.data_ptr(), ws.data_ptr(), B, HIDDEN, HIDDEN, 1, torch.cuda.current_stream().cuda_stream)
+                  gbv.data_ptr(), wws.data_ptr(), B, HIDDEN, HIDDEN, 1, torch.cuda.current_stream().cuda_stream)
 
     kernels = (("linear_ts_kernel (vcnf_linear_tf32x3 fwd/dgrad: hidden 128x128, relu+bias+residual fused)", lin_fwd,
                 4 * (3 * HIDDEN), 224),                       # read h (A and residual), write y
-               ("linear_wgrad_tf32x3 (+ reduce)", lin_wgrad, 4 * (2 * HIDDEN), 96),
-               ("rqs_layer_fwd", fwd, 4 * (P + 2 * D + 1), 16),
-               ("rqs_layer_bwd (+ shared-grad reduce)", bwd, 4 * (2 * P + 3 * D + 1), 16))
+               ("linear_wgrad_tma_kernel (vcnf_linear_wgrad_tf32x3, + reduce)", lin_wgrad, 4 * (2 * HIDDEN), 96),
+               ("rqs_layer_fwd_fast_kernel (vcnf_rqs_layer_fwd)", fwd, 4 * (P + 2 * D + 1), 16),
+               ("rqs_layer_bwd_fast_kernel (vcnf_rqs_layer_bwd, + shared-grad reduce)", bwd, 4 * (2 * P + 3 * D + 1), 16))
     for name, fn, bytes_per_sample, per_step in kernels:
         ms = _time_launches(fn, flush)
         ach = bytes_per_sample * B / (ms * 1e-3) / 1e9
         out[name] = {"ms": ms, "achieved": ach, "frac": ach / peak, "bytes_per_sample": bytes_per_sample,
                      "launches_per_step": per_step, "step_share_ms": ms * per_step}
-    traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        measured = json.load(open(tpath)) if os.path.exists(tpath) else {}
+    except Exception:
+        measured = {}
+    for name in out:        # dram bytes per launch from the committed `ncu --set full` captures
+        out[name]["traffic"] = measured.get(name.split(" ")[0])
     dom_name = max(out, key=lambda k: out[k]["step_share_ms"])
-    if os.path.exists(tpath):
-        try:
-            traffic = json.load(open(tpath)).get(dom_name.split(" ")[0])
-        except Exception:
-            traffic = None
     dom = out[dom_name]
+    traffic = dom["traffic"]
     return {"bound": "hbm", "kernel": dom_name,
             "achieved": dom["achieved"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
             "frac": dom["frac"], "traffic": traffic, "algorithmic_bytes_per_launch": dom["bytes_per_sample"] * B,

@@ -908,13 +908,18 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
   }
 }
 
+// Second stage of the batch-shared parameter gradients: out[j] = sum over CTAs of partial[b, j].  One warp per
+// output: lane l adds blocks l, l+32, ... in order, then a fixed xor tree -> bit-reproducible, and 32 loads in
+// flight per output instead of one dependent chain (12.7 -> ~3 us for 296 x 345).
 template <typename T>
 __global__ void rqs_partial_reduce_kernel(const T* partial, int nblocks, int n, T* out) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (j >= n) return;
   T acc = T(0);
-  for (int b = 0; b < nblocks; ++b) acc += partial[static_cast<size_t>(b) * n + j];
-  out[j] = acc;
+  for (int b = lane; b < nblocks; b += 32) acc += partial[static_cast<size_t>(b) * n + j];
+  acc = warp_sum(acc);
+  if (lane == 0) out[j] = acc;
 }
 
 template <typename T>
@@ -1048,7 +1053,7 @@ static int launch_bwd(RqsLayerArgs<T>& a, T* g_shared, cudaStream_t st) {
   int rc = launch_status();
   if (rc == 0 && a.Ts > 0) {
     const int n = a.Ts * a.Ps;
-    rqs_partial_reduce_kernel<T><<<(n + 127) / 128, 128, 0, st>>>(a.partial, static_cast<int>(grid), n, g_shared);
+    rqs_partial_reduce_kernel<T><<<(n + 3) / 4, 128, 0, st>>>(a.partial, static_cast<int>(grid), n, g_shared);
     rc = launch_status();
   }
   return rc;
@@ -1151,7 +1156,7 @@ static int launch_bwd_fast(RqsLayerArgs<float>& a, float* g_shared, cudaStream_t
   int rc = launch_status();
   if (rc == 0 && a.Ts > 0) {
     const int n = a.Ts * a.Ps;
-    rqs_partial_reduce_kernel<float><<<(n + 127) / 128, 128, 0, st>>>(a.partial, static_cast<int>(grid), n, g_shared);
+    rqs_partial_reduce_kernel<float><<<(n + 3) / 4, 128, 0, st>>>(a.partial, static_cast<int>(grid), n, g_shared);
     rc = launch_status();
   }
   return rc;
