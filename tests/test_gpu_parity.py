@@ -179,6 +179,41 @@ def test_round_trip_full_size_cfg2_layer():
     assert float((ld2 + ld3).abs().max()) < 1e-4
 
 
+@pytest.mark.parametrize("direction", ["inverse", "forward"])
+def test_fast_path_full_size_vs_fp64_kernels(direction):
+    """BASELINE cfg 2 layer at full size (B = 65536): the fp32 / K = 8 fast kernels (packed two-axis math, MUFU
+    closed forms) against the generic kernels evaluating the same layer in fp64 -- values, log-dets, bin indices and
+    every gradient.  Bin indices may only differ where fp32 rounding moves an input across a knot (< 1e-5 of the
+    elements); values stay inside the stated spline tolerance for >= 99.9 % of the elements."""
+    torch.manual_seed(0)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(layer, scale=0.05)
+    l32, l64 = layer.cuda(), copy.deepcopy(layer).double().cuda()
+    x = (1.5 * torch.randn(65536, 29, device="cuda"))
+    x32, x64 = x.clone().requires_grad_(True), x.double().requires_grad_(True)
+    gz, gl = torch.randn(65536, 29, device="cuda"), torch.randn(65536, device="cuda")
+    outs = []
+    for l, xi, dt in ((l32, x32, torch.float32), (l64, x64, torch.float64)):
+        z, ld = getattr(l, direction)(xi)
+        (z * gz.to(dt)).sum().add((ld * gl.to(dt)).sum()).backward()
+        # wrapper.inverse is the transform's forward (wrapper.py:83-89); only that entry returns bin indices
+        bins = l.prqct.forward(xi.detach(), want_bins=True)[2] if direction == "inverse" else torch.zeros(1)
+        outs.append((z.detach(), ld.detach(), xi.grad, bins, l))
+    (z, ld, gx, b, _), (z_, ld_, gx_, b_, _) = outs
+    assert float((b != b_).float().mean()) < 1e-5
+    inside = (z.double() - z_).abs() <= 1e-5 + 1e-4 * z_.abs()
+    assert float(inside.double().mean()) >= 0.999, float(inside.double().mean())
+    inside = (ld.double() - ld_).abs() <= 29e-5 + 1e-4 * ld_.abs()
+    assert float(inside.double().mean()) >= 0.999, float(inside.double().mean())
+    tol = 1e-3 * gx_.abs() + 1e-3 * float(gx_.abs().median())
+    assert float(((gx.double() - gx_).abs() <= tol).double().mean()) >= 0.995
+    for (n, p), (_, q) in zip(l32.named_parameters(), l64.named_parameters()):
+        if q.grad is None:
+            continue
+        err = float((p.grad.double() - q.grad).abs().max())
+        assert err <= 2e-3 * float(q.grad.abs().max()) + 1e-12, (n, err, float(q.grad.abs().max()))
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
 def test_arqs_full_width_vs_oracle(dtype):
     """cfg 3 layer width (d = 64, hidden 256 -> 1472 params/sample), density direction + grads."""
