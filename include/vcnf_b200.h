@@ -153,6 +153,15 @@ int vcnf_small_linear(const void* x, void* y, const void* W, const void* bias, c
                       const int32_t* out_idx, int64_t rows, int D, int S, int sub_bias_first, int dtype,
                       void* stream);
 
+/* Backward of vcnf_small_linear for row-major samples (S == 1, y = W x[in_idx] + bias scattered to out_idx), one
+ * pass over (x, gy): gx [rows, D] (may be NULL), gW [D, D], gb [D] (each may be NULL) -- autograd of
+ * normflow/flows/mixing.py:398-410 behind the permutation (mixing.py:484-492).  Per-CTA partial sums of the
+ * parameter gradients are summed in a fixed order (deterministic).  `workspace` must hold
+ * vcnf_small_linear_bwd_workspace(D, dtype) bytes. */
+int64_t vcnf_small_linear_bwd_workspace(int D, int dtype);
+int vcnf_small_linear_bwd(const void* x, const void* gy, const void* W, const int32_t* in_idx, const int32_t* out_idx,
+                          void* gx, void* gW, void* gb, void* workspace, int64_t rows, int D, int dtype, void* stream);
+
 /* ---- LU-parametrised weight (normflow/flows/mixing.py:352-396, _create_lower_upper / weight / logabsdet) --
  * W[D, D] = L U and *logabsdet = sum_i log diag(U)_i from the parameter vectors, one launch:
  *   lower_entries [D(D-1)/2]  strictly-lower part of L in np.tril_indices(D, -1) order (L has a unit diagonal)

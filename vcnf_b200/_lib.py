@@ -37,6 +37,7 @@ _SIGNATURES = {
     "vcnf_linear_tf32x3": [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp],
     "vcnf_linear_wgrad_tf32x3": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
     "vcnf_small_linear": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
+    "vcnf_small_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp],
     "vcnf_lu_compose_fwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
 }
@@ -44,6 +45,7 @@ _I64_RETURN = {
     "vcnf_rqs_layer_bwd_workspace": [_i32, _i32, _i32],
     "vcnf_const_affine_bwd_workspace": [_i32, _i32],
     "vcnf_linear_wgrad_workspace": [_i64, _i32, _i32],
+    "vcnf_small_linear_bwd_workspace": [_i32, _i32],
 }
 EXPORTED = sorted(list(_SIGNATURES) + list(_I64_RETURN))
 

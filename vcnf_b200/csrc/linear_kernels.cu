@@ -185,6 +185,157 @@ static int dispatch_lin(const LinArgs<T>& a, cudaStream_t st) {
   return VCNF_E_UNSUPPORTED;
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Backward of the row-major map above in ONE pass over (x, gy):
+//   gx[r, in_idx[i]] = sum_o W[o, i] gy[r, out_idx[o]]
+//   gW[o, i]         = sum_r gy[r, out_idx[o]] x[r, in_idx[i]]        gb[o] = sum_r gy[r, out_idx[o]]
+// (autograd of mixing.py:398-410 after the permutation).  It replaces an index_select, a transposed
+// small_linear launch and a [D, rows] x [rows, D] weight-gradient GEMM (36 us per cfg-2 layer) and reads each
+// operand once.  A tile of rows is staged flat in shared memory; thread r back-propagates row r, then the
+// same threads re-map to entries of gW (entry e = tid + 256 k: lanes share o and walk i, so the gy read is a
+// broadcast and the x read conflict-free) and accumulate over the tile's rows in registers.  Per-CTA partial
+// sums go to the workspace and are summed in a fixed order by lin_partial_reduce_kernel (bit-reproducible).
+constexpr int kBwdThreads = 256;
+constexpr int kBwdMaxGrid = 148 * 2;
+
+template <typename T>
+struct LinBwdArgs {
+  const T* x; const T* gy; const T* W; const int32_t* in_idx; const int32_t* out_idx;
+  T* gx; T* partial; int64_t rows; int D; int tile_rows;
+};
+
+template <typename T, int DP, int NE>
+__global__ void __launch_bounds__(kBwdThreads) small_linear_bwd_kernel(const LinBwdArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem_lin[];
+  const int D = a.D, TR = a.tile_rows;
+  T* Wt = reinterpret_cast<T*>(smem_lin);              // [D][DP]: Wt[i][o] = W[o][i], zero padded
+  int* iin = reinterpret_cast<int*>(Wt + static_cast<size_t>(D) * DP);
+  int* iout = iin + DP;
+  T* xs = reinterpret_cast<T*>(iout + DP);             // [TR * D]
+  T* gs = xs + static_cast<size_t>(TR) * D;            // [TR * D]
+  T* os = gs + static_cast<size_t>(TR) * D;            // [TR * D]
+  const int tid = threadIdx.x;
+  for (int e = tid; e < D * DP; e += kBwdThreads) {
+    const int i = e / DP, o = e - i * DP;
+    Wt[e] = o < D ? a.W[o * D + i] : T(0);
+  }
+  for (int e = tid; e < DP; e += kBwdThreads) {
+    iin[e] = e < D ? (a.in_idx ? a.in_idx[e] : e) : 0;
+    iout[e] = e < D ? (a.out_idx ? a.out_idx[e] : e) : 0;
+  }
+  __syncthreads();
+  // gW entries of this thread: column offsets of their two operands inside a staged row
+  int co[NE], ci[NE];
+  T acc[NE];
+#pragma unroll
+  for (int k = 0; k < NE; ++k) {
+    const int e = tid + k * kBwdThreads;
+    const int o = e < D * D ? e / D : 0, i = e < D * D ? e - o * D : 0;
+    co[k] = iout[o]; ci[k] = iin[i]; acc[k] = T(0);
+  }
+  T accb = T(0);
+  const int cb = iout[tid < D ? tid : 0];
+  const int64_t n_tiles = (a.rows + TR - 1) / TR;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t r0 = tile * TR;
+    const int nr = static_cast<int>(a.rows - r0 < TR ? a.rows - r0 : TR);
+    const int n = nr * D;
+    __syncthreads();                                   // previous tile's readers are done
+    const T* sx = a.x + r0 * D;
+    const T* sg = a.gy + r0 * D;
+    for (int e = tid; e < n; e += kBwdThreads) { xs[e] = sx[e]; gs[e] = sg[e]; }
+    __syncthreads();
+    if (a.gx && tid < nr) {
+      T gr[DP];
+#pragma unroll
+      for (int o = 0; o < DP; ++o) gr[o] = o < D ? gs[tid * D + iout[o]] : T(0);
+      for (int i = 0; i < D; ++i) {
+        T a0 = T(0), a1 = T(0);
+        const T* w = Wt + i * DP;
+#pragma unroll
+        for (int o = 0; o < DP; o += 2) { a0 += w[o] * gr[o]; a1 += w[o + 1] * gr[o + 1]; }
+        os[tid * D + iin[i]] = a0 + a1;
+      }
+    }
+#pragma unroll 2
+    for (int r = 0; r < nr; ++r) {
+      const T* gr = gs + r * D;
+      const T* xr = xs + r * D;
+#pragma unroll
+      for (int k = 0; k < NE; ++k) acc[k] += gr[co[k]] * xr[ci[k]];
+    }
+    if (tid < D)
+      for (int r = 0; r < nr; ++r) accb += gs[r * D + cb];
+    if (a.gx) {
+      __syncthreads();
+      T* dst = a.gx + r0 * D;
+      for (int e = tid; e < n; e += kBwdThreads) dst[e] = os[e];
+    }
+  }
+  T* mine = a.partial + static_cast<size_t>(blockIdx.x) * (D * D + D);
+#pragma unroll
+  for (int k = 0; k < NE; ++k) {
+    const int e = tid + k * kBwdThreads;
+    if (e < D * D) mine[e] = acc[k];
+  }
+  if (tid < D) mine[D * D + tid] = accb;
+}
+
+// out[j] = sum_b partial[b, j] in a fixed order (one warp per output, fixed xor tree); j < nw -> gW, else gb
+template <typename T>
+__global__ void lin_partial_reduce_kernel(const T* partial, int nblocks, int nw, int nb, T* gW, T* gb) {
+  const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (j >= nw + nb) return;
+  T acc = T(0);
+  for (int b = lane; b < nblocks; b += 32) acc += partial[static_cast<size_t>(b) * (nw + nb) + j];
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    if (j < nw) { if (gW) gW[j] = acc; }
+    else if (gb) gb[j - nw] = acc;
+  }
+}
+
+template <typename T>
+static int lin_bwd_tile_rows(int D) { return static_cast<size_t>(D) * sizeof(T) <= 128 ? 256 : 128; }
+
+template <typename T, int DP, int NE>
+static int launch_lin_bwd(LinBwdArgs<T>& a, T* gW, T* gb, cudaStream_t st) {
+  a.tile_rows = lin_bwd_tile_rows<T>(a.D);
+  const size_t smem = static_cast<size_t>(a.D) * DP * sizeof(T) + 2 * DP * sizeof(int) +
+                      3 * static_cast<size_t>(a.tile_rows) * a.D * sizeof(T);
+  if (smem > 200 * 1024) return VCNF_E_UNSUPPORTED;
+  auto kern = small_linear_bwd_kernel<T, DP, NE>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr_set = true;
+  }
+  const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
+  const int64_t tiles = (a.rows + a.tile_rows - 1) / a.tile_rows;
+  int per_sm = static_cast<int>((227 * 1024) / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm);
+  int64_t grid = static_cast<int64_t>(sms) * per_sm;
+  if (grid > kBwdMaxGrid) grid = kBwdMaxGrid;
+  if (grid > tiles) grid = tiles;
+  kern<<<static_cast<unsigned>(grid), kBwdThreads, smem, st>>>(a);
+  int rc = launch_status();
+  if (rc) return rc;
+  const int nw = a.D * a.D, nb = a.D;
+  lin_partial_reduce_kernel<T><<<(nw + nb + 3) / 4, 128, 0, st>>>(a.partial, static_cast<int>(grid), nw, nb, gW, gb);
+  return launch_status();
+}
+
+template <typename T>
+static int dispatch_lin_bwd(LinBwdArgs<T>& a, T* gW, T* gb, cudaStream_t st) {
+  if (a.D <= 16) return launch_lin_bwd<T, 16, 1>(a, gW, gb, st);
+  if (a.D <= 32) return launch_lin_bwd<T, 32, 4>(a, gW, gb, st);
+  if (a.D <= 48) return launch_lin_bwd<T, 48, 9>(a, gW, gb, st);
+  if (a.D <= 64) return launch_lin_bwd<T, 64, 16>(a, gW, gb, st);
+  return VCNF_E_UNSUPPORTED;
+}
+
 }  // namespace vcnf
 
 using namespace vcnf;
@@ -202,4 +353,31 @@ extern "C" int vcnf_small_linear(const void* x, void* y, const void* W, const vo
   }
   LinArgs<double> a{(const double*)x, (double*)y, (const double*)W, (const double*)bias, in_idx, out_idx, rows, D, S, sub_bias_first};
   return dispatch_lin<double>(a, (cudaStream_t)stream);
+}
+
+extern "C" int64_t vcnf_small_linear_bwd_workspace(int D, int dtype) {
+  if (D <= 0) return 0;
+  return static_cast<int64_t>(kBwdMaxGrid) * (static_cast<int64_t>(D) * D + D) * (dtype == VCNF_F64 ? 8 : 4);
+}
+
+extern "C" int vcnf_small_linear_bwd(const void* x, const void* gy, const void* W, const int32_t* in_idx,
+                                     const int32_t* out_idx, void* gx, void* gW, void* gb, void* workspace,
+                                     int64_t rows, int D, int dtype, void* stream) {
+  if (D <= 0 || D > 64 || rows < 0 || (dtype != VCNF_F32 && dtype != VCNF_F64)) return VCNF_E_BADARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t es = dtype == VCNF_F64 ? 8 : 4;
+  if (rows == 0) {   /* empty batch: parameter gradients are zero */
+    if (gW) cudaMemsetAsync(gW, 0, es * D * D, st);
+    if (gb) cudaMemsetAsync(gb, 0, es * D, st);
+    return launch_status();
+  }
+  if (!x || !gy || !W || !workspace || (!gW && !gb && !gx)) return VCNF_E_BADARG;
+  if (dtype == VCNF_F32) {
+    LinBwdArgs<float> a{(const float*)x, (const float*)gy, (const float*)W, in_idx, out_idx, (float*)gx,
+                        (float*)workspace, rows, D, 0};
+    return dispatch_lin_bwd<float>(a, (float*)gW, (float*)gb, st);
+  }
+  LinBwdArgs<double> a{(const double*)x, (const double*)gy, (const double*)W, in_idx, out_idx, (double*)gx,
+                       (double*)workspace, rows, D, 0};
+  return dispatch_lin_bwd<double>(a, (double*)gW, (double*)gb, st);
 }

@@ -338,6 +338,19 @@ class _SmallLinear(torch.autograd.Function):
         D, S, rows, sub = ctx.cfg
         gy = gy.contiguous()
         gx = gW = gb = None
+        if S == 1 and not sub and x.dim() == 2:
+            # density direction on tabular rows (LULinearPermute.inverse, the training path): input, weight and
+            # bias gradients from ONE pass over (x, gy) -- vcnf_small_linear_bwd
+            want_w = ctx.needs_input_grad[1]
+            want_b = bias is not None and ctx.needs_input_grad[2]
+            gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+            gW = torch.empty((D, D), dtype=x.dtype, device=x.device) if want_w else None
+            gb = torch.empty(D, dtype=x.dtype, device=x.device) if want_b else None
+            ws = torch.empty(_lib.query("vcnf_small_linear_bwd_workspace", D, dtype_code(x)), dtype=torch.uint8,
+                             device=x.device)
+            _launch("vcnf_small_linear_bwd", ptr(x), ptr(gy), ptr(W), ptr(in_idx), ptr(out_idx), ptr(gx), ptr(gW),
+                    ptr(gb), ptr(ws), rows, D, dtype_code(x), stream(), n=2)
+            return gx, gW, gb, None, None, None
         if ctx.needs_input_grad[0] or (sub and bias is not None and ctx.needs_input_grad[2]):
             gx = torch.empty_like(x)
             Wt = W.t().contiguous()
