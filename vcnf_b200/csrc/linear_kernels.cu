@@ -197,87 +197,159 @@ static int dispatch_lin(const LinArgs<T>& a, cudaStream_t st) {
 // broadcast and the x read conflict-free) and accumulate over the tile's rows in registers.  Per-CTA partial
 // sums go to the workspace and are summed in a fixed order by lin_partial_reduce_kernel (bit-reproducible).
 constexpr int kBwdThreads = 256;
-constexpr int kBwdMaxGrid = 148 * 2;
+constexpr int kBwdMaxGrid = 148 * 4;
 
 template <typename T>
 struct LinBwdArgs {
   const T* x; const T* gy; const T* W; const int32_t* in_idx; const int32_t* out_idx;
-  T* gx; T* partial; int64_t rows; int D; int tile_rows;
+  T* gx; T* partial; int64_t rows; int D; int tile_rows; int bulk;
 };
 
-template <typename T, int DP, int NE>
-__global__ void __launch_bounds__(kBwdThreads) small_linear_bwd_kernel(const LinBwdArgs<T> a) {
-  extern __shared__ __align__(16) unsigned char smem_lin[];
-  const int D = a.D, TR = a.tile_rows;
-  T* Wt = reinterpret_cast<T*>(smem_lin);              // [D][DP]: Wt[i][o] = W[o][i], zero padded
-  int* iin = reinterpret_cast<int*>(Wt + static_cast<size_t>(D) * DP);
-  int* iout = iin + DP;
-  T* xs = reinterpret_cast<T*>(iout + DP);             // [TR * D]
-  T* gs = xs + static_cast<size_t>(TR) * D;            // [TR * D]
-  T* os = gs + static_cast<size_t>(TR) * D;            // [TR * D]
+// Data movement: the raw tile (two contiguous spans, x rows and gy rows) is pulled into a 2-stage ring by the
+// TMA engine (1-D bulk copies on an mbarrier), so the load of tile i+1 overlaps the math of tile i (the first
+// version loaded synchronously: 39 % of its stall samples were the load -> store dependency).  From the ring
+// the tile is re-laid with the permutations applied (xs[r][i] = x[r, in_idx[i]], gs[r][o] = gy[r, out_idx[o]])
+// at an even row pitch, so every later access is a direct, pair-aligned index:
+//   * gW: thread <-> 2 x 2 blocks of (o, i); per row two 2-element loads feed four FMAs;
+//   * gx: two threads per row, each back-propagates half of the input features from the row in registers.
+template <typename T, int DP, int NB>
+__global__ void __launch_bounds__(kBwdThreads, 2) small_linear_bwd_kernel(const LinBwdArgs<T> a) {
+  extern __shared__ __align__(128) unsigned char smem_lin[];
+  const int D = a.D, PD = (D + 1) & ~1, TR = a.tile_rows;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_lin);                    // [2]
+  T* raw = reinterpret_cast<T*>(smem_lin + 128);       // [2 stages][x | gy][TR * D]
+  T* Wt = raw + 4 * static_cast<size_t>(TR) * D;       // [D][DP]: Wt[i][o] = W[o][i], zero padded
+  int* inv_in = reinterpret_cast<int*>(Wt + static_cast<size_t>(D) * DP);   // inv_in[in_idx[i]] = i
+  int* inv_out = inv_in + DP;
+  T* xs = reinterpret_cast<T*>(inv_out + DP);          // [TR][PD]
+  T* gs = xs + static_cast<size_t>(TR) * PD;
+  T* os = gs + static_cast<size_t>(TR) * PD;
   const int tid = threadIdx.x;
+  const int64_t n_tiles = (a.rows + TR - 1) / TR;
+  auto issue = [&](int64_t t, int st) {                // thread 0 only
+    const int64_t r0 = t * TR;
+    const int nr = static_cast<int>(a.rows - r0 < TR ? a.rows - r0 : TR);
+    const uint32_t bytes = static_cast<uint32_t>(static_cast<size_t>(nr) * D * sizeof(T));
+    if (!a.bulk || bytes % 16 != 0) return;
+    T* dst = raw + static_cast<size_t>(st) * 2 * TR * D;
+    mbar_expect_tx(&bars[st], 2 * bytes);
+    bulk_g2s(dst, a.x + r0 * D, bytes, &bars[st]);
+    bulk_g2s(dst + static_cast<size_t>(TR) * D, a.gy + r0 * D, bytes, &bars[st]);
+  };
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_init_fence();
+    if (static_cast<int64_t>(blockIdx.x) < n_tiles) issue(blockIdx.x, 0);
+  }
   for (int e = tid; e < D * DP; e += kBwdThreads) {
     const int i = e / DP, o = e - i * DP;
     Wt[e] = o < D ? a.W[o * D + i] : T(0);
   }
-  for (int e = tid; e < DP; e += kBwdThreads) {
-    iin[e] = e < D ? (a.in_idx ? a.in_idx[e] : e) : 0;
-    iout[e] = e < D ? (a.out_idx ? a.out_idx[e] : e) : 0;
+  for (int e = tid; e < D; e += kBwdThreads) {
+    inv_in[a.in_idx ? a.in_idx[e] : e] = e;
+    inv_out[a.out_idx ? a.out_idx[e] : e] = e;
   }
-  __syncthreads();
-  // gW entries of this thread: column offsets of their two operands inside a staged row
-  int co[NE], ci[NE];
-  T acc[NE];
+  for (int e = tid; e < TR * PD; e += kBwdThreads) { xs[e] = T(0); gs[e] = T(0); }   // pad column stays 0
+  const int nbi = (D + 1) >> 1, nblk = nbi * nbi;
+  int bo[NB], bi[NB];
+  T acc[NB][4];
 #pragma unroll
-  for (int k = 0; k < NE; ++k) {
-    const int e = tid + k * kBwdThreads;
-    const int o = e < D * D ? e / D : 0, i = e < D * D ? e - o * D : 0;
-    co[k] = iout[o]; ci[k] = iin[i]; acc[k] = T(0);
+  for (int k = 0; k < NB; ++k) {
+    const int blk = tid + k * kBwdThreads;
+    const int q = blk < nblk ? blk : 0;
+    bo[k] = 2 * (q / nbi); bi[k] = 2 * (q - (q / nbi) * nbi);
+    acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = T(0);
   }
   T accb = T(0);
-  const int cb = iout[tid < D ? tid : 0];
-  const int64_t n_tiles = (a.rows + TR - 1) / TR;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  uint32_t par0 = 0u, par1 = 0u;
+  int it = 0;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    const int st = it & 1;
     const int64_t r0 = tile * TR;
     const int nr = static_cast<int>(a.rows - r0 < TR ? a.rows - r0 : TR);
     const int n = nr * D;
-    __syncthreads();                                   // previous tile's readers are done
-    const T* sx = a.x + r0 * D;
-    const T* sg = a.gy + r0 * D;
-    for (int e = tid; e < n; e += kBwdThreads) { xs[e] = sx[e]; gs[e] = sg[e]; }
-    __syncthreads();
-    if (a.gx && tid < nr) {
-      T gr[DP];
-#pragma unroll
-      for (int o = 0; o < DP; ++o) gr[o] = o < D ? gs[tid * D + iout[o]] : T(0);
-      for (int i = 0; i < D; ++i) {
-        T a0 = T(0), a1 = T(0);
-        const T* w = Wt + i * DP;
-#pragma unroll
-        for (int o = 0; o < DP; o += 2) { a0 += w[o] * gr[o]; a1 += w[o + 1] * gr[o + 1]; }
-        os[tid * D + iin[i]] = a0 + a1;
+    __syncthreads();                                   // previous tile's readers (ring stage st^1, xs, gs, os) are done
+    if (tid == 0 && tile + gridDim.x < n_tiles) issue(tile + gridDim.x, st ^ 1);
+    const bool bulk = a.bulk && (static_cast<size_t>(n) * sizeof(T)) % 16 == 0;
+    if (bulk) {
+      mbar_wait(&bars[st], st ? par1 : par0);
+      if (st) par1 ^= 1u; else par0 ^= 1u;
+      const T* rx = raw + static_cast<size_t>(st) * 2 * TR * D;
+      const T* rg = rx + static_cast<size_t>(TR) * D;
+      for (int e = tid; e < n; e += kBwdThreads) {
+        const int r = e / D, c = e - r * D;
+        xs[r * PD + inv_in[c]] = rx[e];
+        gs[r * PD + inv_out[c]] = rg[e];
+      }
+    } else {
+      const T* sx = a.x + r0 * D;
+      const T* sg = a.gy + r0 * D;
+      for (int e = tid; e < n; e += kBwdThreads) {
+        const int r = e / D, c = e - r * D;
+        xs[r * PD + inv_in[c]] = sx[e];
+        gs[r * PD + inv_out[c]] = sg[e];
       }
     }
-#pragma unroll 2
-    for (int r = 0; r < nr; ++r) {
-      const T* gr = gs + r * D;
-      const T* xr = xs + r * D;
+    __syncthreads();
+    if (a.gx) {
+      const int r = tid >> 1;
+      if (r < nr) {
+        T gr[DP];
 #pragma unroll
-      for (int k = 0; k < NE; ++k) acc[k] += gr[co[k]] * xr[ci[k]];
+        for (int o = 0; o < DP; ++o) gr[o] = o < D ? gs[r * PD + o] : T(0);
+        const int half = (D + 1) >> 1;
+        const int i0 = (tid & 1) * half, i1 = i0 + half < D ? i0 + half : D;
+        for (int i = i0; i < i1; ++i) {
+          T a0 = T(0), a1 = T(0);
+          const T* w = Wt + i * DP;
+#pragma unroll
+          for (int o = 0; o < DP; o += 2) { a0 += w[o] * gr[o]; a1 += w[o + 1] * gr[o + 1]; }
+          os[r * PD + i] = a0 + a1;
+        }
+      }
+      for (int r2 = r + kBwdThreads / 2; r2 < nr; r2 += kBwdThreads / 2) {   // tiles taller than 128 rows
+        for (int i = (tid & 1); i < D; i += 2) {
+          T a0 = T(0);
+          for (int o = 0; o < D; ++o) a0 += Wt[i * DP + o] * gs[r2 * PD + o];
+          os[r2 * PD + i] = a0;
+        }
+      }
+    }
+#pragma unroll 4
+    for (int r = 0; r < nr; ++r) {
+      const T* grow = gs + r * PD;
+      const T* xrow = xs + r * PD;
+#pragma unroll
+      for (int k = 0; k < NB; ++k) {
+        const T g0 = grow[bo[k]], g1 = grow[bo[k] + 1];
+        const T x0 = xrow[bi[k]], x1 = xrow[bi[k] + 1];
+        acc[k][0] += g0 * x0; acc[k][1] += g0 * x1; acc[k][2] += g1 * x0; acc[k][3] += g1 * x1;
+      }
     }
     if (tid < D)
-      for (int r = 0; r < nr; ++r) accb += gs[r * D + cb];
+      for (int r = 0; r < nr; ++r) accb += gs[r * PD + tid];
     if (a.gx) {
       __syncthreads();
       T* dst = a.gx + r0 * D;
-      for (int e = tid; e < n; e += kBwdThreads) dst[e] = os[e];
+      for (int e = tid; e < n; e += kBwdThreads) {
+        const int r = e / D, c = e - r * D;
+        dst[e] = os[r * PD + inv_in[c]];
+      }
     }
   }
   T* mine = a.partial + static_cast<size_t>(blockIdx.x) * (D * D + D);
 #pragma unroll
-  for (int k = 0; k < NE; ++k) {
-    const int e = tid + k * kBwdThreads;
-    if (e < D * D) mine[e] = acc[k];
+  for (int k = 0; k < NB; ++k) {
+    if (tid + k * kBwdThreads < nblk) {
+      const int o = bo[k], i = bi[k];
+      mine[o * D + i] = acc[k][0];
+      if (i + 1 < D) mine[o * D + i + 1] = acc[k][1];
+      if (o + 1 < D) {
+        mine[(o + 1) * D + i] = acc[k][2];
+        if (i + 1 < D) mine[(o + 1) * D + i + 1] = acc[k][3];
+      }
+    }
   }
   if (tid < D) mine[D * D + tid] = accb;
 }
@@ -298,15 +370,21 @@ __global__ void lin_partial_reduce_kernel(const T* partial, int nblocks, int nw,
 }
 
 template <typename T>
-static int lin_bwd_tile_rows(int D) { return static_cast<size_t>(D) * sizeof(T) <= 128 ? 256 : 128; }
+static size_t lin_bwd_smem(int D, int DP, int rows) {
+  const int PD = (D + 1) & ~1;
+  return 128 + 4 * static_cast<size_t>(rows) * D * sizeof(T) + static_cast<size_t>(D) * DP * sizeof(T) +
+         2 * DP * sizeof(int) + 3 * static_cast<size_t>(rows) * PD * sizeof(T);
+}
 
-template <typename T, int DP, int NE>
+template <typename T, int DP, int NB>
 static int launch_lin_bwd(LinBwdArgs<T>& a, T* gW, T* gb, cudaStream_t st) {
-  a.tile_rows = lin_bwd_tile_rows<T>(a.D);
-  const size_t smem = static_cast<size_t>(a.D) * DP * sizeof(T) + 2 * DP * sizeof(int) +
-                      3 * static_cast<size_t>(a.tile_rows) * a.D * sizeof(T);
+  a.tile_rows = 128;                                   // two CTAs per SM when the tile allows it
+  while (a.tile_rows > 16 && lin_bwd_smem<T>(a.D, DP, a.tile_rows) > 110 * 1024) a.tile_rows >>= 1;
+  const size_t smem = lin_bwd_smem<T>(a.D, DP, a.tile_rows);
   if (smem > 200 * 1024) return VCNF_E_UNSUPPORTED;
-  auto kern = small_linear_bwd_kernel<T, DP, NE>;
+  a.bulk = (reinterpret_cast<uintptr_t>(a.x) % 16 == 0) && (reinterpret_cast<uintptr_t>(a.gy) % 16 == 0) &&
+           (static_cast<size_t>(a.tile_rows) * a.D * sizeof(T)) % 16 == 0;
+  auto kern = small_linear_bwd_kernel<T, DP, NB>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -329,10 +407,10 @@ static int launch_lin_bwd(LinBwdArgs<T>& a, T* gW, T* gb, cudaStream_t st) {
 
 template <typename T>
 static int dispatch_lin_bwd(LinBwdArgs<T>& a, T* gW, T* gb, cudaStream_t st) {
-  if (a.D <= 16) return launch_lin_bwd<T, 16, 1>(a, gW, gb, st);
-  if (a.D <= 32) return launch_lin_bwd<T, 32, 4>(a, gW, gb, st);
-  if (a.D <= 48) return launch_lin_bwd<T, 48, 9>(a, gW, gb, st);
-  if (a.D <= 64) return launch_lin_bwd<T, 64, 16>(a, gW, gb, st);
+  if (a.D <= 16) return launch_lin_bwd<T, 16, 1>(a, gW, gb, st);     // NB = ceil(ceil(D/2)^2 / 256) blocks per thread
+  if (a.D <= 32) return launch_lin_bwd<T, 32, 1>(a, gW, gb, st);
+  if (a.D <= 48) return launch_lin_bwd<T, 48, 3>(a, gW, gb, st);
+  if (a.D <= 64) return launch_lin_bwd<T, 64, 4>(a, gW, gb, st);
   return VCNF_E_UNSUPPORTED;
 }
 
@@ -374,10 +452,10 @@ extern "C" int vcnf_small_linear_bwd(const void* x, const void* gy, const void* 
   if (!x || !gy || !W || !workspace || (!gW && !gb && !gx)) return VCNF_E_BADARG;
   if (dtype == VCNF_F32) {
     LinBwdArgs<float> a{(const float*)x, (const float*)gy, (const float*)W, in_idx, out_idx, (float*)gx,
-                        (float*)workspace, rows, D, 0};
+                        (float*)workspace, rows, D, 0, 0};
     return dispatch_lin_bwd<float>(a, (float*)gW, (float*)gb, st);
   }
   LinBwdArgs<double> a{(const double*)x, (const double*)gy, (const double*)W, in_idx, out_idx, (double*)gx,
-                       (double*)workspace, rows, D, 0};
+                       (double*)workspace, rows, D, 0, 0};
   return dispatch_lin_bwd<double>(a, (double*)gW, (double*)gb, st);
 }
