@@ -306,17 +306,27 @@ def gpu_run(args):
     e2e_value = world * BATCH * args.steps / float(t)
 
     # sampling direction (second half of the BASELINE metric), device-timed
+    draw = parallel.GraphedSampler(model, BATCH) if not args.no_graph else (lambda: model.sample(BATCH))
     with torch.no_grad():
-        for _ in range(2):
-            model.sample(BATCH)
+        for _ in range(3):
+            draw()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(3):
-            model.sample(BATCH)
+        for _ in range(10):
+            flush.zero_()               # L2 flush between draws, as between training steps
+            z_s, lq_s = draw()
         e1.record()
         torch.cuda.synchronize()
-        sample_rate = world * 3 * BATCH / (e0.elapsed_time(e1) * 1e-3)
+        ef0, ef1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ef0.record()
+        for _ in range(10):
+            flush.zero_()
+        ef1.record()
+        torch.cuda.synchronize()
+        sample_ms = (e0.elapsed_time(e1) - ef0.elapsed_time(ef1)) / 10
+        sample_rate = world * BATCH / (sample_ms * 1e-3)
+        sample_ok = bool(torch.isfinite(z_s).all() and torch.isfinite(lq_s).all())
 
     if rank != 0:
         return
@@ -336,7 +346,9 @@ def gpu_run(args):
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * D * 4,
                 "d2h_bytes_per_step": 4},
         "roofline": roof, "cpu_baseline": cpu,
-        "sample": {"value": sample_rate, "unit": "samples/s", "batch": BATCH},
+        "sample": {"value": sample_rate, "unit": "samples/s", "batch": BATCH, "ms_per_draw": sample_ms,
+                   "cuda_graph": bool(getattr(draw, "graph", None) is not None),
+                   "cuda_graph_error": getattr(draw, "capture_error", None), "finite": sample_ok},
         "loss": float(loss_val),
     }
     _emit(line)

@@ -158,3 +158,43 @@ class GraphedTrainStep:
             return self._eager()
         self.graph.replay()
         return self.loss
+
+
+class GraphedSampler:
+    """`model.sample(num_samples)` (core.py:144-168: base draw + every flow in the sampling direction) captured
+    ONCE into a CUDA graph and replayed.  Eagerly the call is ~500 kernel launches from the Python layer loop and
+    is bound by the launch stream, not by the GPU (6 M samples/s at 65 536 on B200 whatever the kernels do);
+    replayed, the host is out of the loop.  Every replay draws fresh base samples (the CUDA generator's Philox
+    offset is advanced by graph replays) and sees the current parameters.
+
+        draw = GraphedSampler(model, 65536)
+        z, log_q = draw()        # static output tensors, overwritten by the next call -- clone to keep them
+
+    If capture is not possible `.graph` stays None and the call runs eagerly (same results)."""
+
+    def __init__(self, model, num_samples, warmup=3):
+        self.model, self.n = model, int(num_samples)
+        self.graph, self.out, self.capture_error = None, None, None
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(warmup):
+                model.sample(self.n)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.no_grad(), torch.cuda.graph(g):
+                self.out = model.sample(self.n)
+            self.graph = g
+        except Exception as exc:            # noqa: BLE001 -- report and run eagerly
+            self.capture_error = repr(exc)
+            torch.cuda.synchronize()
+            self.graph = None
+
+    def __call__(self):
+        if self.graph is None:
+            with torch.no_grad():
+                return self.model.sample(self.n)
+        self.graph.replay()
+        return self.out
