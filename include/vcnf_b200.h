@@ -176,6 +176,12 @@ int vcnf_lu_compose_bwd(const void* lower_entries, const void* upper_entries, co
                         const void* gW, const void* glogabsdet, void* g_lower, void* g_upper, void* g_diag, int dtype,
                         void* stream);
 
+/* Sampling direction of the same layer (mixing.py:412-429, two triangular solves per call): Winv[D, D] =
+ * U^-1 L^-1 and *logabsdet = log|det W| from the parameter vectors, one launch; substitutions in fp64 for
+ * either dtype.  No gradient (callers that differentiate through the sampling direction keep the solves). */
+int vcnf_lu_inverse(const void* lower_entries, const void* upper_entries, const void* diag_raw, double eps, int D,
+                    void* Winv, void* logabsdet, int dtype, void* stream);
+
 /* ---- K6/K7: conditioner dense layer on tcgen05 tensor cores, fp32-faithful (3xTF32) -------------
  * Replaces F.linear (+ ReLU / residual add / ReLU-backward mask) of the conditioner nets:
  * normflow/nets/resnet.py:38-58,76-106 (ResidualBlock / ResidualNet), nets/mlp.py:7-58,

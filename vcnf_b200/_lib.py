@@ -39,6 +39,7 @@ _SIGNATURES = {
     "vcnf_small_linear": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
     "vcnf_small_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp],
     "vcnf_lu_compose_fwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
+    "vcnf_lu_inverse": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
 }
 _I64_RETURN = {

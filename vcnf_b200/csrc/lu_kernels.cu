@@ -65,6 +65,65 @@ __global__ void __launch_bounds__(kLuThreads) lu_compose_fwd_kernel(const T* low
   }
 }
 
+// Sampling direction (mixing.py:412-429: two triangular solves per call): W^-1 = U^-1 L^-1 and log|det W| from
+// the parameter vectors in ONE launch.  The reference (and round 1's first version) ran index_put x 4, two
+// batched fp64 trsm, casts and fills: ~25 tiny launches, 1.2 ms of a 5.3 ms sample(65536) call of cfg 2.
+// One WARP per column c of the identity: lane l keeps y[l] and y[l + 32] in registers (D <= 64), every
+// substitution step is a masked dot product across the lanes + a shuffle reduction (the first version gave a
+// column to one thread: 2 D^2 dependent fp64 FMAs on shared-memory operands, 32 us per launch).  The arithmetic
+// is fp64 whatever the parameter dtype (like the fp64 solve it replaces), the result is rounded once.
+constexpr int kLuInvThreads = 1024;
+
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kLuInvThreads) lu_inverse_kernel(const T* lower, const T* upper, const T* diag_raw, T eps,
+                                                                   int D, T* Winv, T* logabsdet) {
+  extern __shared__ __align__(16) unsigned char lu_smem[];
+  const int ld = D + 1;
+  T* Ls = reinterpret_cast<T*>(lu_smem);
+  T* Us = Ls + D * ld;
+  for (int e = threadIdx.x; e < D * D; e += kLuInvThreads) {
+    const int i = e / D, j = e - i * D;
+    Ls[i * ld + j] = j < i ? lower[i * (i - 1) / 2 + j] : (j == i ? T(1) : T(0));
+    Us[i * ld + j] = j > i ? upper[i * D - i * (i + 1) / 2 + j - i - 1] : (j == i ? lu_softplus(diag_raw[i]) + eps : T(0));
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = kLuInvThreads / 32;
+  for (int c = warp; c < D; c += nwarp) {
+    double y0 = 0.0, y1 = 0.0;                            // y[lane], y[lane + 32]
+    for (int i = c; i < D; ++i) {                         // L y = e_c (unit diagonal; y_k = 0 for k < c)
+      double part = 0.0;
+      if (lane >= c && lane < i) part += static_cast<double>(Ls[i * ld + lane]) * y0;
+      if (lane + 32 >= c && lane + 32 < i) part += static_cast<double>(Ls[i * ld + lane + 32]) * y1;
+      const double yi = (i == c ? 1.0 : 0.0) - warp_sum_f64(part);
+      if (lane == (i & 31)) { if (i < 32) y0 = yi; else y1 = yi; }
+    }
+    for (int i = D - 1; i >= 0; --i) {                    // U z = y, in place
+      double part = 0.0;
+      if (lane > i && lane < D) part += static_cast<double>(Us[i * ld + lane]) * y0;
+      if (lane + 32 > i && lane + 32 < D) part += static_cast<double>(Us[i * ld + lane + 32]) * y1;
+      const double s = warp_sum_f64(part);
+      if (lane == (i & 31)) {
+        const double d = static_cast<double>(Us[i * ld + i]);
+        if (i < 32) y0 = (y0 - s) / d; else y1 = (y1 - s) / d;
+      }
+    }
+    if (lane < D) Winv[lane * D + c] = static_cast<T>(y0);              // column c of the inverse
+    if (lane + 32 < D) Winv[(lane + 32) * D + c] = static_cast<T>(y1);
+  }
+  if (threadIdx.x < 32) {
+    T acc = T(0);
+    for (int i = threadIdx.x; i < D; i += 32) acc += lu_log(Us[i * ld + i]);
+    acc = warp_sum(acc);
+    if (threadIdx.x == 0) *logabsdet = acc;
+  }
+}
+
 // Given gW = dLoss/dW and gl = dLoss/d log|det|:  gL = gW U^T (strictly lower part), gU = L^T gW (upper part),
 // g_diag_raw[i] = (gU[i][i] + gl / diag(U)_i) * softplus'(raw_i).
 template <typename T>
@@ -147,5 +206,30 @@ extern "C" int vcnf_lu_compose_bwd(const void* lower, const void* upper, const v
     lu_compose_bwd_kernel<double><<<1, kLuThreads, smem, st>>>((const double*)lower, (const double*)upper, (const double*)diag_raw,
                                                             eps, D, (const double*)gW, (const double*)glogabsdet,
                                                             (double*)g_lower, (double*)g_upper, (double*)g_diag);
+  return launch_status();
+}
+
+extern "C" int vcnf_lu_inverse(const void* lower, const void* upper, const void* diag_raw, double eps, int D, void* Winv,
+                               void* logabsdet, int dtype, void* stream) {
+  if (!diag_raw || !Winv || !logabsdet || D <= 0 || (D > 1 && (!lower || !upper)) || (dtype != VCNF_F32 && dtype != VCNF_F64))
+    return VCNF_E_BADARG;
+  if (D > kLuMaxD) return VCNF_E_UNSUPPORTED;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t es = dtype == VCNF_F32 ? 4 : 8;
+  const size_t smem = 2 * static_cast<size_t>(D) * (D + 1) * es;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(lu_inverse_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(lu_inverse_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    attr_set = true;
+  }
+  if (dtype == VCNF_F32)
+    lu_inverse_kernel<float><<<1, kLuInvThreads, smem, st>>>(static_cast<const float*>(lower), static_cast<const float*>(upper),
+                                                          static_cast<const float*>(diag_raw), static_cast<float>(eps), D,
+                                                          static_cast<float*>(Winv), static_cast<float*>(logabsdet));
+  else
+    lu_inverse_kernel<double><<<1, kLuInvThreads, smem, st>>>(static_cast<const double*>(lower), static_cast<const double*>(upper),
+                                                           static_cast<const double*>(diag_raw), eps, D,
+                                                           static_cast<double*>(Winv), static_cast<double*>(logabsdet));
   return launch_status();
 }

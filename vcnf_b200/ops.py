@@ -429,6 +429,18 @@ def lu_compose(lower_entries, upper_entries, unconstrained_upper_diag, eps):
     return _LuCompose.apply(lower_entries, upper_entries, unconstrained_upper_diag, eps)
 
 
+def lu_inverse(lower_entries, upper_entries, unconstrained_upper_diag, eps):
+    """(L U)^-1 and log|det L U| in one launch (sampling direction, no gradient; D <= 64)."""
+    lo, up, dg = _promote(lower_entries.detach(), upper_entries.detach(), unconstrained_upper_diag.detach())
+    lo, up, dg = lo.contiguous(), up.contiguous(), dg.contiguous()
+    D = dg.shape[0]
+    winv = torch.empty((D, D), dtype=dg.dtype, device=dg.device)
+    logabsdet = torch.empty((), dtype=dg.dtype, device=dg.device)
+    _launch("vcnf_lu_inverse", ptr(lo), ptr(up), ptr(dg), float(eps), D, ptr(winv), ptr(logabsdet), dtype_code(dg),
+            stream())
+    return winv, logabsdet
+
+
 KSLICE = 128   # contraction width of one vcnf_linear_tf32x3 / vcnf_linear_wgrad_tf32x3 launch (W resident in TMEM)
 
 
