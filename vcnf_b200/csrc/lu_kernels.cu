@@ -68,11 +68,10 @@ __global__ void __launch_bounds__(kLuThreads) lu_compose_fwd_kernel(const T* low
 // Sampling direction (mixing.py:412-429: two triangular solves per call): W^-1 = U^-1 L^-1 and log|det W| from
 // the parameter vectors in ONE launch.  The reference (and round 1's first version) ran index_put x 4, two
 // batched fp64 trsm, casts and fills: ~25 tiny launches, 1.2 ms of a 5.3 ms sample(65536) call of cfg 2.
-// One WARP per column c of the identity: lane l keeps y[l] and y[l + 32] in registers (D <= 64), every
-// substitution step is a masked dot product across the lanes + a shuffle reduction (the first version gave a
-// column to one thread: 2 D^2 dependent fp64 FMAs on shared-memory operands, 32 us per launch).  The arithmetic
+// One CTA (one solving warp) per column c of the identity, so the D independent solves run on D SMs.  Lane l
+// keeps y[l] and y[l + 32] in registers (D <= 64).  The arithmetic
 // is fp64 whatever the parameter dtype (like the fp64 solve it replaces), the result is rounded once.
-constexpr int kLuInvThreads = 1024;
+constexpr int kLuInvThreads = 128;
 
 __device__ __forceinline__ double warp_sum_f64(double v) {
 #pragma unroll
@@ -93,34 +92,33 @@ __global__ void __launch_bounds__(kLuInvThreads) lu_inverse_kernel(const T* lowe
     Us[i * ld + j] = j > i ? upper[i * D - i * (i + 1) / 2 + j - i - 1] : (j == i ? lu_softplus(diag_raw[i]) + eps : T(0));
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = kLuInvThreads / 32;
-  for (int c = warp; c < D; c += nwarp) {
-    double y0 = 0.0, y1 = 0.0;                            // y[lane], y[lane + 32]
-    for (int i = c; i < D; ++i) {                         // L y = e_c (unit diagonal; y_k = 0 for k < c)
-      double part = 0.0;
-      if (lane >= c && lane < i) part += static_cast<double>(Ls[i * ld + lane]) * y0;
-      if (lane + 32 >= c && lane + 32 < i) part += static_cast<double>(Ls[i * ld + lane + 32]) * y1;
-      const double yi = (i == c ? 1.0 : 0.0) - warp_sum_f64(part);
-      if (lane == (i & 31)) { if (i < 32) y0 = yi; else y1 = yi; }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) {
+    const int c = blockIdx.x;
+    // column-oriented substitution: once y_i is final it is broadcast (one shuffle) and every lane updates the
+    // entries it owns -- no reduction on the dependent chain (the dot-product form cost ~700 clk per step)
+    double y0 = lane == c ? 1.0 : 0.0, y1 = lane + 32 == c ? 1.0 : 0.0;      // y[lane], y[lane + 32] = e_c
+    const double rd0 = lane < D ? 1.0 / static_cast<double>(Us[lane * ld + lane]) : 0.0;
+    const double rd1 = lane + 32 < D ? 1.0 / static_cast<double>(Us[(lane + 32) * ld + lane + 32]) : 0.0;
+    for (int i = c; i < D; ++i) {                         // L y = e_c (unit diagonal)
+      const double yi = __shfl_sync(0xffffffffu, i < 32 ? y0 : y1, i & 31);
+      if (lane > i && lane < D) y0 -= static_cast<double>(Ls[lane * ld + i]) * yi;
+      if (lane + 32 > i && lane + 32 < D) y1 -= static_cast<double>(Ls[(lane + 32) * ld + i]) * yi;
     }
     for (int i = D - 1; i >= 0; --i) {                    // U z = y, in place
-      double part = 0.0;
-      if (lane > i && lane < D) part += static_cast<double>(Us[i * ld + lane]) * y0;
-      if (lane + 32 > i && lane + 32 < D) part += static_cast<double>(Us[i * ld + lane + 32]) * y1;
-      const double s = warp_sum_f64(part);
-      if (lane == (i & 31)) {
-        const double d = static_cast<double>(Us[i * ld + i]);
-        if (i < 32) y0 = (y0 - s) / d; else y1 = (y1 - s) / d;
-      }
+      if (lane == (i & 31)) { if (i < 32) y0 *= rd0; else y1 *= rd1; }
+      const double zi = __shfl_sync(0xffffffffu, i < 32 ? y0 : y1, i & 31);
+      if (lane < i) y0 -= static_cast<double>(Us[lane * ld + i]) * zi;
+      if (lane + 32 < i) y1 -= static_cast<double>(Us[(lane + 32) * ld + i]) * zi;
     }
     if (lane < D) Winv[lane * D + c] = static_cast<T>(y0);              // column c of the inverse
     if (lane + 32 < D) Winv[(lane + 32) * D + c] = static_cast<T>(y1);
   }
-  if (threadIdx.x < 32) {
+  if (blockIdx.x == 0 && warp == 1) {
     T acc = T(0);
-    for (int i = threadIdx.x; i < D; i += 32) acc += lu_log(Us[i * ld + i]);
+    for (int i = lane; i < D; i += 32) acc += lu_log(Us[i * ld + i]);
     acc = warp_sum(acc);
-    if (threadIdx.x == 0) *logabsdet = acc;
+    if (lane == 0) *logabsdet = acc;
   }
 }
 
@@ -224,11 +222,11 @@ extern "C" int vcnf_lu_inverse(const void* lower, const void* upper, const void*
     attr_set = true;
   }
   if (dtype == VCNF_F32)
-    lu_inverse_kernel<float><<<1, kLuInvThreads, smem, st>>>(static_cast<const float*>(lower), static_cast<const float*>(upper),
+    lu_inverse_kernel<float><<<D, kLuInvThreads, smem, st>>>(static_cast<const float*>(lower), static_cast<const float*>(upper),
                                                           static_cast<const float*>(diag_raw), static_cast<float>(eps), D,
                                                           static_cast<float*>(Winv), static_cast<float*>(logabsdet));
   else
-    lu_inverse_kernel<double><<<1, kLuInvThreads, smem, st>>>(static_cast<const double*>(lower), static_cast<const double*>(upper),
+    lu_inverse_kernel<double><<<D, kLuInvThreads, smem, st>>>(static_cast<const double*>(lower), static_cast<const double*>(upper),
                                                            static_cast<const double*>(diag_raw), eps, D,
                                                            static_cast<double*>(Winv), static_cast<double*>(logabsdet));
   return launch_status();
