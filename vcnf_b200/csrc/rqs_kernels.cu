@@ -611,6 +611,12 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
   // a full tile whose spans all go through the TMA engine needs nothing but the mbarrier wait
   const bool full_tiles_bulk = (Tc == 0 || span_bulk<float>(a.bulk_p, static_cast<int64_t>(a.R) * a.prow)) &&
                                span_bulk<float>(a.bulk_x, static_cast<int64_t>(a.R) * D);
+  // pass C fast form: at most two output elements and one log-det row pair per lane
+  const bool small_c = rpw * D <= 64 && D <= 32 && rpw <= 2 && a.ldy == D;
+  float* const y_run = a.y + (static_cast<int64_t>(blockIdx.x) * a.R + r_lo) * D;      // + it * y_step per tile
+  const int64_t y_step = static_cast<int64_t>(gridDim.x) * a.R * D;
+  float* const ld_run = a.logdet + static_cast<int64_t>(blockIdx.x) * a.R + r_lo;
+  const int64_t ld_step = static_cast<int64_t>(gridDim.x) * a.R;
 
   int flag = 0;
   for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
@@ -681,30 +687,48 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_fwd_fast_kernel(const RqsL
     if (nrow > 0) {
       const int n = nrow * D;
       const float* src = ys + r_lo * D;
-      if (a.ldy == D) {
-        float* dst = a.y + (row0 + r_lo) * D;
-#pragma unroll 1
-        for (int e = lane; e < n; e += 32) dst[e] = src[e];
-      } else {
-        for (int rr = 0; rr < nrow; ++rr)
-#pragma unroll 1
-          for (int c = lane; c < D; c += 32) a.y[(row0 + r_lo + rr) * a.ldy + c] = src[rr * D + c];
-      }
-      const int hl = lane & 15;
-#pragma unroll 1
-      for (int rr0 = 0; rr0 < nrow; rr0 += 2) {
-        const int rr = rr0 + (lane >> 4);
+      if (small_c) {
+        // common shapes (rpw * D <= 64, D <= 32, contiguous y): two predicated stores per lane, no loops and no
+        // per-tile 64-bit index arithmetic beyond the running row pointer
+        float* dst = y_run + static_cast<int64_t>(it) * y_step;
+        if (lane < n) dst[lane] = src[lane];
+        if (lane + 32 < n) dst[lane + 32] = src[lane + 32];
+        const int hl = lane & 15, rr = lane >> 4;
+        const float* lrow = lads + (r_lo + rr) * D;
         float acc = 0.f;
-        if (rr < nrow) {
-          const float* lrow = lads + (r_lo + rr) * D;
-#pragma unroll 1
-          for (int c = hl; c < D; c += 16) acc += lrow[c];
-        }
+        if (rr < nrow) acc = (hl < D ? lrow[hl] : 0.f) + (hl + 16 < D ? lrow[hl + 16] : 0.f);
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (rr < nrow && hl == 0) {
-          const int64_t g = row0 + r_lo + rr;
-          a.logdet[g] = a.accumulate ? acc + a.logdet[g] : acc;
+          float* ldp = ld_run + static_cast<int64_t>(it) * ld_step + rr;
+          *ldp = a.accumulate ? acc + *ldp : acc;
+        }
+      } else {
+        if (a.ldy == D) {
+          float* dst = a.y + (row0 + r_lo) * D;
+#pragma unroll 1
+          for (int e = lane; e < n; e += 32) dst[e] = src[e];
+        } else {
+          for (int rr = 0; rr < nrow; ++rr)
+#pragma unroll 1
+            for (int c = lane; c < D; c += 32) a.y[(row0 + r_lo + rr) * a.ldy + c] = src[rr * D + c];
+        }
+        const int hl = lane & 15;
+#pragma unroll 1
+        for (int rr0 = 0; rr0 < nrow; rr0 += 2) {
+          const int rr = rr0 + (lane >> 4);
+          float acc = 0.f;
+          if (rr < nrow) {
+            const float* lrow = lads + (r_lo + rr) * D;
+#pragma unroll 1
+            for (int c = hl; c < D; c += 16) acc += lrow[c];
+          }
+#pragma unroll
+          for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+          if (rr < nrow && hl == 0) {
+            const int64_t g = row0 + r_lo + rr;
+            a.logdet[g] = a.accumulate ? acc + a.logdet[g] : acc;
+          }
         }
       }
     }
@@ -774,6 +798,9 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
   const int r_lo = warp * rpw;
   const int Gw = Ts > 0 ? (Ts <= 32 ? 32 / Ts : 1) : 0;      // row groups per warp of the batch-shared pass
   float* my_gst = gst + static_cast<size_t>(r_lo) * a.grow;
+  const bool small_c = rpw * D <= 64 && a.ldgx == D;       // pass C: at most two input-gradient elements per lane
+  float* const gx_run = a.gx + (static_cast<int64_t>(blockIdx.x) * a.R + r_lo) * D;
+  const int64_t gx_step = static_cast<int64_t>(gridDim.x) * a.R * D;
   bool store_pending = false;                                // lane 0: a bulk store of my_gst may still be reading it
 
   for (int it = 0; tile < a.num_tiles; tile += gridDim.x, ++it) {
@@ -877,7 +904,11 @@ __global__ void __launch_bounds__(kThreads) rqs_layer_bwd_fast_kernel(const RqsL
     if (nrow > 0) {
       const int n = nrow * D;
       const float* src = gxs + r_lo * D;
-      if (a.ldgx == D) {
+      if (small_c) {
+        float* dst = gx_run + static_cast<int64_t>(it) * gx_step;
+        if (lane < n) dst[lane] = src[lane];
+        if (lane + 32 < n) dst[lane + 32] = src[lane + 32];
+      } else if (a.ldgx == D) {
         float* dst = a.gx + (row0 + r_lo) * D;
 #pragma unroll 1
         for (int e = lane; e < n; e += 32) dst[e] = src[e];
