@@ -204,6 +204,22 @@ int64_t vcnf_linear_wgrad_workspace(int64_t B, int N, int K);
 int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void* X, int64_t ldx, void* gW, void* gb,
                              void* workspace, int64_t B, int N, int K, int relu_in, void* stream);
 
+/* ---- K6 (small nets): MLP conditioner evaluated in registers, one launch per direction --------------
+ * normflow/nets/mlp.py:7-58: Linear + LeakyReLU(slope) ... Linear, nl <= 4 linear layers, every width <= 32
+ * (the [1,32,32,2] net of the README Real NVP, the [15,30,15] / [1,4,1] nets of the dequantisation flows).
+ * W / b are HOST arrays of nl device pointers (W[l] is [dims[l+1], dims[l]] row-major, b[l] may be NULL),
+ * dims a HOST array of nl+1 widths; slope >= 0.  x [B, dims[0]] (ldx), y [B, dims[nl]] (ldy). */
+int vcnf_mlp_fwd(const void* x, int64_t ldx, void* y, int64_t ldy, const void* const* W, const void* const* b,
+                 const int32_t* dims, int nl, double slope, int64_t B, int dtype, void* stream);
+/* Backward (autograd of the nn.Sequential above): gx [B, dims[0]] (may be NULL) and the parameter gradients
+ * gparams = for l = 0..nl-1: [gW_l (dims[l+1] x dims[l]) | gb_l (dims[l+1])], summed over the batch in a fixed
+ * order (deterministic).  `workspace` must hold vcnf_mlp_bwd_workspace(dims, nl, dtype) bytes.  Returns
+ * VCNF_E_UNSUPPORTED when the per-CTA accumulators do not fit in shared memory (wide fp64 nets). */
+int64_t vcnf_mlp_bwd_workspace(const int32_t* dims, int nl, int dtype);
+int vcnf_mlp_bwd(const void* x, int64_t ldx, const void* gy, int64_t ldgy, const void* const* W, const void* const* b,
+                 const int32_t* dims, int nl, double slope, void* gx, int64_t ldgx, void* gparams, void* workspace,
+                 int64_t B, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,8 @@ _SIGNATURES = {
     "vcnf_small_linear": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
     "vcnf_small_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp],
     "vcnf_lu_compose_fwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
+    "vcnf_mlp_fwd": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _dbl, _i64, _i32, _vp],
+    "vcnf_mlp_bwd": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _dbl, _vp, _i64, _vp, _vp, _i64, _i32, _vp],
     "vcnf_lu_inverse": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
 }
@@ -47,6 +49,7 @@ _I64_RETURN = {
     "vcnf_const_affine_bwd_workspace": [_i32, _i32],
     "vcnf_linear_wgrad_workspace": [_i64, _i32, _i32],
     "vcnf_small_linear_bwd_workspace": [_i32, _i32],
+    "vcnf_mlp_bwd_workspace": [_vp, _i32, _i32],
 }
 EXPORTED = sorted(list(_SIGNATURES) + list(_I64_RETURN))
 

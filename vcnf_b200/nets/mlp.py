@@ -1,7 +1,9 @@
-"""MLP conditioner (reference: normflow/nets/mlp.py:7-58).  fp32 CUDA operands with the default
-`leaky=0.0` run every dense layer on the tcgen05 3xTF32 kernel (`ops.linear`), the ReLU fused into the
-load of the following layer; fp64 models (`nfm.double()`) and leaky slopes != 0 keep nn.Linear (library
-GEMM).  Same module tree / state_dict keys (`net.0.weight`, ...) as the reference either way."""
+"""MLP conditioner (reference: normflow/nets/mlp.py:7-58).  Nets whose widths are all <= 32 (the [1,32,32,2]
+net of the README Real NVP, the [15,30,15] / [1,4,1] nets of the dequantisation flows; fp32 and fp64, any
+LeakyReLU slope >= 0) are evaluated in registers by ONE kernel per direction (`ops.mlp_small`).  Wider fp32
+nets with `leaky=0.0` run every dense layer on the tcgen05 3xTF32 kernel (`ops.linear`), the ReLU fused into
+the load of the following layer; anything else keeps nn.Linear (library GEMM).  Same module tree /
+state_dict keys (`net.0.weight`, ...) as the reference either way."""
 import torch
 from torch import nn
 
@@ -33,10 +35,33 @@ class MLP(nn.Module):
                 stack.append(utils.ConstScaleLayer(output_scale))
         self.net = nn.Sequential(*stack)
 
+    def _fused_prefix(self):
+        """Leading `Linear (LeakyReLU Linear)*` run of self.net with one common slope, and how many modules it spans."""
+        mods = list(self.net)
+        lin, slope, k = [mods[0]], None, 1
+        while k + 1 < len(mods) and isinstance(mods[k], nn.LeakyReLU) and isinstance(mods[k + 1], nn.Linear):
+            if slope is not None and mods[k].negative_slope != slope:
+                break
+            slope = mods[k].negative_slope
+            lin.append(mods[k + 1])
+            k += 2
+        return lin, (0.0 if slope is None else slope), k
+
     def forward(self, x):
-        if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2):
+        if not (x.is_cuda and x.dim() == 2 and x.dtype in (torch.float32, torch.float64)):
             return self.net(x)
         mods = list(self.net)
+        if isinstance(mods[0], nn.Linear):
+            lin, slope, k = self._fused_prefix()
+            weights, biases = [m.weight for m in lin], [m.bias for m in lin]
+            if ops.mlp_small_supported(x, weights, slope):
+                # the whole net in registers: one launch forward, one (+ reduce) backward -- vcnf_mlp_fwd / _bwd
+                h = ops.mlp_small(x, weights, biases, slope)
+                for m in mods[k:]:
+                    h = m(h)
+                return h
+        if x.dtype != torch.float32:
+            return self.net(x)
         h, pending_relu = x, False
         for i, m in enumerate(mods):
             if isinstance(m, nn.Linear) and ops.linear_supported(h, m.weight):

@@ -441,6 +441,78 @@ def lu_inverse(lower_entries, upper_entries, unconstrained_upper_diag, eps):
     return winv, logabsdet
 
 
+# ------------------------------------------------------------------ small MLP conditioner (registers)
+MLP_MAX_WIDTH, MLP_MAX_LAYERS = 32, 4
+
+
+def mlp_small_supported(x, weights, slope):
+    """vcnf_mlp_fwd / _bwd: CUDA fp32 / fp64 rows, <= 4 linear layers, every width <= 32, LeakyReLU slope >= 0."""
+    return (x.is_cuda and x.dim() == 2 and x.dtype in (torch.float32, torch.float64) and slope >= 0.0
+            and 1 <= len(weights) <= MLP_MAX_LAYERS and all(w.dtype == x.dtype and w.dim() == 2 for w in weights)
+            and x.shape[1] == weights[0].shape[1]
+            and all(max(w.shape) <= MLP_MAX_WIDTH for w in weights)
+            # the backward keeps 4 per-warp copies of the parameter gradient in shared memory (200 KB limit)
+            and (16640 + 4 * sum(w.numel() + w.shape[0] for w in weights)) * x.element_size() <= 200 * 1024)
+
+
+def _ptr_array(tensors):
+    import ctypes
+    return (ctypes.c_void_p * len(tensors))(*[ptr(t) for t in tensors])
+
+
+class _MlpSmall(torch.autograd.Function):
+    """y = Linear_n(act(... act(Linear_1(x)))) with act = LeakyReLU(slope): one kernel forward, one kernel (plus
+    the fixed-order reduce) backward.  args = (x, slope, n, W_1..W_n, b_1..b_n) with None for missing biases."""
+
+    @staticmethod
+    def forward(ctx, x, slope, n, *wb):
+        import ctypes
+        weights, biases = [w.contiguous() for w in wb[:n]], [b.contiguous() if b is not None else None for b in wb[n:]]
+        x = _rows(x)
+        B = x.shape[0]
+        dims = [weights[0].shape[1]] + [w.shape[0] for w in weights]
+        cdims = (ctypes.c_int32 * len(dims))(*dims)
+        y = torch.empty((B, dims[-1]), dtype=x.dtype, device=x.device)
+        _launch("vcnf_mlp_fwd", ptr(x), x.stride(0), ptr(y), y.stride(0), _ptr_array(weights), _ptr_array(biases),
+                cdims, n, float(slope), B, dtype_code(x), stream())
+        ctx.cfg = (float(slope), n, dims)
+        ctx.has_bias = [b is not None for b in biases]
+        ctx.save_for_backward(x, *weights, *[b for b in biases if b is not None])
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        import ctypes
+        slope, n, dims = ctx.cfg
+        saved = ctx.saved_tensors
+        x, weights = saved[0], list(saved[1:1 + n])
+        it = iter(saved[1 + n:])
+        biases = [next(it) if hb else None for hb in ctx.has_bias]
+        gy = _rows(gy)
+        B = x.shape[0]
+        cdims = (ctypes.c_int32 * len(dims))(*dims)
+        psize = sum(dims[l + 1] * dims[l] + dims[l + 1] for l in range(n))
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        gparams = torch.empty(psize, dtype=x.dtype, device=x.device)
+        ws = torch.empty(max(1, _lib.query("vcnf_mlp_bwd_workspace", cdims, n, dtype_code(x))), dtype=torch.uint8,
+                         device=x.device)
+        _launch("vcnf_mlp_bwd", ptr(x), x.stride(0), ptr(gy), gy.stride(0), _ptr_array(weights), _ptr_array(biases),
+                cdims, n, slope, ptr(gx), gx.stride(0) if gx is not None else 0, ptr(gparams), ptr(ws), B,
+                dtype_code(x), stream(), n=2)
+        gws, gbs, off = [], [], 0
+        for l in range(n):
+            nw = dims[l + 1] * dims[l]
+            gws.append(gparams[off:off + nw].view(dims[l + 1], dims[l]))
+            gbs.append(gparams[off + nw:off + nw + dims[l + 1]] if ctx.has_bias[l] else None)
+            off += nw + dims[l + 1]
+        return (gx, None, None, *gws, *gbs)
+
+
+def mlp_small(x, weights, biases, slope):
+    return _MlpSmall.apply(x, float(slope), len(weights), *weights, *biases)
+
+
 KSLICE = 128   # contraction width of one vcnf_linear_tf32x3 / vcnf_linear_wgrad_tf32x3 launch (W resident in TMEM)
 
 
