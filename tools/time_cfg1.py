@@ -35,6 +35,31 @@ for B in (1024, 1 << 20):
     ms = e0.elapsed_time(e1) / n
     print("cfg1 reverse_kld B=%d: %.3f ms/step eager, %.2f M samples/s, loss %.4f, %d vcnf launches/step" % (
         B, ms, B / ms / 1e3, float(loss), (ops.LAUNCHES - launches) // n))
+# the same step replayed from a CUDA graph (parallel.GraphedTrainStep with a reverse_kld loss); the eager loss must
+# be released first: it keeps AccumulateGrad nodes bound to the legacy stream alive, which capture cannot wait on
+del loss
+from vcnf_b200 import parallel
+for B in (1024, 1 << 16, 1 << 20):
+    opt_g = torch.optim.Adam(model.parameters(), lr=1e-4, capturable=True)
+    bucket = parallel.GradBucket(model.parameters())
+    dummy = torch.zeros(1, device=dev)
+    gstep = parallel.GraphedTrainStep(model, opt_g, bucket, dummy, world=1,
+                                      loss_fn=lambda m, x, B=B: m.reverse_kld(num_samples=B))
+    if gstep.graph is None:
+        print("capture failed:", gstep.capture_error[:600])
+        break
+    for _ in range(3):
+        gstep(dummy)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(50):
+        gloss = gstep(dummy)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 50
+    print("cfg1 reverse_kld B=%d graphed: %.3f ms/step, %.2f M samples/s, loss %.4f" % (B, ms, B / ms / 1e3, float(gloss)))
+    del gstep, gloss
 # the MLP kernels alone
 B = 1 << 20
 net = nf.nets.MLP([1, 32, 32, 2]).to(dev)

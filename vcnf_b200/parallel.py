@@ -104,6 +104,27 @@ def sync_actnorm_init(model, src=0):
             dist.broadcast(m.t.data, src)
 
 
+def _after_failed_capture(exc):
+    """A capture that raised leaves the CUDA generator in capture mode (the next eager `torch.randn` raises
+    "Offset increment outside graph capture"): a trivial capture that succeeds runs the generator's prologue and
+    epilogue again and clears it.  Returns the error text, with a hint for the one failure a caller can fix."""
+    text = repr(exc)
+    torch.cuda.synchronize()
+    try:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            torch.zeros(1, device="cuda").add_(1)
+        del g
+        torch.cuda.synchronize()
+    except Exception:                   # noqa: BLE001 -- best effort, the caller falls back to eager steps
+        pass
+    if "legacy stream" in text or "StreamCaptureImplicit" in text or "StreamCaptureInvalidated" in text:
+        text += (" [hint: a loss / output of an earlier eager backward on the default stream is still alive; "
+                 "it keeps the parameters' AccumulateGrad nodes, which are bound to the legacy stream, in use. "
+                 "Drop those references (del loss) before building the graphed step.]")
+    return text
+
+
 class GraphedTrainStep:
     """One `forward_kld` training step (zero grads -> loss -> backward -> [gradient all-reduce] -> optimizer
     step) captured ONCE into a CUDA graph and replayed.  A cfg-2 step is ~1600 kernel launches from a
@@ -115,15 +136,19 @@ class GraphedTrainStep:
         loss = step(batch)          # copies `batch` into the static input, replays, returns the 0-dim loss
 
     The optimizer must be graph-capturable (e.g. torch.optim.Adam(..., capturable=True)).  If capture is
-    not possible (a layer with a host-side branch such as ActNorm's first-call init), `.graph` stays None
-    and the step runs eagerly -- same results, launch-bound."""
+    not possible (a layer with a host-side branch such as ActNorm's first-call init), `.graph` stays None,
+    `.capture_error` says why and the step runs eagerly -- same results, launch-bound.  `loss_fn(model, x)`
+    replaces the loss, e.g. `lambda m, x: m.reverse_kld(num_samples=1024)` for the README's 2-D Real NVP
+    (cfg 1; the base distribution's draw is captured and every replay advances the Philox offset).
+    Tensors of an earlier eager backward on the default stream (a kept `loss`) must be released first: they
+    hold the parameters' AccumulateGrad nodes, whose stream is the legacy stream, and capture cannot wait on it."""
 
     def __init__(self, model, optimizer, bucket, example, world=None, warmup=3, loss_fn=None):
         self.model, self.opt, self.bucket = model, optimizer, bucket
         self.world = world
         self.loss_fn = loss_fn if loss_fn is not None else (lambda m, x: m.forward_kld(x))
         self.x = example.clone()
-        self.graph, self.loss = None, None
+        self.graph, self.loss, self.capture_error = None, None, None
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -137,8 +162,7 @@ class GraphedTrainStep:
                 self.loss = self._eager()
             self.graph = g
         except Exception as exc:            # noqa: BLE001 -- report and run eagerly
-            self.capture_error = repr(exc)
-            torch.cuda.synchronize()
+            self.capture_error = _after_failed_capture(exc)
             self.graph = None
 
     def _eager(self):
@@ -188,8 +212,7 @@ class GraphedSampler:
                 self.out = model.sample(self.n)
             self.graph = g
         except Exception as exc:            # noqa: BLE001 -- report and run eagerly
-            self.capture_error = repr(exc)
-            torch.cuda.synchronize()
+            self.capture_error = _after_failed_capture(exc)
             self.graph = None
 
     def __call__(self):
