@@ -232,8 +232,13 @@ def gpu_run(args):
     torch.cuda.set_device(dev)
     torch.manual_seed(0)
     model = build_model(nf).to(dev)
-    bucket = parallel.GradBucket(model.parameters())
-    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True, capturable=not args.no_graph)
+    if args.torch_adam:
+        bucket = parallel.GradBucket(model.parameters())
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True, capturable=not args.no_graph)
+    else:
+        # Adam on flat parameter / gradient / moment buffers, one launch per step (vcnf_b200/optim.py)
+        opt = nf.optim.FlatAdam(model.parameters(), lr=1e-3)
+        bucket = opt.bucket
     x_host = synth_batch(BATCH, 1234 + rank).pin_memory()
     x_dev = x_host.to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -340,7 +345,7 @@ def gpu_run(args):
         "config": {"workload": WORKLOAD, "global_batch": world * BATCH, "features": D, "layers": LAYERS,
                    "hidden": HIDDEN, "bins": BINS, "parallelism": "dp%d" % world,
                    "l2": "256 MiB buffer written between timed steps (L2 flush)",
-                   "conditioner_gemms": "tcgen05 3xTF32 (vcnf_linear_tf32x3 fwd/dgrad, vcnf_linear_wgrad_tf32x3)", "optimizer": "Adam(fused)", "cuda_graph": graphed,
+                   "conditioner_gemms": "tcgen05 3xTF32 (vcnf_linear_tf32x3 fwd/dgrad, vcnf_linear_wgrad_tf32x3)", "optimizer": "torch Adam(fused)" if args.torch_adam else "Adam, flat buffers (vcnf_adam_flat)", "cuda_graph": graphed,
                    "cuda_graph_error": getattr(step, "capture_error", None) if not args.no_graph else None},
         "clocks": clocks, "gpu_launches": launches,
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * D * 4,
@@ -404,6 +409,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--torch-adam", action="store_true", help="torch.optim.Adam(fused=True) instead of optim.FlatAdam")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_run(args)

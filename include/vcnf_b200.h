@@ -220,6 +220,17 @@ int vcnf_mlp_bwd(const void* x, int64_t ldx, const void* gy, int64_t ldgy, const
                  const int32_t* dims, int nl, double slope, void* gx, int64_t ldgx, void* gparams, void* workspace,
                  int64_t B, int dtype, void* stream);
 
+/* ---- K10: optimiser step on flat buffers -------------------------------------------------------
+ * Replaces torch.optim.Adam(...).step() of the reference's training loops (runcred.py:192,257; run.py:139:
+ * lr, weight_decay, default betas / eps, amsgrad off) when parameters, gradients and both moments each live in
+ * ONE contiguous buffer of n elements (16 B aligned): one launch, 28 B per fp32 parameter.
+ *   g' = g + weight_decay p;  m = beta1 m + (1 - beta1) g';  v = beta2 v + (1 - beta2) g'^2;
+ *   p -= lr / (1 - beta1^t) * m / (sqrt(v) / sqrt(1 - beta2^t) + eps),   t = *step + 1.
+ * `step` (device fp32 [1], steps taken so far) is advanced by the kernel itself after every CTA has read it
+ * (`ticket`: device uint32 [1], zero before the first call), so a captured launch replays correctly. */
+int vcnf_adam_flat(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n, double lr,
+                   double beta1, double beta2, double eps, double weight_decay, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,3 +15,4 @@ from . import ops
 
 __version__ = "0.1"
 from . import parallel
+from . import optim

@@ -43,6 +43,7 @@ _SIGNATURES = {
     "vcnf_mlp_bwd": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _dbl, _vp, _i64, _vp, _vp, _i64, _i32, _vp],
     "vcnf_lu_inverse": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
+    "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
 }
 _I64_RETURN = {
     "vcnf_rqs_layer_bwd_workspace": [_i32, _i32, _i32],

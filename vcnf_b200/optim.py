@@ -1,0 +1,77 @@
+"""Optimiser step of the training loops on flat buffers.
+
+The reference trains with `torch.optim.Adam(nfm.parameters(), lr=1e-4, weight_decay=1e-6)` (runcred.py:192,
+run.py:139) and calls `optimizer.step()` after `loss.backward()` (runcred.py:246-258).  A cfg-2 model has ~260
+parameter tensors; the library's multi-tensor Adam needs 0.58 ms per step for 1.8 M parameters (chunk tables, one
+step counter per tensor).  `FlatAdam` re-homes the parameters into ONE buffer (each `p.data` becomes a view of it),
+keeps both moments flat, takes the gradients from a `parallel.GradBucket` laid out the same way and runs ONE
+kernel (`vcnf_adam_flat`, 28 B per fp32 parameter).  Arithmetic and hyper-parameters are torch.optim.Adam's
+(amsgrad off, maximize off); a parameter that received no gradient counts as a zero gradient."""
+import torch
+
+from . import ops
+from ._lib import ptr, stream, dtype_code
+from .parallel import GradBucket
+
+ALIGN = 32          # elements: every parameter starts on a 128 B (fp32) / 256 B (fp64) boundary
+
+
+class FlatAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, bucket=None):
+        params = [p for p in params if p.requires_grad]
+        if not params:
+            raise ValueError("FlatAdam: no parameters to optimise")
+        if not all(p.is_cuda for p in params):
+            raise RuntimeError("FlatAdam runs on CUDA parameters only (vcnf_b200 has no CPU path)")
+        if lr < 0 or eps < 0 or weight_decay < 0 or not (0 <= betas[0] < 1 and 0 <= betas[1] < 1):
+            raise ValueError("FlatAdam: invalid hyper-parameter")
+        super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
+        if bucket is None:
+            bucket = GradBucket(params, align=ALIGN)
+        if [id(p) for p in bucket.params] != [id(p) for p in params] or any(o % ALIGN for o in bucket.offsets):
+            raise ValueError("FlatAdam: the gradient bucket must hold the same parameters in the same order, "
+                             "GradBucket(params, align=optim.ALIGN)")
+        self.bucket = bucket
+        p0 = params[0]
+        self.flat_p = torch.zeros(bucket.total, dtype=p0.dtype, device=p0.device)
+        with torch.no_grad():
+            for p, off in zip(params, bucket.offsets):
+                view = self.flat_p[off:off + p.numel()].view_as(p)
+                view.copy_(p)
+                p.data = view                 # the module keeps its Parameter objects; only the storage moves
+        self.exp_avg = torch.zeros_like(self.flat_p)
+        self.exp_avg_sq = torch.zeros_like(self.flat_p)
+        self.steps = torch.zeros(1, dtype=torch.float32, device=p0.device)
+        self._ticket = torch.zeros(1, dtype=torch.int32, device=p0.device)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        g = self.param_groups[0]
+        self.bucket.collect()                 # no-op when the gradients already are the bucket's views
+        ops._launch("vcnf_adam_flat", ptr(self.flat_p), ptr(self.bucket.flat), ptr(self.exp_avg),
+                    ptr(self.exp_avg_sq), ptr(self.steps), ptr(self._ticket), self.bucket.total, float(g["lr"]),
+                    float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), float(g["weight_decay"]),
+                    dtype_code(self.flat_p), stream())
+        return loss
+
+    def zero_grad(self, set_to_none=True):
+        if set_to_none:
+            self.bucket.begin()
+        else:
+            self.bucket.collect()
+            self.bucket.zero()
+
+    def state_dict(self):
+        return {"exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(), "steps": self.steps.clone(),
+                "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]}
+
+    def load_state_dict(self, state):
+        self.exp_avg.copy_(state["exp_avg"])
+        self.exp_avg_sq.copy_(state["exp_avg_sq"])
+        self.steps.copy_(state["steps"])
+        for g, saved in zip(self.param_groups, state["param_groups"]):
+            g.update(saved)

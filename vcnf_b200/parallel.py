@@ -38,20 +38,24 @@ class GradBucket:
     """Flat gradient bucket: grads are views into one contiguous buffer, so the all-reduce is a
     single collective on 7-32 MB (latency-bound on NVSwitch)."""
 
-    def __init__(self, params):
+    def __init__(self, params, align=1):
+        """`align`: every parameter's slice starts at a multiple of `align` elements (pad elements stay zero);
+        optim.FlatAdam lays its parameter / moment buffers out the same way."""
         self.params = [p for p in params if p.requires_grad]
+        self.offsets, total = [], 0
+        for p in self.params:
+            self.offsets.append(total)
+            total += (p.numel() + align - 1) // align * align
+        self.total = total
         if not self.params:
             self.flat = None
             return
         p0 = self.params[0]
-        total = sum(p.numel() for p in self.params)
         self.flat = torch.zeros(total, dtype=p0.dtype, device=p0.device)
-        off = 0
-        for p in self.params:
+        for p, off in zip(self.params, self.offsets):
             if p.dtype != p0.dtype:
                 raise TypeError("GradBucket needs a single parameter dtype")
             p.grad = self.flat[off:off + p.numel()].view_as(p)
-            off += p.numel()
 
     def zero(self):
         if self.flat is not None:
@@ -69,10 +73,9 @@ class GradBucket:
     def collect(self):
         if self.flat is None:
             return
-        off, views, grads, missing = 0, [], [], []
-        for p in self.params:
+        views, grads, missing = [], [], []
+        for p, off in zip(self.params, self.offsets):
             v = self.flat[off:off + p.numel()].view_as(p)
-            off += p.numel()
             if p.grad is None:
                 missing.append(v)
             elif p.grad.data_ptr() != v.data_ptr():
