@@ -9,8 +9,21 @@ from .base import Flow
 from .. import ops
 
 
+_I32_CACHE = {}
+
+
 def _i32(t):
-    return t.to(torch.int32).contiguous()
+    """int32 copy of an index buffer for the kernels, converted once per (storage, version, device) instead of
+    once per call (one tiny launch per layer and direction otherwise)."""
+    key = (t.data_ptr(), t._version, t.device, tuple(t.shape))
+    hit = _I32_CACHE.get(id(t))
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    if len(_I32_CACHE) > 4096:
+        _I32_CACHE.clear()
+    out = t.to(torch.int32).contiguous()
+    _I32_CACHE[id(t)] = (key, out, t)          # holding `t` keeps its id from being reused
+    return out
 
 
 class Permute(Flow):
@@ -216,7 +229,7 @@ class _LULinear(Flow):
         else:
             weight, logabsdet = self.weight(), self.logabsdet()
         out = ops.small_linear(inputs, weight, self.bias, in_idx=in_idx)
-        return out, logabsdet * inputs.new_ones(out.shape[0])
+        return out, ops.broadcast_scalar(logabsdet.to(torch.promote_types(logabsdet.dtype, inputs.dtype)), out.shape[0])
 
     def inverse(self, inputs, context=None, out_idx=None):
         needs_grad = torch.is_grad_enabled() and (inputs.requires_grad or self.lower_entries.requires_grad)
@@ -229,7 +242,7 @@ class _LULinear(Flow):
         else:
             winv, logabsdet = self.weight_inverse(), self.logabsdet()
         out = ops.small_linear(inputs, winv, self.bias, out_idx=out_idx, sub_bias_first=True)
-        return out, -logabsdet * inputs.new_ones(out.shape[0])
+        return out, ops.broadcast_scalar(-logabsdet.to(torch.promote_types(logabsdet.dtype, inputs.dtype)), out.shape[0])
 
 
 class LULinearPermute(Flow):
