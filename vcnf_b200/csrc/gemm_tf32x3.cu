@@ -702,6 +702,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
         const int s = it % kStages;
         mbar_wait(&full[s], (it / kStages) & 1u);
         unsigned char* hi_p = ring + static_cast<uint32_t>(s) * 2 * kPlane + tid * 16;
+#ifndef VCNF_EXP_SKIP_CONVERT                                    // tools/gemm_exp.cu: timing experiments only
 #pragma unroll
         for (int i = 0; i < kChunksPerThread; ++i) {
           float4 v = *reinterpret_cast<const float4*>(hi_p + i * (kProd * 16));
@@ -712,6 +713,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
           *reinterpret_cast<float4*>(hi_p + i * (kProd * 16)) = h;
           *reinterpret_cast<float4*>(hi_p + kPlane + i * (kProd * 16)) = l;
         }
+#endif
         fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&ready[s]);
@@ -814,6 +816,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
         const uint32_t acc0 = kc > 0 ? 1u : 0u;
         const bool last = kc == nk - 1;
         if (elect_one()) {
+#ifndef VCNF_EXP_SKIP_MMA
           if (steps == 4) {
             mma_stage4(d_main, d_small, w_hi_col, w_lo_col, bd_hi, bd_lo, idesc, acc0);
           } else {
@@ -821,6 +824,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
               mma_step(d_main, d_small, w_hi_col + kk * 8, w_lo_col + kk * 8, bd_hi + kk * 2, bd_lo + kk * 2, idesc,
                        (kc > 0 || kk > 0) ? 1u : 0u);
           }
+#endif
           tc_commit(&empty[s]);
           if (last) tc_commit(&acc_full[buf]);
         }
@@ -935,9 +939,14 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
       if (warp == kProdWarps && lane == 0 && tc == 0) VTRACE(5);
       uint32_t r[32], r2[32];
       const uint32_t taddr = lane_base + kColAcc + buf * (2 * kTN) + h * 32;
+#ifndef VCNF_EXP_SKIP_EPI
       tmem_ld32(taddr, r);
       tmem_ld32(taddr + kTN, r2);
       tmem_ld_wait();
+#else
+#pragma unroll
+      for (int j = 0; j < 32; ++j) { r[j] = 0u; r2[j] = 0u; }
+#endif
       tc_fence_before();                                          // values are in registers: hand the
       __syncwarp();                                               // accumulator back before the stores
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -965,8 +974,10 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
         for (int j = 0; j < 32; ++j) acc[j] += res[j];
       }
       if (a.c_tma) {
+#ifndef VCNF_EXP_SKIP_EPI
 #pragma unroll
         for (int j = 0; j < 32; ++j) et[j * 128] = acc[j];        // lane = column: conflict-free rows
+#endif
         fence_async_smem();
       } else {
         float* cp = a.C + row0 * a.ldc + o;
