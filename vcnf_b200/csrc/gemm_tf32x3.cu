@@ -29,6 +29,42 @@
 #include "common.cuh"
 #include "../../include/vcnf_b200.h"
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------------------------
+// A training step is ~340 back-to-back GEMM launches of 13-50 us, each with a serial prologue (barrier init, TMEM
+// allocation, W -> TMEM: 4.4 us) behind ~2.5 us of launch latency.  The single-wave GEMM kernels signal
+// `launch_dependents` as soon as they are set up, and are themselves launched with the programmatic-serialization
+// attribute: the next GEMM's CTAs are placed on an SM the moment the previous kernel's CTA leaves it and run their
+// prologue (which only touches parameters) while the rest of the previous grid drains; `griddepcontrol.wait` stands
+// before the first access to anything a preceding kernel may have produced (activations, gradients) or may still
+// read (outputs).  Kernels that do not signal (everything else in the stream) keep the ordinary full dependency.
+// VCNF_PDL=0 turns the attribute off.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+static bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("VCNF_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
+
+template <typename... KArgs, typename... Args>
+static void launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(block, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 namespace vcnf {
 namespace gemm {
 
@@ -672,9 +708,11 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (tid == 0) VTRACE(1);
+  pdl_trigger();                                                 // the next launch may start its prologue
 
   if (warp < kProdWarps) {
     // ===================================== producers =====================================
+    pdl_wait();                                                  // activations come from preceding kernels
     // Stage g of this CTA's stream = (tile g / nk, k-chunk g % nk): 64 rows x 32 fp32.  Thread item i:
     // 16 B chunk c = tid & 7 of row r = (tid >> 3) + 16 i -- 8 consecutive lanes read one 128 B line,
     // and land in 8 different 16 B bank groups (128 B swizzle).
@@ -900,6 +938,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
       if (lane == 0) mbar_arrive(w_ready);
       if (warp == kProdWarps && lane == 0) VTRACE(2);
     }
+    pdl_wait();                                                  // W, bias: parameters; everything below: activations
     const float bv = (a.bias && o_ok) ? __ldg(a.bias + o) : 0.f;
     // Elementwise operand E (the residual, or the ReLU mask of the input-gradient call) and the output
     // tile travel by TMA through three 64 x 128 fp32 tiles in shared memory: E for tile t+2 is requested
@@ -1377,7 +1416,9 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Arg
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if (tid == 0) { WTRACE(1); }
-
+  pdl_trigger();
+  pdl_wait();                                                    // both operands and the partial buffer belong to
+                                                                 // preceding kernels until they have completed
   if (warp < kConvWarps) {
     // ------------------------------ TMA issue (thread 0) + X conversion (256 threads)
     const uint32_t tx_bytes = static_cast<uint32_t>(4 + a.gx) * kGroup;
@@ -1618,8 +1659,8 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
                            static_cast<int>(gemm::v2::kSmemBytes));
       attr2 = true;
     }
-    gemm::v2::linear_ts_kernel<<<static_cast<unsigned>(b.n_tiles * cpt2), gemm::v2::kThreads, gemm::v2::kSmemBytes,
-                                 static_cast<cudaStream_t>(stream)>>>(b, tm, tm_e, tm_c);
+    launch_pdl(gemm::v2::linear_ts_kernel, static_cast<unsigned>(b.n_tiles * cpt2), gemm::v2::kThreads, gemm::v2::kSmemBytes,
+               static_cast<cudaStream_t>(stream), b, tm, tm_e, tm_c);
     return launch_status();
   }
   gemm::Args a{};
@@ -1714,7 +1755,8 @@ extern "C" int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void*
       cudaFuncSetAttribute(gemm::wg2::linear_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
       attr_set2 = true;
     }
-    gemm::wg2::linear_wgrad_tma_kernel<<<static_cast<unsigned>(w.o_tiles * w.splits), gemm::kThreads, smem, st>>>(w, tm_g, tm_x);
+    launch_pdl(gemm::wg2::linear_wgrad_tma_kernel, static_cast<unsigned>(w.o_tiles * w.splits), gemm::kThreads, smem, st, w,
+               tm_g, tm_x);
     rc = launch_status();
   } else {
     const size_t smem = 1024 + static_cast<size_t>(gemm::kWStages) * 2 * (128 / 8 + static_cast<size_t>(a.NX) / 8) * gemm::kWSbo;
