@@ -1563,6 +1563,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_wgrad_tma_kernel(const Arg
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* partial, int splits, int rows_pad, int N, int K,
                                                            float* gW, float* gb) {
   __shared__ float sub[8][33];
+  pdl_wait();                                                    // the partials of the weight-gradient launch
+  pdl_trigger();                                                 // writes gW / gb only: no GEMM prologue reads them
   const int W1 = K + 1;
   const int64_t total = static_cast<int64_t>(N) * W1;
   const int ex = threadIdx.x & 31, g = threadIdx.x >> 5;
@@ -1772,7 +1774,7 @@ extern "C" int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void*
   const int64_t total = static_cast<int64_t>(N) * (K + 1);
   int grid = static_cast<int>((total + 31) / 32);
   if (grid > 1184) grid = 1184;
-  gemm::wgrad_reduce_kernel<<<grid, 256, 0, st>>>(a.partial, a.splits, a.o_tiles * 128, N, K, static_cast<float*>(gW),
-                                                   static_cast<float*>(gb));
+  launch_pdl(gemm::wgrad_reduce_kernel, static_cast<unsigned>(grid), 256u, 0, st, static_cast<const float*>(a.partial), a.splits,
+             a.o_tiles * 128, N, K, static_cast<float*>(gW), static_cast<float*>(gb));
   return launch_status();
 }
