@@ -735,29 +735,50 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
         for (int g = 0; g < kAhead; ++g) issue_tma(g);
         VTRACE(11);
       }
-      for (int64_t g = 0; g < G; ++g) {
-        const uint32_t it = static_cast<uint32_t>(g);
-        const int s = it % kStages;
-        mbar_wait(&full[s], (it / kStages) & 1u);
-        unsigned char* hi_p = ring + static_cast<uint32_t>(s) * 2 * kPlane + tid * 16;
+      // Two stages per pass: the fixed cost of a pass (barrier polls, the async-proxy fence, the arrives and the
+      // look-ahead TMA issue) is paid once per 16 KB instead of once per 8 KB, and the 8 independent 16 B chunks of
+      // a thread cover the shared-memory latency that 4 did not (one producer warp per scheduler: nothing else
+      // hides it).  tools/gemm_exp.cu: the head layer lost 10 us of 53 to this loop.
+      for (int64_t g = 0; g < G; g += 2) {
+        const uint32_t it0 = static_cast<uint32_t>(g), it1 = it0 + 1;
+        const int s0 = it0 % kStages, s1 = it1 % kStages;
+        const bool two = g + 1 < G;
+        mbar_wait(&full[s0], (it0 / kStages) & 1u);
+        if (two) mbar_wait(&full[s1], (it1 / kStages) & 1u);
+        unsigned char* p0 = ring + static_cast<uint32_t>(s0) * 2 * kPlane + tid * 16;
+        unsigned char* p1 = ring + static_cast<uint32_t>(s1) * 2 * kPlane + tid * 16;
 #ifndef VCNF_EXP_SKIP_CONVERT                                    // tools/gemm_exp.cu: timing experiments only
+        float4 v[2 * kChunksPerThread];
 #pragma unroll
-        for (int i = 0; i < kChunksPerThread; ++i) {
-          float4 v = *reinterpret_cast<const float4*>(hi_p + i * (kProd * 16));
-          if (a.relu_in) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+        for (int i = 0; i < kChunksPerThread; ++i) v[i] = *reinterpret_cast<const float4*>(p0 + i * (kProd * 16));
+        if (two) {
+#pragma unroll
+          for (int i = 0; i < kChunksPerThread; ++i)
+            v[kChunksPerThread + i] = *reinterpret_cast<const float4*>(p1 + i * (kProd * 16));
+        }
+#pragma unroll
+        for (int i = 0; i < 2 * kChunksPerThread; ++i) {
+          if (i >= kChunksPerThread && !two) break;
+          unsigned char* dst = (i < kChunksPerThread ? p0 : p1) + (i % kChunksPerThread) * (kProd * 16);
+          float4 x = v[i];
+          if (a.relu_in) { x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f); }
           float4 h, l;
-          split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
-          split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
-          *reinterpret_cast<float4*>(hi_p + i * (kProd * 16)) = h;
-          *reinterpret_cast<float4*>(hi_p + kPlane + i * (kProd * 16)) = l;
+          split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y);
+          split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
+          *reinterpret_cast<float4*>(dst) = h;
+          *reinterpret_cast<float4*>(dst + kPlane) = l;
         }
 #endif
         fence_async_smem();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&ready[s]);
+        if (lane == 0) {
+          mbar_arrive(&ready[s0]);
+          if (two) mbar_arrive(&ready[s1]);
+        }
         if (tid == 0) {
           if (g == 0) { VTRACE(3); }
           issue_tma(g + kAhead);
+          issue_tma(g + 1 + kAhead);
         }
       }
       if (tid == 0) { VTRACE(7); }
