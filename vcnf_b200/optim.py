@@ -6,7 +6,10 @@ parameter tensors; the library's multi-tensor Adam needs 0.58 ms per step for 1.
 step counter per tensor).  `FlatAdam` re-homes the parameters into ONE buffer (each `p.data` becomes a view of it),
 keeps both moments flat, takes the gradients from a `parallel.GradBucket` laid out the same way and runs ONE
 kernel (`vcnf_adam_flat`, 28 B per fp32 parameter).  Arithmetic and hyper-parameters are torch.optim.Adam's
-(amsgrad off, maximize off); a parameter that received no gradient counts as a zero gradient."""
+(amsgrad off, maximize off); a parameter that received no gradient counts as a zero gradient.
+Build it AFTER the model is on its device and in its dtype (`nfm.double().to(device)` first, like the run scripts
+do before creating their optimiser): `.to()` / `.double()` afterwards re-allocates the parameters and cuts
+them loose from the flat buffer."""
 import torch
 
 from . import ops
