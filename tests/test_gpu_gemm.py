@@ -156,3 +156,43 @@ def test_lu_compose_matches_index_put_route(D, dtype):
     for a, b in zip(got, ref):
         if b is not None and b.numel():
             torch.testing.assert_close(a, b, **tol)
+
+
+def test_dependent_launch_chain_is_race_free():
+    """The GEMM kernels are launched with programmatic stream serialization and signal their dependents early
+    (gemm_tf32x3.cu, `pdl_trigger` / `pdl_wait`): a kernel's prologue may run while its predecessor drains.  A chain
+    of dependent layers launched back to back must give bit-identical values and gradients to the same chain with
+    a device synchronisation between all launches (which rules every overlap out), run after run."""
+    from vcnf_b200 import ops
+    torch.manual_seed(11)
+    B, H = 40000, 128                               # 625 tiles: several per CTA, ragged last wave
+    x0 = torch.randn(B, H, device="cuda")
+    Ws = [torch.randn(H, H, device="cuda") * 0.08 for _ in range(6)]
+    bs = [torch.randn(H, device="cuda") * 0.1 for _ in range(6)]
+
+    def run(sync):
+        x = x0.clone().requires_grad_(True)
+        ws = [w.clone().requires_grad_(True) for w in Ws]
+        bb = [b.clone().requires_grad_(True) for b in bs]
+
+        def barrier(t):
+            if sync:
+                torch.cuda.synchronize()
+                if t.requires_grad:
+                    t.register_hook(lambda g: (torch.cuda.synchronize(), g)[1])
+            return t
+        h = barrier(ops.linear(x, ws[0], bb[0]))
+        for k in (1, 3):                            # two residual blocks out of single launches
+            t = barrier(ops.linear(h, ws[k], bb[k], relu_in=True))
+            h = barrier(ops.linear(t, ws[k + 1], bb[k + 1], residual=h, relu_in=True))
+        y = barrier(ops.linear(h, ws[5], bb[5], relu_in=True))
+        gy = torch.ones_like(y) * 0.01
+        grads = torch.autograd.grad(y, [x] + ws + bb, gy)
+        torch.cuda.synchronize()
+        return [y.detach()] + [g.detach() for g in grads]
+
+    ref = run(sync=True)
+    for _ in range(12):
+        got = run(sync=False)
+        for i, (a, b) in enumerate(zip(ref, got)):
+            assert torch.equal(a, b), (i, float((a - b).abs().max()))
