@@ -22,7 +22,53 @@ class Autoregressive(Flow):
         params = self.autoregressive_net(inputs, context)
         return self._elementwise_forward(inputs, params)
 
+    # Sampling direction without a gradient.  The reference runs D full conditioner passes; pass t can only fix the
+    # feature of degree t + 1, whose parameters are rows [f P, (f + 1) P) of the final masked layer and depend on
+    # lower-degree features alone (made.py:56-60: strict mask at the output).  So passes 0 .. D-2 evaluate the hidden
+    # layers, THOSE rows and ONE column of the elementwise inverse; the last pass is the reference's full pass and
+    # yields every output and the log-determinant.  Same dot products, same values (a masked weight is an exact
+    # zero), 1 / D of the final layer's work and of the [B, D P] parameter traffic in D - 1 of D passes.
+    # `full_inverse = True` keeps the reference's loop (tests compare the two).
+    full_inverse = False
+
+    def _sliced_inverse_ok(self, inputs, context):
+        net = self.autoregressive_net
+        if self.full_inverse or context is not None or inputs.dim() != 2 or not hasattr(self, "_inverse_feature"):
+            return False
+        if not isinstance(net, made_module.MADE) or not hasattr(net, "final_rows"):
+            return False
+        if torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in net.parameters())):
+            return False
+        for m in net.modules():
+            if isinstance(m, torch.nn.modules.batchnorm._BatchNorm):
+                return False
+            if isinstance(m, torch.nn.Dropout) and m.p > 0. and m.training:
+                return False
+        return inputs.shape[1] > 1
+
+    def _degree_order(self):
+        """Features sorted by input degree (sequential, or permuted with `permute_mask`); cached host list."""
+        deg = self.autoregressive_net.final_layer.degrees
+        key = (deg.data_ptr(), deg._version)
+        if getattr(self, "_order_key", None) != key:
+            P = self._output_dim_multiplier()
+            self._order = torch.argsort(deg[::P].cpu(), stable=True).tolist()
+            self._order_key = key
+        return self._order
+
+    def _inverse_sliced(self, inputs):
+        net, P = self.autoregressive_net, self._output_dim_multiplier()
+        order = self._degree_order()
+        outputs = torch.zeros_like(inputs)
+        for f in order[:-1]:
+            h = net.hidden(outputs)
+            params_f = net.final_rows(h, f * P, (f + 1) * P)
+            outputs[:, f] = self._inverse_feature(inputs[:, f:f + 1], params_f, f)[:, 0]
+        return self._elementwise_inverse(inputs, net(outputs))
+
     def inverse(self, inputs, context=None):
+        if self._sliced_inverse_ok(inputs, context):
+            return self._inverse_sliced(inputs)
         num_inputs = int(np.prod(inputs.shape[1:]))
         outputs = torch.zeros_like(inputs)
         logabsdet = None
@@ -66,3 +112,7 @@ class MaskedAffineAutoregressive(Autoregressive):
     def _elementwise_inverse(self, inputs, autoregressive_params):
         return ops.affine_coupling(inputs, autoregressive_params, 0, self.features,
                                    ops.SCALE_MAPS["maf"], True, swap_ts=True)
+
+    def _inverse_feature(self, x_f, params_f, f):
+        """One column of `_elementwise_inverse`: x_f [B, 1], params_f [B, 2] = (u, shift) of feature f."""
+        return ops.affine_coupling(x_f.contiguous(), params_f, 0, 1, ops.SCALE_MAPS["maf"], True, swap_ts=True)[0]

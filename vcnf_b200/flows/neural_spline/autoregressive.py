@@ -75,3 +75,20 @@ class MaskedPiecewiseRationalQuadraticAutoregressive(Autoregressive):
 
     def _elementwise_inverse(self, inputs, autoregressive_params):
         return self._elementwise(inputs, autoregressive_params, inverse=True)
+
+    def _inverse_feature(self, x_f, params_f, f):
+        """One column of `_elementwise_inverse` (affine/autoregressive.py `_inverse_sliced`): x_f [B, 1],
+        params_f [B, P] = the parameters of feature f."""
+        D, P = self.features, self._output_dim_multiplier()
+        cache = self.__dict__.setdefault("_feature_specs", {})
+        if "mb" not in cache:                                   # once: a tensor tail_bound is read back here
+            cache["mb"] = _modes_and_bounds(self.tails, self.tail_bound, D)
+        modes, bounds = cache["mb"]
+        key = (int(modes[f]), float(bounds[f]))
+        if key not in cache:
+            scale = 1.0
+            if hasattr(self.autoregressive_net, "hidden_features"):
+                scale = 1.0 / np.sqrt(self.autoregressive_net.hidden_features)
+            cache[key] = ops.SplineSpec(1, self.num_bins, [(ops.COL_COND << 16) | 0], [modes[f]], [bounds[f]], P, scale,
+                                        [], [], P, isinstance(self.tails, (list, tuple)))
+        return ops.rqs_layer(x_f, params_f, None, cache[key], True)[0]

@@ -139,10 +139,23 @@ class MADE(nn.Module):
         self.final_layer = MaskedLinear(prev, features * output_multiplier, features, random_mask, True,
                                         out_degrees_=input_degrees_)
 
-    def forward(self, inputs, context=None):
+    def hidden(self, inputs, context=None):
+        """Everything but the final masked layer (made.py:288-299 up to the last hidden activation)."""
         h = self.initial_layer(self.preprocessing(inputs))
         if context is not None:
             h = h + self.context_layer(context)
         for block in self.blocks:
             h = block(h, context)
-        return self.final_layer(h)
+        return h
+
+    def forward(self, inputs, context=None):
+        return self.final_layer(self.hidden(inputs, context))
+
+    def final_rows(self, h, lo, hi):
+        """Outputs [lo, hi) of the final layer only -- the same dot products as `forward(...)[:, lo:hi]`."""
+        fl = self.final_layer
+        w = (fl.weight * fl.mask)[lo:hi]
+        b = fl.bias[lo:hi] if fl.bias is not None else None
+        if ops.linear_supported(h, w):
+            return ops.linear(h, w, b, pad_out=True)
+        return F.linear(h, w, b)
