@@ -60,11 +60,12 @@ class Autoregressive(Flow):
         net, P = self.autoregressive_net, self._output_dim_multiplier()
         order = self._degree_order()
         outputs = torch.zeros_like(inputs)
-        for f in order[:-1]:
-            h = net.hidden(outputs)
-            params_f = net.final_rows(h, f * P, (f + 1) * P)
-            outputs[:, f] = self._inverse_feature(inputs[:, f:f + 1], params_f, f)[:, 0]
-        return self._elementwise_inverse(inputs, net(outputs))
+        with torch.no_grad(), net.frozen_masks():
+            for f in order[:-1]:
+                h = net.hidden(outputs)
+                params_f = net.final_rows(h, f * P, (f + 1) * P)
+                outputs[:, f] = self._inverse_feature(inputs[:, f:f + 1], params_f, f)[:, 0]
+            return self._elementwise_inverse(inputs, net(outputs))
 
     def inverse(self, inputs, context=None):
         if self._sliced_inverse_ok(inputs, context):

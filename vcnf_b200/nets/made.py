@@ -38,11 +38,15 @@ class MaskedLinear(nn.Linear):
             out_degrees = torch.arange(out_features) % max(1, d - 1) + min(1, d - 1)
         return (out_degrees[..., None] >= in_degrees).float(), out_degrees
 
+    # W * mask held for the duration of a no-grad multi-pass call (MADE.frozen_masks): the D passes of the sampling
+    # direction would otherwise recompute the same product D times per layer
+    _masked = None
+
     def forward(self, x, relu_in=False, residual=None):
         """F.linear(act(x), W * mask, b) (+ residual) -- made.py:79-80.  fp32 CUDA operands run the tcgen05
         3xTF32 kernels (ReLU, bias and the residual add fused; hidden widths > 128 as contraction slices);
         fp64 models (`nfm.double()`) keep the library DGEMM: the tensor cores have no fp64-faithful path."""
-        w = self.weight * self.mask
+        w = self._masked if self._masked is not None else self.weight * self.mask
         if ops.linear_supported(x, w):
             return ops.linear(x, w, self.bias, residual=residual, relu_in=relu_in)
         y = F.linear(F.relu(x) if relu_in else x, w, self.bias)
@@ -151,10 +155,29 @@ class MADE(nn.Module):
     def forward(self, inputs, context=None):
         return self.final_layer(self.hidden(inputs, context))
 
+    def frozen_masks(self):
+        """Context manager: every masked layer computes W * mask once and reuses it until exit (no-grad callers
+        whose weights do not change inside the block)."""
+        net = self
+
+        class _Frozen:
+            def __enter__(self):
+                with torch.no_grad():
+                    for m in net.modules():
+                        if isinstance(m, MaskedLinear):
+                            m._masked = m.weight * m.mask
+
+            def __exit__(self, *exc):
+                for m in net.modules():
+                    if isinstance(m, MaskedLinear):
+                        m._masked = None
+                return False
+        return _Frozen()
+
     def final_rows(self, h, lo, hi):
         """Outputs [lo, hi) of the final layer only -- the same dot products as `forward(...)[:, lo:hi]`."""
         fl = self.final_layer
-        w = (fl.weight * fl.mask)[lo:hi]
+        w = (fl._masked if fl._masked is not None else fl.weight * fl.mask)[lo:hi]
         b = fl.bias[lo:hi] if fl.bias is not None else None
         if ops.linear_supported(h, w):
             return ops.linear(h, w, b, pad_out=True)
