@@ -56,3 +56,35 @@ torch.cuda.synchronize()
 ms = e0.elapsed_time(e1)
 print("cfg3a sample(32768) replayed from a graph: %.1f ms, %.3f M samples/s, finite %s" % (
     ms, 32768 / ms / 1e3, bool(torch.isfinite(z).all())))
+# cfg 3b: 8 x [Reverse(MaskedAffineAutoregressive(64, 256)), Permute(64, 'shuffle')]
+del step, draw
+torch.manual_seed(0)
+flows = []
+for _ in range(8):
+    flows += [nf.flows.Reverse(nf.flows.MaskedAffineAutoregressive(D, 256)), nf.flows.Permute(D, mode="shuffle")]
+model_b = nf.NormalizingFlow(nf.distributions.DiagGaussian(D, trainable=False), flows).to(dev)
+opt_b = nf.optim.FlatAdam(model_b.parameters(), lr=1e-3)
+step_b = parallel.GraphedTrainStep(model_b, opt_b, opt_b.bucket, x)
+print("cfg3b graph:", step_b.graph is not None, step_b.capture_error)
+for _ in range(3):
+    step_b(x)
+torch.cuda.synchronize()
+ts = []
+for _ in range(10):
+    flush.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); loss = step_b(x); e1.record()
+    torch.cuda.synchronize()
+    ts.append(e0.elapsed_time(e1))
+ms = sum(ts) / len(ts)
+print("cfg3b forward_kld train step B=%d: %.3f ms/step, %.2f M samples/s, loss %.4f" % (B, ms, B / ms / 1e3, float(loss)))
+draw_b = parallel.GraphedSampler(model_b, 32768)
+for _ in range(2):
+    draw_b()
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(); z, lq = draw_b(); e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1)
+print("cfg3b sample(32768) graph=%s: %.1f ms, %.3f M samples/s, finite %s" % (
+    draw_b.graph is not None, ms, 32768 / ms / 1e3, bool(torch.isfinite(z).all())))
