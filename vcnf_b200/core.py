@@ -24,6 +24,15 @@ class NormalizingFlow(nn.Module):
             self.vdeqs = nn.ModuleList(catvdeqs)
             self.catlevels = catlevels
 
+    def _cat_index(self, device):
+        """The categorical column list as a device index tensor, built once per device: indexing with the Python
+        list uploads it from pageable host memory on every call (and cannot be captured into a CUDA graph)."""
+        cache = self.__dict__.setdefault("_cat_idx", {})
+        key = (str(device), tuple(self.categoricals))
+        if key not in cache:
+            cache[key] = torch.tensor(list(self.categoricals), dtype=torch.long, device=device)
+        return cache[key]
+
     def forward_kld(self, x, extended=False):
         """core.py:33-66."""
         log_qt = torch.zeros(len(x), device=x.device)
@@ -31,7 +40,7 @@ class NormalizingFlow(nn.Module):
         z = x
         zarr, zparr = [], []
         if self.categoricals is not None:
-            zc = x[:, self.categoricals]
+            zc = x[:, self._cat_index(x.device)]
             for vcn in range(len(self.categoricals)):
                 zct, log_det = self.vdeqs[vcn].forward(z=zc[:, vcn].view([zc.shape[0], 1]), ldj=log_q,
                                                        reverse=False)
@@ -40,7 +49,7 @@ class NormalizingFlow(nn.Module):
                     zarr.append(z.cpu().detach().numpy())
                     zparr.append(log_det.cpu().detach().numpy())
                 log_qt += log_det
-            z[:, self.categoricals] = zc.float()
+            z[:, self._cat_index(z.device)] = zc.float()
         log_q = log_qt
         for i in range(len(self.flows) - 1, -1, -1):
             z, log_det = self.flows[i].inverse(z)
@@ -118,13 +127,13 @@ class NormalizingFlow(nn.Module):
             z, log_det = flow(z)
             log_q -= log_det
         if self.categoricals is not None and len(self.categoricals) > 0:
-            zc = z[:, self.categoricals]
+            zc = z[:, self._cat_index(z.device)]
             for vct in range(len(self.categoricals)):
                 zct, log_det = self.vdeqs[vct].forward(z=zc[:, vct].view([zc.shape[0], 1]), ldj=log_q,
                                                        reverse=True)
                 zc[:, vct] = zct.squeeze()
                 log_q += log_det
-            z[:, self.categoricals] = zc.to(z.dtype)
+            z[:, self._cat_index(z.device)] = zc.to(z.dtype)
         return z, log_q
 
     def log_prob(self, x):

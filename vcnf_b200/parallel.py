@@ -154,10 +154,14 @@ class GraphedTrainStep:
         self.graph, self.loss, self.capture_error = None, None, None
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
+        # forward_kld dequantises categorical columns INTO its argument (core.py:54): every run starts from a fresh
+        # copy of the batch, and the model sees a detached alias so that no autograd history sticks to the static input
         with torch.cuda.stream(side):
             for _ in range(warmup):
+                self.x.copy_(example)
                 self._eager()
         torch.cuda.current_stream().wait_stream(side)
+        self.x.copy_(example)
         torch.cuda.synchronize()
         try:
             g = torch.cuda.CUDAGraph()
@@ -170,7 +174,7 @@ class GraphedTrainStep:
 
     def _eager(self):
         self.bucket.begin()
-        loss = self.loss_fn(self.model, self.x)
+        loss = self.loss_fn(self.model, self.x.detach())
         loss.backward()
         world = self.world if self.world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
         if world > 1:
