@@ -39,3 +39,27 @@ for B in (128, 512):
     ms = e0.elapsed_time(e1) / n
     print("cfg5 Glow forward_kld train step B=%d (eager): %.2f ms/step, %.0f images/s, loss %.3f, %d vcnf launches/step" % (
         B, ms, B / ms * 1e3, float(loss), (ops.LAUNCHES - l0) // n))
+# the same step replayed from a CUDA graph
+from vcnf_b200 import parallel
+del loss
+for B in (128, 512):
+    x = (torch.rand(B, 3, 32, 32) * 255 / 256 + torch.rand(B, 3, 32, 32) / 256).to(dev)
+    y = torch.randint(0, 10, (B,)).to(dev)
+    opt_g = torch.optim.Adamax(model.parameters(), lr=1e-3, weight_decay=1e-5, capturable=True)
+    bucket = parallel.GradBucket(model.parameters())
+    gstep = parallel.GraphedTrainStep(model, opt_g, bucket, x, world=1, loss_fn=lambda m, xb, y=y: m.forward_kld(xb, y))
+    if gstep.graph is None:
+        print("cfg5 capture failed:", (gstep.capture_error or "")[:400])
+        break
+    for _ in range(3):
+        gstep(x)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(8):
+        gl = gstep(x)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 8
+    print("cfg5 Glow forward_kld train step B=%d (graph): %.2f ms/step, %.0f images/s, loss %.3f" % (B, ms, B / ms * 1e3, float(gl)))
+    del gstep, gl
