@@ -136,6 +136,19 @@ int vcnf_const_affine_bwd(const void* z, const void* s, const void* t, const voi
                           void* gt, void* workspace, int64_t B, int Pn, int S, int inverse, int dtype,
                           void* stream);
 
+/* Same result as vcnf_const_affine_bwd without a caller workspace and without any allocation (no cudaMalloc /
+ * cudaFree / allocating library call), for callers that may not allocate: code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it.  NO COUNTERPART IN THE REFERENCE.
+ * The per-chunk partial sums go to a file-scope `static __device__` array of
+ * 592 * 2 * VCNF_CONST_AFFINE_STATIC_MAX_PN * 8 bytes (2.3 MiB) that every GPU loading the library holds until exit;
+ * its device address is taken once per device (cudaGetSymbolAddress with that device current, on the first call
+ * there).  Pn > VCNF_CONST_AFFINE_STATIC_MAX_PN returns VCNF_E_UNSUPPORTED.  All calls share the array and it keeps the
+ * last call's contents; each call writes every slot it later reads, so nothing has to be cleared -- but two calls
+ * that overlap on the GPU (different streams, or graphs replayed concurrently) RACE on it: keep them on one stream. */
+#define VCNF_CONST_AFFINE_STATIC_MAX_PN 256
+int vcnf_const_affine_bwd_static(const void* z, const void* s, const void* t, const void* gout, void* gz, void* gs,
+                                 void* gt, int64_t B, int Pn, int S, int inverse, int dtype, void* stream);
+
 /* dst[b, j, s] = src[b, perm[j], s]  (Permute, normflow/flows/mixing.py:32-54). */
 int vcnf_permute_channels(const void* src, void* dst, int64_t B, int C, int S, const int32_t* perm, int dtype,
                           void* stream);

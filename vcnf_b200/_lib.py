@@ -32,6 +32,7 @@ _SIGNATURES = {
     "vcnf_masked_affine_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
     "vcnf_const_affine_fwd": [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
     "vcnf_const_affine_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
+    "vcnf_const_affine_bwd_static": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp],
     "vcnf_permute_channels": [_vp, _vp, _i64, _i32, _i32, _vp, _i32, _vp],
     "vcnf_squeeze": [_vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
     "vcnf_linear_tf32x3": [_vp, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _vp],

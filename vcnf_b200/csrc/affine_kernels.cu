@@ -5,6 +5,7 @@
 //
 // Work decomposition: G threads cooperate on one sample (G = 1 for tiny rows such as the 2-D
 // RealNVP of cfg 1, G = 32 one warp per row for tabular widths, G = 256 one CTA per image).
+#include <mutex>
 #include "common.cuh"
 #include "affine_math.cuh"
 #include "../../include/vcnf_b200.h"
@@ -298,6 +299,34 @@ using namespace vcnf;
 
 #define VCNF_BAD_DTYPE(d) ((d) != VCNF_F32 && (d) != VCNF_F64)
 
+/* No-allocation variant of vcnf_const_affine_bwd (no counterpart in the reference; see include/vcnf_b200.h).
+ * The per-chunk partial sums live in a file-scope device array instead of a caller workspace.  In host code the
+ * array's name is only a handle: its device address is looked up once per device with cudaGetSymbolAddress
+ * (that device current) and that pointer is what the kernels get. */
+constexpr int kStaticMaxPn = VCNF_CONST_AFFINE_STATIC_MAX_PN;
+static __device__ __align__(256) unsigned char g_const_affine_scratch[kConstAffineChunks * 2 * kStaticMaxPn * 8];
+
+static int const_affine_static_scratch(void** out) {
+  constexpr int kMaxDev = 64;
+  static void* ptrs[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= kMaxDev) return VCNF_E_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_const_affine_scratch);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (!p) return static_cast<int>(cudaErrorInvalidSymbol);
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+
 extern "C" {
 
 int vcnf_affine_coupling_fwd(const void* z, const void* param, void* out, void* logdet, int64_t B, int C, int S,
@@ -424,6 +453,20 @@ int vcnf_const_affine_bwd(const void* z, const void* s, const void* t, const voi
   }
   if (dtype == VCNF_F32) GO(float) else GO(double)
 #undef GO
+}
+
+/* No-allocation variant of vcnf_const_affine_bwd: scratch = g_const_affine_scratch (file scope, above). */
+int vcnf_const_affine_bwd_static(const void* z, const void* s, const void* t, const void* gout, void* gz, void* gs,
+                                 void* gt, int64_t B, int Pn, int S, int inverse, int dtype, void* stream) {
+  if (B == 0) return 0;   /* empty batch: pointers may be NULL */
+  if (!z || !s || !t || !gout || !gz || !gs || !gt || B < 0 || Pn <= 0 || S <= 0 || VCNF_BAD_DTYPE(dtype))
+    return VCNF_E_BADARG;
+  if (Pn > kStaticMaxPn) return VCNF_E_UNSUPPORTED;   /* the static scratch is sized for Pn <= 256 */
+  void* scratch = nullptr;
+  int rc = const_affine_static_scratch(&scratch);
+  if (rc) return rc;
+  /* every partial the reduce reads is written by this call's first kernel: nothing needs clearing */
+  return vcnf_const_affine_bwd(z, s, t, gout, gz, gs, gt, scratch, B, Pn, S, inverse, dtype, stream);
 }
 
 int vcnf_permute_channels(const void* src, void* dst, int64_t B, int C, int S, const int32_t* perm, int dtype,
