@@ -217,6 +217,47 @@ int64_t vcnf_linear_wgrad_workspace(int64_t B, int N, int K);
 int vcnf_linear_wgrad_tf32x3(const void* gY, int64_t ldg, const void* X, int64_t ldx, void* gW, void* gb,
                              void* workspace, int64_t B, int N, int K, int relu_in, void* stream);
 
+/* ---- K9: convolutional conditioner of the Glow coupling (normflow/nets/cnn.py:7-47: conv3x3 -> LeakyReLU ->
+ * conv1x1 -> LeakyReLU -> conv3x3, called from flows/affine/glow.py:41-56; the reference runs nn.Conv2d = cuDNN) ----
+ *
+ * Patch matrix:  col[p, t*C + c] = act(src[b, c, h + s*dy(t), w + s*dx(t)]), zero outside the image and in the pad
+ * columns [ksize^2 * C, Kp);  p = (b*H + h)*W + w, t = ky*3 + kx, (dy, dx) = (ky-1, kx-1), s = +1, or -1 when flip != 0
+ * (patch matrix of the transposed convolution, i.e. of F.conv2d's input gradient).  src is fp32 with element strides
+ * (sb, sc, sh, sw) -- NCHW or NHWC; act != 0 applies LeakyReLU(slope) while reading.  col is fp32 (out_bf16 = 0: the
+ * fp32-faithful route feeds it to vcnf_linear_tf32x3) or bf16 (operand of vcnf_conv_gemm_bf16).  ksize is 1 or 3
+ * (stride 1, padding ksize/2: what cnn.py:29-44 builds). */
+int vcnf_im2col(const void* src, int64_t sb, int64_t sc, int64_t sh, int64_t sw, void* col, int64_t ldcol, int64_t B,
+                int C, int H, int W, int ksize, int Kp, int flip, int act, double slope, int out_bf16, void* stream);
+/* Adjoint of vcnf_im2col (fp32): gsrc[b, c, h, w] = act'(src[b, c, h, w]) * sum_t gcol[p - s*off(t), t*C + c]; every
+ * element is written once (gather form, deterministic).  src is only read when act != 0. */
+int vcnf_col2im(const void* gcol, int64_t ldcol, const void* src, void* gsrc, int64_t sb, int64_t sc, int64_t sh,
+                int64_t sw, int64_t B, int C, int H, int W, int ksize, int flip, int act, double slope, void* stream);
+/* out[c] (fp32) = sum over rows of X[., c]: bias gradients of the convolutions (autograd of nn.Conv2d's bias).
+ * layout 0: X bf16 [rows, ld_or_S] row-major; layout 1: X fp32 NCHW [rows = B, C, ld_or_S = H*W].  Two stages, fixed
+ * order.  `workspace`: vcnf_colsum_workspace(C) bytes. */
+int64_t vcnf_colsum_workspace(int C);
+int vcnf_colsum(const void* X, int layout, int64_t rows, int C, int64_t ld_or_S, void* out, void* workspace,
+                void* stream);
+/* Implicit-GEMM convolution on the tcgen05 tensor cores, bf16 operands, fp32 accumulation (replaces F.conv2d and,
+ * with transposed / flipped weights, its input gradient):
+ *   out[p, n] = epi( sum_{t < taps} sum_{c < Cp} act[p (+) t, c] * Wp[t][n][c] + bias[n] )
+ * act [B, H, W, Cp] NHWC bf16, Cp % 64 == 0; taps = 1 (1x1, or a 3x3 whose patches were laid out by vcnf_im2col) or 9
+ * (3x3, padding 1: nine shifted TMA loads of the same tensor, rows / columns outside the image read as zeros);
+ * Wp [taps][Np][Cp] bf16 (Np % 16 == 0); bias fp32 [Np] or NULL.  epi: 0 none, 1 LeakyReLU(slope), 2 multiply by the
+ * LeakyReLU derivative taken from `mask` = the layer's saved bf16 output [P, ldm] (> 0 ? 1 : slope).
+ * out_mode 0: NHWC bf16 [P, ldo] (all Np channels); 1: NCHW fp32 [B, Cout, H, W] (channels n < Cout).
+ * W must divide 128 and H*W be a multiple or a divisor of 128 / a power of two (tiles of 128 pixels). */
+int vcnf_conv_gemm_bf16(const void* act, int64_t B, int H, int W, int Cp, int taps, const void* Wp, int Np,
+                        const void* bias, const void* mask, int64_t ldm, double slope, int epi, void* out, int out_mode,
+                        int Cout, int64_t ldo, void* stream);
+/* Weight gradient of the same convolutions: G[m, n] (fp32, [Mx, Ny]) = sum_p X[p, m] * Y[p, n], X [P, ldx] and
+ * Y [P, ldy] bf16 (pixel-major activations / gradients / patch matrices), Mx % 64 == 0, Ny % 64 == 0.  Split over the
+ * pixels across the SMs, partial sums added in a fixed order (deterministic).  `workspace`:
+ * vcnf_conv_wgrad_workspace(P, Mx, Ny) bytes. */
+int64_t vcnf_conv_wgrad_workspace(int64_t P, int Mx, int Ny);
+int vcnf_conv_wgrad_bf16(const void* X, int64_t ldx, int Mx, const void* Y, int64_t ldy, int Ny, int64_t P, void* G,
+                         void* workspace, void* stream);
+
 /* ---- K6 (small nets): MLP conditioner evaluated in registers, one launch per direction --------------
  * normflow/nets/mlp.py:7-58: Linear + LeakyReLU(slope) ... Linear, nl <= 4 linear layers, every width <= 32
  * (the [1,32,32,2] net of the README Real NVP, the [15,30,15] / [1,4,1] nets of the dequantisation flows).

@@ -13,6 +13,9 @@ from cases import build_glow_small
 
 dev = "cuda"
 torch.manual_seed(0)
+from vcnf_b200.nets import cnn
+cnn.set_precision(os.environ.get("VCNF_CONV_PRECISION", "bf16"))
+print("ConvNet2d precision:", cnn.get_precision())
 model = build_glow_small(nf, L=3, K=16, hidden=256, in_shape=(3, 32, 32), classes=10).to(dev)
 opt = torch.optim.Adamax(model.parameters(), lr=1e-3, weight_decay=1e-5)
 for B in (128, 512):

@@ -44,6 +44,12 @@ _SIGNATURES = {
     "vcnf_mlp_bwd": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _dbl, _vp, _i64, _vp, _vp, _i64, _i32, _vp],
     "vcnf_lu_inverse": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
+    "vcnf_im2col": [_vp, _i64, _i64, _i64, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _dbl, _i32, _vp],
+    "vcnf_col2im": [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _dbl, _vp],
+    "vcnf_colsum": [_vp, _i32, _i64, _i32, _i64, _vp, _vp, _vp],
+    "vcnf_conv_gemm_bf16": [_vp, _i64, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _i64, _dbl, _i32, _vp, _i32, _i32,
+                            _i64, _vp],
+    "vcnf_conv_wgrad_bf16": [_vp, _i64, _i32, _vp, _i64, _i32, _i64, _vp, _vp, _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
 }
 _I64_RETURN = {
@@ -52,6 +58,8 @@ _I64_RETURN = {
     "vcnf_linear_wgrad_workspace": [_i64, _i32, _i32],
     "vcnf_small_linear_bwd_workspace": [_i32, _i32],
     "vcnf_mlp_bwd_workspace": [_vp, _i32, _i32],
+    "vcnf_colsum_workspace": [_i32],
+    "vcnf_conv_wgrad_workspace": [_i64, _i32, _i32],
 }
 EXPORTED = sorted(list(_SIGNATURES) + list(_I64_RETURN))
 

@@ -694,3 +694,168 @@ class _ResBlock(torch.autograd.Function):
 def residual_block(x, w0, b0, w1, b1):
     """x + Linear1(relu(Linear0(relu(x)))) with square weights [F, F], F <= 128, biases required."""
     return _ResBlock.apply(x, w0, b0, w1, b1)
+
+
+# ------------------------------------------------------------------ convolutional conditioner (Glow, K9)
+def _ceil_to(n, q):
+    return (n + q - 1) // q * q
+
+
+def _src_strides(x, layout, H, W):
+    """Element strides (sb, sc, sh, sw) of an image batch held as NCHW [B, C, H, W] or as NHWC rows [B*H*W, C]
+    (any row pitch)."""
+    if layout == "nchw":
+        return x.stride(0), x.stride(1), x.stride(2), x.stride(3)
+    ld = x.stride(0)
+    return H * W * ld, 1, W * ld, ld
+
+
+def im2col_raw(x, layout, B, C, H, W, ksize, Kp, flip=False, act=False, slope=0.0, bf16=False):
+    """Patch matrix [B*H*W, Kp] of vcnf_im2col (no autograd)."""
+    P = B * H * W
+    col = (torch.empty((P, Kp), dtype=torch.bfloat16, device=x.device) if bf16
+           else _padded_empty(P, Kp, torch.float32, x.device))
+    sb, sc, sh, sw = _src_strides(x, layout, H, W)
+    _launch("vcnf_im2col", ptr(x), sb, sc, sh, sw, ptr(col), col.stride(0), B, C, H, W, ksize, Kp, int(flip), int(act),
+            float(slope), int(bf16), stream())
+    return col
+
+
+class _Im2Col(torch.autograd.Function):
+    """fp32 patch matrix of a stride-1 'same' convolution (ksize 1 or 3) with LeakyReLU(slope) optionally applied
+    while reading; backward = vcnf_col2im (gather form)."""
+
+    @staticmethod
+    def forward(ctx, x, layout, B, C, H, W, ksize, Kp, act, slope):
+        if layout == "nchw":
+            x = x.contiguous()
+        else:
+            x = _rows(x)
+        ctx.cfg = (layout, B, C, H, W, ksize, bool(act), float(slope))
+        ctx.save_for_backward(x)
+        return im2col_raw(x, layout, B, C, H, W, ksize, Kp, act=act, slope=slope)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gcol):
+        (x,) = ctx.saved_tensors
+        layout, B, C, H, W, ksize, act, slope = ctx.cfg
+        gcol = _rows(gcol)
+        if layout == "nchw":
+            gx = torch.empty_like(x)
+        else:
+            gx = _padded_empty(x.shape[0], C, x.dtype, x.device) if x.stride(0) != C else torch.empty_like(x)
+        sb, sc, sh, sw = _src_strides(gx, layout, H, W)
+        assert (sb, sc, sh, sw) == _src_strides(x, layout, H, W)
+        _launch("vcnf_col2im", ptr(gcol), gcol.stride(0), ptr(x) if act else None, ptr(gx), sb, sc, sh, sw, B, C, H, W,
+                ksize, 0, int(act), slope, stream())
+        return gx, None, None, None, None, None, None, None, None, None
+
+
+def im2col(x, layout, B, C, H, W, ksize, Kp=None, act=False, slope=0.0):
+    return _Im2Col.apply(x, layout, B, C, H, W, ksize, Kp if Kp is not None else ksize * ksize * C, act, slope)
+
+
+def colsum(x, layout, rows, C, ld_or_S):
+    """fp32 [C] column sums (bias gradients): layout 0 = bf16 rows [rows, ld], 1 = fp32 NCHW [rows, C, S]."""
+    out = torch.empty(C, dtype=torch.float32, device=x.device)
+    ws = torch.empty(_lib.query("vcnf_colsum_workspace", C), dtype=torch.uint8, device=x.device)
+    _launch("vcnf_colsum", ptr(x), layout, rows, C, ld_or_S, ptr(out), ptr(ws), stream(), n=2)
+    return out
+
+
+def conv_gemm_bf16(act, B, H, W, taps, Wp, bias=None, mask=None, slope=0.0, epi=0, out_nchw_channels=None):
+    """vcnf_conv_gemm_bf16: act [B*H*W, Cp] bf16 (NHWC), Wp [taps, Np, Cp] bf16.  Returns NHWC bf16 [B*H*W, Np], or
+    NCHW fp32 [B, Cout, H, W] when out_nchw_channels = Cout."""
+    Cp, Np = act.shape[1], Wp.shape[1]
+    assert act.is_contiguous() and Wp.is_contiguous() and Wp.shape[0] == taps and Wp.shape[2] == Cp
+    if out_nchw_channels is None:
+        out = torch.empty((B * H * W, Np), dtype=torch.bfloat16, device=act.device)
+        mode, cout, ldo = 0, Np, Np
+    else:
+        cout = int(out_nchw_channels)
+        out = torch.empty((B, cout, H, W), dtype=torch.float32, device=act.device)
+        mode, ldo = 1, 0
+    _launch("vcnf_conv_gemm_bf16", ptr(act), B, H, W, Cp, taps, ptr(Wp), Np, ptr(bias), ptr(mask),
+            mask.stride(0) if mask is not None else 0, float(slope), epi, ptr(out), mode, cout, ldo, stream())
+    return out
+
+
+def conv_wgrad_bf16(X, Y):
+    """G [Mx, Ny] fp32 = X^T Y over the pixel rows (X [P, Mx], Y [P, Ny] bf16)."""
+    P, Mx = X.shape
+    Ny = Y.shape[1]
+    G = torch.empty((Mx, Ny), dtype=torch.float32, device=X.device)
+    ws = torch.empty(max(16, _lib.query("vcnf_conv_wgrad_workspace", P, Mx, Ny)), dtype=torch.uint8, device=X.device)
+    _launch("vcnf_conv_wgrad_bf16", ptr(X), X.stride(0), Mx, ptr(Y), Y.stride(0), Ny, P, ptr(G), ptr(ws), stream(), n=2)
+    return G
+
+
+class _ConvNet3Bf16(torch.autograd.Function):
+    """conv3x3 -> LeakyReLU -> conv1x1 -> LeakyReLU -> conv3x3 (normflow/nets/cnn.py:29-47 as GlowBlock builds it,
+    flows/affine/glow.py:24-34) with bf16 operands on the tcgen05 tensor cores, fp32 accumulation, fp32 in / out
+    (NCHW).  Activations between the layers are NHWC bf16 and never leave that layout; the 3x3 convolution over the
+    hidden channels is nine shifted TMA loads per tile (no patch matrix); the two few-channel ends (coupling input,
+    gradient of the parameter output) are laid out as patch matrices by the pack kernel that converts them anyway."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, w3, b3, slope):
+        x = x.contiguous()
+        B, C0, H, W = x.shape
+        Hd, C3 = w1.shape[0], w3.shape[0]
+        bf = torch.bfloat16
+        K1p = _ceil_to(9 * C0, 64)
+        a1 = im2col_raw(x, "nchw", B, C0, H, W, 3, K1p, bf16=True)
+        w1p = torch.nn.functional.pad(w1.detach().permute(0, 2, 3, 1).reshape(Hd, 9 * C0), (0, K1p - 9 * C0)).to(bf)
+        h1 = conv_gemm_bf16(a1, B, H, W, 1, w1p.view(1, Hd, K1p), b1.detach().float().contiguous(), slope=slope, epi=1)
+        w2p = w2.detach().reshape(Hd, Hd).to(bf).contiguous()
+        h2 = conv_gemm_bf16(h1, B, H, W, 1, w2p.view(1, Hd, Hd), b2.detach().float().contiguous(), slope=slope, epi=1)
+        Np3 = _ceil_to(C3, 16)
+        w3p = torch.nn.functional.pad(w3.detach().permute(2, 3, 0, 1).reshape(9, C3, Hd), (0, 0, 0, Np3 - C3)).to(bf)
+        b3p = torch.nn.functional.pad(b3.detach().float(), (0, Np3 - C3))
+        out = conv_gemm_bf16(h2, B, H, W, 9, w3p.contiguous(), b3p, out_nchw_channels=C3)
+        ctx.slope = float(slope)
+        ctx.dims = (B, C0, H, W, Hd, C3, K1p)
+        ctx.save_for_backward(a1, h1, h2, w1, w2, w3)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        a1, h1, h2, w1, w2, w3 = ctx.saved_tensors
+        B, C0, H, W, Hd, C3, K1p = ctx.dims
+        slope, bf = ctx.slope, torch.bfloat16
+        P = B * H * W
+        g = g.contiguous().float()
+        need = ctx.needs_input_grad
+        pad = torch.nn.functional.pad
+        K3p = _ceil_to(9 * C3, 64)
+        a3g = im2col_raw(g, "nchw", B, C3, H, W, 3, K3p, flip=True, bf16=True)
+        wd3 = pad(w3.permute(1, 2, 3, 0).reshape(Hd, 9 * C3), (0, K3p - 9 * C3)).to(bf)
+        gh2 = conv_gemm_bf16(a3g, B, H, W, 1, wd3.view(1, Hd, K3p), mask=h2, slope=slope, epi=2)
+        wd2 = w2.reshape(Hd, Hd).t().contiguous().to(bf)
+        gh1 = conv_gemm_bf16(gh2, B, H, W, 1, wd2.view(1, Hd, Hd), mask=h1, slope=slope, epi=2)
+        gx = gw1 = gb1 = gw2 = gb2 = gw3 = gb3 = None
+        if need[0]:
+            Np1 = _ceil_to(C0, 16)
+            wd1 = pad(w1.flip(2, 3).permute(2, 3, 1, 0).reshape(9, C0, Hd), (0, 0, 0, Np1 - C0)).to(bf).contiguous()
+            gx = conv_gemm_bf16(gh1, B, H, W, 9, wd1, out_nchw_channels=C0)
+        if need[5]:
+            G3 = conv_wgrad_bf16(a3g, h2)
+            gw3 = G3[:9 * C3].view(3, 3, C3, Hd).permute(2, 3, 0, 1).contiguous().to(w3.dtype)
+        if need[6]:
+            gb3 = colsum(g, 1, B, C3, H * W).to(w3.dtype)
+        if need[3]:
+            gw2 = conv_wgrad_bf16(gh2, h1).view(Hd, Hd, 1, 1).to(w2.dtype)
+        if need[4]:
+            gb2 = colsum(gh2, 0, P, Hd, Hd).to(w2.dtype)
+        if need[1]:
+            G1 = conv_wgrad_bf16(gh1, a1)
+            gw1 = G1[:, :9 * C0].view(Hd, 3, 3, C0).permute(0, 3, 1, 2).contiguous().to(w1.dtype)
+        if need[2]:
+            gb1 = colsum(gh1, 0, P, Hd, Hd).to(w1.dtype)
+        return gx, gw1, gb1, gw2, gb2, gw3, gb3, None
+
+
+def convnet3_bf16(x, w1, b1, w2, b2, w3, b3, slope):
+    return _ConvNet3Bf16.apply(x, w1, b1, w2, b2, w3, b3, float(slope))
