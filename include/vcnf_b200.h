@@ -274,6 +274,30 @@ int vcnf_mlp_bwd(const void* x, int64_t ldx, const void* gy, int64_t ldgy, const
                  const int32_t* dims, int nl, double slope, void* gx, int64_t ldgx, void* gparams, void* workspace,
                  int64_t B, int dtype, void* stream);
 
+/* ---- K11: variational dequantisation of the categorical columns, all columns in one launch ---------------------
+ * Replaces the per-column loop of normflow/core.py:42-54 around VariationalDequantization.forward
+ * (normflow/nets/varquant.py:22-25,33-43,64-83) when every layer of the dequantisers' flow stacks is an elementwise
+ * affine map on the [B, 1] column: ActNorm / AffineConstFlow (flows/affine/coupling.py:37-53), MaskedAffineFlow with a
+ * one-element mask (coupling.py:202-222).  tab [n, L, 2] fp64 = (log-scale a_l, shift c_l) of layer l of column k's
+ * stack, evaluated by the host from the parameters.
+ *   x [B, ldx] (first n columns = the categorical values, dtype), noise [B, n] fp64 uniform(0,1) (varquant.py:70),
+ *   quants [n] fp64, alpha (varquant.py:55);  zc [B, n] (dtype) = dequantised logits (core.py:48),
+ *   logq_tot [B] fp32 = what core.py:52 accumulates in log_qt: column k's log-det counted (n - k) times (the
+ *   accumulator is passed by reference and mutated in place), logq_run [B] fp32 (optional) = the plain sum. */
+int vcnf_vdeq_fwd(const void* x, int64_t ldx, const void* noise, const void* tab, const void* quants, double alpha,
+                  int64_t B, int n, int L, void* zc, void* logq_tot, void* logq_run, int dtype, void* stream);
+/* Gradient of the table: g_tab [n, L, 2] fp64 from g_zc [B, n] (dtype, may be NULL) and g_logq [B] fp32 (gradient of
+ * logq_tot, may be NULL); fixed-order reduction over the batch.  workspace: vcnf_vdeq_bwd_workspace(n, L) bytes. */
+int64_t vcnf_vdeq_bwd_workspace(int n, int L);
+int vcnf_vdeq_bwd(const void* x, int64_t ldx, const void* noise, const void* tab, const void* quants, double alpha,
+                  int64_t B, int n, int L, const void* g_zc, const void* g_logq, void* g_tab, void* workspace,
+                  int dtype, void* stream);
+/* Sampling direction (varquant.py:26-30 driven by core.py:157-165) for all columns: out[b, k] =
+ * clamp(floor(sigmoid(z[b, k]) * quants[k]), 0, quants[k] - 1); logq [B] (dtype) is updated in place the way the
+ * reference does (log-dets added, then doubled after every column because the returned log-det aliases it). */
+int vcnf_vdeq_decode(const void* z, int64_t ldz, const void* quants, int64_t B, int n, void* out, void* logq, int dtype,
+                     void* stream);
+
 /* ---- K10: optimiser step on flat buffers -------------------------------------------------------
  * Replaces torch.optim.Adam(...).step() of the reference's training loops (runcred.py:192,257; run.py:139:
  * lr, weight_decay, default betas / eps, amsgrad off) when parameters, gradients and both moments each live in

@@ -117,6 +117,31 @@ class NormalizingFlow(nn.Module):
                 p.requires_grad_(True)
         return torch.mean(log_q) - beta * torch.mean(self.p.log_prob(z))
 
+    def reverse_alpha_div(self, num_samples=1, alpha=1, dreg=False):   # core.py:102-142
+        z, log_q = self.q0(num_samples)
+        for f in self.flows:
+            z, ld = f(z)
+            log_q = log_q - ld
+        log_p = self.p.log_prob(z)
+        if not dreg:
+            return np.sign(alpha - 1) * torch.logsumexp(alpha * (log_p - log_q), 0)
+        w_const = torch.exp(log_p - log_q).detach()            # doubly reparametrised estimator (:121-136)
+        z_ = z
+        log_q = torch.zeros(len(z_), device=z_.device)
+        for p in self.parameters():
+            p.requires_grad_(False)
+        for f in reversed(self.flows):
+            z_, ld = f.inverse(z_)
+            log_q = log_q + ld
+        log_q = log_q + self.q0.log_prob(z_)
+        for p in self.parameters():
+            p.requires_grad_(True)
+        w = torch.exp(log_p - log_q)
+        w_alpha = w_const ** alpha
+        w_alpha = w_alpha / torch.mean(w_alpha)
+        weights = (1 - alpha) * w_alpha + alpha * w_alpha ** 2
+        return -alpha * torch.mean(weights * torch.log(w))
+
     def sample(self, num_samples=1):                                 # core.py:144-168
         z, log_q = self.q0(num_samples)
         for f in self.flows:

@@ -11,6 +11,15 @@ SPLINE = dict(rtol=1e-4, atol=1e-5)
 F64 = dict(rtol=1e-9, atol=1e-11)
 
 
+# observed maxima per check (worst error / tolerance), written out by tests/conftest.py at session end
+OBSERVED = {}
+
+
+def record(what, value):
+    if what:
+        OBSERVED[what] = max(float(value), OBSERVED.get(what, 0.0))
+
+
 def excess(a, b, rtol, atol):
     """max over elements of |a-b| / (atol + rtol*|b|); <= 1 passes."""
     a, b = a.detach().double().cpu(), b.detach().double().cpu()
@@ -26,6 +35,7 @@ def excess(a, b, rtol, atol):
 def assert_close(a, b, rtol, atol, what=""):
     assert tuple(a.shape) == tuple(b.shape), (what, a.shape, b.shape)
     e = excess(a, b, rtol, atol)
+    record(what, e)
     assert e <= 1.0, "%s: error is %.3g x tolerance (rtol=%g atol=%g, max|ref|=%.3g)" % (
         what, e, rtol, atol, float(b.abs().max()) if b.numel() else 0.0)
 
@@ -42,10 +52,10 @@ def assert_grads_close(got, ref, rtol, what=""):
         assert_close(g, r, rtol=rtol, atol=rtol * max(scale, 1e-30), what="%s grad[%s]" % (what, name))
 
 
-def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.999):
+def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.9999, worst=2.0):
     """fp32 outputs: >= `frac` of the elements inside the stated tolerance of the
     reference (its fp32 or its fp64 evaluation); the ill-conditioned remainder must be no further from the
-    fp64 reference than 4x the fp32 reference's own worst error against it (+ 10 atol).  (Rounding errors on
+    fp64 reference than `worst` (2) x the fp32 reference's own worst error against it (+ 10 atol).  (Rounding errors on
     such elements are amplified by the same huge factor for any fp32 evaluation order; which order gets
     the luckier draw on a given element is chance -- golden case crqs_linear: the reference itself is off
     by 0.42 in one per-sample log-det.)"""
@@ -66,14 +76,17 @@ def assert_close_tail(a, ref32, ref64, rtol, atol, what="", frac=0.999):
     # they are covered by the worst-error clause below instead
     excused = (r32 - r64).abs()[ok] > 0.25 * tol
     share = float((near | excused).double().mean())
+    record(what + " (worst err / tol, tail clause)", float((err / tol).max()))
+    record(what + " (share outside tol, %)", 100.0 * (1.0 - float(near.double().mean())))
     e64 = float(err64[~near].max()) if (~near).any() else 0.0
     ref_e = float((r32 - r64).abs()[ok].max())
     assert share >= frac, "%s: only %.4f%% of elements inside rtol=%g atol=%g (worst %.3g x tol)" % (
         what, 100 * share, rtol, atol, float((err / tol).max()))
-    assert e64 <= 4 * ref_e + 10 * atol, "%s: max error vs fp64 reference %.3g > 4 x %.3g + 10 atol" % (what, e64, ref_e)
+    record(what + " (worst err vs fp64 / reference's own fp32-vs-fp64 worst)", e64 / ref_e if ref_e > 0 else 0.0)
+    assert e64 <= worst * ref_e + 10 * atol, "%s: max error vs fp64 reference %.3g > %g x %.3g + 10 atol" % (what, e64, worst, ref_e)
 
 
-def assert_grads_close_tail(got, ref32, ref64, rtol, what=""):
+def assert_grads_close_tail(got, ref32, ref64, rtol, what="", frac=0.9999, worst=2.0):
     """Gradients of an fp32 spline layer: an element passes when it is inside the stated tolerance
     of the fp32 reference, OR no further from the fp64 reference than twice the fp32 reference's own
     error there (+ the same tolerance).  The second clause exists because the reference's fp32
@@ -88,13 +101,17 @@ def assert_grads_close_tail(got, ref32, ref64, rtol, what=""):
         g_, r32_, r64_ = g.detach().double().cpu(), r32.detach().double().cpu(), ref64[name].detach().double().cpu()
         scale = float(r32_.abs().max()) if r32_.numel() else 0.0
         tol = rtol * max(scale, 1e-30) + rtol * r32_.abs()
-        ok = ((g_ - r32_).abs() <= tol) | ((g_ - r64_).abs() <= 4 * (r32_ - r64_).abs() + tol)
+        ok = ((g_ - r32_).abs() <= tol) | ((g_ - r64_).abs() <= worst * (r32_ - r64_).abs() + tol)
         # population clause (rounding errors are independent per element, amplified by 1/f' on the
         # ill-conditioned ones): >= 99.9 % inside, and the worst error against fp64 no larger than
         # twice the fp32 reference's own worst error against fp64
         share = float(ok.double().mean()) if ok.numel() else 1.0
+        if ok.numel():
+            record("%s grad[%s] (worst err / (rtol*max|ref|), tail clause)" % (what, name),
+                   float(((g_ - r32_).abs() / tol).max()))
         e64 = float((g_ - r64_).abs().max()) if ok.numel() else 0.0
         ref_e = float((r32_ - r64_).abs().max()) if ok.numel() else 0.0
-        assert share >= 0.999 and e64 <= 4 * ref_e + float(tol.max()), (
+        record("%s grad[%s] (share outside both clauses, %%)" % (what, name), 100.0 * (1.0 - share))
+        assert share >= frac and e64 <= worst * ref_e + float(tol.max()), (
             "%s grad[%s]: %d of %d elements outside both clauses; worst vs fp64 %.3g (reference fp32: %.3g)" % (
                 what, name, int((~ok).sum()), ok.numel(), e64, ref_e))

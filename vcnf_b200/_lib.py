@@ -50,6 +50,9 @@ _SIGNATURES = {
     "vcnf_conv_gemm_bf16": [_vp, _i64, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _vp, _i64, _dbl, _i32, _vp, _i32, _i32,
                             _i64, _vp],
     "vcnf_conv_wgrad_bf16": [_vp, _i64, _i32, _vp, _i64, _i32, _i64, _vp, _vp, _vp],
+    "vcnf_vdeq_fwd": [_vp, _i64, _vp, _vp, _vp, _dbl, _i64, _i32, _i32, _vp, _vp, _vp, _i32, _vp],
+    "vcnf_vdeq_bwd": [_vp, _i64, _vp, _vp, _vp, _dbl, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp],
+    "vcnf_vdeq_decode": [_vp, _i64, _vp, _i64, _i32, _vp, _vp, _i32, _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
 }
 _I64_RETURN = {
@@ -59,6 +62,7 @@ _I64_RETURN = {
     "vcnf_small_linear_bwd_workspace": [_i32, _i32],
     "vcnf_mlp_bwd_workspace": [_vp, _i32, _i32],
     "vcnf_colsum_workspace": [_i32],
+    "vcnf_vdeq_bwd_workspace": [_i32, _i32],
     "vcnf_conv_wgrad_workspace": [_i64, _i32, _i32],
 }
 EXPORTED = sorted(list(_SIGNATURES) + list(_I64_RETURN))

@@ -10,7 +10,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-from . import utils
+from . import ops, utils
 
 
 class NormalizingFlow(nn.Module):
@@ -23,6 +23,38 @@ class NormalizingFlow(nn.Module):
         if categoricals is not None:
             self.vdeqs = nn.ModuleList(catvdeqs)
             self.catlevels = catlevels
+
+    vdeq_noise_fn = None      # optional callable(B, n_columns, device) -> fp64 uniform noise (parity tests inject it)
+
+    def _vdeq_plan(self, device):
+        """(table [n, L, 2] fp64, quants [n] fp64, alpha) when every categorical column's dequantiser reduces to
+        elementwise affine layers (nets.VariationalDequantization.affine_table), else None -> per-column route."""
+        from .nets.varquant import VariationalDequantization
+        vd = list(self.vdeqs)[:len(self.categoricals)]
+        if not vd or any(type(v) is not VariationalDequantization for v in vd):
+            return None
+        if len({float(v.alpha) for v in vd}) != 1 or len({len(v.flows) for v in vd}) != 1:
+            return None
+        tabs, seen = [], {}
+        for v in vd:
+            key = tuple(id(f) for f in v.flows)        # dequantisers that share their layer objects share the table
+            if key not in seen:
+                t = v.affine_table()
+                if t is None:
+                    return None
+                seen[key] = t.to(device=device, dtype=torch.float64)
+            tabs.append(seen[key])
+        tab = tabs[0].unsqueeze(0).expand(len(vd), -1, -1) if len(seen) == 1 else torch.stack(tabs)
+        return tab.contiguous(), self._vdeq_quants_on(device), float(vd[0].alpha)
+
+    def _vdeq_quants_on(self, device):
+        """Number of levels per categorical column as a device fp64 vector (built once per device)."""
+        vd = list(self.vdeqs)[:len(self.categoricals)]
+        cache = self.__dict__.setdefault("_vdeq_quants", {})
+        qkey = (str(device), tuple(float(v.quants) for v in vd))
+        if qkey not in cache:
+            cache[qkey] = torch.tensor(qkey[1], dtype=torch.float64, device=device)
+        return cache[qkey]
 
     def _cat_index(self, device):
         """The categorical column list as a device index tensor, built once per device: indexing with the Python
@@ -39,17 +71,27 @@ class NormalizingFlow(nn.Module):
         log_q = torch.zeros(len(x), device=x.device)
         z = x
         zarr, zparr = [], []
-        if self.categoricals is not None:
-            zc = x[:, self._cat_index(x.device)]
-            for vcn in range(len(self.categoricals)):
-                zct, log_det = self.vdeqs[vcn].forward(z=zc[:, vcn].view([zc.shape[0], 1]), ldj=log_q,
-                                                       reverse=False)
-                zc[:, vcn] = zct.squeeze()
-                if extended:
-                    zarr.append(z.cpu().detach().numpy())
-                    zparr.append(log_det.cpu().detach().numpy())
-                log_qt += log_det
-            z[:, self._cat_index(z.device)] = zc.float()
+        if self.categoricals is not None and len(self.categoricals) > 0:
+            idx = self._cat_index(x.device)
+            zc = x[:, idx]
+            fused = self._vdeq_plan(x.device) if not extended else None
+            if fused is not None:
+                # every column through its dequantiser in ONE kernel (same triangular accumulation, fp32)
+                tab, quants, alpha = fused
+                n = len(self.categoricals)
+                noise = (self.vdeq_noise_fn(len(x), n, x.device) if self.vdeq_noise_fn is not None
+                         else torch.rand(len(x), n, dtype=torch.float64, device=x.device))
+                zc, log_qt = ops.vdeq_fused(zc, noise, tab, quants, alpha)
+            else:
+                for vcn in range(len(self.categoricals)):
+                    zct, log_det = self.vdeqs[vcn].forward(z=zc[:, vcn].view([zc.shape[0], 1]), ldj=log_q,
+                                                           reverse=False)
+                    zc[:, vcn] = zct.squeeze()
+                    if extended:
+                        zarr.append(z.cpu().detach().numpy())
+                        zparr.append(log_det.cpu().detach().numpy())
+                    log_qt += log_det
+            z[:, idx] = zc.float()
         log_q = log_qt
         for i in range(len(self.flows) - 1, -1, -1):
             z, log_det = self.flows[i].inverse(z)
@@ -127,13 +169,22 @@ class NormalizingFlow(nn.Module):
             z, log_det = flow(z)
             log_q -= log_det
         if self.categoricals is not None and len(self.categoricals) > 0:
-            zc = z[:, self._cat_index(z.device)]
-            for vct in range(len(self.categoricals)):
-                zct, log_det = self.vdeqs[vct].forward(z=zc[:, vct].view([zc.shape[0], 1]), ldj=log_q,
-                                                       reverse=True)
-                zc[:, vct] = zct.squeeze()
-                log_q += log_det
-            z[:, self._cat_index(z.device)] = zc.to(z.dtype)
+            idx = self._cat_index(z.device)
+            zc = z[:, idx]
+            plain = all(type(v).__name__ in ("VariationalDequantization", "Dequantization")
+                        for v in list(self.vdeqs)[:len(self.categoricals)])
+            if plain and not torch.is_grad_enabled() and log_q.dtype == zc.dtype and log_q.is_contiguous():
+                # floor / clamp to the level index for all columns in one kernel; log_q updated in place with the
+                # reference's aliasing (`log_q += log_det` where log_det IS log_q, core.py:160-164)
+                quants = self._vdeq_quants_on(z.device)
+                zc = ops.vdeq_decode(zc, quants, log_q)
+            else:
+                for vct in range(len(self.categoricals)):
+                    zct, log_det = self.vdeqs[vct].forward(z=zc[:, vct].view([zc.shape[0], 1]), ldj=log_q,
+                                                           reverse=True)
+                    zc[:, vct] = zct.squeeze()
+                    log_q += log_det
+            z[:, idx] = zc.to(z.dtype)
         return z, log_q
 
     def log_prob(self, x):

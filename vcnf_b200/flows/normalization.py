@@ -14,8 +14,20 @@ class ActNorm(AffineConstFlow):
         self.data_dep_init_done_cpu = torch.tensor(0.)
         self.register_buffer("data_dep_init_done", self.data_dep_init_done_cpu)
 
+    def initialised(self):
+        """True once the data-dependent initialisation has run (or was loaded).  A flag that lives on the device
+        (module moved / state_dict loaded after the initialisation) is read once and then kept on the host like the
+        reference keeps it after initialising (normalization.py:27,37): no device synchronisation per call."""
+        flag = self.data_dep_init_done
+        if flag.is_cuda:
+            if not bool(flag > 0.):
+                return False
+            self.data_dep_init_done = torch.tensor(1.)
+            return True
+        return bool(flag > 0.)
+
     def forward(self, z):
-        if not self.data_dep_init_done > 0.:
+        if not self.initialised():
             assert self.s is not None and self.t is not None
             with torch.no_grad():
                 s_init = -torch.log(z.std(dim=self.batch_dims, keepdim=True) + 1e-6)
@@ -25,7 +37,7 @@ class ActNorm(AffineConstFlow):
         return super().forward(z)
 
     def inverse(self, z):
-        if not self.data_dep_init_done:
+        if not self.initialised():
             assert self.s is not None and self.t is not None
             with torch.no_grad():
                 self.s.data = torch.log(z.std(dim=self.batch_dims, keepdim=True) + 1e-6).data.to(self.s.dtype)

@@ -859,3 +859,52 @@ class _ConvNet3Bf16(torch.autograd.Function):
 
 def convnet3_bf16(x, w1, b1, w2, b2, w3, b3, slope):
     return _ConvNet3Bf16.apply(x, w1, b1, w2, b2, w3, b3, float(slope))
+
+
+# ------------------------------------------------------------------ variational dequantisation (K11)
+class _VdeqFused(torch.autograd.Function):
+    """All categorical columns through their dequantisers in one launch (vcnf_vdeq_fwd); the gradient of the
+    per-layer (log-scale, shift) table comes from vcnf_vdeq_bwd."""
+
+    @staticmethod
+    def forward(ctx, xcat, noise, tab, quants, alpha):
+        xcat = _rows(xcat)
+        B, n = xcat.shape
+        L = tab.shape[1]
+        noise, tab = noise.contiguous(), tab.contiguous()
+        zc = torch.empty((B, n), dtype=xcat.dtype, device=xcat.device)
+        logq = torch.empty(B, dtype=torch.float32, device=xcat.device)
+        _launch("vcnf_vdeq_fwd", ptr(xcat), xcat.stride(0), ptr(noise), ptr(tab), ptr(quants), float(alpha), B, n, L,
+                ptr(zc), ptr(logq), None, dtype_code(xcat), stream())
+        ctx.alpha = float(alpha)
+        ctx.save_for_backward(xcat, noise, tab, quants)
+        return zc, logq
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g_zc, g_logq):
+        xcat, noise, tab, quants = ctx.saved_tensors
+        B, n = xcat.shape
+        L = tab.shape[1]
+        g_zc = g_zc.contiguous().to(xcat.dtype) if g_zc is not None else None
+        g_logq = g_logq.contiguous().float() if g_logq is not None else None
+        g_tab = torch.empty_like(tab)
+        ws = torch.empty(max(16, _lib.query("vcnf_vdeq_bwd_workspace", n, L)), dtype=torch.uint8, device=xcat.device)
+        _launch("vcnf_vdeq_bwd", ptr(xcat), xcat.stride(0), ptr(noise), ptr(tab), ptr(quants), ctx.alpha, B, n, L,
+                ptr(g_zc), ptr(g_logq), ptr(g_tab), ptr(ws), dtype_code(xcat), stream(), n=2)
+        return None, None, g_tab, None, None
+
+
+def vdeq_fused(xcat, noise, tab, quants, alpha):
+    """(dequantised logits [B, n], triangularly accumulated log-det [B] fp32); tab [n, L, 2] fp64."""
+    return _VdeqFused.apply(xcat, noise, tab, quants, alpha)
+
+
+def vdeq_decode(zc, quants, log_q):
+    """Sampling direction for all categorical columns (no gradient); log_q is updated in place."""
+    zc = _rows(zc)
+    B, n = zc.shape
+    out = torch.empty((B, n), dtype=zc.dtype, device=zc.device)
+    assert log_q.is_contiguous() and log_q.dtype == zc.dtype
+    _launch("vcnf_vdeq_decode", ptr(zc), zc.stride(0), ptr(quants), B, n, ptr(out), ptr(log_q), dtype_code(zc), stream())
+    return out
