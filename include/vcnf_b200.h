@@ -298,6 +298,54 @@ int vcnf_vdeq_bwd(const void* x, int64_t ldx, const void* noise, const void* tab
 int vcnf_vdeq_decode(const void* z, int64_t ldz, const void* quants, int64_t B, int n, void* out, void* logq, int dtype,
                      void* stream);
 
+/* ---- f1: base-distribution ends of the flow -----------------------------------------------------------------
+ * Diagonal Gaussian, optionally class-conditional (normflow/distributions/base.py:609-652 DiagGaussian.forward /
+ * log_prob; :715-775 ClassCondDiagGaussian), one launch per call instead of ~10 ATen launches:
+ *   mode 0: logp[b] = (accum ? accum[b] : 0) - n/2 log(2 pi) - sum_j (l_j + ((zin[b,j] - loc_j) exp(-l_j))^2 / 2)
+ *   mode 1: zout[b,j] = loc_j + exp(l_j) zin[b,j]  (zin = standard-normal draws), logp from the same pass
+ * with loc_j = loc[j*j_stride + y[b]*c_stride], l_j = log_scale[same] + log_temp (temperature annealing,
+ * base.py:636-640).  DiagGaussian: j_stride 1, c_stride 0, y NULL; ClassCondDiagGaussian (parameters
+ * [*shape, classes]): j_stride = classes, c_stride 1, y int64 [B].  n = number of event elements. */
+int vcnf_gauss_fwd(const void* zin, const void* loc, const void* log_scale, int64_t j_stride, int64_t c_stride,
+                   const int64_t* y, double log_temp, const void* accum, void* zout, void* logp, int64_t B, int n,
+                   int mode, int dtype, void* stream);
+/* Backward: mode 0: gz [B, n] from g_logp [B]; mode 1: from g_zout [B, n] and g_logp.  g_loc / g_log_scale (both or
+ * neither) are DENSE [classes, n] sums over the batch (fixed order); workspace: vcnf_gauss_bwd_workspace bytes. */
+int64_t vcnf_gauss_bwd_workspace(int n, int classes, int dtype);
+int vcnf_gauss_bwd(const void* zin, const void* loc, const void* log_scale, int64_t j_stride, int64_t c_stride,
+                   const int64_t* y, double log_temp, const void* g_logp, const void* g_zout, void* gz, void* g_loc,
+                   void* g_log_scale, void* workspace, int64_t B, int n, int classes, int mode, int dtype, void* stream);
+/* Mixture of K diagonal Gaussians (base.py:1023-1034): logp[b] = logsumexp_k( log softmax(weight_scores)_k +
+ * log N(z[b]; mu_k, exp(log_scale_k)) ) (+ accum[b]).  mu, log_scale [K, d]; weight_scores [K]. */
+int vcnf_gmm_logprob(const void* z, const void* mu, const void* log_scale, const void* weight_scores,
+                     const void* accum, void* logp, int64_t B, int K, int d, int dtype, void* stream);
+/* Backward: gz [B, d] (may be NULL) and g_params = [g_mu (K*d) | g_log_scale (K*d) | g_weight_scores (K)], fixed-order
+ * reduction over the batch; workspace: vcnf_gmm_bwd_workspace(K, d, dtype) bytes. */
+int64_t vcnf_gmm_bwd_workspace(int K, int d, int dtype);
+int vcnf_gmm_logprob_bwd(const void* z, const void* mu, const void* log_scale, const void* weight_scores,
+                         const void* g_logp, void* gz, void* g_params, void* workspace, int64_t B, int K, int d,
+                         int dtype, void* stream);
+
+/* ---- f4 / f2: preprocessing either side of the path, checkerboard split -----------------------------------------
+ * Logit transform (normflow/transforms.py:7-39, the optional MultiscaleFlow.transform; utils/preprocessing.py:5-22):
+ *   to_logit = 1: u = a0 + beta z, out = log u - log(1 - u), logdet[b] = n log beta - sum_j (log u + log(1 - u))
+ *   to_logit = 0: out = (sigmoid(z) - a0) / beta, logdet[b] = -n log beta + sum_j (logsigmoid(z) + logsigmoid(-z))
+ * z, out [B, n]; logdet [B] or NULL.  transforms.Logit(alpha): a0 = alpha, beta = 1 - 2 alpha. */
+int vcnf_logit_fwd(const void* z, void* out, void* logdet, int64_t B, int n, double a0, double beta, int to_logit,
+                   int dtype, void* stream);
+int vcnf_logit_bwd(const void* z, const void* gy, const void* gld, void* gz, int64_t B, int n, double a0, double beta,
+                   int to_logit, int dtype, void* stream);
+/* out = a x + b + c noise (noise may be NULL; out may alias x): Scale, Jitter (utils/preprocessing.py:25-56), Shift
+ * (transforms.py:42-62, in place like the reference). */
+int vcnf_axpb(const void* x, const void* noise, void* out, int64_t total, double a, double b, double c, int dtype,
+              void* stream);
+/* Split / Merge in the 'checkerboard' modes (normflow/flows/reshape.py:30-44,56-72): z [B, M, W] (M = product of the
+ * dims between batch and last, W even) <-> z1, z2 [B, M, W/2]; z1 takes the positions whose non-batch indices sum to an
+ * odd number (even when inv != 0).  mid_parity [M] uint8 = parity of the middle indices.  merge 0: z -> z1, z2;
+ * merge 1: z1, z2 -> z. */
+int vcnf_checkerboard(void* z, void* z1, void* z2, const uint8_t* mid_parity, int64_t B, int M, int W, int inv, int merge,
+                      int dtype, void* stream);
+
 /* ---- K10: optimiser step on flat buffers -------------------------------------------------------
  * Replaces torch.optim.Adam(...).step() of the reference's training loops (runcred.py:192,257; run.py:139:
  * lr, weight_decay, default betas / eps, amsgrad off) when parameters, gradients and both moments each live in

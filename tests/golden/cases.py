@@ -101,6 +101,38 @@ LAYER_CASES = {
 }
 
 
+def _img_coupling(nf, uncond):
+    cpl = nf.flows.neural_spline.coupling
+    mk = lambda cin, cout: nf.nets.ConvResidualNet(in_channels=cin, out_channels=cout, hidden_channels=16)
+    kw = dict(apply_unconditional_transform=True, img_shape=[4, 4]) if uncond else {}
+    return cpl.PiecewiseRationalQuadraticCoupling(mask=nf.utils.masks.create_mid_split_binary_mask(2),
+                                                  transform_net_create_fn=mk, tails="linear", tail_bound=3.0, **kw)
+
+
+# Round-2 cases: golden vectors in layers_r2.pt, generated from the unmodified reference by
+# `make_golden.py --r2`.  The oracle does not restate these rows; the CUDA product is compared with the reference's
+# outputs directly.
+LAYER_CASES_R2 = {
+    "prq_coupling_img": dict(      # the reference's own test shape [10, 2, 4, 4] (coupling_test.py:49-50)
+        build=lambda nf: _img_coupling(nf, False),
+        x=lambda: 1.5 * torch.randn(10, 2, 4, 4, generator=_g(41)), scale=0.2),
+    "prq_coupling_img_uncond": dict(
+        build=lambda nf: _img_coupling(nf, True),
+        x=lambda: 1.5 * torch.randn(10, 2, 4, 4, generator=_g(42)), scale=0.2),
+    "affine_block_checkerboard": dict(
+        build=lambda nf: nf.flows.AffineCouplingBlock(nf.nets.ConvNet2d((3, 8, 6), (3, 3), init_zeros=False),
+                                                      split_mode="checkerboard"),
+        x=lambda: torch.randn(5, 3, 4, 6, generator=_g(43)), scale=0.1),
+    "affine_block_checkerboard_inv": dict(
+        build=lambda nf: nf.flows.AffineCouplingBlock(nf.nets.ConvNet2d((3, 8, 6), (3, 3), init_zeros=False),
+                                                      split_mode="checkerboard_inv"),
+        x=lambda: torch.randn(5, 3, 4, 6, generator=_g(44)), scale=0.1),
+    "logit_transform": dict(
+        build=lambda nf: nf.transforms.Logit(alpha=0.05),
+        x=lambda: torch.rand(6, 3, 8, 8, generator=_g(45)), randomize=False),
+}
+
+
 def build_cfg2_small(nf, layers=3, d=29, hidden=32):
     flows = []
     for _ in range(layers):

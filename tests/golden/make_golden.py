@@ -18,16 +18,15 @@ import torch
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
 from ref_shim import load_reference          # noqa: E402
-from cases import LAYER_CASES, MODEL_CASES, randomize   # noqa: E402
+from cases import LAYER_CASES, LAYER_CASES_R2, MODEL_CASES, randomize   # noqa: E402
 from harness import eval_layer, eval_model   # noqa: E402
 
 warnings.filterwarnings("ignore")
 
 
-def main():
-    nf = load_reference()
+def layer_records(nf, cases, full64=False):
     layers = {}
-    for name, case in LAYER_CASES.items():
+    for name, case in cases.items():
         torch.manual_seed(0)
         dtype = case.get("dtype", torch.float32)
         layer = case["build"](nf)
@@ -42,10 +41,19 @@ def main():
             if dtype == torch.float32:
                 f64 = copy.deepcopy(layer).double()
                 r = eval_layer(f64, x.double(), direction, case.get("nograd", False))
-                rec[direction + "_f64"] = {"z": r["z"], "log_det": r["log_det"]}
+                rec[direction + "_f64"] = r if full64 else {"z": r["z"], "log_det": r["log_det"]}
         layers[name] = rec
         print("layer", name, tuple(x.shape), "ok")
-    torch.save(layers, os.path.join(HERE, "layers.pt"))
+    return layers
+
+
+def main():
+    nf = load_reference()
+    if "--r2" in sys.argv:                 # round-2 rows only: the round-1 fixtures stay byte-identical
+        torch.save(layer_records(nf, LAYER_CASES_R2, full64=True), os.path.join(HERE, "layers_r2.pt"))
+        print("layers_r2.pt", os.path.getsize(os.path.join(HERE, "layers_r2.pt")) // 1024, "KiB")
+        return
+    torch.save(layer_records(nf, LAYER_CASES), os.path.join(HERE, "layers.pt"))
 
     models = {}
     for name, case in MODEL_CASES.items():

@@ -9,6 +9,7 @@ The kernels live in libvcnf_b200.so (C ABI: include/vcnf_b200.h); there is no CP
 from .core import NormalizingFlow, MultiscaleFlow
 from . import flows
 from . import distributions
+from . import transforms
 from . import nets
 from . import utils
 from . import ops

@@ -53,6 +53,15 @@ _SIGNATURES = {
     "vcnf_vdeq_fwd": [_vp, _i64, _vp, _vp, _vp, _dbl, _i64, _i32, _i32, _vp, _vp, _vp, _i32, _vp],
     "vcnf_vdeq_bwd": [_vp, _i64, _vp, _vp, _vp, _dbl, _i64, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp],
     "vcnf_vdeq_decode": [_vp, _i64, _vp, _i64, _i32, _vp, _vp, _i32, _vp],
+    "vcnf_gauss_fwd": [_vp, _vp, _vp, _i64, _i64, _vp, _dbl, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
+    "vcnf_gauss_bwd": [_vp, _vp, _vp, _i64, _i64, _vp, _dbl, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32,
+                       _vp],
+    "vcnf_gmm_logprob": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
+    "vcnf_gmm_logprob_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
+    "vcnf_logit_fwd": [_vp, _vp, _vp, _i64, _i32, _dbl, _dbl, _i32, _i32, _vp],
+    "vcnf_logit_bwd": [_vp, _vp, _vp, _vp, _i64, _i32, _dbl, _dbl, _i32, _i32, _vp],
+    "vcnf_axpb": [_vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _i32, _vp],
+    "vcnf_checkerboard": [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
 }
 _I64_RETURN = {
@@ -62,6 +71,8 @@ _I64_RETURN = {
     "vcnf_small_linear_bwd_workspace": [_i32, _i32],
     "vcnf_mlp_bwd_workspace": [_vp, _i32, _i32],
     "vcnf_colsum_workspace": [_i32],
+    "vcnf_gauss_bwd_workspace": [_i32, _i32, _i32],
+    "vcnf_gmm_bwd_workspace": [_i32, _i32, _i32],
     "vcnf_vdeq_bwd_workspace": [_i32, _i32],
     "vcnf_conv_wgrad_workspace": [_i64, _i32, _i32],
 }

@@ -1,9 +1,12 @@
-"""Base distributions at the two ends of the flow (reference: normflow/distributions/base.py).
-O(B*D) once per step, not per layer: plain tensor ops here; fusing the Gaussian log-prob into
-the last bijector kernel is SURVEY.md 8(f1) "next"."""
+"""Base distributions at the two ends of the flow (reference: normflow/distributions/base.py).  On a CUDA device
+DiagGaussian / ClassCondDiagGaussian (log_prob and the reparametrised draw) and GaussianMixture.log_prob are one
+kernel each with hand-written backward (vcnf_gauss_fwd / _bwd, vcnf_gmm_logprob / _bwd); the
+tensor-op bodies below are the host mirror the CPU tests and soft-label calls use."""
 import numpy as np
 import torch
 from torch import nn
+
+from .. import ops
 
 
 class BaseDistribution(nn.Module):
@@ -37,8 +40,13 @@ class DiagGaussian(BaseDistribution):
             return self.log_scale
         return self.log_scale + np.log(self.temperature)
 
+    def _log_temp(self):
+        return 0.0 if self.temperature is None else float(np.log(self.temperature))
+
     def forward(self, num_samples=1):
         eps = torch.randn((num_samples,) + self.shape, dtype=self.loc.dtype, device=self.loc.device)
+        if eps.is_cuda:
+            return ops.gauss_sample(eps, self.loc, self.log_scale, log_temp=self._log_temp())
         log_scale = self._log_scale()
         z = self.loc + torch.exp(log_scale) * eps
         log_p = - 0.5 * self.d * np.log(2 * np.pi) \
@@ -46,6 +54,8 @@ class DiagGaussian(BaseDistribution):
         return z, log_p
 
     def log_prob(self, z):
+        if z.is_cuda:
+            return ops.gauss_logprob(z, self.loc, self.log_scale, log_temp=self._log_temp())
         log_scale = self._log_scale()
         return - 0.5 * self.d * np.log(2 * np.pi) \
             - torch.sum(log_scale + 0.5 * torch.pow((z - self.loc) / torch.exp(log_scale), 2),
@@ -86,14 +96,20 @@ class ClassCondDiagGaussian(BaseDistribution):
             num_samples = len(y)
         else:
             y = torch.randint(self.num_classes, (num_samples,), device=self.loc.device)
-        loc, log_scale = self._class_params(y)
         eps = torch.randn((num_samples,) + self.shape, dtype=self.loc.dtype, device=self.loc.device)
+        if eps.is_cuda and y.dim() == 1:
+            return ops.gauss_sample(eps, self.loc, self.log_scale, y=y.long(), classes=self.num_classes,
+                                    log_temp=0.0 if self.temperature is None else float(np.log(self.temperature)))
+        loc, log_scale = self._class_params(y)
         z = loc + torch.exp(log_scale) * eps
         log_p = - 0.5 * self.d * np.log(2 * np.pi) \
             - torch.sum(log_scale + 0.5 * torch.pow(eps, 2), list(range(1, self.n_dim + 1)))
         return z, log_p
 
     def log_prob(self, z, y):
+        if z.is_cuda and y.dim() == 1:
+            return ops.gauss_logprob(z, self.loc, self.log_scale, y=y.long(), classes=self.num_classes,
+                                     log_temp=0.0 if self.temperature is None else float(np.log(self.temperature)))
         loc, log_scale = self._class_params(y)
         return - 0.5 * self.d * np.log(2 * np.pi) \
             - torch.sum(log_scale + 0.5 * torch.pow((z - loc) / torch.exp(log_scale), 2),
@@ -121,6 +137,8 @@ class GaussianMixture(BaseDistribution):
                 self.register_buffer(name, value)
 
     def log_prob(self, z):
+        if z.is_cuda and z.dim() == 2:
+            return ops.gmm_logprob(z, self.loc, self.log_scale, self.weight_scores)
         weights = torch.softmax(self.weight_scores, 1)
         eps = (z[:, None, :] - self.loc) / torch.exp(self.log_scale)
         log_p = - 0.5 * self.dim * np.log(2 * np.pi) + torch.log(weights) \

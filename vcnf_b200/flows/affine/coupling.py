@@ -125,6 +125,13 @@ class AffineCouplingBlock(Flow):
         self.split_mode = split_mode
 
     def _run(self, z, inverse):
+        if "checkerboard" in self.split_mode:
+            # checkerboard split (reshape.py:30-44): the three layers in sequence, index-map kernels either side
+            log_det_tot = torch.zeros(z.shape[0], dtype=z.dtype, device=z.device)
+            for flow in (reversed(self.flows) if inverse else self.flows):
+                z, log_det = flow.inverse(z) if inverse else flow(z)
+                log_det_tot = log_det_tot + log_det
+            return z, log_det_tot
         if self.split_mode not in ("channel", "channel_inv"):
             raise NotImplementedError("Mode " + self.split_mode + " is not implemented.")
         coupling = self.flows[1]

@@ -53,8 +53,9 @@ class PiecewiseRationalQuadraticCDF(Flow):
         splines.check_minimums(num_bins, min_bin_width, min_bin_height, min_derivative)
         if tails is None:
             raise NotImplementedError("tails=None (bounded spline) is not on the B200 path")
-        if len(shape) != 1:
-            raise NotImplementedError("image-shaped spline parameters are a SURVEY.md 8(f2) next row")
+        if len(shape) not in (1, 3):
+            raise NotImplementedError("spline parameters must be per feature [D] or per pixel [C, H, W]")
+        self._img = len(shape) == 3
         if torch.is_tensor(tail_bound):
             self.register_buffer("tail_bound", tail_bound)
         else:
@@ -81,7 +82,29 @@ class PiecewiseRationalQuadraticCDF(Flow):
         n = self.unnormalized_widths.shape[0]
         return _modes_and_bounds(self.tails, self.tail_bound, n)
 
+    def pixel_rows(self, batch):
+        """Image-shaped parameters [C, H, W, P] laid out as the per-row parameters of NHWC pixel rows:
+        [batch*H*W, C*P] (the batch expansion of coupling.py:207-216; its adjoint sums over the batch)."""
+        p = self.packed_params()                                   # [C, H, W, P]
+        C, H, W, P = p.shape
+        rows = p.permute(1, 2, 0, 3).reshape(H * W, C * P)
+        return rows.unsqueeze(0).expand(batch, H * W, C * P).reshape(batch * H * W, C * P)
+
+    def _spline_image(self, inputs, inverse):
+        B, C, H, W = inputs.shape
+        if self._spec is None:
+            modes, bounds = self.segment()
+            P = _params_per_feature(self.tails, self.num_bins)
+            cmap = [(ops.COL_COND << 16) | i for i in range(C)]
+            self._spec = ops.SplineSpec(C, self.num_bins, cmap, modes, bounds, P, 1.0, [], [], P,
+                                        isinstance(self.tails, (list, tuple)))
+        rows = inputs.permute(0, 2, 3, 1).reshape(B * H * W, C)
+        y, ld = ops.rqs_layer(rows, self.pixel_rows(B), None, self._spec, inverse)
+        return y.reshape(B, H, W, C).permute(0, 3, 1, 2).contiguous(), ld.reshape(B, H * W).sum(1)
+
     def _spline(self, inputs, inverse=False):
+        if self._img:
+            return self._spline_image(inputs, inverse)
         if self._spec is None:
             n = self.unnormalized_widths.shape[0]
             modes, bounds = self.segment()
@@ -99,7 +122,8 @@ class PiecewiseRationalQuadraticCDF(Flow):
 
 
 class Coupling(Flow):
-    """Base coupling layer on a binary feature mask (coupling.py:18-137), 2-D inputs."""
+    """Base coupling layer on a binary feature mask (coupling.py:18-137): 2-D inputs [B, D], or images [B, C, H, W]
+    split along the channels (coupling.py:147-151), which run as NHWC pixel rows through the same spline kernel."""
 
     def __init__(self, mask, transform_net_create_fn, unconditional_transform=None):
         mask = torch.as_tensor(mask)
@@ -139,8 +163,6 @@ class Coupling(Flow):
             raise ValueError("Inputs must be a 2D or a 4D tensor.")
         if inputs.shape[1] != self.features:
             raise ValueError("Expected features = {}, got {}.".format(self.features, inputs.shape[1]))
-        if inputs.dim() == 4:
-            raise NotImplementedError("4-D spline coupling is a SURVEY.md 8(f2) next row")
 
     def _transform_dim_multiplier(self):
         raise NotImplementedError()
@@ -205,11 +227,19 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         cmodes, cbounds = _modes_and_bounds(self.tails, self.tail_bound, len(trans))
         list_mode = isinstance(self.tails, (list, tuple))
         ut = self.unconditional_transform
+        img_ut = ut is not None and getattr(ut, "_img", False)
         if ut is not None:
             smodes, sbounds = ut.segment()
             Ps = _params_per_feature(ut.tails, K)
         else:
             smodes, sbounds, Ps = [], [], Pc
+        if img_ut:
+            # per-pixel parameters are not shared across rows: they enter as per-row parameters of their own launch
+            n_id = len(ident)
+            self._ident_rows_spec = ops.SplineSpec(n_id, K, [(ops.COL_COND << 16) | j for j in range(n_id)],
+                                                   smodes, sbounds, Ps, 1.0, [], [], Ps,
+                                                   isinstance(ut.tails, (list, tuple)))
+            ut, smodes, sbounds = None, [], []
         wh = self._wh_scale()
         cond_map, shared_map, both = [0] * D, [0] * D, [0] * D
         for j, c in enumerate(trans):
@@ -223,6 +253,8 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
             "shared": mk(shared_map, [], [], smodes, sbounds),         # sampling direction, step 1
             "cond": mk(cond_map, cmodes, cbounds, [], []),             # sampling direction, step 2
         }
+        if img_ut:
+            self._specs["ident_rows"] = self._ident_rows_spec
         self._id_cols = self.identity_features.to(torch.int32)
 
     def _cols(self, device):
@@ -230,8 +262,54 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
             self._id_cols = self._id_cols.to(device)
         return self._id_cols
 
+    # ---- images: every pixel is a row of C features; conditioner output [B, Ct*P, H, W] = rows [B*H*W, Ct*P] ----
+    def _net_rows(self, identity_nchw, context):
+        net = self.transform_net
+        if context is None and hasattr(net, "forward_rows") and net.kernel_route(identity_nchw):
+            return net.forward_rows(identity_nchw)
+        out = net(identity_nchw, context)
+        B, CP, H, W = out.shape
+        return out.permute(0, 2, 3, 1).reshape(B * H * W, CP)
+
+    def _image(self, inputs, context, inverse):
+        if self._specs is None:
+            self._build_specs()
+        B, C, H, W = inputs.shape
+        rows = inputs.permute(0, 2, 3, 1).reshape(B * H * W, C).contiguous()
+        ut = self.unconditional_transform
+        idf = self.identity_features
+        logabsdet = 0.0
+
+        def unconditional(rows):
+            if not getattr(ut, "_img", False):
+                raise ValueError("image inputs need img_shape for the unconditional transform (coupling.py:207-216)")
+            ident = ops.gather_cols(rows, self._cols(rows.device))
+            yi, ld = ops.rqs_layer(ident, ut.pixel_rows(B), None, self._specs["ident_rows"], inverse)
+            rows = rows.index_copy(1, idf, yi)
+            return rows, ld
+
+        def net_params(rows):
+            ident = rows.index_select(1, idf).reshape(B, H, W, len(idf)).permute(0, 3, 1, 2).contiguous()
+            return self._net_rows(ident, context)
+        if not inverse:
+            params = net_params(rows)                                # conditioner sees the ORIGINAL identity part
+            out, ld = ops.rqs_layer(rows, params, None, self._specs["cond"], False)
+            if ut is not None:
+                out, ld_i = unconditional(out)
+                ld = ld + ld_i
+        else:
+            ld = 0.0
+            if ut is not None:
+                rows, ld = unconditional(rows)                       # coupling.py:108-110: identity part first
+            params = net_params(rows)
+            out, ld_c = ops.rqs_layer(rows, params, None, self._specs["cond"], True)
+            ld = ld_c + ld
+        return out.reshape(B, H, W, C).permute(0, 3, 1, 2).contiguous(), ld.reshape(B, H * W).sum(1) + logabsdet
+
     def forward(self, inputs, context=None, want_bins=False):
         self._check(inputs)
+        if inputs.dim() == 4:
+            return self._image(inputs, context, False)
         if self._specs is None:
             self._build_specs()
         identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
@@ -241,6 +319,8 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
 
     def inverse(self, inputs, context=None):
         self._check(inputs)
+        if inputs.dim() == 4:
+            return self._image(inputs, context, True)
         if self._specs is None:
             self._build_specs()
         logabsdet = 0.0

@@ -1,5 +1,6 @@
-"""Residual MLP conditioner of the coupling spline layers (reference: normflow/nets/resnet.py:8-106).
-`hidden_features` is read by the coupling layer for the 1/sqrt(hidden) scaling (coupling.py:314)."""
+"""Residual conditioners of the coupling spline layers (reference: normflow/nets/resnet.py): the dense ResidualNet
+(:8-106) and the convolutional ConvResidualNet of the image path (:109-213).  `hidden_features` / `hidden_channels`
+are read by the coupling layer for the 1/sqrt(hidden) scaling (coupling.py:314-316)."""
 import torch
 from torch import nn
 from torch.nn import functional as F, init
@@ -83,3 +84,106 @@ class ResidualNet(nn.Module):
         if fast:
             return ops.linear(h, self.final_layer.weight, self.final_layer.bias, pad_out=self.padded_out)
         return self.final_layer(h)
+
+
+def _is_relu(fn):
+    return fn is F.relu or fn is torch.relu or isinstance(fn, nn.ReLU)
+
+
+class ConvResidualBlock(nn.Module):
+    """x + conv3x3(act(conv3x3(act(x)))) (resnet.py:109-161).  On fp32 CUDA inputs each convolution is
+    vcnf_im2col (the ReLU fused into the read) -> vcnf_linear_tf32x3 on NHWC pixel rows, the skip connection rides on
+    the second GEMM's residual operand; no library convolution."""
+
+    def __init__(self, channels, context_channels=None, activation=F.relu, dropout_probability=0.,
+                 use_batch_norm=False, zero_initialization=True):
+        super().__init__()
+        self.activation = activation
+        if context_channels is not None:
+            self.context_layer = nn.Conv2d(context_channels, channels, kernel_size=1, padding=0)
+        self.use_batch_norm = use_batch_norm
+        if use_batch_norm:
+            self.batch_norm_layers = nn.ModuleList([nn.BatchNorm2d(channels, eps=1e-3) for _ in range(2)])
+        self.conv_layers = nn.ModuleList([nn.Conv2d(channels, channels, kernel_size=3, padding=1) for _ in range(2)])
+        self.dropout = nn.Dropout(p=dropout_probability)
+        if zero_initialization:
+            init.uniform_(self.conv_layers[-1].weight, -1e-3, 1e-3)
+            init.uniform_(self.conv_layers[-1].bias, -1e-3, 1e-3)
+
+    def kernel_route(self, context):
+        return (context is None and not self.use_batch_norm and _is_relu(self.activation)
+                and (self.dropout.p == 0. or not self.training))
+
+    def forward_rows(self, rows, B, H, W):
+        """rows: NHWC pixel rows [B*H*W, C] fp32."""
+        C = self.conv_layers[0].in_channels
+        kk = 9 * C
+        kp = kk if kk <= ops.KSLICE else (kk + 3) // 4 * 4
+        cur = rows
+        for i, conv in enumerate(self.conv_layers):
+            wr = conv.weight.permute(0, 2, 3, 1).reshape(C, kk)
+            if kp != kk:
+                wr = F.pad(wr, (0, kp - kk))
+            col = ops.im2col(cur, "nhwc", B, C, H, W, 3, kp, act=True, slope=0.0)
+            cur = ops.linear(col, wr, conv.bias, residual=rows if i == 1 else None, pad_out=C % 4 != 0)
+        return cur
+
+    def forward(self, inputs, context=None):
+        temps = inputs
+        if self.use_batch_norm:
+            temps = self.batch_norm_layers[0](temps)
+        temps = self.conv_layers[0](self.activation(temps))
+        if self.use_batch_norm:
+            temps = self.batch_norm_layers[1](temps)
+        temps = self.conv_layers[1](self.dropout(self.activation(temps)))
+        if context is not None:
+            temps = F.glu(torch.cat((temps, self.context_layer(context)), dim=1), dim=1)
+        return inputs + temps
+
+
+class ConvResidualNet(nn.Module):
+    """1x1 conv -> residual blocks -> 1x1 conv (resnet.py:164-213), the conditioner of the 4-D spline coupling.
+    fp32 CUDA inputs without context / batch norm / active dropout run entirely on the package's kernels in NHWC
+    (`forward_rows` hands the coupling layer the [B*H*W, out] parameter rows it consumes directly); everything else
+    (fp64, context, batch norm) evaluates the modules as the reference does."""
+
+    def __init__(self, in_channels, out_channels, hidden_channels, context_channels=None, num_blocks=2,
+                 activation=F.relu, dropout_probability=0., use_batch_norm=False):
+        super().__init__()
+        self.context_channels = context_channels
+        self.hidden_channels = hidden_channels
+        n_in = in_channels if context_channels is None else in_channels + context_channels
+        self.initial_layer = nn.Conv2d(n_in, hidden_channels, kernel_size=1, padding=0)
+        self.blocks = nn.ModuleList([
+            ConvResidualBlock(channels=hidden_channels, context_channels=context_channels, activation=activation,
+                              dropout_probability=dropout_probability, use_batch_norm=use_batch_norm)
+            for _ in range(num_blocks)])
+        self.final_layer = nn.Conv2d(hidden_channels, out_channels, kernel_size=1, padding=0)
+
+    def kernel_route(self, inputs, context=None):
+        return (inputs.is_cuda and inputs.dtype == torch.float32 and inputs.dim() == 4
+                and self.initial_layer.weight.dtype == torch.float32
+                and all(b.kernel_route(context) for b in self.blocks) and context is None)
+
+    def forward_rows(self, inputs):
+        """NCHW fp32 [B, C, H, W] -> parameter rows [B*H*W, out_channels] (NHWC)."""
+        B, C, H, W = inputs.shape
+        hid = self.hidden_channels
+        rows = ops.im2col(inputs, "nchw", B, C, H, W, 1)                      # layout change only (1x1 patches)
+        cur = ops.linear(rows, self.initial_layer.weight.reshape(hid, C), self.initial_layer.bias,
+                         pad_out=hid % 4 != 0)
+        for block in self.blocks:
+            cur = block.forward_rows(cur, B, H, W)
+        out_c = self.final_layer.out_channels
+        return ops.linear(cur, self.final_layer.weight.reshape(out_c, hid), self.final_layer.bias,
+                          pad_out=out_c % 4 != 0)
+
+    def forward(self, inputs, context=None):
+        if self.kernel_route(inputs, context):
+            B, _, H, W = inputs.shape
+            rows = self.forward_rows(inputs)
+            return rows.reshape(B, H, W, -1).permute(0, 3, 1, 2).contiguous()
+        temps = self.initial_layer(inputs if context is None else torch.cat((inputs, context), dim=1))
+        for block in self.blocks:
+            temps = block(temps, context)
+        return self.final_layer(temps)

@@ -908,3 +908,210 @@ def vdeq_decode(zc, quants, log_q):
     assert log_q.is_contiguous() and log_q.dtype == zc.dtype
     _launch("vcnf_vdeq_decode", ptr(zc), zc.stride(0), ptr(quants), B, n, ptr(out), ptr(log_q), dtype_code(zc), stream())
     return out
+
+
+# ------------------------------------------------------------------ base-distribution ends (f1)
+class _Gauss(torch.autograd.Function):
+    """Diagonal (class-conditional) Gaussian: mode 0 = log_prob(z), mode 1 = (z, log_p) from standard-normal draws.
+    `loc`, `log_scale` are passed in the module's own layout; (js, cs, classes) describe it (see vcnf_gauss_fwd)."""
+
+    @staticmethod
+    def forward(ctx, zin, loc, log_scale, y, log_temp, js, cs, classes, mode):
+        zin = zin.contiguous()
+        B = zin.shape[0]
+        n = zin.numel() // B if B else int(loc.numel() // classes)
+        loc_, ls_ = loc.contiguous(), log_scale.contiguous()
+        logp = torch.empty(B, dtype=zin.dtype, device=zin.device)
+        zout = torch.empty_like(zin) if mode == 1 else None
+        _launch("vcnf_gauss_fwd", ptr(zin), ptr(loc_), ptr(ls_), js, cs, ptr(y), float(log_temp), None, ptr(zout),
+                ptr(logp), B, n, mode, dtype_code(zin), stream())
+        ctx.cfg = (float(log_temp), js, cs, classes, mode, n, loc.shape)
+        ctx.save_for_backward(zin, loc_, ls_, y)
+        if mode == 1:
+            return zout, logp
+        return logp
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, *grads):
+        zin, loc_, ls_, y = ctx.saved_tensors
+        log_temp, js, cs, classes, mode, n, pshape = ctx.cfg
+        B = zin.shape[0]
+        if mode == 1:
+            g_z, g_logp = grads
+            g_z = g_z.contiguous() if g_z is not None else None
+        else:
+            (g_logp,), g_z = grads, None
+        g_logp = g_logp.contiguous() if g_logp is not None else None
+        want_z = mode == 0 and ctx.needs_input_grad[0]
+        want_p = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        gz = torch.empty_like(zin) if want_z else None
+        gl = gs = ws = None
+        if want_p:
+            gl = torch.empty((classes, n), dtype=zin.dtype, device=zin.device)
+            gs = torch.empty_like(gl)
+            ws = torch.empty(_lib.query("vcnf_gauss_bwd_workspace", n, classes, dtype_code(zin)), dtype=torch.uint8,
+                             device=zin.device)
+        if want_z or want_p:
+            _launch("vcnf_gauss_bwd", ptr(zin), ptr(loc_), ptr(ls_), js, cs, ptr(y), log_temp, ptr(g_logp), ptr(g_z),
+                    ptr(gz), ptr(gl), ptr(gs), ptr(ws), B, n, classes, mode, dtype_code(zin), stream(),
+                    n=3 if want_p else 1)
+        if want_p:
+            # dense [classes, n] -> the parameter's layout ([1, *shape] or [*shape, classes])
+            if cs == 0:
+                gl, gs = gl.reshape(pshape), gs.reshape(pshape)
+            else:
+                gl, gs = gl.t().reshape(pshape), gs.t().reshape(pshape)
+        return gz, gl, gs, None, None, None, None, None, None
+
+
+def gauss_logprob(z, loc, log_scale, y=None, log_temp=0.0, classes=1):
+    z, loc, log_scale = _promote(z, loc, log_scale)
+    js, cs = (1, 0) if classes == 1 else (classes, 1)
+    return _Gauss.apply(z, loc, log_scale, y, log_temp, js, cs, classes, 0)
+
+
+def gauss_sample(eps, loc, log_scale, y=None, log_temp=0.0, classes=1):
+    eps, loc, log_scale = _promote(eps, loc, log_scale)
+    js, cs = (1, 0) if classes == 1 else (classes, 1)
+    return _Gauss.apply(eps, loc, log_scale, y, log_temp, js, cs, classes, 1)
+
+
+class _GmmLogProb(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, mu, log_scale, weight_scores):
+        z, mu_, ls_, ws_ = z.contiguous(), mu.contiguous(), log_scale.contiguous(), weight_scores.contiguous()
+        B, d = z.shape
+        K = ws_.numel()
+        logp = torch.empty(B, dtype=z.dtype, device=z.device)
+        _launch("vcnf_gmm_logprob", ptr(z), ptr(mu_), ptr(ls_), ptr(ws_), None, ptr(logp), B, K, d, dtype_code(z),
+                stream())
+        ctx.shapes = (mu.shape, log_scale.shape, weight_scores.shape, K, d)
+        ctx.save_for_backward(z, mu_, ls_, ws_)
+        return logp
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        z, mu_, ls_, ws_ = ctx.saved_tensors
+        s_mu, s_ls, s_ws, K, d = ctx.shapes
+        B = z.shape[0]
+        g = g.contiguous()
+        gz = torch.empty_like(z) if ctx.needs_input_grad[0] else None
+        gp = torch.empty(2 * K * d + K, dtype=z.dtype, device=z.device)
+        ws = torch.empty(_lib.query("vcnf_gmm_bwd_workspace", K, d, dtype_code(z)), dtype=torch.uint8, device=z.device)
+        _launch("vcnf_gmm_logprob_bwd", ptr(z), ptr(mu_), ptr(ls_), ptr(ws_), ptr(g), ptr(gz), ptr(gp), ptr(ws), B, K, d,
+                dtype_code(z), stream(), n=2)
+        return gz, gp[:K * d].view(s_mu), gp[K * d:2 * K * d].view(s_ls), gp[2 * K * d:].view(s_ws)
+
+
+def gmm_logprob(z, mu, log_scale, weight_scores):
+    z, mu, log_scale, weight_scores = _promote(z, mu, log_scale, weight_scores)
+    return _GmmLogProb.apply(z, mu, log_scale, weight_scores)
+
+
+# ------------------------------------------------------------------ preprocessing transforms (f4), checkerboard (f2)
+class _Logit(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z, a0, beta, to_logit, want_ld):
+        z = z.contiguous()
+        B = z.shape[0]
+        n = z.numel() // max(B, 1)
+        out = torch.empty_like(z)
+        ld = torch.empty(B, dtype=z.dtype, device=z.device) if want_ld else None
+        _launch("vcnf_logit_fwd", ptr(z), ptr(out), ptr(ld), B, n, float(a0), float(beta), int(to_logit),
+                dtype_code(z), stream())
+        ctx.cfg = (float(a0), float(beta), int(to_logit), B, n)
+        ctx.save_for_backward(z)
+        if want_ld:
+            return out, ld
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy, gld=None):
+        (z,) = ctx.saved_tensors
+        a0, beta, to_logit, B, n = ctx.cfg
+        gy = gy.contiguous() if gy is not None else None
+        gld = gld.contiguous() if gld is not None else None
+        gz = torch.empty_like(z)
+        _launch("vcnf_logit_bwd", ptr(z), ptr(gy), ptr(gld), ptr(gz), B, n, a0, beta, to_logit, dtype_code(z), stream())
+        return gz, None, None, None, None
+
+
+def logit_transform(z, a0, beta, to_logit, want_logdet=True):
+    """to_logit: logit(a0 + beta z) (+ per-sample log-det); else (sigmoid(z) - a0) / beta."""
+    return _Logit.apply(z, a0, beta, to_logit, want_logdet)
+
+
+def axpb(x, a=1.0, b=0.0, noise=None, c=0.0, out=None):
+    """out = a x + b + c noise in one launch (no autograd; out may be x for the in-place Shift)."""
+    x = x if x.is_contiguous() else x.contiguous()
+    out = torch.empty_like(x) if out is None else out
+    assert out.is_contiguous() and out.shape == x.shape
+    noise = noise.contiguous() if noise is not None else None
+    _launch("vcnf_axpb", ptr(x), ptr(noise), ptr(out), x.numel(), float(a), float(b), float(c), dtype_code(x), stream())
+    return out
+
+
+_CB_PARITY = {}
+
+
+def _mid_parity(mid_shape, device):
+    key = (tuple(mid_shape), str(device))
+    if key not in _CB_PARITY:
+        par = torch.zeros(mid_shape if len(mid_shape) else (1,), dtype=torch.int64)
+        for d, size in enumerate(mid_shape):
+            shape = [1] * len(mid_shape)
+            shape[d] = size
+            par = par + torch.arange(size).view(shape)
+        _CB_PARITY[key] = (par % 2).to(torch.uint8).reshape(-1).contiguous().to(device)
+    return _CB_PARITY[key]
+
+
+class _Checkerboard(torch.autograd.Function):
+    """merge = False: z -> (z1, z2); merge = True: (z1, z2) -> z.  The adjoint is the opposite index map."""
+
+    @staticmethod
+    def forward(ctx, inv, merge, *ts):
+        if not merge:
+            z = ts[0].contiguous()
+            W = z.shape[-1]
+            half = z.shape[:-1] + (W // 2,)
+            z1, z2 = torch.empty(half, dtype=z.dtype, device=z.device), torch.empty(half, dtype=z.dtype, device=z.device)
+        else:
+            z1, z2 = ts[0].contiguous(), ts[1].contiguous()
+            W = 2 * z1.shape[-1]
+            z = torch.empty(z1.shape[:-1] + (W,), dtype=z1.dtype, device=z1.device)
+        B = z.shape[0]
+        mid = tuple(z.shape[1:-1])
+        M = math.prod(mid) if mid else 1
+        par = _mid_parity(mid, z.device)
+        _launch("vcnf_checkerboard", ptr(z), ptr(z1), ptr(z2), ptr(par), B, M, W, int(inv), int(merge), dtype_code(z),
+                stream())
+        ctx.cfg = (inv, merge)
+        return z if merge else (z1, z2)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, *gs):
+        inv, merge = ctx.cfg
+        if merge:
+            g1, g2 = _Checkerboard.apply(inv, False, gs[0])
+            return None, None, g1, g2
+        g1, g2 = gs
+        ref = g1 if g1 is not None else g2
+        g1 = g1 if g1 is not None else torch.zeros_like(ref)
+        g2 = g2 if g2 is not None else torch.zeros_like(ref)
+        return None, None, _Checkerboard.apply(inv, True, g1, g2)
+
+
+def checkerboard_split(z, inv):
+    if z.shape[-1] % 2:
+        raise ValueError("checkerboard split needs an even last dimension")
+    return _Checkerboard.apply(bool(inv), False, z)
+
+
+def checkerboard_merge(z1, z2, inv):
+    z1, z2 = _promote(z1, z2)
+    return _Checkerboard.apply(bool(inv), True, z1, z2)
