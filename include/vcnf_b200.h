@@ -203,7 +203,9 @@ int vcnf_lu_inverse(const void* lower_entries, const void* upper_entries, const 
  * A [M, K] (lda), C [M, N] (ldc), float32 only; act = ReLU when relu_in != 0 (pre-activation blocks,
  * resnet.py:49-55); bias / residual / mask may be NULL.  Forward: W = weight [N, K], sw_n = K, sw_k = 1.
  * Input gradient: A = grad-output [M, out], W = weight [out, in] read as [n = in, k = out]:
- * sw_n = 1, sw_k = in; mask = the saved pre-activation input.  K <= 128.  C must not alias A. */
+ * sw_n = 1, sw_k = in; mask = the saved pre-activation input.  K <= 128.  C must not alias A.
+ * relu_in bit 1 (value 2): W / bias were written by the preceding kernel on this stream (MADE's W * mask) -- the
+ * kernel then orders its W fetch after the programmatic-dependent-launch wait instead of overlapping it. */
 int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int64_t sw_n, int64_t sw_k,
                        const void* bias, const void* residual, int64_t ldr, const void* mask, int64_t ldm,
                        void* C, int64_t ldc, int64_t M, int N, int K, int relu_in, void* stream);
@@ -356,6 +358,15 @@ int vcnf_checkerboard(void* z, void* z1, void* z2, const uint8_t* mid_parity, in
  * (`ticket`: device uint32 [1], zero before the first call), so a captured launch replays correctly. */
 int vcnf_adam_flat(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n, double lr,
                    double beta1, double beta2, double eps, double weight_decay, int dtype, void* stream);
+
+/* The same step for training loops replayed from a CUDA graph / data-parallel loops: the learning rate is read
+ * from a device fp64 scalar (edits take effect on the next replay), gradients are multiplied by grad_scale first
+ * (1 / world_size after a summing all-reduce), and when `guard` (device scalar of guard_dtype, the step's loss) is
+ * NaN or Inf the whole update is skipped -- parameters, moments and the step counter keep their values -- which is
+ * what the reference's loops do on the host (`if ~(isnan(loss) | isinf(loss))`, runcred.py:249-250). */
+int vcnf_adam_flat_guarded(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n,
+                           const void* lr_dev, double beta1, double beta2, double eps, double weight_decay,
+                           double grad_scale, const void* guard, int guard_dtype, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

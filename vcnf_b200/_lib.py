@@ -62,6 +62,8 @@ _SIGNATURES = {
     "vcnf_logit_bwd": [_vp, _vp, _vp, _vp, _i64, _i32, _dbl, _dbl, _i32, _i32, _vp],
     "vcnf_axpb": [_vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _i32, _vp],
     "vcnf_checkerboard": [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
+    "vcnf_adam_flat_guarded": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _dbl, _dbl, _dbl, _dbl, _dbl, _vp, _i32, _i32,
+                               _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
 }
 _I64_RETURN = {

@@ -35,10 +35,24 @@ template <typename T, typename V, int W>
 __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(T* __restrict__ p, const T* __restrict__ g,
                                                                  T* __restrict__ m, T* __restrict__ v,
                                                                  float* step, unsigned* ticket, int64_t n, double lr,
-                                                                 double beta1, double beta2, double eps, double wd) {
+                                                                 double beta1, double beta2, double eps, double wd,
+                                                                 double grad_scale, const double* lr_dev,
+                                                                 const void* guard, int guard_dtype) {
   __shared__ T s_step_size, s_inv_sqrt_bc2;
   __shared__ float s_t;
+  __shared__ int s_skip;
   if (threadIdx.x == 0) {
+    // guard: a device scalar (the step's loss); a NaN / Inf there skips the whole update -- parameters, both
+    // moments and the step counter stay as they are (the reference's loops test the loss on the host before
+    // optimizer.step(), runcred.py:249-250; a replayed graph has no host in the loop)
+    int skip = 0;
+    if (guard) {
+      const double gv = guard_dtype == VCNF_F64 ? *static_cast<const double*>(guard)
+                                                : static_cast<double>(*static_cast<const float*>(guard));
+      skip = !(gv - gv == 0.0);
+    }
+    s_skip = skip;
+    if (lr_dev) lr = *lr_dev;
     const float t = *step + 1.f;
     const double bc1 = 1.0 - pow(beta1, static_cast<double>(t));
     const double bc2 = 1.0 - pow(beta2, static_cast<double>(t));
@@ -47,7 +61,9 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(T* __restrict__
     s_t = t;
   }
   __syncthreads();
+  if (s_skip) return;
   AdamCoef<T> c;
+  const T gsc = static_cast<T>(grad_scale);
   c.b1 = static_cast<T>(beta1);
   c.b2 = static_cast<T>(beta2);
   c.omb1 = static_cast<T>(1.0 - beta1);
@@ -68,13 +84,14 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(T* __restrict__
     T* mp = reinterpret_cast<T*>(&M);
     T* vp = reinterpret_cast<T*>(&Vv);
 #pragma unroll
-    for (int k = 0; k < W; ++k) adam_one(pp[k], gp[k], mp[k], vp[k], c, step_size, isb);
+    for (int k = 0; k < W; ++k) adam_one(pp[k], gp[k] * gsc, mp[k], vp[k], c, step_size, isb);
     pv[i] = P;
     mv[i] = M;
     vv[i] = Vv;
   }
   if (blockIdx.x == 0) {                                // ragged tail (n not a multiple of the vector width)
-    for (int64_t i = nv * W + threadIdx.x; i < n; i += kAdamThreads) adam_one(p[i], g[i], m[i], v[i], c, step_size, isb);
+    for (int64_t i = nv * W + threadIdx.x; i < n; i += kAdamThreads)
+      adam_one(p[i], g[i] * gsc, m[i], v[i], c, step_size, isb);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -92,9 +109,12 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(T* __restrict__
 
 using namespace vcnf;
 
-extern "C" int vcnf_adam_flat(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n, double lr,
-                              double beta1, double beta2, double eps, double weight_decay, int dtype, void* stream) {
-  if (n < 0 || (dtype != VCNF_F32 && dtype != VCNF_F64) || !step || !ticket) return VCNF_E_BADARG;
+static int adam_launch(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n, double lr,
+                       double beta1, double beta2, double eps, double weight_decay, double grad_scale,
+                       const void* lr_dev, const void* guard, int guard_dtype, int dtype, void* stream) {
+  if (n < 0 || (dtype != VCNF_F32 && dtype != VCNF_F64) || !step || !ticket ||
+      (guard && guard_dtype != VCNF_F32 && guard_dtype != VCNF_F64))
+    return VCNF_E_BADARG;
   if (n == 0) return 0;
   if (!p || !g || !m || !v) return VCNF_E_BADARG;
   const uintptr_t bits = reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
@@ -110,10 +130,26 @@ extern "C" int vcnf_adam_flat(void* p, const void* g, void* m, void* v, void* st
   if (dtype == VCNF_F32)
     adam_flat_kernel<float, float4, 4><<<static_cast<unsigned>(blocks), kAdamThreads, 0, st>>>(
         static_cast<float*>(p), static_cast<const float*>(g), static_cast<float*>(m), static_cast<float*>(v),
-        static_cast<float*>(step), static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay);
+        static_cast<float*>(step), static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay, grad_scale,
+        static_cast<const double*>(lr_dev), guard, guard_dtype);
   else
     adam_flat_kernel<double, double2, 2><<<static_cast<unsigned>(blocks), kAdamThreads, 0, st>>>(
         static_cast<double*>(p), static_cast<const double*>(g), static_cast<double*>(m), static_cast<double*>(v),
-        static_cast<float*>(step), static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay);
+        static_cast<float*>(step), static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay, grad_scale,
+        static_cast<const double*>(lr_dev), guard, guard_dtype);
   return launch_status();
+}
+
+extern "C" int vcnf_adam_flat(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n, double lr,
+                              double beta1, double beta2, double eps, double weight_decay, int dtype, void* stream) {
+  return adam_launch(p, g, m, v, step, ticket, n, lr, beta1, beta2, eps, weight_decay, 1.0, nullptr, nullptr, 0, dtype,
+                     stream);
+}
+
+extern "C" int vcnf_adam_flat_guarded(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n,
+                                      const void* lr_dev, double beta1, double beta2, double eps, double weight_decay,
+                                      double grad_scale, const void* guard, int guard_dtype, int dtype, void* stream) {
+  if (!lr_dev) return VCNF_E_BADARG;
+  return adam_launch(p, g, m, v, step, ticket, n, 0.0, beta1, beta2, eps, weight_decay, grad_scale, lr_dev, guard,
+                     guard_dtype, dtype, stream);
 }

@@ -662,6 +662,7 @@ struct Args2 {
   float* C; int64_t ldc;
   int64_t M; int N; int K;
   int relu_in;
+  int w_dynamic;      // W was written by a preceding kernel of this stream (MADE's W * mask): wait before reading it
   int n_tiles;        // ceil(N / 128) column slices
   int ctas_per_ntile; // persistent CTAs sharing one column slice
   int use_tma;        // A is 16 B aligned with a 16 B multiple row pitch: stages arrive by tensor-map TMA
@@ -900,6 +901,10 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
     const bool o_ok = o_loc < NT;
     const int o = n0 + o_loc;
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    // W and bias are normally parameters (no kernel of this chain writes them), so they are fetched BEFORE the
+    // dependency wait and overlap the previous launch's tail.  A weight produced by the preceding kernel (the masked
+    // weight W * mask of nets/made.py) is only guaranteed visible after griddepcontrol.wait.
+    if (a.w_dynamic) pdl_wait();
     {
       const float* wrow = a.W + static_cast<int64_t>(o_ok ? o : n0) * a.sw_n;
       // 32 x 32 transpose tile per warp, xor-swizzled; aliases epilogue tile 2, which is first requested
@@ -1650,7 +1655,7 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
     b.residual = static_cast<const float*>(residual); b.ldr = ldr;
     b.mask = static_cast<const float*>(mask); b.ldm = ldm;
     b.C = static_cast<float*>(C); b.ldc = ldc;
-    b.M = M; b.N = N; b.K = K; b.relu_in = relu_in;
+    b.M = M; b.N = N; b.K = K; b.relu_in = relu_in & 1; b.w_dynamic = (relu_in >> 1) & 1;
     b.n_tiles = (N + 127) / 128;
     const int64_t m_tiles2 = (M + gemm::v2::kTN - 1) / gemm::v2::kTN;
     int cpt2 = sms / b.n_tiles;
@@ -1693,7 +1698,7 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
   a.residual = static_cast<const float*>(residual); a.ldr = ldr;
   a.mask = static_cast<const float*>(mask); a.ldm = ldm;
   a.C = static_cast<float*>(C); a.ldc = ldc;
-  a.M = M; a.N = N; a.K = K; a.relu_in = relu_in;
+  a.M = M; a.N = N; a.K = K; a.relu_in = relu_in & 1;
   { const char* e = getenv("VCNF_GEMM_DEBUG"); a.dbg = e ? atoi(e) : 0; }
   a.n_tiles = (N + gemm::kBN - 1) / gemm::kBN;
   a.KP = (K + gemm::kBK - 1) / gemm::kBK * gemm::kBK;

@@ -388,8 +388,40 @@ class _SmallLinear(torch.autograd.Function):
         return gx, gW, gb, None, None, None
 
 
+SMALL_LINEAR_MAX = 64      # widest per-row map of vcnf_small_linear (W in shared memory, one row per thread group)
+
+
+def _wide_linear(x, W, bias, in_idx, out_idx, sub_bias_first):
+    """The same map for D > 64 (LULinearPermute on wide tabular data, Glow levels with > 64 channels): a dense
+    contraction, so it runs on the conditioner GEMM (vcnf_linear_tf32x3, fp32) with the permutations as column
+    gathers; fp64 operands use the library GEMM (no fp64 tensor-core path)."""
+    D = W.shape[0]
+    img = x.dim() == 4
+    if img:
+        B, _, H, Wd = x.shape
+        rows = im2col(x, "nchw", B, D, H, Wd, 1) if x.dtype == torch.float32 else x.permute(0, 2, 3, 1).reshape(-1, D)
+    else:
+        rows = x
+    if in_idx is not None:
+        rows = gather_cols(rows, in_idx) if rows.dtype in (torch.float32, torch.float64) else rows[:, in_idx.long()]
+    b_eff = bias
+    if sub_bias_first and bias is not None:
+        b_eff = -(W @ bias)                                        # W (x - b) = W x - W b
+    if rows.dtype == torch.float32 and linear_supported(rows, W):
+        out = linear(rows, W, b_eff)
+    else:
+        out = torch.nn.functional.linear(rows, W, b_eff)
+    if out_idx is not None:                                        # out[:, out_idx[o]] = v[:, o]
+        out = gather_cols(out, torch.argsort(out_idx.long()).to(torch.int32))
+    if img:
+        out = out.reshape(B, H, Wd, D).permute(0, 3, 1, 2).contiguous()
+    return out
+
+
 def small_linear(x, W, bias=None, in_idx=None, out_idx=None, sub_bias_first=False):
     x, W, bias = _promote(x, W, bias)
+    if W.shape[0] > SMALL_LINEAR_MAX:
+        return _wide_linear(x, W, bias, in_idx, out_idx, sub_bias_first)
     return _SmallLinear.apply(x, W, bias, in_idx, out_idx, sub_bias_first)
 
 
@@ -560,6 +592,10 @@ class _Linear(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, residual, relu_in, pad_out):
+        # anything but the Parameter objects themselves may have been written by a kernel earlier on this stream
+        # (MADE's W * mask, a re-laid convolution weight): the GEMM then fetches W after its dependency wait
+        is_param = lambda t: t is None or isinstance(t, torch.nn.Parameter)
+        w_dyn = 0 if (is_param(weight) and is_param(bias)) else 2
         x, weight = _rows(x), weight.contiguous()
         M, K = x.shape
         N = weight.shape[0]
@@ -572,8 +608,9 @@ class _Linear(torch.autograd.Function):
             r_ptr, r_ld = (ptr(res_), res_.stride(0) if res_ is not None else 0) if first else (ptr(y), y.stride(0))
             _launch("vcnf_linear_tf32x3", ptr(x) + 4 * k0, x.stride(0), ptr(weight) + 4 * k0, K, 1,
                     ptr(bias_) if first else None, r_ptr, r_ld, None, 0,
-                    ptr(y), y.stride(0), M, N, min(K, k0 + KSLICE) - k0, int(relu_in), stream())
+                    ptr(y), y.stride(0), M, N, min(K, k0 + KSLICE) - k0, int(relu_in) | w_dyn, stream())
         ctx.relu_in = bool(relu_in)
+        ctx.w_dyn = w_dyn
         ctx.has_bias, ctx.has_res = bias is not None, residual is not None
         ctx.save_for_backward(x, weight)
         return y
@@ -593,7 +630,7 @@ class _Linear(torch.autograd.Function):
             # gx[m, k] = [x > 0] * sum_n gy[m, n] W[n, k]  : W read as [n' = k, k' = n] -> sw_n = 1, sw_k = K
             if N <= 128:
                 _launch("vcnf_linear_tf32x3", ptr(gy), ldg, ptr(weight), 1, K, None, None, 0,
-                        ptr(x) if ctx.relu_in else None, ldx, ptr(gx), ldo, M, K, N, 0, stream())
+                        ptr(x) if ctx.relu_in else None, ldx, ptr(gx), ldo, M, K, N, ctx.w_dyn, stream())
             else:
                 # out_features > 128 (the 3K-1 wide head): reduce over column slices of <= 128
                 first = True
@@ -602,7 +639,7 @@ class _Linear(torch.autograd.Function):
                     last = n1 == N
                     _launch("vcnf_linear_tf32x3", ptr(gy) + 4 * n0, ldg, ptr(weight) + 4 * n0 * K, 1, K, None,
                             None if first else ptr(gx), ldo, ptr(x) if (ctx.relu_in and last and first) else None, ldx,
-                            ptr(gx), ldo, M, K, n1 - n0, 0, stream())
+                            ptr(gx), ldo, M, K, n1 - n0, ctx.w_dyn, stream())
                     first = False
                 if ctx.relu_in and N > 128:
                     gx = gx * (x > 0)

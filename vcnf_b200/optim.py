@@ -46,6 +46,26 @@ class FlatAdam(torch.optim.Optimizer):
         self.exp_avg_sq = torch.zeros_like(self.flat_p)
         self.steps = torch.zeros(1, dtype=torch.float32, device=p0.device)
         self._ticket = torch.zeros(1, dtype=torch.int32, device=p0.device)
+        # the learning rate lives in a device scalar the kernel reads, so a step replayed from a CUDA graph follows
+        # later edits of param_groups[0]["lr"] (sync_hyper() is called by step() and by GraphedTrainStep)
+        self._lr_dev = torch.full((1,), float(lr), dtype=torch.float64, device=p0.device)
+        self._lr_host = float(lr)
+        self.guard = None          # device scalar (the loss): a non-finite value skips the update (runcred.py:249-250)
+        self.grad_scale = 1.0      # folded into the kernel: 1 / world_size after a summing all-reduce
+        self._skip = torch.full((1,), float("nan"), dtype=torch.float32, device=p0.device)
+        self.frozen = False        # True: every step is skipped (GraphedTrainStep's warm-up iterations)
+
+    def add_param_group(self, group):
+        if getattr(self, "param_groups", None):
+            raise ValueError("FlatAdam keeps ONE parameter group (one flat buffer, one set of hyper-parameters)")
+        super().add_param_group(group)
+
+    def sync_hyper(self):
+        """Push a changed learning rate to the device scalar (outside graph capture)."""
+        lr = float(self.param_groups[0]["lr"])
+        if lr != self._lr_host and not torch.cuda.is_current_stream_capturing():
+            self._lr_dev.fill_(lr)
+            self._lr_host = lr
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -54,10 +74,15 @@ class FlatAdam(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         g = self.param_groups[0]
+        self.sync_hyper()
         self.bucket.collect()                 # no-op when the gradients already are the bucket's views
-        ops._launch("vcnf_adam_flat", ptr(self.flat_p), ptr(self.bucket.flat), ptr(self.exp_avg),
-                    ptr(self.exp_avg_sq), ptr(self.steps), ptr(self._ticket), self.bucket.total, float(g["lr"]),
+        guard = self._skip if self.frozen else self.guard
+        if guard is not None and guard.dtype not in (torch.float32, torch.float64):
+            guard = guard.float()
+        ops._launch("vcnf_adam_flat_guarded", ptr(self.flat_p), ptr(self.bucket.flat), ptr(self.exp_avg),
+                    ptr(self.exp_avg_sq), ptr(self.steps), ptr(self._ticket), self.bucket.total, ptr(self._lr_dev),
                     float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), float(g["weight_decay"]),
+                    float(self.grad_scale), ptr(guard), dtype_code(guard) if guard is not None else 0,
                     dtype_code(self.flat_p), stream())
         return loss
 

@@ -87,13 +87,42 @@ class GradBucket:
         if missing:
             torch._foreach_zero_(missing)
 
-    def allreduce_mean(self, world=None):
+    def allreduce_mean(self, world=None, scale=True):
+        """Sum the bucket over the ranks; scale=False leaves the division by `world` to the consumer
+        (optim.FlatAdam folds it into its kernel: grad_scale = 1 / world)."""
         if self.flat is None or not dist.is_initialized():
             return
         world = dist.get_world_size() if world is None else world
         if world > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-            self.flat.div_(world)
+            if scale:
+                self.flat.div_(world)
+
+
+def sync_model(model, src=0):
+    """Make every rank start from rank `src`'s parameters AND buffers (initial weights, the random permutations of
+    Permute / LULinearPermute, feature masks, ActNorm flags): ranks seeded differently would otherwise train
+    different models whose gradients are averaged.  In-place broadcasts, so views (optim.FlatAdam's flat buffer) stay
+    valid.  No-op for a single process."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    want_cuda = dist.get_backend() == "nccl"
+    for t in list(model.parameters()) + list(model.buffers()):
+        if t.numel() and t.is_cuda == want_cuda:       # host-side flags (ActNorm's init marker) are set per process
+            dist.broadcast(t.data, src)
+
+
+def check_equal_shards(n_local):
+    """Data-parallel steps average the per-rank mean losses with equal weight; that is the global-batch gradient
+    only when every rank holds the same number of rows.  Raises if the shard sizes differ."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    sizes = torch.tensor([n_local, -n_local], dtype=torch.int64, device=dev)
+    dist.all_reduce(sizes, op=dist.ReduceOp.MAX)
+    if int(sizes[0]) != -int(sizes[1]):
+        raise ValueError("data-parallel forward_kld needs equal shards on every rank (got between %d and %d rows): "
+                         "drop or pad the remainder" % (-int(sizes[1]), int(sizes[0])))
 
 
 def sync_actnorm_init(model, src=0):
@@ -152,8 +181,25 @@ class GraphedTrainStep:
         self.loss_fn = loss_fn if loss_fn is not None else (lambda m, x: m.forward_kld(x))
         self.x = example.clone()
         self.graph, self.loss, self.capture_error = None, None, None
+        w = self._world()
+        if w > 1:
+            sync_model(model)                 # same weights, permutations and masks on every rank
+            check_equal_shards(len(example))
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
+        # The warm-up iterations must not train: parameters, moments and the step counter are what the caller built
+        # when the first real step runs.  FlatAdam skips its update (`frozen`); any other optimiser runs with lr = 0
+        # and gets its state back afterwards.  (Data-dependent ActNorm initialisation still happens here, on the
+        # example batch, exactly as it would in the first real step.)
+        flat = hasattr(optimizer, "frozen")
+        saved = None
+        if flat:
+            optimizer.frozen = True
+        else:
+            import copy
+            saved = (copy.deepcopy(optimizer.state_dict()), [g["lr"] for g in optimizer.param_groups])
+            for g in optimizer.param_groups:
+                g["lr"] = 0.0 * g["lr"] if not torch.is_tensor(g["lr"]) else torch.zeros_like(g["lr"])
         # forward_kld dequantises categorical columns INTO its argument (core.py:54): every run starts from a fresh
         # copy of the batch, and the model sees a detached alias so that no autograd history sticks to the static input
         with torch.cuda.stream(side):
@@ -161,6 +207,12 @@ class GraphedTrainStep:
                 self.x.copy_(example)
                 self._eager()
         torch.cuda.current_stream().wait_stream(side)
+        if flat:
+            optimizer.frozen = False
+        else:
+            optimizer.load_state_dict(saved[0])
+            for g, lr in zip(optimizer.param_groups, saved[1]):
+                g["lr"] = lr
         self.x.copy_(example)
         torch.cuda.synchronize()
         try:
@@ -172,18 +224,29 @@ class GraphedTrainStep:
             self.capture_error = _after_failed_capture(exc)
             self.graph = None
 
+    def _world(self):
+        return self.world if self.world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
+
     def _eager(self):
         self.bucket.begin()
         loss = self.loss_fn(self.model, self.x.detach())
         loss.backward()
-        world = self.world if self.world is not None else (dist.get_world_size() if dist.is_initialized() else 1)
+        world = self._world()
+        flat = hasattr(self.opt, "grad_scale")
         if world > 1:
             self.bucket.collect()
-            self.bucket.allreduce_mean(world)
+            self.bucket.allreduce_mean(world, scale=not flat)     # FlatAdam divides by `world` inside its kernel
+        if flat:
+            # a NaN / Inf loss must not reach the parameters or the moments (runcred.py:249-250 tests it on the
+            # host; a replayed graph cannot): the optimiser kernel reads the loss and skips the update
+            self.opt.guard = loss.detach()
+            self.opt.grad_scale = 1.0 / world
         self.opt.step()
         return loss
 
     def __call__(self, x):
+        if hasattr(self.opt, "sync_hyper"):
+            self.opt.sync_hyper()             # a changed learning rate reaches the replayed kernel
         self.x.copy_(x, non_blocking=True)
         if self.graph is None:
             return self._eager()
