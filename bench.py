@@ -7,10 +7,14 @@ LULinearPermute(29)], base DiagGaussian(29), batch 65 536 per GPU, fp32, Adam(1e
 = forward_kld + backward + (gradient all-reduce for N > 1) + optimizer step on one synthetic batch
 x = 1.5 * randn(B, 29).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config cfg2]
 
 Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port of the reference
-algorithm (oracle/, torch CPU, all host threads) on a bounded sample of the same workload.
+algorithm (oracle/, torch CPU, all host threads) on the same workload (bounded number of steps).
+
+`--config {cfg1,cfg2,cfg3a,cfg3b,cfg4,cfg5}` selects another BASELINE.json configuration for the whole
+line; the default line (cfg 2) additionally carries a `configs` object with a short measurement of each of the
+others (train step and, where the model samples, sample()), so that one driver run records all of them.
 """
 import argparse
 import json
@@ -48,20 +52,33 @@ def synth_batch(n, seed):
 
 
 # --------------------------------------------------------------------------------- CPU arm
+def _cpu_rows():
+    """Rows per CPU step: the full 65 536-row batch when the host has the memory for the oracle's autograd graph
+    (~0.6 MB per row over 16 layers), else a quarter of it."""
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 0
+    return BATCH if avail > 64 * (1 << 30) else (BATCH // 4 if avail > 20 * (1 << 30) else CPU_SAMPLE)
+
+
 def cpu_reference_run(steps, warmup, sample=CPU_SAMPLE):
-    """The reference algorithm's CPU path: oracle port, all host threads."""
+    """The reference algorithm's CPU path: oracle port, all host threads.  Warm-up steps run on 1 024 rows (thread pool,
+    allocator); the timed steps on `sample` rows of the bench batch."""
     import oracle
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(0)
     model = build_model(oracle)
     opt = torch.optim.Adam(model.parameters(), lr=1e-3)
-    x = synth_batch(sample, 1234)
+    x = synth_batch(BATCH, 1234)[:sample]
     times = []
     for i in range(warmup + steps):
+        xb = x[:1024] if i < warmup else x
         t0 = time.perf_counter()
         opt.zero_grad(set_to_none=True)
-        loss = model.forward_kld(x.clone())
+        loss = model.forward_kld(xb.clone())
         loss.backward()
         opt.step()
         dt = time.perf_counter() - t0
@@ -69,9 +86,9 @@ def cpu_reference_run(steps, warmup, sample=CPU_SAMPLE):
             times.append(dt)
     total = sum(times)
     return {"value": sample * len(times) / total, "unit": "samples/s", "cores": cores, "kind": "port",
-            "sample": "%d of the %d-row batch per step, %d timed steps after %d warm-up, torch CPU %d threads"
-                      % (sample, BATCH, len(times), warmup, torch.get_num_threads()),
-            "ms_per_step": 1e3 * total / len(times), "loss": float(loss.detach())}
+            "sample": "%d of the %d-row batch per step, %d timed step(s) after %d warm-up step(s) on 1024 rows, "
+                      "torch CPU %d threads" % (sample, BATCH, len(times), warmup, torch.get_num_threads()),
+            "rows_per_step": sample, "ms_per_step": 1e3 * total / len(times), "loss": float(loss.detach())}
 
 
 # --------------------------------------------------------------------------------- clocks
@@ -220,6 +237,323 @@ def kernel_roofline(model, dev, flush):
             "other_kernels": {k: v for k, v in out.items() if k != dom_name}}
 
 
+# --------------------------------------------------------------------------------- the other BASELINE configurations
+CFG4_CATS = (1, 3, 4, 5, 6, 7, 8, 9, 13, 14)
+CFG4_LEVELS = (9, 16, 16, 7, 15, 6, 5, 2, 42, 2)
+
+
+def config_spec(name, nf):
+    """SURVEY.md 8d instantiation of BASELINE.json `configs`: dict(build, batch, data(n, seed), loss_fn | None,
+    optimizer(params), dtype, workload, sample_batch | None, setup)."""
+    from cases import build_cfg4_small, cfg4_data, build_glow_small
+    if name == "cfg1":
+        def build():
+            flows = []
+            for _ in range(16):
+                flows += [nf.flows.AffineCouplingBlock(nf.nets.MLP([1, 32, 32, 2], init_zeros=True)),
+                          nf.flows.Permute(2, mode="swap")]
+            return nf.NormalizingFlow(nf.distributions.DiagGaussian(2), flows, nf.distributions.TwoMoons())
+        return dict(build=build, batch=1024, data=lambda n, seed: torch.zeros(1), dtype="f32",
+                    loss_fn=lambda m, x, B=1024: m.reverse_kld(num_samples=B), lr=1e-4, wd=0.0, sample_batch=65536,
+                    workload="cfg1 README 2-D Real NVP 16x[AffineCouplingBlock(MLP[1,32,32,2])+Permute swap], TwoMoons, "
+                             "reverse_kld batch 1024/GPU, fp32")
+    if name in ("cfg3a", "cfg3b"):
+        def build():
+            flows = []
+            for _ in range(8):
+                if name == "cfg3a":
+                    flows += [nf.flows.AutoregressiveRationalQuadraticSpline(64, 2, 256), nf.flows.LULinearPermute(64)]
+                else:
+                    flows += [nf.flows.Reverse(nf.flows.MaskedAffineAutoregressive(64, 256)),
+                              nf.flows.Permute(64, mode="shuffle")]
+            return nf.NormalizingFlow(nf.distributions.DiagGaussian(64, trainable=False), flows,
+                                      categoricals=[], catlevels=[], catvdeqs=[])
+        layer = "AutoregressiveRQS(64,2,256)+LULinearPermute(64)" if name == "cfg3a" else \
+            "Reverse(MaskedAffineAutoregressive(64,256))+Permute(64,shuffle)"
+        return dict(build=build, batch=32768, dtype="f32", loss_fn=None, lr=1e-3, wd=0.0, sample_batch=32768,
+                    data=lambda n, seed: 1.5 * torch.randn(n, 64, generator=torch.Generator().manual_seed(seed)),
+                    workload="%s 8x[%s] forward_kld train, batch 32768/GPU (262144 over 8), fp32" % (name, layer))
+    if name == "cfg4":
+        return dict(build=lambda: build_cfg4_small(nf, d=15, cats=CFG4_CATS, levels=CFG4_LEVELS, n_main=12,
+                                                   n_vdeq=8).double(),
+                    batch=2048, dtype="f64", loss_fn=None, lr=1e-4, wd=1e-6, sample_batch=None,
+                    data=lambda n, seed: cfg4_data(n=n, d=15, cats=CFG4_CATS, levels=CFG4_LEVELS, seed=seed),
+                    workload="cfg4 runadultvdeq1ft recipe: 10 categorical columns x VariationalDequantization(8x[ActNorm,"
+                             "MaskedAffineFlow(MLP[1,4,1]),ActNorm]) + 12x[MaskedAffineFlow(MLP[15,30,15]x2),ActNorm(15)], "
+                             "GaussianMixture(100,15), fp64 model / fp32 batch 2048/GPU, forward_kld train")
+    if name == "cfg5":
+        def setup():
+            from vcnf_b200.nets import cnn
+            cnn.set_precision("bf16")
+        return dict(build=lambda: build_glow_small(nf, L=3, K=16, hidden=256, in_shape=(3, 32, 32), classes=10),
+                    batch=128, dtype="bf16 conv conditioner (fp32 accumulation), fp32 bijectors", loss_fn="xy",
+                    lr=1e-3, wd=1e-5, sample_batch=None, setup=setup, optimizer="adamax",
+                    data=lambda n, seed: (torch.rand(n, 3, 32, 32, generator=torch.Generator().manual_seed(seed))
+                                          * 255 / 256 + torch.rand(n, 3, 32, 32,
+                                                                   generator=torch.Generator().manual_seed(seed + 1)) / 256),
+                    workload="cfg5 Glow multiscale L=3 K=16 hidden 256 (example/glow.ipynb), 3x32x32, 10 classes, "
+                             "forward_kld train, batch 128/GPU, ConvNet2d on tcgen05 bf16 implicit-GEMM kernels")
+    raise ValueError(name)
+
+
+def measure_config(name, dev, world, rank, steps, warmup, flush, batch=None, with_e2e=True):
+    """Train-step (and sample()) rate of one configuration, the step replayed from a CUDA graph."""
+    import vcnf_b200 as nf
+    from vcnf_b200 import ops, parallel
+    import torch.distributed as dist
+    spec = config_spec(name, nf)
+    if spec.get("setup"):
+        spec["setup"]()
+    B = batch or spec["batch"]
+    torch.manual_seed(0)
+    model = spec["build"]().to(dev)
+    x_host = spec["data"](B, 1234 + rank)
+    x_host = x_host.pin_memory() if x_host.numel() > 1 else x_host
+    x_dev = x_host.to(dev)
+    loss_fn = spec["loss_fn"]
+    if name == "cfg1":
+        loss_fn = lambda m, x, B=B: m.reverse_kld(num_samples=B)       # noqa: E731
+    if loss_fn == "xy":
+        y = torch.randint(0, 10, (B,), generator=torch.Generator().manual_seed(99 + rank)).to(dev)
+        loss_fn = lambda m, xb, y=y: m.forward_kld(xb, y)              # noqa: E731
+    if spec.get("optimizer") == "adamax":
+        # data-dependent ActNorm initialisation first (one eager step's forward), then the capturable optimiser
+        with torch.no_grad():
+            loss_fn(model, x_dev.clone())
+        opt = torch.optim.Adamax(model.parameters(), lr=spec["lr"], weight_decay=spec["wd"], capturable=True)
+        bucket = parallel.GradBucket(model.parameters())
+        opt_name = "torch Adamax(capturable)"
+    else:
+        if name == "cfg4":
+            with torch.no_grad():
+                model.forward_kld(x_dev.clone())                       # ActNorm initialisation (first call)
+        opt = nf.optim.FlatAdam(model.parameters(), lr=spec["lr"], weight_decay=spec["wd"])
+        bucket = opt.bucket
+        opt_name = "Adam, flat buffers (vcnf_adam_flat_guarded)"
+    step = parallel.GraphedTrainStep(model, opt, bucket, x_dev, world=world, loss_fn=loss_fn)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(max(warmup, 3)):
+        step(x_dev)
+    barrier()
+    l0 = ops.LAUNCHES
+    step._eager()
+    per_step = ops.LAUNCHES - l0
+    barrier()
+    evs = []
+    for _ in range(steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        loss = step(x_dev)
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t)
+    out = {"workload": spec["workload"] if batch is None else spec["workload"] + " [batch %d/GPU]" % B,
+           "batch_per_gpu": B, "ms_per_step": total_ms / steps, "value": world * B * steps / (total_ms * 1e-3),
+           "unit": "samples/s", "steps": steps, "gpu_launches_per_step": per_step, "optimizer": opt_name,
+           "cuda_graph": step.graph is not None, "cuda_graph_error": step.capture_error, "dtype": spec["dtype"],
+           "loss": float(loss)}
+    if with_e2e:
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            xb = x_host.to(dev, non_blocking=True)
+            step(xb).item()
+        barrier()
+        t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["e2e"] = {"value": world * B * steps / float(t), "unit": "samples/s",
+                      "h2d_bytes_per_step": int(x_host.numel() * x_host.element_size()) if x_host.numel() > 1 else 0,
+                      "d2h_bytes_per_step": 4}
+    if spec.get("sample_batch"):
+        n = spec["sample_batch"]
+        draw = parallel.GraphedSampler(model, n)
+        for _ in range(2):
+            draw()
+        torch.cuda.synchronize()
+        reps = 5
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            z_s, lq_s = draw()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        out["sample"] = {"value": world * n / (ms * 1e-3), "unit": "samples/s", "batch": n, "ms_per_draw": ms,
+                         "cuda_graph": draw.graph is not None, "finite": bool(torch.isfinite(z_s).all())}
+        del draw
+    del step, opt, bucket, model
+    torch.cuda.empty_cache()
+    return out
+
+
+def extra_kernel_rooflines(dev, flush):
+    """HBM roofline of the affine family, the per-row linear maps and the optimiser kernel at their configuration
+    shapes (SURVEY.md 8d algorithmic bytes), straight through the C ABI, CUDA-event timed after an L2 flush."""
+    from vcnf_b200 import _lib, ops
+    from vcnf_b200._lib import ptr
+    peak, _ = _peak()
+    st = lambda: torch.cuda.current_stream().cuda_stream       # noqa: E731
+    out = {}
+
+    def add(name, fn, bytes_per_launch, note=None):
+        ms = _time_launches(fn, flush, reps=10)
+        ach = bytes_per_launch / (ms * 1e-3) / 1e9
+        out[name] = {"ms": ms, "achieved": ach, "frac": ach / peak, "unit": "GB/s", "bytes_per_launch": bytes_per_launch}
+        if note:
+            out[name]["note"] = note
+    # K1 affine coupling block, cfg 1 rows at the roofline-meaningful batch 2^20: 28 B / sample fwd, 52 B bwd
+    B = 1 << 20
+    z, prm = torch.randn(B, 2, device=dev), 0.1 * torch.randn(B, 2, device=dev)
+    o, ld, gz, gp = torch.empty_like(z), torch.empty(B, device=dev), torch.empty_like(z), torch.empty_like(prm)
+    add("coupling_kernel<fwd> (vcnf_affine_coupling_fwd, cfg 1, B = 2^20)",
+        lambda: _lib.call("vcnf_affine_coupling_fwd", ptr(z), ptr(prm), ptr(o), ptr(ld), B, 2, 1, 1, 1, 0, 0, 0, 0, st()),
+        28 * B)
+    add("coupling_kernel<bwd> (vcnf_affine_coupling_bwd, cfg 1, B = 2^20)",
+        lambda: _lib.call("vcnf_affine_coupling_bwd", ptr(z), ptr(prm), ptr(o), ptr(ld), ptr(gz), ptr(gp), B, 2, 1, 1, 1,
+                          0, 0, 0, 0, st()), 52 * B)
+    # K2 masked affine, cfg 4 main flow (d = 15, fp64) at B = 65536: s (4 D + 1) fwd, s (7 D + 1) bwd
+    B, n = 65536, 15
+    z = torch.randn(B, n, device=dev, dtype=torch.float64)
+    sc, tr = 0.1 * torch.randn_like(z), torch.randn_like(z)
+    mask = (torch.arange(n, device=dev) % 2).double()
+    o, ld = torch.empty_like(z), torch.empty(B, device=dev, dtype=torch.float64)
+    gz, gs, gt = torch.empty_like(z), torch.empty_like(z), torch.empty_like(z)
+    add("masked_affine_kernel<fwd> (vcnf_masked_affine_fwd, cfg 4, d = 15 fp64, B = 65536)",
+        lambda: _lib.call("vcnf_masked_affine_fwd", ptr(z), ptr(mask), ptr(sc), ptr(tr), ptr(o), ptr(ld), B, n, 1, 1, st()),
+        8 * (4 * n + 1) * B)
+    add("masked_affine_kernel<bwd> (vcnf_masked_affine_bwd)",
+        lambda: _lib.call("vcnf_masked_affine_bwd", ptr(z), ptr(mask), ptr(sc), ptr(tr), ptr(o), ptr(ld), ptr(gz), ptr(gs),
+                          ptr(gt), B, n, 1, 1, st()), 8 * (7 * n + 1) * B)
+    # K3 ActNorm (d = 15 fp64): s 2 D fwd, s 3 D bwd (+ parameter-gradient reduce)
+    s_, t_ = torch.randn(n, device=dev, dtype=torch.float64) * 0.1, torch.randn(n, device=dev, dtype=torch.float64)
+    gs_, gt_ = torch.empty_like(s_), torch.empty_like(t_)
+    ws = torch.empty(_lib.query("vcnf_const_affine_bwd_workspace", n, 1), dtype=torch.uint8, device=dev)
+    add("const_affine_kernel (vcnf_const_affine_fwd, ActNorm(15) fp64, B = 65536)",
+        lambda: _lib.call("vcnf_const_affine_fwd", ptr(z), ptr(s_), ptr(t_), ptr(o), B, n, 1, 1, 1, st()), 8 * 2 * n * B)
+    add("const_affine_bwd_kernel + reduce (vcnf_const_affine_bwd)",
+        lambda: _lib.call("vcnf_const_affine_bwd", ptr(z), ptr(s_), ptr(t_), ptr(o), ptr(gz), ptr(gs_), ptr(gt_), ptr(ws),
+                          B, n, 1, 1, 1, st()), 8 * 3 * n * B)
+    # K10 LULinearPermute rows (cfg 2: D = 29 fp32, B = 65536): s (2 D + 1) fwd, s 3 D bwd
+    B, n = BATCH, D
+    x, W = torch.randn(B, n, device=dev), torch.randn(n, n, device=dev) / 5
+    bias, y, gx = torch.randn(n, device=dev), torch.empty(B, n, device=dev), torch.empty(B, n, device=dev)
+    perm = torch.randperm(n, device=dev).to(torch.int32)
+    gW, gb = torch.empty_like(W), torch.empty_like(bias)
+    ws2 = torch.empty(_lib.query("vcnf_small_linear_bwd_workspace", n, 0), dtype=torch.uint8, device=dev)
+    add("small_linear_rows_kernel (vcnf_small_linear, LULinearPermute(29), B = 65536)",
+        lambda: _lib.call("vcnf_small_linear", ptr(x), ptr(y), ptr(W), ptr(bias), ptr(perm), None, B, n, 1, 0, 0, st()),
+        4 * (2 * n + 1) * B)
+    add("small_linear_bwd_kernel + reduce (vcnf_small_linear_bwd)",
+        lambda: _lib.call("vcnf_small_linear_bwd", ptr(x), ptr(y), ptr(W), ptr(perm), None, ptr(gx), ptr(gW), ptr(gb),
+                          ptr(ws2), B, n, 0, st()), 4 * 3 * n * B)
+    lo, up, dg = torch.randn(n * (n - 1) // 2, device=dev) / 5, torch.randn(n * (n - 1) // 2, device=dev) / 5, torch.randn(n, device=dev)
+    lad = torch.empty((), device=dev)
+    add("lu_compose_fwd_kernel (vcnf_lu_compose_fwd, D = 29)",
+        lambda: _lib.call("vcnf_lu_compose_fwd", ptr(lo), ptr(up), ptr(dg), 1e-3, n, ptr(W), ptr(lad), 0, st()),
+        4 * (n * n + n * n), note="launch-bound single-CTA kernel: D^2 parameters; the time is what matters")
+    # optimiser: 28 B per fp32 parameter (cfg 2: 1.8 M parameters)
+    N = 1835008
+    p_, g_, m_, v_ = (torch.randn(N, device=dev) for _ in range(4))
+    v_.abs_()
+    stp, tick = torch.zeros(1, device=dev), torch.zeros(1, dtype=torch.int32, device=dev)
+    add("adam_flat_kernel (vcnf_adam_flat, 1.8 M fp32 parameters)",
+        lambda: _lib.call("vcnf_adam_flat", ptr(p_), ptr(g_), ptr(m_), ptr(v_), ptr(stp), ptr(tick), N, 1e-3, 0.9, 0.999,
+                          1e-8, 0.0, 0, st()), 28 * N)
+    # K6 register-resident MLP (cfg 1 [1,32,32,2], B = 2^20): FP32 FMA pipe, 2 240 flop / sample
+    B = 1 << 20
+    xm = torch.randn(B, 1, device=dev)
+    mlp = [torch.randn(32, 1, device=dev), torch.randn(32, 32, device=dev) / 6, torch.randn(2, 32, device=dev) / 6]
+    mb = [torch.randn(32, device=dev), torch.randn(32, device=dev), torch.randn(2, device=dev)]
+    with torch.no_grad():
+        ms = _time_launches(lambda: ops.mlp_small(xm, mlp, mb, 0.0), flush, reps=10)
+    flops = 2.0 * (32 + 32 * 32 + 64) * B
+    out["mlp_fwd_kernel (vcnf_mlp_fwd, cfg 1 [1,32,32,2], B = 2^20)"] = {
+        "ms": ms, "achieved": 12 * B / (ms * 1e-3) / 1e9, "frac": 12 * B / (ms * 1e-3) / 1e9 / peak, "unit": "GB/s",
+        "bytes_per_launch": 12 * B, "tflops_fp32_fma": flops / (ms * 1e-3) / 1e12,
+        "note": "FP32 FMA-pipe bound (~100 flop / B, SURVEY.md K6): the TFLOP/s figure is the relevant one"}
+    return out
+
+
+def conv_roofline(dev, flush):
+    """Tensor-pipe fraction of the cfg-5 convolution kernels at the level-2 shapes (B = 128, 16x16, hidden 256), live."""
+    from vcnf_b200 import ops
+    B, H, W, Hd, C = 128, 16, 16, 256, 12
+    bf = torch.bfloat16
+    h = torch.randn(B * H * W, Hd, device=dev).to(bf)
+    w1 = (torch.randn(1, Hd, Hd, device=dev) / 16).to(bf)
+    w9 = (torch.randn(9, 16, Hd, device=dev) / 48).to(bf)
+    bias = torch.zeros(Hd, device=dev)
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        peak = float(json.load(open(path))["bf16_tflops_sustained"])
+        src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+    except Exception:
+        peak, src = 1400.0, "fallback (B200_PROFILING.md)"
+    out = {}
+    for label, fn, flops in (
+            ("conv_gemm_bf16_kernel 1x1 256->256 @16x16 B=128", lambda: ops.conv_gemm_bf16(h, B, H, W, 1, w1, bias, epi=1),
+             2.0 * B * H * W * Hd * Hd),
+            ("conv_gemm_bf16_kernel 3x3 256->12 @16x16 B=128", lambda: ops.conv_gemm_bf16(h, B, H, W, 9, w9, None,
+                                                                                          out_nchw_channels=C),
+             2.0 * B * H * W * 9 * Hd * C),
+            ("conv_wgrad_bf16_kernel 256x256 over 32768 pixels (+ reduce)", lambda: ops.conv_wgrad_bf16(h, h),
+             2.0 * B * H * W * Hd * Hd)):
+        ms = _time_launches(fn, flush, reps=10)
+        tf = flops / (ms * 1e-3) / 1e12
+        out[label] = {"ms": ms, "achieved": tf, "unit": "TFLOP/s", "frac": tf / peak, "flops_per_launch": flops}
+    dom = max(out, key=lambda k: out[k]["ms"])
+    return {"bound": "tensor", "kernel": dom, "achieved": out[dom]["achieved"], "peak": peak, "peak_source": src,
+            "unit": "TFLOP/s", "frac": out[dom]["frac"], "traffic": None, "launch_ms": out[dom]["ms"],
+            "note": "real (unpadded) multiply-adds of the convolution / kernel time; the 3x3 -> C layer pads C to 16 "
+                    "columns and re-reads the activation tile once per tap from L2",
+            "other_kernels": {k: v for k, v in out.items() if k != dom}}
+
+
+def reference_eager_cuda(dev, steps=3):
+    """The reference algorithm as users run it today: the oracle port (plain PyTorch ops, no package kernel) moved
+    to the same B200, same model / batch / optimiser, eager, CUDA-event timed.  A baseline beside `cpu_baseline`."""
+    try:
+        import oracle
+        torch.manual_seed(0)
+        model = build_model(oracle).to(dev)
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+        x = synth_batch(BATCH, 1234).to(dev)
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            loss = model.forward_kld(x.clone())
+            loss.backward()
+            opt.step()
+            return loss
+        step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out = {"value": BATCH / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms, "steps": steps,
+               "kind": "oracle port (.to('cuda')), eager PyTorch ops on the same GPU, fp32 (TF32 off)",
+               "loss": float(loss)}
+        del model, opt, x
+        torch.cuda.empty_cache()
+        return out
+    except Exception as exc:            # noqa: BLE001
+        return {"unavailable": repr(exc)[:300]}
+
+
 def gpu_run(args):
     import vcnf_b200 as nf
     from vcnf_b200 import ops, parallel
@@ -333,10 +667,53 @@ def gpu_run(args):
         sample_rate = world * BATCH / (sample_ms * 1e-3)
         sample_ok = bool(torch.isfinite(z_s).all() and torch.isfinite(lq_s).all())
 
+    # strong-scaling point of cfg 3a (BASELINE: "batch 256K sharded over 8 GPUs"): global batch fixed at 262 144
+    strong = None
+    step_err = getattr(step, "capture_error", None) if not args.no_graph else None
+    draw_graph, draw_err = bool(getattr(draw, "graph", None) is not None), getattr(draw, "capture_error", None)
+    if not args.no_configs:
+        del step, draw
+        torch.cuda.empty_cache()
+        try:
+            strong = measure_config("cfg3a", dev, world, rank, steps=5, warmup=3, flush=flush, batch=262144 // world,
+                                    with_e2e=False)
+            strong["scaling"] = "strong"
+            strong["global_batch"] = 262144
+            strong.pop("sample", None)
+        except Exception as exc:        # noqa: BLE001
+            strong = {"unavailable": repr(exc)[:300]}
     if rank != 0:
         return
     roof = kernel_roofline(model, dev, flush)
-    cpu = cpu_reference_run(steps=2, warmup=1) if world == 1 else None
+    others = {}
+    eager_cuda = None
+    cpu = None
+    if world == 1:
+        try:
+            roof["other_kernels"].update(extra_kernel_rooflines(dev, flush))
+        except Exception as exc:        # noqa: BLE001
+            roof["other_kernels"]["error"] = repr(exc)[:300]
+        if not args.no_configs:
+            for name in ("cfg1", "cfg3a", "cfg3b", "cfg4", "cfg5"):
+                try:
+                    others[name] = measure_config(name, dev, 1, 0, steps=5, warmup=3, flush=flush)
+                    if name == "cfg1":
+                        big = measure_config(name, dev, 1, 0, steps=5, warmup=3, flush=flush, batch=1 << 20,
+                                             with_e2e=False)
+                        others[name]["batch_2^20"] = {k: big[k] for k in ("ms_per_step", "value", "unit")}
+                    if name == "cfg4":
+                        big = measure_config(name, dev, 1, 0, steps=5, warmup=3, flush=flush, batch=65536, with_e2e=False)
+                        others[name]["batch_65536"] = {k: big[k] for k in ("ms_per_step", "value", "unit")}
+                    if name == "cfg5":
+                        big = measure_config(name, dev, 1, 0, steps=5, warmup=3, flush=flush, batch=512, with_e2e=False)
+                        others[name]["batch_512"] = {k: big[k] for k in ("ms_per_step", "value", "unit")}
+                        others[name]["roofline"] = conv_roofline(dev, flush)
+                except Exception as exc:        # noqa: BLE001
+                    others[name] = {"unavailable": repr(exc)[:300]}
+            from vcnf_b200.nets import cnn
+            cnn.set_precision("fp32")
+        eager_cuda = reference_eager_cuda(dev)
+        cpu = cpu_reference_run(steps=1, warmup=1, sample=_cpu_rows())
     line = {
         "metric": "forward_kld_train_samples_per_sec", "value": value, "unit": "samples/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -346,15 +723,60 @@ def gpu_run(args):
                    "hidden": HIDDEN, "bins": BINS, "parallelism": "dp%d" % world,
                    "l2": "256 MiB buffer written between timed steps (L2 flush)",
                    "conditioner_gemms": "tcgen05 3xTF32 (vcnf_linear_tf32x3 fwd/dgrad, vcnf_linear_wgrad_tf32x3)", "optimizer": "torch Adam(fused)" if args.torch_adam else "Adam, flat buffers (vcnf_adam_flat)", "cuda_graph": graphed,
-                   "cuda_graph_error": getattr(step, "capture_error", None) if not args.no_graph else None},
+                   "cuda_graph_error": step_err},
         "clocks": clocks, "gpu_launches": launches,
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": BATCH * D * 4,
                 "d2h_bytes_per_step": 4},
-        "roofline": roof, "cpu_baseline": cpu,
+        "roofline": roof, "cpu_baseline": cpu, "reference_eager_cuda": eager_cuda,
+        "configs": others, "cfg3a_strong": strong,
         "sample": {"value": sample_rate, "unit": "samples/s", "batch": BATCH, "ms_per_draw": sample_ms,
-                   "cuda_graph": bool(getattr(draw, "graph", None) is not None),
-                   "cuda_graph_error": getattr(draw, "capture_error", None), "finite": sample_ok},
+                   "cuda_graph": draw_graph, "cuda_graph_error": draw_err, "finite": sample_ok},
         "loss": float(loss_val),
+    }
+    _emit(line)
+
+
+def config_run(args):
+    """`--config X`: the whole line for another BASELINE configuration."""
+    from vcnf_b200 import parallel
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference)")
+    rank, world, local = parallel.init_from_env()
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    sampler = ClockSampler(local)
+    sampler.start()
+    r = measure_config(args.config, dev, world, rank, steps=args.steps, warmup=max(args.warmup, 3), flush=flush)
+    clocks = sampler.summary()
+    if rank != 0:
+        return
+    if args.config == "cfg5":
+        roof = conv_roofline(dev, flush)
+    else:
+        extras = extra_kernel_rooflines(dev, flush)
+        key = {"cfg1": "coupling_kernel<fwd>", "cfg4": "masked_affine_kernel<fwd>"}.get(args.config)
+        if key:
+            name = next(k for k in extras if k.startswith(key))
+            peak, src = _peak()
+            d = extras.pop(name)
+            roof = {"bound": "hbm", "kernel": name, "achieved": d["achieved"], "peak": peak, "peak_source": src,
+                    "unit": "GB/s", "frac": d["frac"], "traffic": None, "launch_ms": d["ms"], "other_kernels": extras}
+        else:
+            import vcnf_b200 as nf
+            torch.manual_seed(0)
+            roof = kernel_roofline(build_model(nf).to(dev), dev, flush)
+            roof["note"] = "cfg 3 shares the conditioner GEMM / spline kernels of cfg 2; measured at the cfg-2 shapes"
+    line = {
+        "metric": "forward_kld_train_samples_per_sec" if args.config != "cfg1" else "reverse_kld_train_samples_per_sec",
+        "value": r["value"], "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": r["dtype"], "data": "synthetic",
+        "config": {"workload": r["workload"], "global_batch": world * r["batch_per_gpu"], "parallelism": "dp%d" % world,
+                   "l2": "256 MiB buffer written between timed steps (L2 flush)", "optimizer": r["optimizer"],
+                   "cuda_graph": r["cuda_graph"], "cuda_graph_error": r["cuda_graph_error"]},
+        "clocks": clocks, "gpu_launches": r["gpu_launches_per_step"] * args.steps, "e2e": r.get("e2e"),
+        "roofline": roof, "cpu_baseline": None, "sample": r.get("sample"), "loss": r["loss"],
     }
     _emit(line)
 
@@ -363,15 +785,16 @@ def reference_run(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warmup = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
-    r = cpu_reference_run(steps=steps, warmup=warmup)
+    rows = _cpu_rows()
+    steps, warmup = max(1, min(args.steps, 2 if rows == BATCH else 5)), max(1, min(args.warmup, 1))
+    r = cpu_reference_run(steps=steps, warmup=warmup, sample=rows)
     world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     line = {
         "impl": "reference", "metric": "forward_kld_train_samples_per_sec", "value": r["value"],
         "unit": "samples/s", "n_gpus": world, "steps": steps, "warmup": warmup,
         "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "global_batch": CPU_SAMPLE, "features": D, "layers": LAYERS,
+        "config": {"workload": WORKLOAD, "global_batch": rows, "features": D, "layers": LAYERS,
                    "hidden": HIDDEN, "bins": BINS, "parallelism": "cpu"},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -410,9 +833,13 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--torch-adam", action="store_true", help="torch.optim.Adam(fused=True) instead of optim.FlatAdam")
+    ap.add_argument("--config", default="cfg2", choices=["cfg1", "cfg2", "cfg3a", "cfg3b", "cfg4", "cfg5"])
+    ap.add_argument("--no-configs", action="store_true", help="default line without the `configs` / `cfg3a_strong` extras")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_run(args)
+    elif args.config != "cfg2":
+        config_run(args)
     else:
         gpu_run(args)
     import torch.distributed as dist

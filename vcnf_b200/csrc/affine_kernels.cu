@@ -448,7 +448,9 @@ int vcnf_const_affine_bwd(const void* z, const void* s, const void* t, const voi
                                                             (const T*)gout, (T*)gz, (T*)workspace, B, Pn, S, inverse, rpc); \
     int rc = launch_status();                                                                            \
     if (rc) return rc;                                                                                   \
-    const_affine_reduce_kernel<T><<<(Pn + 127) / 128, 128, 0, st>>>((const T*)workspace, (int)chunks, Pn, (T*)gs, (T*)gt); \
+    /* partial layout [chunk][2][Pn]: one warp per output sums the chunks (fixed order) */                \
+    launch_warp_reduce<T>((const T*)workspace, (int)chunks, 2 * Pn, Pn, (T*)gs, st);                      \
+    launch_warp_reduce<T>((const T*)workspace + Pn, (int)chunks, 2 * Pn, Pn, (T*)gt, st);                 \
     return launch_status();                                                                              \
   }
   if (dtype == VCNF_F32) GO(float) else GO(double)

@@ -70,52 +70,76 @@ __global__ void __launch_bounds__(kThreads) gauss_fwd_kernel(const T* __restrict
   }
 }
 
-// Backward.  gz (mode 0: d/dz; mode 1: nothing, eps has no gradient) and per-chunk partial parameter gradients
-// partial[chunk][2][classes][n]; a CTA owns a contiguous chunk of rows and walks it row by row, thread j-strided, so
-// every (class, j) accumulator has a single writer (shared-memory table, no atomics, fixed order).
+// Backward, input gradient only (frozen base parameters: cfg 2 / 3): a flat elementwise pass.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) gauss_gz_kernel(const T* __restrict__ zin, const T* __restrict__ loc,
+                                                            const T* __restrict__ ls, int64_t js, int64_t cs,
+                                                            const int64_t* __restrict__ y, T log_temp,
+                                                            const T* __restrict__ g_logp, T* __restrict__ gz,
+                                                            int64_t total, int n) {
+  for (int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t b = e / n;
+    const int j = static_cast<int>(e - b * n);
+    const int64_t c = y ? y[b] : 0;
+    const T il = texp(-(__ldg(ls + j * js + c * cs) + log_temp));
+    gz[e] = -g_logp[b] * (zin[e] - __ldg(loc + j * js + c * cs)) * il * il;
+  }
+}
+
+// Backward with parameter gradients.  gz (mode 0: d/dz; mode 1: nothing, eps has no gradient) and per-chunk partial
+// parameter gradients partial[chunk][2][classes][n].  A CTA owns a contiguous chunk of rows; thread t keeps column
+// j = t % npad of the rows t / npad, t / npad + G, ... (G = 256 / npad row groups, npad = n rounded up so that whole
+// groups fit), so all 256 threads work for narrow rows too; its sums go to a private slot [group][class][j] of the
+// shared table (single writer, no atomics), the G slots are added in group order at the end (fixed order).
 template <typename T>
 __global__ void __launch_bounds__(kThreads) gauss_bwd_kernel(const T* __restrict__ zin, const T* __restrict__ loc,
                                                              const T* __restrict__ ls, int64_t js, int64_t cs,
                                                              const int64_t* __restrict__ y, T log_temp,
                                                              const T* __restrict__ g_logp, const T* __restrict__ g_zout,
                                                              T* __restrict__ gz, T* __restrict__ partial, int64_t B,
-                                                             int n, int classes, int mode, int64_t rows_per_chunk) {
+                                                             int n, int classes, int mode, int64_t rows_per_chunk,
+                                                             int G) {
   extern __shared__ unsigned char smem_raw[];
-  T* tab = reinterpret_cast<T*>(smem_raw);          // [2][classes][n] when partial != NULL
+  T* tab = reinterpret_cast<T*>(smem_raw);          // [G][2][classes][n]
   const int chunk = blockIdx.x;
   const int64_t b0 = chunk * rows_per_chunk, b1 = b0 + rows_per_chunk < B ? b0 + rows_per_chunk : B;
   const int64_t tsize = static_cast<int64_t>(classes) * n;
-  if (partial)
-    for (int64_t i = threadIdx.x; i < 2 * tsize; i += kThreads) tab[i] = T(0);
+  for (int64_t i = threadIdx.x; i < 2 * tsize * G; i += kThreads) tab[i] = T(0);
   __syncthreads();
-  for (int64_t b = b0; b < b1; ++b) {
-    const int64_t c = y ? y[b] : 0;
-    const T g = g_logp ? g_logp[b] : T(0);
-    for (int j = threadIdx.x; j < n; j += kThreads) {
-      const T l = __ldg(ls + j * js + c * cs) + log_temp;
-      const T v = zin[b * n + j];
-      T gl, gs;
-      if (mode == 0) {
-        const T il = texp(-l);
-        const T e = (v - __ldg(loc + j * js + c * cs)) * il;
-        const T gzv = -g * e * il;
-        if (gz) gz[b * n + j] = gzv;
-        gl = -gzv;
-        gs = g * (e * e - T(1));
-      } else {
-        const T go = g_zout ? g_zout[b * n + j] : T(0);
-        gl = go;
-        gs = go * texp(l) * v - g;
-      }
-      if (partial) {
-        tab[c * n + j] += gl;
-        tab[tsize + c * n + j] += gs;
+  const int per = kThreads / G;                     // threads per row group
+  const int grp = threadIdx.x / per, j0 = threadIdx.x - grp * per;
+  T* mine = tab + static_cast<int64_t>(grp) * 2 * tsize;
+  if (grp < G) {
+    for (int64_t b = b0 + grp; b < b1; b += G) {
+      const int64_t c = y ? y[b] : 0;
+      const T g = g_logp ? g_logp[b] : T(0);
+      for (int j = j0; j < n; j += per) {
+        const T l = __ldg(ls + j * js + c * cs) + log_temp;
+        const T v = zin[b * n + j];
+        T gl, gs;
+        if (mode == 0) {
+          const T il = texp(-l);
+          const T e = (v - __ldg(loc + j * js + c * cs)) * il;
+          const T gzv = -g * e * il;
+          if (gz) gz[b * n + j] = gzv;
+          gl = -gzv;
+          gs = g * (e * e - T(1));
+        } else {
+          const T go = g_zout ? g_zout[b * n + j] : T(0);
+          gl = go;
+          gs = go * texp(l) * v - g;
+        }
+        mine[c * n + j] += gl;
+        mine[tsize + c * n + j] += gs;
       }
     }
   }
-  if (partial) {
-    __syncthreads();
-    for (int64_t i = threadIdx.x; i < 2 * tsize; i += kThreads) partial[static_cast<int64_t>(chunk) * 2 * tsize + i] = tab[i];
+  __syncthreads();
+  for (int64_t i = threadIdx.x; i < 2 * tsize; i += kThreads) {
+    T acc = T(0);
+    for (int g2 = 0; g2 < G; ++g2) acc += tab[static_cast<int64_t>(g2) * 2 * tsize + i];
+    partial[static_cast<int64_t>(chunk) * 2 * tsize + i] = acc;
   }
 }
 
@@ -144,7 +168,9 @@ __global__ void __launch_bounds__(kThreads) gmm_kernel(const T* __restrict__ z, 
   T* s_z = s_t + kGmmRows * K;                      // [kGmmRows][d]
   T* s_g = s_z + kGmmRows * d;                      // [kGmmRows]
   T* s_red = s_g + kGmmRows;                        // [8]
-  T* s_acc = s_red + 8;                             // bwd: [K*d*2 + K] accumulators of this CTA's chunk
+  T* s_il = s_red + 8;                              // [K*d] exp(-log_scale): one exp per parameter, not per sample
+  T* s_sl = s_il + K * d;                           // [K]   sum_j log_scale
+  T* s_acc = s_sl + K;                              // bwd: [K*d*2 + K] accumulators of this CTA's chunk
   // log-softmax of the weight scores
   T m = -INFINITY;
   for (int k = threadIdx.x; k < K; k += kThreads) m = fmax(m, ws[k]);
@@ -158,6 +184,12 @@ __global__ void __launch_bounds__(kThreads) gmm_kernel(const T* __restrict__ z, 
   se = block_sum(se, s_red);
   const T lse_w = m + log(se);
   for (int k = threadIdx.x; k < K; k += kThreads) s_lw[k] = ws[k] - lse_w;
+  for (int i = threadIdx.x; i < K * d; i += kThreads) s_il[i] = texp(-__ldg(ls + i));
+  for (int k = threadIdx.x; k < K; k += kThreads) {
+    T t = T(0);
+    for (int j = 0; j < d; ++j) t += __ldg(ls + k * d + j);
+    s_sl[k] = t;
+  }
   const int nacc = K * d * 2 + K;
   if (bwd)
     for (int i = threadIdx.x; i < nacc; i += kThreads) s_acc[i] = T(0);
@@ -172,14 +204,12 @@ __global__ void __launch_bounds__(kThreads) gmm_kernel(const T* __restrict__ z, 
     __syncthreads();
     for (int i = threadIdx.x; i < rows * K; i += kThreads) {
       const int b = i / K, k = i - b * K;
-      T q = T(0), sl = T(0);
+      T q = T(0);
       for (int j = 0; j < d; ++j) {
-        const T l = __ldg(ls + k * d + j);
-        const T e = (s_z[b * d + j] - __ldg(mu + k * d + j)) * texp(-l);
+        const T e = (s_z[b * d + j] - __ldg(mu + k * d + j)) * s_il[k * d + j];
         q += e * e;
-        sl += l;
       }
-      s_t[b * K + k] = static_cast<T>(-kHalfLog2Pi * d) + s_lw[k] - T(0.5) * q - sl;
+      s_t[b * K + k] = static_cast<T>(-kHalfLog2Pi * d) + s_lw[k] - T(0.5) * q - s_sl[k];
     }
     __syncthreads();
     // per-row logsumexp: one warp per row
@@ -201,7 +231,7 @@ __global__ void __launch_bounds__(kThreads) gmm_kernel(const T* __restrict__ z, 
       // parameter gradients: thread per (k, j), rows in order
       for (int i = threadIdx.x; i < K * d; i += kThreads) {
         const int k = i / d, j = i - k * d;
-        const T l = __ldg(ls + i), il = texp(-l), mk = __ldg(mu + i);
+        const T il = s_il[i], mk = __ldg(mu + i);
         T am = T(0), al = T(0);
         for (int b = 0; b < rows; ++b) {
           const T w = s_g[b] * s_t[b * K + k];
@@ -223,7 +253,7 @@ __global__ void __launch_bounds__(kThreads) gmm_kernel(const T* __restrict__ z, 
           const int b = i / d, j = i - b * d;
           T a = T(0);
           for (int k = 0; k < K; ++k) {
-            const T il = texp(-__ldg(ls + k * d + j));
+            const T il = s_il[k * d + j];
             a -= s_t[b * K + k] * (s_z[i] - __ldg(mu + k * d + j)) * il * il;
           }
           gz[r0 * d + i] = s_g[b] * a;
@@ -293,10 +323,32 @@ int vcnf_gauss_bwd(const void* zin, const void* loc, const void* log_scale, int6
     if (g_loc) { cudaMemsetAsync(g_loc, 0, tsize * eb, st); cudaMemsetAsync(g_log_scale, 0, tsize * eb, st); }
     return launch_status();
   }
-  const size_t smem = g_loc ? static_cast<size_t>(2 * tsize) * eb : 0;
+  const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
+  if (!g_loc) {
+    // input gradient only: one flat elementwise launch
+    if (mode != 0 || !gz) return 0;
+    if (!g_logp) { cudaMemsetAsync(gz, 0, static_cast<size_t>(B) * n * eb, st); return launch_status(); }
+    const int64_t total = B * n;
+    int64_t blocks = (total + base::kThreads - 1) / base::kThreads;
+    if (blocks > static_cast<int64_t>(sms) * 16) blocks = static_cast<int64_t>(sms) * 16;
+    if (dtype == VCNF_F32)
+      base::gauss_gz_kernel<float><<<static_cast<unsigned>(blocks), base::kThreads, 0, st>>>(
+          static_cast<const float*>(zin), static_cast<const float*>(loc), static_cast<const float*>(log_scale), j_stride,
+          c_stride, y, static_cast<float>(log_temp), static_cast<const float*>(g_logp), static_cast<float*>(gz), total, n);
+    else
+      base::gauss_gz_kernel<double><<<static_cast<unsigned>(blocks), base::kThreads, 0, st>>>(
+          static_cast<const double*>(zin), static_cast<const double*>(loc), static_cast<const double*>(log_scale),
+          j_stride, c_stride, y, log_temp, static_cast<const double*>(g_logp), static_cast<double*>(gz), total, n);
+    return launch_status();
+  }
+  // row groups: as many as fit 256 threads and 200 KB of shared table
+  int G = n >= base::kThreads ? 1 : base::kThreads / n;
+  while (G > 1 && static_cast<size_t>(2 * tsize) * G * eb > 200 * 1024) G >>= 1;
+  if (G > 32) G = 32;
+  const size_t smem = static_cast<size_t>(2 * tsize) * G * eb;
   if (smem > 200 * 1024) return VCNF_E_UNSUPPORTED;
   int64_t rpc = 0;
-  const int64_t chunks = plan_chunks(B, &rpc, 4);
+  const int64_t chunks = plan_chunks(B, &rpc, 4 * G);
 #define GO(T)                                                                                                          \
   {                                                                                                                    \
     static bool attr = false;                                                                                          \
@@ -304,17 +356,13 @@ int vcnf_gauss_bwd(const void* zin, const void* loc, const void* log_scale, int6
     base::gauss_bwd_kernel<T><<<static_cast<unsigned>(chunks), base::kThreads, smem, st>>>(                             \
         static_cast<const T*>(zin), static_cast<const T*>(loc), static_cast<const T*>(log_scale), j_stride, c_stride, y, \
         static_cast<T>(log_temp), static_cast<const T*>(g_logp), static_cast<const T*>(g_zout), static_cast<T*>(gz),   \
-        g_loc ? static_cast<T*>(workspace) : nullptr, B, n, classes, mode, rpc);                                       \
+        static_cast<T*>(workspace), B, n, classes, mode, rpc, G);                                                      \
     int rc = launch_status();                                                                                          \
     if (rc) return rc;                                                                                                 \
-    if (g_loc) {                                                                                                       \
-      /* partial layout [chunk][2][classes][n]: the two halves are the dense [classes][n] gradients */                  \
-      const T* pw = static_cast<const T*>(workspace);                                                                  \
-      base::reduce_chunks_kernel<T><<<static_cast<unsigned>((tsize + 255) / 256), 256, 0, st>>>(                       \
-          pw, static_cast<int>(chunks), 2 * tsize, tsize, static_cast<T*>(g_loc));                                     \
-      base::reduce_chunks_kernel<T><<<static_cast<unsigned>((tsize + 255) / 256), 256, 0, st>>>(                       \
-          pw + tsize, static_cast<int>(chunks), 2 * tsize, tsize, static_cast<T*>(g_log_scale));                       \
-    }                                                                                                                  \
+    /* partial layout [chunk][2][classes][n]: the two halves are the dense [classes][n] gradients */                    \
+    const T* pw = static_cast<const T*>(workspace);                                                                    \
+    launch_warp_reduce<T>(pw, static_cast<int>(chunks), 2 * tsize, tsize, static_cast<T*>(g_loc), st);                 \
+    launch_warp_reduce<T>(pw + tsize, static_cast<int>(chunks), 2 * tsize, tsize, static_cast<T*>(g_log_scale), st);   \
   }
   if (dtype == VCNF_F32) GO(float) else GO(double)
 #undef GO
@@ -323,7 +371,7 @@ int vcnf_gauss_bwd(const void* zin, const void* loc, const void* log_scale, int6
 
 static size_t gmm_smem(int K, int d, int bwd, size_t eb) {
   return (static_cast<size_t>(K) + base::kGmmRows * K + base::kGmmRows * d + base::kGmmRows + 8 +
-          (bwd ? static_cast<size_t>(K) * d * 2 + K : 0)) * eb;
+          static_cast<size_t>(K) * d + K + (bwd ? static_cast<size_t>(K) * d * 2 + K : 0)) * eb;
 }
 
 int64_t vcnf_gmm_bwd_workspace(int K, int d, int dtype) {
@@ -390,8 +438,8 @@ int vcnf_gmm_logprob_bwd(const void* z, const void* mu, const void* log_scale, c
         static_cast<T*>(workspace), B, K, d, rpc, 1);                                                                  \
     int rc = launch_status();                                                                                          \
     if (rc) return rc;                                                                                                 \
-    base::reduce_chunks_kernel<T><<<static_cast<unsigned>((nacc + 255) / 256), 256, 0, st>>>(                          \
-        static_cast<const T*>(workspace), static_cast<int>(chunks), nacc, nacc, static_cast<T*>(g_params));                  \
+    launch_warp_reduce<T>(static_cast<const T*>(workspace), static_cast<int>(chunks), nacc, nacc,                       \
+                          static_cast<T*>(g_params), st);                                                              \
   }
   if (dtype == VCNF_F32) GO(float) else GO(double)
 #undef GO

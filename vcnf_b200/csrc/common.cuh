@@ -68,6 +68,27 @@ __device__ __forceinline__ T warp_sum(T v) {
   return v;
 }
 
+// out[i] = sum over chunks c of partial[c * stride + i], one WARP per output: lane l adds chunks l, l + 32, ... in
+// order, then a fixed xor tree -- the same summation order on every run (bit-reproducible), and 32 independent
+// loads in flight per output instead of one thread walking all chunks serially.
+template <typename T>
+__global__ void __launch_bounds__(256) warp_reduce_chunks_kernel(const T* __restrict__ partial, int chunks, int64_t stride,
+                                                                 int64_t total, T* __restrict__ out) {
+  const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (i >= total) return;
+  T acc = T(0);
+  for (int c = lane; c < chunks; c += 32) acc += partial[static_cast<int64_t>(c) * stride + i];
+  acc = warp_sum(acc);
+  if (lane == 0) out[i] = acc;
+}
+template <typename T>
+inline void launch_warp_reduce(const T* partial, int chunks, int64_t stride, int64_t total, T* out, cudaStream_t st) {
+  if (total <= 0) return;
+  const int64_t blocks = (total * 32 + 255) / 256;
+  warp_reduce_chunks_kernel<T><<<static_cast<unsigned>(blocks), 256, 0, st>>>(partial, chunks, stride, total, out);
+}
+
 inline int sm_count() {
   static int n = -1;
   if (n < 0) {

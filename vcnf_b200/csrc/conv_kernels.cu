@@ -622,8 +622,8 @@ int vcnf_colsum(const void* X, int layout, int64_t rows, int C, int64_t ld_or_S,
   }
   int rc = launch_status();
   if (rc) return rc;
-  conv::sum_partials_kernel<<<(C + 127) / 128, 128, 0, st>>>(static_cast<const float*>(workspace),
-                                                             static_cast<int>(chunks), C, static_cast<float*>(out));
+  launch_warp_reduce<float>(static_cast<const float*>(workspace), static_cast<int>(chunks), C, C,
+                            static_cast<float*>(out), st);
   return launch_status();
 }
 

@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(kLinRows) small_linear_kernel(const LinArgs<T>
 // span in HBM, so it is staged and written back as a flat coalesced copy (no index arithmetic per
 // element); the feature gather / scatter happens on the shared-memory side, where a row pitch of D
 // (odd for the shapes in use) is conflict-free.  Two tiles per CTA iteration share one W load.
-constexpr int kRowThreads = 256;
+constexpr int kRowThreads = 128;   // 128-row tiles: 512 CTAs at B = 65 536, ~4 resident per SM, whose load / compute / store phases overlap
 
 template <typename T, int DP>
 __global__ void __launch_bounds__(kRowThreads) small_linear_rows_kernel(const LinArgs<T> a) {
@@ -160,7 +160,7 @@ static int launch_lin(const LinArgs<T>& a, cudaStream_t st) {
     }
     const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
     const int64_t tiles = (a.rows + kRowThreads - 1) / kRowThreads;
-    const int64_t cap = static_cast<int64_t>(sms) * 2;
+    const int64_t cap = static_cast<int64_t>(sms) * 6;
     kern<<<static_cast<unsigned>(tiles < cap ? tiles : cap), kRowThreads, smem, st>>>(a);
     return launch_status();
   }

@@ -78,28 +78,33 @@ __global__ void __launch_bounds__(kThreads) vdeq_bwd_kernel(const XT* __restrict
                                                             int n, int L, const XT* __restrict__ g_zc,
                                                             const float* __restrict__ g_logq, int64_t rows_per_chunk,
                                                             double* __restrict__ partial) {
+  // thread-private columns of three [L][kThreads] shared tables (accumulators of d/da, d/dc and the layer inputs of
+  // the current row): indexed arrays in registers would live in local memory (measured: 510 MB of spill traffic)
+  extern __shared__ double s_dyn[];
+  double* s_ga = s_dyn;
+  double* s_gc = s_ga + static_cast<size_t>(L) * kThreads;
+  double* s_vs = s_gc + static_cast<size_t>(L) * kThreads;
   __shared__ double s_a[kMaxL], s_c[kMaxL], s_ea[kMaxL];
   __shared__ double red[kThreads / 32][2];
-  const int k = blockIdx.y, chunk = blockIdx.x;
-  for (int l = threadIdx.x; l < L; l += blockDim.x) {
+  const int k = blockIdx.y, chunk = blockIdx.x, tid = threadIdx.x;
+  for (int l = tid; l < L; l += blockDim.x) {
     s_a[l] = tab[(k * L + l) * 2];
     s_c[l] = tab[(k * L + l) * 2 + 1];
     s_ea[l] = exp(s_a[l]);
   }
+  for (int l = 0; l < L; ++l) { s_ga[l * kThreads + tid] = 0.0; s_gc[l * kThreads + tid] = 0.0; }
   __syncthreads();
-  double ga[kMaxL], gc[kMaxL], vs[kMaxL];
-  for (int l = 0; l < L; ++l) { ga[l] = 0.0; gc[l] = 0.0; }
   const double q = quants[k];
   const int64_t b0 = chunk * rows_per_chunk;
   const int64_t b1 = b0 + rows_per_chunk < B ? b0 + rows_per_chunk : B;
-  for (int64_t b = b0 + threadIdx.x; b < b1; b += blockDim.x) {
+  for (int64_t b = b0 + tid; b < b1; b += blockDim.x) {
     const double g_out = g_zc ? static_cast<double>(g_zc[b * n + k]) : 0.0;
     const double g_ld = g_logq ? static_cast<double>(g_logq[b]) * (n - k) : 0.0;
     const double xf = static_cast<double>(static_cast<float>(x[b * ldx + k]));
     const double up = noise[b * n + k] * (1.0 - alpha) + 0.5 * alpha;
     double v = log(up) - log(1.0 - up);
     for (int l = 0; l < L; ++l) {
-      vs[l] = v;
+      s_vs[l * kThreads + tid] = v;
       v = v * s_ea[l] + s_c[l];
     }
     const double w = 1.0 / (1.0 + exp(-v));
@@ -108,17 +113,17 @@ __global__ void __launch_bounds__(kThreads) vdeq_bwd_kernel(const XT* __restrict
     const double g_w = g_zp * (1.0 - alpha) / q;
     double g_v = g_w * w * (1.0 - w) + g_ld * (1.0 - 2.0 * w);
     for (int l = L - 1; l >= 0; --l) {
-      gc[l] += g_v;
-      ga[l] += g_v * vs[l] * s_ea[l] + g_ld;
+      s_gc[l * kThreads + tid] += g_v;
+      s_ga[l * kThreads + tid] += g_v * s_vs[l * kThreads + tid] * s_ea[l] + g_ld;
       g_v *= s_ea[l];
     }
   }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = tid >> 5, lane = tid & 31;
   for (int l = 0; l < L; ++l) {
-    const double sa = warp_sum(ga[l]), sc = warp_sum(gc[l]);
+    const double sa = warp_sum(s_ga[l * kThreads + tid]), sc = warp_sum(s_gc[l * kThreads + tid]);
     if (lane == 0) { red[warp][0] = sa; red[warp][1] = sc; }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       double ta = 0.0, tc = 0.0;
       for (int w2 = 0; w2 < kThreads / 32; ++w2) { ta += red[w2][0]; tc += red[w2][1]; }
       double* dst = partial + ((static_cast<int64_t>(chunk) * n + k) * L + l) * 2;
@@ -218,21 +223,27 @@ int vcnf_vdeq_bwd(const void* x, int64_t ldx, const void* noise, const void* tab
   const int64_t rpc = (B + chunks - 1) / chunks;
   chunks = (B + rpc - 1) / rpc;
   dim3 grid(static_cast<unsigned>(chunks), n);
+  const size_t dsm = static_cast<size_t>(3) * L * vdeq::kThreads * sizeof(double);      // <= 196 KB at L = 64
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(vdeq::vdeq_bwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(vdeq::vdeq_bwd_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr = true;
+  }
   if (dtype == VCNF_F32)
-    vdeq::vdeq_bwd_kernel<float><<<grid, vdeq::kThreads, 0, st>>>(
+    vdeq::vdeq_bwd_kernel<float><<<grid, vdeq::kThreads, dsm, st>>>(
         static_cast<const float*>(x), ldx, static_cast<const double*>(noise), static_cast<const double*>(tab),
         static_cast<const double*>(quants), alpha, B, n, L, static_cast<const float*>(g_zc),
         static_cast<const float*>(g_logq), rpc, static_cast<double*>(workspace));
   else
-    vdeq::vdeq_bwd_kernel<double><<<grid, vdeq::kThreads, 0, st>>>(
+    vdeq::vdeq_bwd_kernel<double><<<grid, vdeq::kThreads, dsm, st>>>(
         static_cast<const double*>(x), ldx, static_cast<const double*>(noise), static_cast<const double*>(tab),
         static_cast<const double*>(quants), alpha, B, n, L, static_cast<const double*>(g_zc),
         static_cast<const float*>(g_logq), rpc, static_cast<double*>(workspace));
   int rc = launch_status();
   if (rc) return rc;
-  vdeq::vdeq_reduce_kernel<<<(total + 127) / 128, 128, 0, st>>>(static_cast<const double*>(workspace),
-                                                                 static_cast<int>(chunks), total,
-                                                                 static_cast<double*>(g_tab));
+  launch_warp_reduce<double>(static_cast<const double*>(workspace), static_cast<int>(chunks), total, total,
+                             static_cast<double*>(g_tab), st);
   return launch_status();
 }
 
