@@ -348,6 +348,28 @@ int vcnf_axpb(const void* x, const void* noise, void* out, int64_t total, double
 int vcnf_checkerboard(void* z, void* z1, void* z2, const uint8_t* mid_parity, int64_t B, int M, int W, int inv, int merge,
                       int dtype, void* stream);
 
+/* ---- K7: autoregressive layers in the sampling direction, all D passes in one launch ----------------------------
+ * Replaces the D-pass loop of normflow/flows/affine/autoregressive.py:29-36 (each pass: MADE, nets/made.py:288-299, then
+ * the elementwise inverse, flows/affine/autoregressive.py:92-103 or flows/neural_spline/autoregressive.py:92-131) for a
+ * MADE with residual blocks, ReLU, sequential (possibly permuted) degrees: pass t evaluates only the hidden units of
+ * degree t (they are final from then on) and the P output rows of the feature of degree t + 1 -- one MADE evaluation
+ * in total instead of D.  Host-packed operands (fp32, device, 16 B aligned), one contiguous block per pass t so that a
+ * single bulk copy brings it on chip (n_layers = 1 + 2 blocks <= 5: initial layer, then first / second of each block):
+ *   band [D][(D + (n_layers-1) H) 8 + n_layers 8]: [Wb_0[t] (D x 8) | Wb_1[t] (H x 8) | ... | bb_0[t] (8) | ...] =
+ *        masked weights (transposed: contraction index major) and biases of layer l's hidden units of degree t,
+ *        8 slots per degree; band_idx [D][8] = their unit indices (-1 = padding); band_units = the largest number
+ *        of units any degree has (slots >= band_units are padding everywhere: the kernel skips their products)
+ *   fin  [D][(H + 1) Pp]: [Wf[t] (H x Pp) | bf[t] (Pp)] = the final masked layer's rows of feature order[t],
+ *        transposed, Pp = P rounded up to a multiple of 4
+ *   order [D]: feature fixed in pass t (ascending input degree)
+ * map 0: MAF map, P = 2 (unconstrained scale, shift); map 1: RQ spline, P = 3K - 1 / 3K / 3K + 1 with per-feature tail
+ * `modes` (uint8, VCNF_TAIL_*) and `bounds` (fp32).  y, x [B, D] fp32; logdet [B] = the inverse's log|det|.
+ * D and H must be multiples of 16. */
+int vcnf_made_inverse(const void* y, void* x, void* logdet, int64_t B, int D, int H, int P, int n_layers,
+                      const void* band, const void* fin, const int32_t* band_idx, const int32_t* order, int band_units,
+                      const void* bounds, const uint8_t* modes, int K, int map, int outside_zero, int32_t* err_flag,
+                      void* stream);
+
 /* ---- K10: optimiser step on flat buffers -------------------------------------------------------
  * Replaces torch.optim.Adam(...).step() of the reference's training loops (runcred.py:192,257; run.py:139:
  * lr, weight_decay, default betas / eps, amsgrad off) when parameters, gradients and both moments each live in

@@ -64,6 +64,8 @@ _SIGNATURES = {
     "vcnf_checkerboard": [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
     "vcnf_adam_flat_guarded": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _dbl, _dbl, _dbl, _dbl, _dbl, _vp, _i32, _i32,
                                _vp],
+    "vcnf_made_inverse": [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32,
+                          _i32, _vp, _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
 }
 _I64_RETURN = {

@@ -219,7 +219,9 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
 
 // ------------------------------------------------------------------------------------------------ implicit GEMM
 constexpr int kStages = 4;
-constexpr int kThreads = 192;                 // warp 0 producer, warp 1 MMA, warps 2-5 epilogue
+constexpr int kEpiWarps = 8;                  // two warps per TMEM lane quarter, alternating 32-column chunks
+constexpr int kThreads = (2 + kEpiWarps) * 32;   // warp 0 producer, warp 1 MMA, warps 2-9 epilogue
+constexpr int kWgThreads = 192;               // weight-gradient kernel: warp 0 producer, warp 1 MMA, warps 2-5 epilogue
 constexpr uint32_t kATile = 128 * 128;        // 128 pixels x 64 bf16 channels
 constexpr uint32_t kWTileMax = 256 * 128;     // <= 256 output channels x 64 bf16 channels
 constexpr uint32_t kStageBytes = kATile + kWTileMax;
@@ -258,7 +260,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_bf16_kernel(const GemmA
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull + s, 1); mbar_init(tempty + s, kEpiWarps); }
     mbar_init_fence();
   }
   if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
@@ -322,12 +324,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_bf16_kernel(const GemmA
       }
     }
   } else {
-    // ---------------- epilogue: warp w may read TMEM lanes [32 (w % 4), 32 (w % 4) + 32)
+    // ---------------- epilogue: warp w may read TMEM lanes [32 (w % 4), 32 (w % 4) + 32); the two warps of a lane
+    // quarter take alternate 32-column chunks.  (With one warp per scheduler the epilogue -- ~300 dependent
+    // instructions per chunk -- was the whole kernel: 15 k cycles per 128 x 256 tile against ~2 k for the MMAs; ncu:
+    // tensor pipe 9.5 % active, issue 11.6 %.  Vector bias / mask loads, fmax for slope 0 and twice the warps.)
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;          // 0 or 1
     const int r = q * 32 + lane;               // pixel row of the tile
     const int w_ = r % a.BW;
     const int h_ = (r / a.BW) % a.BH;
     const int bb = r / (a.BW * a.BH);
+    const bool relu = a.slope == 0.f;
     uint32_t tcount = 0;
     for (int64_t tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const uint32_t buf = tcount & 1;
@@ -340,36 +347,51 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_bf16_kernel(const GemmA
       mbar_wait_sleep(tfull + buf, (tcount >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(q * 32) << 16);
-      for (int c0 = 0; c0 < a.NT; c0 += 32) {
+      for (int c0 = half * 32; c0 < a.NT; c0 += 64) {
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
-        tmem_ld_wait();
         const int nbase = n * a.NT + c0;
+        const int ncol = a.NT - c0 < 32 ? a.NT - c0 : 32;      // 16 or 32 (NT is a multiple of 16)
+        float4 bv[8];
+        if (a.bias) {
+          const float4* bp = reinterpret_cast<const float4*>(a.bias + nbase);
+#pragma unroll
+          for (int g = 0; g < 8; ++g) bv[g] = (g * 4 < ncol) ? __ldg(bp + g) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        uint4 mv[4];
+        if (a.epi == 2 && live) {
+          const uint4* mp = reinterpret_cast<const uint4*>(a.mask + p * a.ldm + nbase);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) mv[g] = (g * 8 < ncol) ? __ldg(mp + g) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        tmem_ld_wait();
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
         if (a.bias) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c0 + j < a.NT) f[j] += __ldg(a.bias + nbase + j);
+          for (int g = 0; g < 8; ++g) {
+            f[g * 4 + 0] += bv[g].x; f[g * 4 + 1] += bv[g].y; f[g * 4 + 2] += bv[g].z; f[g * 4 + 3] += bv[g].w;
+          }
         }
         if (a.epi == 1) {
+          if (relu) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = f[j] > 0.f ? f[j] : f[j] * a.slope;
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = f[j] > 0.f ? f[j] : f[j] * a.slope;
+          }
         } else if (a.epi == 2 && live) {
-          const uint4* mp = reinterpret_cast<const uint4*>(a.mask + p * a.ldm + nbase);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            if (c0 + g * 8 < a.NT) {
-              const uint4 mv = __ldg(mp + g);
-              const uint32_t mw[4] = {mv.x, mv.y, mv.z, mv.w};
+            const uint32_t mw[4] = {mv[g].x, mv[g].y, mv[g].z, mv[g].w};
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                // bf16 sign / zero test on the raw halves: value > 0  <=>  sign clear and magnitude non-zero
-                const uint32_t lo = mw[j] & 0xffffu, hi = mw[j] >> 16;
-                if (!(lo != 0u && lo < 0x8000u)) f[g * 8 + 2 * j] *= a.slope;
-                if (!(hi != 0u && hi < 0x8000u)) f[g * 8 + 2 * j + 1] *= a.slope;
-              }
+            for (int j = 0; j < 4; ++j) {
+              // bf16 sign / zero test on the raw halves: value > 0  <=>  sign clear and magnitude non-zero
+              const uint32_t lo = mw[j] & 0xffffu, hi = mw[j] >> 16;
+              if (!(lo != 0u && lo < 0x8000u)) f[g * 8 + 2 * j] *= a.slope;
+              if (!(hi != 0u && hi < 0x8000u)) f[g * 8 + 2 * j + 1] *= a.slope;
             }
           }
         }
@@ -378,7 +400,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_bf16_kernel(const GemmA
             __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(a.out) + p * a.ldo + nbase;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-              if (c0 + g * 8 < a.NT) {
+              if (g * 8 < ncol) {
                 uint4 o;
                 __nv_bfloat162 t0 = __floats2bfloat162_rn(f[g * 8 + 0], f[g * 8 + 1]);
                 __nv_bfloat162 t1 = __floats2bfloat162_rn(f[g * 8 + 2], f[g * 8 + 3]);
@@ -395,7 +417,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_gemm_bf16_kernel(const GemmA
             const int64_t base = b * a.Cout * hw + static_cast<int64_t>(h) * a.W + w_;
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-              if (c0 + j < a.NT && nbase + j < a.Cout) op[base + (nbase + j) * hw] = f[j];
+              if (j < ncol && nbase + j < a.Cout) op[base + (nbase + j) * hw] = f[j];
           }
         }
       }
@@ -423,7 +445,7 @@ struct WgArgs {
   float* partial;                // [splits][m_tiles*128][Ny]
 };
 
-__global__ void __launch_bounds__(kThreads, 1) conv_wgrad_bf16_kernel(const WgArgs a,
+__global__ void __launch_bounds__(kWgThreads, 1) conv_wgrad_bf16_kernel(const WgArgs a,
                                                                        const __grid_constant__ CUtensorMap tm_x,
                                                                        const __grid_constant__ CUtensorMap tm_y) {
   extern __shared__ unsigned char smem_raw[];
@@ -662,6 +684,8 @@ int vcnf_conv_gemm_bf16(const void* act, int64_t B, int H, int W, int Cp, int ta
   if (epi == 2 && (NT % 32 != 0 || ldm % 8 != 0)) return VCNF_E_UNSUPPORTED;
   a.NT = NT;
   a.n_tiles = Np / NT;
+  if (bias && reinterpret_cast<uintptr_t>(bias) % 16 != 0) return VCNF_E_UNSUPPORTED;   // read as float4
+  if (mask && reinterpret_cast<uintptr_t>(mask) % 16 != 0) return VCNF_E_UNSUPPORTED;
   a.bias = static_cast<const float*>(bias);
   a.mask = static_cast<const __nv_bfloat16*>(mask);
   a.ldm = ldm;
@@ -747,7 +771,7 @@ int vcnf_conv_wgrad_bf16(const void* X, int64_t ldx, int Mx, const void* Y, int6
     attr = true;
   }
   const unsigned grid = static_cast<unsigned>(a.m_tiles * a.n_tiles * a.splits);
-  conv::conv_wgrad_bf16_kernel<<<grid, conv::kThreads, conv::kSmemWg, st>>>(a, tm_x, tm_y);
+  conv::conv_wgrad_bf16_kernel<<<grid, conv::kWgThreads, conv::kSmemWg, st>>>(a, tm_x, tm_y);
   int rc = launch_status();
   if (rc) return rc;
   const int64_t n = static_cast<int64_t>(Mx) * Ny;

@@ -30,6 +30,11 @@ class Autoregressive(Flow):
     # zero), 1 / D of the final layer's work and of the [B, D P] parameter traffic in D - 1 of D passes.
     # `full_inverse = True` keeps the reference's loop (tests compare the two).
     full_inverse = False
+    # One more exact reduction (default): the hidden units of degree t are final after pass t, so the whole D-pass
+    # loop needs ONE evaluation of MADE, done band by band inside a single kernel launch (vcnf_made_inverse,
+    # csrc/made_kernels.cu).  Same dot products in a different summation order: equal to the loop within 1e-5.
+    # `fused_inverse = False` keeps the sliced passes above (bit-identical to the reference's loop).
+    fused_inverse = True
 
     def _sliced_inverse_ok(self, inputs, context):
         net = self.autoregressive_net
@@ -67,8 +72,27 @@ class Autoregressive(Flow):
                 outputs[:, f] = self._inverse_feature(inputs[:, f:f + 1], params_f, f)[:, 0]
             return self._elementwise_inverse(inputs, net(outputs))
 
+    def _fused_spec(self):
+        """(map code, K, modes, bounds, outside_zero) of the elementwise inverse for vcnf_made_inverse; None when the
+        layer's map is not one the kernel evaluates."""
+        return None
+
+    def _inverse_fused(self, inputs):
+        net = self.autoregressive_net
+        spec = self._fused_spec()
+        if spec is None or not self.fused_inverse or inputs.dtype != torch.float32 or not net.sampling_kernel_ok():
+            return None
+        packed = net.pack_for_sampling()
+        if packed is None:
+            return None
+        map_code, K, modes, bounds, oz = spec
+        return ops.made_inverse(inputs, packed, map_code, K, modes, bounds, oz)
+
     def inverse(self, inputs, context=None):
         if self._sliced_inverse_ok(inputs, context):
+            out = self._inverse_fused(inputs)
+            if out is not None:
+                return out
             return self._inverse_sliced(inputs)
         num_inputs = int(np.prod(inputs.shape[1:]))
         outputs = torch.zeros_like(inputs)
@@ -113,6 +137,9 @@ class MaskedAffineAutoregressive(Autoregressive):
     def _elementwise_inverse(self, inputs, autoregressive_params):
         return ops.affine_coupling(inputs, autoregressive_params, 0, self.features,
                                    ops.SCALE_MAPS["maf"], True, swap_ts=True)
+
+    def _fused_spec(self):
+        return 0, 0, None, None, False
 
     def _inverse_feature(self, x_f, params_f, f):
         """One column of `_elementwise_inverse`: x_f [B, 1], params_f [B, 2] = (u, shift) of feature f."""

@@ -76,6 +76,18 @@ class MaskedPiecewiseRationalQuadraticAutoregressive(Autoregressive):
     def _elementwise_inverse(self, inputs, autoregressive_params):
         return self._elementwise(inputs, autoregressive_params, inverse=True)
 
+    def _fused_spec(self):
+        if hasattr(self.autoregressive_net, "hidden_features"):
+            return None                                      # (MADE has none: the parameters are not rescaled, A.8)
+        D = self.features
+        cache = self.__dict__.setdefault("_fused_cache", {})
+        dev = self.autoregressive_net.initial_layer.weight.device
+        if cache.get("dev") != dev:
+            modes, bounds = _modes_and_bounds(self.tails, self.tail_bound, D)
+            cache.update(dev=dev, modes=torch.tensor(modes, dtype=torch.uint8, device=dev),
+                         bounds=torch.tensor(bounds, dtype=torch.float32, device=dev))
+        return 1, self.num_bins, cache["modes"], cache["bounds"], isinstance(self.tails, (list, tuple))
+
     def _inverse_feature(self, x_f, params_f, f):
         """One column of `_elementwise_inverse` (affine/autoregressive.py `_inverse_sliced`): x_f [B, 1],
         params_f [B, P] = the parameters of feature f."""

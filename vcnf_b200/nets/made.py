@@ -125,6 +125,7 @@ class MADE(nn.Module):
             raise ValueError("Residual blocks can't be used with random masks.")
         super().__init__()
         self.preprocessing = (lambda inputs: inputs) if preprocessing is None else preprocessing
+        self._plain_inputs = preprocessing is None
         input_degrees_ = _get_input_degrees(features)
         if permute_mask:
             input_degrees_ = input_degrees_[torch.randperm(features)]
@@ -173,6 +174,81 @@ class MADE(nn.Module):
                         m._masked = None
                 return False
         return _Frozen()
+
+    def sampling_kernel_ok(self):
+        """vcnf_made_inverse covers: residual blocks (<= 2) with ReLU, no preprocessing / context / batch norm / active
+        dropout, fp32 CUDA parameters, widths that split over 8 warps, <= 8 hidden units per degree, one degree
+        vector shared by all hidden layers."""
+        if not getattr(self, "_plain_inputs", False) or hasattr(self, "context_layer"):
+            return False
+        if not all(isinstance(b, MaskedResidualBlock) for b in self.blocks) or not 1 <= 1 + 2 * len(self.blocks) <= 5:
+            return False
+        w = self.initial_layer.weight
+        if not w.is_cuda or w.dtype != torch.float32:
+            return False
+        H, D = w.shape
+        P = self.final_layer.weight.shape[0] // D
+        nl, Pp = 1 + 2 * len(self.blocks), (P + 3) // 4 * 4
+        smem = ((D + (nl - 1) * H) * 8 + nl * 8 + (H + 1) * Pp + (2 * D + nl * H + 16 * 32 + 32) * 16) * 4
+        if D % 16 or H % 16 or P > 32 or smem > 220 * 1024:
+            return False
+        for b in self.blocks:
+            relu = b.activation is F.relu or b.activation is torch.relu or isinstance(b.activation, nn.ReLU)
+            if b.use_batch_norm or not relu or (b.dropout.p > 0. and b.training) or hasattr(b, "context_layer"):
+                return False
+        return True
+
+    def pack_for_sampling(self):
+        """Operands of vcnf_made_inverse (include/vcnf_b200.h): per-degree bands of the masked weights of every hidden
+        layer, the final layer's rows grouped by feature in degree order.  Built per call (the weights are frozen only
+        for its duration); None when the degree structure does not fit the kernel."""
+        dev = self.initial_layer.weight.device
+        H, D = self.initial_layer.weight.shape
+        fl = self.final_layer
+        P = fl.weight.shape[0] // D
+        hdeg = self.initial_layer.degrees
+        layers = [self.initial_layer]
+        for b in self.blocks:
+            layers += list(b.linear_layers)
+        cache = self.__dict__.setdefault("_pack_index", {})
+        key = (str(dev), hdeg.data_ptr(), hdeg._version, fl.degrees.data_ptr(), fl.degrees._version)
+        if cache.get("key") != key:
+            if any(not torch.equal(l.degrees, hdeg) for l in layers[1:]):
+                cache.update(key=key, ok=False)
+            else:
+                hd = hdeg.cpu().tolist()
+                bands = [[j for j, d in enumerate(hd) if d == t] for t in range(D)]
+                fdeg = fl.degrees[::P].cpu()
+                ok = max(len(b) for b in bands) <= 8 and max(hd) <= D - 1 and sorted(fdeg.tolist()) == list(range(1, D + 1))
+                idx = torch.full((D, 8), -1, dtype=torch.int32)
+                for t, b in enumerate(bands):
+                    if b and len(b) <= 8:
+                        idx[t, :len(b)] = torch.tensor(b, dtype=torch.int32)
+                order = torch.argsort(fdeg, stable=True).to(torch.int32)
+                cache.update(key=key, ok=ok, band_idx=idx.to(dev), band_units=max(len(b) for b in bands), gather=torch.where(idx < 0, H, idx).long().view(-1).to(dev),
+                             order=order.to(dev), order_l=order.long().to(dev))
+        if not cache["ok"]:
+            return None
+        gather = cache["gather"]
+        Pp = (P + 3) // 4 * 4
+        Wb, bb = [], []
+        with torch.no_grad():
+            for l in layers:
+                wm = l._masked if l._masked is not None else l.weight * l.mask
+                hin = wm.shape[1]
+                ext = torch.cat([wm, wm.new_zeros(1, hin)])
+                Wb.append(ext[gather].view(D, 8, hin).permute(0, 2, 1).reshape(D, hin * 8))
+                bias = l.bias if l.bias is not None else wm.new_zeros(H)
+                bb.append(torch.cat([bias, bias.new_zeros(1)])[gather].view(D, 8))
+            band = torch.cat(Wb + bb, dim=1).contiguous()              # one contiguous block per pass
+            wf = fl._masked if fl._masked is not None else fl.weight * fl.mask
+            wf = wf.view(D, P, H)[cache["order_l"]]
+            Wf = F.pad(wf, (0, 0, 0, Pp - P)).permute(0, 2, 1).reshape(D, H * Pp)
+            bfv = fl.bias if fl.bias is not None else wf.new_zeros(D * P)
+            bf = F.pad(bfv.view(D, P)[cache["order_l"]], (0, Pp - P))
+            fin = torch.cat([Wf, bf], dim=1).contiguous()
+        return dict(H=H, P=P, n_layers=len(layers), band=band, fin=fin, band_idx=cache["band_idx"], order=cache["order"],
+                    band_units=cache["band_units"])
 
     def final_rows(self, h, lo, hi):
         """Outputs [lo, hi) of the final layer only -- the same dot products as `forward(...)[:, lo:hi]`."""

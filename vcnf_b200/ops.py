@@ -1152,3 +1152,17 @@ def checkerboard_split(z, inv):
 def checkerboard_merge(z1, z2, inv):
     z1, z2 = _promote(z1, z2)
     return _Checkerboard.apply(bool(inv), True, z1, z2)
+
+
+# ------------------------------------------------------------------ autoregressive sampling (K7)
+def made_inverse(y, packed, map_code, K=0, modes=None, bounds=None, outside_zero=False):
+    """All D passes of an autoregressive layer's sampling direction in one launch (vcnf_made_inverse); `packed` is
+    the dict built by nets.made.MADE.pack_for_sampling().  Returns (x, logabsdet).  No gradient."""
+    y = y.contiguous()
+    B, D = y.shape
+    x = torch.empty_like(y)
+    ld = torch.empty(B, dtype=y.dtype, device=y.device)
+    _launch("vcnf_made_inverse", ptr(y), ptr(x), ptr(ld), B, D, packed["H"], packed["P"], packed["n_layers"],
+            ptr(packed["band"]), ptr(packed["fin"]), ptr(packed["band_idx"]), ptr(packed["order"]),
+            packed["band_units"], ptr(bounds), ptr(modes), int(K), int(map_code), int(outside_zero), None, stream())
+    return x, ld
