@@ -320,9 +320,9 @@ def measure_config(name, dev, world, rank, steps, warmup, flush, batch=None, wit
         # data-dependent ActNorm initialisation first (one eager step's forward), then the capturable optimiser
         with torch.no_grad():
             loss_fn(model, x_dev.clone())
-        opt = torch.optim.Adamax(model.parameters(), lr=spec["lr"], weight_decay=spec["wd"], capturable=True)
-        bucket = parallel.GradBucket(model.parameters())
-        opt_name = "torch Adamax(capturable)"
+        opt = nf.optim.FlatAdamax(model.parameters(), lr=spec["lr"], weight_decay=spec["wd"])
+        bucket = opt.bucket
+        opt_name = "Adamax, flat buffers (vcnf_adamax_flat_guarded)"
     else:
         if name == "cfg4":
             with torch.no_grad():

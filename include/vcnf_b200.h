@@ -175,6 +175,13 @@ int64_t vcnf_small_linear_bwd_workspace(int D, int dtype);
 int vcnf_small_linear_bwd(const void* x, const void* gy, const void* W, const int32_t* in_idx, const int32_t* out_idx,
                           void* gx, void* gW, void* gb, void* workspace, int64_t rows, int D, int dtype, void* stream);
 
+/* Parameter gradients of the same map on image tensors x, gy [B, D, S] (autograd of Invertible1x1Conv's conv2d,
+ * mixing.py:101-128): gW[o, i] = sum_{b,s} gy[b, out_idx[o], s] x[b, in_idx[i], s], gb[o] = sum gy[b, out_idx[o], s]
+ * (either output may be NULL).  Operands are read in place; fixed-order reduction.  D <= 64. */
+int64_t vcnf_small_linear_wgrad_img_workspace(int D, int dtype);
+int vcnf_small_linear_wgrad_img(const void* x, const void* gy, const int32_t* in_idx, const int32_t* out_idx, void* gW,
+                                void* gb, void* workspace, int64_t B, int D, int S, int dtype, void* stream);
+
 /* ---- LU-parametrised weight (normflow/flows/mixing.py:352-396, _create_lower_upper / weight / logabsdet) --
  * W[D, D] = L U and *logabsdet = sum_i log diag(U)_i from the parameter vectors, one launch:
  *   lower_entries [D(D-1)/2]  strictly-lower part of L in np.tril_indices(D, -1) order (L has a unit diagonal)
@@ -240,6 +247,17 @@ int vcnf_col2im(const void* gcol, int64_t ldcol, const void* src, void* gsrc, in
 int64_t vcnf_colsum_workspace(int C);
 int vcnf_colsum(const void* X, int layout, int64_t rows, int C, int64_t ld_or_S, void* out, void* workspace,
                 void* stream);
+/* All bf16 weight layouts of one ConvNet2d (nets/cnn.py:29-47: conv3x3 C0->Hd, conv1x1 Hd->Hd, conv3x3 Hd->C3; fp32
+ * weights w1 [Hd,C0,3,3], w2 [Hd,Hd,1,1], w3 [C3,Hd,3,3]) in one launch.  Segments of out_bf16, in order, with
+ * K1p = ceil64(9 C0), Np3 = ceil16(C3), K3p = ceil64(9 C3), Np1 = ceil16(C0), t = 3 ky + kx, zero padding:
+ *   w1p [Hd][K1p] (w1p[o][t C0 + c] = w1[o][c][ky][kx]) | w2p [Hd][Hd] | w3p [9][Np3][Hd] (w3p[t][o][i] = w3[o][i][ky][kx])
+ *   and, when with_bwd != 0, the operands of the input-gradient convolutions:
+ *   wd3 [Hd][K3p] (wd3[i][t C3 + o] = w3[o][i][ky][kx]) | wd2 [Hd][Hd] = w2^T | wd1 [9][Np1][Hd] (wd1[t][c][o] =
+ *   w1[o][c][2-ky][2-kx]).  b3p [Np3] fp32 = b3 (may be NULL) zero-padded.  vcnf_convnet3_pack_elems = length of out_bf16. */
+int64_t vcnf_convnet3_pack_elems(int C0, int Hd, int C3, int with_bwd);
+int vcnf_convnet3_pack(const void* w1, const void* w2, const void* w3, const void* b3, int C0, int Hd, int C3, int with_bwd,
+                       void* out_bf16, void* b3p, void* stream);
+
 /* Implicit-GEMM convolution on the tcgen05 tensor cores, bf16 operands, fp32 accumulation (replaces F.conv2d and,
  * with transposed / flipped weights, its input gradient):
  *   out[p, n] = epi( sum_{t < taps} sum_{c < Cp} act[p (+) t, c] * Wp[t][n][c] + bias[n] )
@@ -348,6 +366,18 @@ int vcnf_axpb(const void* x, const void* noise, void* out, int64_t total, double
 int vcnf_checkerboard(void* z, void* z1, void* z2, const uint8_t* mid_parity, int64_t B, int M, int W, int inv, int merge,
                       int dtype, void* stream);
 
+/* ---- Glow's LU-parametrised 1x1 convolution weight (normflow/flows/mixing.py:83-102 `_assemble_W`, :117-118) ----
+ * W[C, C] = P (tril(L, -1) + I) (triu(U, 1) + diag(sign_S exp(log_S))) and *logdet = ld_scale * sum(log_S) in one
+ * launch (ld_scale = +-H W of the call site, mixing.py:123).  P, L, U are the module's full C x C tensors, sign_S /
+ * log_S [C].  C <= 64.  Replaces tril, triu, diag, exp, two matmuls, sum and the scalar multiply. */
+int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, const void* sign_S, const void* log_S, int C,
+                    double ld_scale, void* W, void* logdet, int dtype, void* stream);
+/* Adjoint: gW [C, C] (may be NULL) and g_logdet [1] (may be NULL) -> gL, gU [C, C] (zero outside the strict triangles,
+ * like autograd through tril / triu) and g_log_S [C]. */
+int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, const void* sign_S, const void* log_S, int C,
+                    double ld_scale, const void* gW, const void* g_logdet, void* gL, void* gU, void* g_log_S, int dtype,
+                    void* stream);
+
 /* ---- K7: autoregressive layers in the sampling direction, all D passes in one launch ----------------------------
  * Replaces the D-pass loop of normflow/flows/affine/autoregressive.py:29-36 (each pass: MADE, nets/made.py:288-299, then
  * the elementwise inverse, flows/affine/autoregressive.py:92-103 or flows/neural_spline/autoregressive.py:92-131) for a
@@ -389,6 +419,12 @@ int vcnf_adam_flat(void* p, const void* g, void* m, void* v, void* step, void* t
 int vcnf_adam_flat_guarded(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n,
                            const void* lr_dev, double beta1, double beta2, double eps, double weight_decay,
                            double grad_scale, const void* guard, int guard_dtype, int dtype, void* stream);
+
+/* Adamax on the same flat buffers (torch.optim.Adamax of example/glow.ipynb:88): u = max(beta2 u, |g'| + eps),
+ * p -= lr / (1 - beta1^t) * m / u; arguments as vcnf_adam_flat_guarded (`u` in place of `v`). */
+int vcnf_adamax_flat_guarded(void* p, const void* g, void* m, void* u, void* step, void* ticket, int64_t n,
+                             const void* lr_dev, double beta1, double beta2, double eps, double weight_decay,
+                             double grad_scale, const void* guard, int guard_dtype, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

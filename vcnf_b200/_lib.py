@@ -64,6 +64,12 @@ _SIGNATURES = {
     "vcnf_checkerboard": [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _vp],
     "vcnf_adam_flat_guarded": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _dbl, _dbl, _dbl, _dbl, _dbl, _vp, _i32, _i32,
                                _vp],
+    "vcnf_adamax_flat_guarded": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _dbl, _dbl, _dbl, _dbl, _dbl, _vp, _i32, _i32,
+                               _vp],
+    "vcnf_small_linear_wgrad_img": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
+    "vcnf_convnet3_pack": [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
+    "vcnf_glow_w_fwd": [_vp, _vp, _vp, _vp, _vp, _i32, _dbl, _vp, _vp, _i32, _vp],
+    "vcnf_glow_w_bwd": [_vp, _vp, _vp, _vp, _vp, _i32, _dbl, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
     "vcnf_made_inverse": [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32,
                           _i32, _vp, _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
@@ -71,6 +77,8 @@ _SIGNATURES = {
 _I64_RETURN = {
     "vcnf_rqs_layer_bwd_workspace": [_i32, _i32, _i32],
     "vcnf_const_affine_bwd_workspace": [_i32, _i32],
+    "vcnf_small_linear_wgrad_img_workspace": [_i32, _i32],
+    "vcnf_convnet3_pack_elems": [_i32, _i32, _i32, _i32],
     "vcnf_linear_wgrad_workspace": [_i64, _i32, _i32],
     "vcnf_small_linear_bwd_workspace": [_i32, _i32],
     "vcnf_mlp_bwd_workspace": [_vp, _i32, _i32],

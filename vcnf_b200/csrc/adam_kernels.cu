@@ -19,19 +19,27 @@ struct AdamCoef {
   T b1, b2, omb1, omb2, wd, eps;
 };
 
-template <typename T>
+// ALGO 0: Adam.  ALGO 1: Adamax (the Glow notebook's optimiser, example/glow.ipynb:88: torch.optim.Adamax): the second
+// moment is the running infinity norm u = max(b2 u, |g| + eps) and the step is lr / (1 - b1^t) * m / u.
+template <typename T, int ALGO>
 __device__ __forceinline__ void adam_one(T& p, T g, T& m, T& v, const AdamCoef<T>& c, T step_size, T inv_sqrt_bc2) {
   g = g + c.wd * p;                                   // wd == 0: exact
   m = c.b1 * m + c.omb1 * g;
-  v = c.b2 * v + c.omb2 * g * g;
-  const T denom = sqrt(v) * inv_sqrt_bc2 + c.eps;
-  p = p - step_size * (m / denom);
+  if (ALGO == 0) {
+    v = c.b2 * v + c.omb2 * g * g;
+    const T denom = sqrt(v) * inv_sqrt_bc2 + c.eps;
+    p = p - step_size * (m / denom);
+  } else {
+    const T a = c.b2 * v, b = (g < T(0) ? -g : g) + c.eps;
+    v = (a > b || b != b) ? (b != b ? b : a) : b;      // max that propagates NaN like torch.amax
+    p = p - step_size * (m / v);
+  }
 }
 
 // `step` (device, fp32 like torch's capturable step tensors) holds the number of steps taken so far; every CTA reads
 // it before any CTA can advance it: the LAST CTA to finish (ticket counter) writes step + 1 and clears the ticket,
 // so a captured launch replays correctly with no second kernel.
-template <typename T, typename V, int W>
+template <typename T, typename V, int W, int ALGO>
 __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(T* __restrict__ p, const T* __restrict__ g,
                                                                  T* __restrict__ m, T* __restrict__ v,
                                                                  float* step, unsigned* ticket, int64_t n, double lr,
@@ -84,14 +92,14 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(T* __restrict__
     T* mp = reinterpret_cast<T*>(&M);
     T* vp = reinterpret_cast<T*>(&Vv);
 #pragma unroll
-    for (int k = 0; k < W; ++k) adam_one(pp[k], gp[k] * gsc, mp[k], vp[k], c, step_size, isb);
+    for (int k = 0; k < W; ++k) adam_one<T, ALGO>(pp[k], gp[k] * gsc, mp[k], vp[k], c, step_size, isb);
     pv[i] = P;
     mv[i] = M;
     vv[i] = Vv;
   }
   if (blockIdx.x == 0) {                                // ragged tail (n not a multiple of the vector width)
     for (int64_t i = nv * W + threadIdx.x; i < n; i += kAdamThreads)
-      adam_one(p[i], g[i] * gsc, m[i], v[i], c, step_size, isb);
+      adam_one<T, ALGO>(p[i], g[i] * gsc, m[i], v[i], c, step_size, isb);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -111,7 +119,7 @@ using namespace vcnf;
 
 static int adam_launch(void* p, const void* g, void* m, void* v, void* step, void* ticket, int64_t n, double lr,
                        double beta1, double beta2, double eps, double weight_decay, double grad_scale,
-                       const void* lr_dev, const void* guard, int guard_dtype, int dtype, void* stream) {
+                       const void* lr_dev, const void* guard, int guard_dtype, int dtype, void* stream, int algo = 0) {
   if (n < 0 || (dtype != VCNF_F32 && dtype != VCNF_F64) || !step || !ticket ||
       (guard && guard_dtype != VCNF_F32 && guard_dtype != VCNF_F64))
     return VCNF_E_BADARG;
@@ -127,16 +135,19 @@ static int adam_launch(void* p, const void* g, void* m, void* v, void* step, voi
   const int64_t cap = 8 * static_cast<int64_t>(sm_count());
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  if (dtype == VCNF_F32)
-    adam_flat_kernel<float, float4, 4><<<static_cast<unsigned>(blocks), kAdamThreads, 0, st>>>(
-        static_cast<float*>(p), static_cast<const float*>(g), static_cast<float*>(m), static_cast<float*>(v),
-        static_cast<float*>(step), static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay, grad_scale,
-        static_cast<const double*>(lr_dev), guard, guard_dtype);
-  else
-    adam_flat_kernel<double, double2, 2><<<static_cast<unsigned>(blocks), kAdamThreads, 0, st>>>(
-        static_cast<double*>(p), static_cast<const double*>(g), static_cast<double*>(m), static_cast<double*>(v),
-        static_cast<float*>(step), static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay, grad_scale,
-        static_cast<const double*>(lr_dev), guard, guard_dtype);
+#define VCNF_ADAM_LAUNCH(T, V, W, ALGO)                                                                              \
+  adam_flat_kernel<T, V, W, ALGO><<<static_cast<unsigned>(blocks), kAdamThreads, 0, st>>>(                            \
+      static_cast<T*>(p), static_cast<const T*>(g), static_cast<T*>(m), static_cast<T*>(v), static_cast<float*>(step), \
+      static_cast<unsigned*>(ticket), n, lr, beta1, beta2, eps, weight_decay, grad_scale,                             \
+      static_cast<const double*>(lr_dev), guard, guard_dtype)
+  if (dtype == VCNF_F32) {
+    if (algo == 0) VCNF_ADAM_LAUNCH(float, float4, 4, 0);
+    else VCNF_ADAM_LAUNCH(float, float4, 4, 1);
+  } else {
+    if (algo == 0) VCNF_ADAM_LAUNCH(double, double2, 2, 0);
+    else VCNF_ADAM_LAUNCH(double, double2, 2, 1);
+  }
+#undef VCNF_ADAM_LAUNCH
   return launch_status();
 }
 
@@ -152,4 +163,12 @@ extern "C" int vcnf_adam_flat_guarded(void* p, const void* g, void* m, void* v, 
   if (!lr_dev) return VCNF_E_BADARG;
   return adam_launch(p, g, m, v, step, ticket, n, 0.0, beta1, beta2, eps, weight_decay, grad_scale, lr_dev, guard,
                      guard_dtype, dtype, stream);
+}
+
+extern "C" int vcnf_adamax_flat_guarded(void* p, const void* g, void* m, void* u, void* step, void* ticket, int64_t n,
+                                        const void* lr_dev, double beta1, double beta2, double eps, double weight_decay,
+                                        double grad_scale, const void* guard, int guard_dtype, int dtype, void* stream) {
+  if (!lr_dev) return VCNF_E_BADARG;
+  return adam_launch(p, g, m, u, step, ticket, n, 0.0, beta1, beta2, eps, weight_decay, grad_scale, lr_dev, guard,
+                     guard_dtype, dtype, stream, 1);
 }

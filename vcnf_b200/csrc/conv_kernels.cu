@@ -59,6 +59,45 @@ __global__ void __launch_bounds__(256) im2col_kernel(const float* __restrict__ s
   }
 }
 
+// bf16 patch matrix, one thread per (pixel, 8 adjacent columns): blockIdx.y = column group, consecutive threads =
+// consecutive pixels, so for an NCHW source each of the 8 gathers is a coalesced read of the warp and the 8 values leave
+// as one 16 B store (the element-per-thread kernel above: 64-bit divisions and 2 B stores, 48 us for 16 MB).
+__global__ void __launch_bounds__(256) im2col_bf16_vec_kernel(const float* __restrict__ src, int64_t sb, int64_t sc, int64_t sh,
+                                                             int64_t sw, __nv_bfloat16* __restrict__ col, int64_t ldcol,
+                                                             int P, int C, int H, int W, int T, int flip, int act,
+                                                             float slope) {
+  const int k0 = blockIdx.y * 8;
+  int t0 = k0 / C, c0 = k0 - t0 * C;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < P; p += gridDim.x * blockDim.x) {
+    const int w = p % W, bh = p / W;
+    const int h = bh % H, b = bh / H;
+    const float* base = src + static_cast<int64_t>(b) * sb;
+    int t = t0, c = c0;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[j] = 0.f;
+      if (t < T) {
+        int dy = 0, dx = 0;
+        if (T == 9) { dy = t / 3 - 1; dx = t - (t / 3) * 3 - 1; }
+        if (flip) { dy = -dy; dx = -dx; }
+        const int hh = h + dy, ww = w + dx;
+        if (hh >= 0 && hh < H && ww >= 0 && ww < W) {
+          float x = __ldg(base + c * sc + hh * sh + ww * sw);
+          if (act && x < 0.f) x *= slope;
+          v[j] = x;
+        }
+      }
+      if (++c == C) { c = 0; ++t; }
+    }
+    uint4 o;
+    __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ho[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    *reinterpret_cast<uint4*>(col + static_cast<int64_t>(p) * ldcol + k0) = o;
+  }
+}
+
 // Adjoint of im2col (fp32): gsrc[b, c, h, w] = act'(src) * sum_t gcol[p - s*off(t), t*C + c]  (gather form: every
 // output element is written once, no atomics).
 __global__ void __launch_bounds__(256) col2im_kernel(const float* __restrict__ gcol, int64_t ldcol,
@@ -103,6 +142,53 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
     partial[static_cast<int64_t>(chunk) * C + c] = acc;
   }
 }
+// Same sums for C % 8 == 0, C <= 256, 16 B aligned rows: a thread owns 8 adjacent channels (one 16 B load per row) and
+// every (256 / (C / 8))-th row of the chunk, four rows in flight; the row groups are then added in a fixed order.
+__global__ void __launch_bounds__(256) colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ X, int64_t ld, int64_t P,
+                                                             int C, int64_t rows_per_chunk, float* __restrict__ partial) {
+  __shared__ float red[256 * 8];
+  const int chunk = blockIdx.x, lanes = C >> 3, groups = 256 / lanes;
+  const int cl = threadIdx.x % lanes, g = threadIdx.x / lanes;
+  const int64_t p0 = chunk * rows_per_chunk, p1 = p0 + rows_per_chunk < P ? p0 + rows_per_chunk : P;
+  float acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+  if (g < groups) {
+    const __nv_bfloat16* col = X + cl * 8;
+    int64_t p = p0 + g;
+    for (; p + 3 * groups < p1; p += 4 * groups) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(col + (p + static_cast<int64_t>(u) * groups) * ld);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __bfloat1622float2(h[k]);
+          acc[2 * k] += f.x; acc[2 * k + 1] += f.y;
+        }
+      }
+    }
+    for (; p < p1; p += groups) {
+      const uint4 v = *reinterpret_cast<const uint4*>(col + p * ld);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = __bfloat1622float2(h[k]);
+        acc[2 * k] += f.x; acc[2 * k + 1] += f.y;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) red[(g * lanes + cl) * 8 + k] = acc[k];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float t = 0.f;
+    for (int gg = 0; gg < groups; ++gg) t += red[gg * C + c];
+    partial[static_cast<int64_t>(chunk) * C + c] = t;
+  }
+}
 __global__ void __launch_bounds__(256) chansum_nchw_kernel(const float* __restrict__ X, int64_t B, int C, int S,
                                                           int64_t b_per_chunk, float* __restrict__ partial) {
   __shared__ float red[256];
@@ -125,6 +211,60 @@ __global__ void sum_partials_kernel(const float* __restrict__ partial, int n_chu
   float acc = 0.f;
   for (int k = 0; k < n_chunks; ++k) acc += partial[static_cast<int64_t>(k) * n + i];
   out[i] = acc;
+}
+
+
+// ------------------------------------------------------------------------------------------------ weight packs
+// All bf16 operand layouts of one ConvNet2d (3x3 C0 -> Hd, 1x1 Hd -> Hd, 3x3 Hd -> C3; nets/cnn.py:29-47) from its
+// three fp32 weight tensors in ONE launch -- as library ops (permute, reshape, pad, flip, cast) they were ~20
+// launches per ConvNet2d call and step, 1 000 of the 5 100 launches of a cfg-5 step.  Segments of `out`, in order:
+//   w1p [Hd][K1p]      w1p[o][t C0 + c] = w1[o][c][ky][kx]            (forward conv 1 on the patch matrix of x)
+//   w2p [Hd][Hd]       w2p[o][i] = w2[o][i]
+//   w3p [9][Np3][Hd]   w3p[t][o][i] = w3[o][i][ky][kx]                (implicit-GEMM conv 3)
+//   wd3 [Hd][K3p]      wd3[i][t C3 + o] = w3[o][i][ky][kx]            (input gradient of conv 3 on the flipped patches of g)
+//   wd2 [Hd][Hd]       wd2[i][o] = w2[o][i]
+//   wd1 [9][Np1][Hd]   wd1[t][c][o] = w1[o][c][2 - ky][2 - kx]         (input gradient of conv 1, implicit GEMM)
+// t = 3 ky + kx; padding entries are zero.  b3p [Np3] = b3 zero-padded (fp32).
+struct PackArgs {
+  const float* w1; const float* w2; const float* w3; const float* b3;
+  __nv_bfloat16* out; float* b3p;
+  int C0, Hd, C3, K1p, Np3, K3p, Np1, with_bwd;
+};
+__global__ void __launch_bounds__(256) convnet3_pack_kernel(const PackArgs a) {
+  const int Hd = a.Hd, C0 = a.C0, C3 = a.C3;
+  const int64_t n1 = static_cast<int64_t>(Hd) * a.K1p, n2 = static_cast<int64_t>(Hd) * Hd,
+                n3 = static_cast<int64_t>(9) * a.Np3 * Hd, n4 = static_cast<int64_t>(Hd) * a.K3p, n5 = n2,
+                n6 = static_cast<int64_t>(9) * a.Np1 * Hd;
+  const int64_t total = n1 + n2 + n3 + (a.with_bwd ? n4 + n5 + n6 : 0);
+  for (int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    int64_t r = e;
+    float v = 0.f;
+    if (r < n1) {
+      const int o = static_cast<int>(r / a.K1p), k = static_cast<int>(r - static_cast<int64_t>(o) * a.K1p);
+      if (k < 9 * C0) { const int t = k / C0, c = k - t * C0; v = a.w1[(static_cast<int64_t>(o) * C0 + c) * 9 + t]; }
+    } else if ((r -= n1) < n2) {
+      v = a.w2[r];
+    } else if ((r -= n2) < n3) {
+      const int i = static_cast<int>(r % Hd); const int64_t q = r / Hd;
+      const int o = static_cast<int>(q % a.Np3), t = static_cast<int>(q / a.Np3);
+      if (o < C3) v = a.w3[(static_cast<int64_t>(o) * Hd + i) * 9 + t];
+    } else if ((r -= n3) < n4) {
+      const int i = static_cast<int>(r / a.K3p), k = static_cast<int>(r - static_cast<int64_t>(i) * a.K3p);
+      if (k < 9 * C3) { const int t = k / C3, o = k - t * C3; v = a.w3[(static_cast<int64_t>(o) * Hd + i) * 9 + t]; }
+    } else if ((r -= n4) < n5) {
+      const int i = static_cast<int>(r / Hd), o = static_cast<int>(r - static_cast<int64_t>(i) * Hd);
+      v = a.w2[static_cast<int64_t>(o) * Hd + i];
+    } else {
+      r -= n5;
+      const int o = static_cast<int>(r % Hd); const int64_t q = r / Hd;
+      const int c = static_cast<int>(q % a.Np1), t = static_cast<int>(q / a.Np1);
+      if (c < C0) v = a.w1[(static_cast<int64_t>(o) * C0 + c) * 9 + (8 - t)];
+    }
+    a.out[e] = __float2bfloat16_rn(v);
+  }
+  if (blockIdx.x == 0)
+    for (int o = threadIdx.x; o < a.Np3; o += blockDim.x) a.b3p[o] = (o < C3 && a.b3) ? a.b3[o] : 0.f;
 }
 
 // ------------------------------------------------------------------------------------------------ tcgen05 helpers
@@ -592,7 +732,15 @@ int vcnf_im2col(const void* src, int64_t sb, int64_t sc, int64_t sh, int64_t sw,
   const int64_t cap = static_cast<int64_t>(sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT) * 16;
   if (blocks > cap) blocks = cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (out_bf16)
+  if (out_bf16 && Kp % 8 == 0 && ldcol % 8 == 0 && reinterpret_cast<uintptr_t>(col) % 16 == 0 &&
+      B * H * W < (1ll << 31)) {
+    const int P = static_cast<int>(B * H * W);
+    int bx = (P + 255) / 256;
+    if (bx > 2048) bx = 2048;
+    conv::im2col_bf16_vec_kernel<<<dim3(static_cast<unsigned>(bx), static_cast<unsigned>(Kp / 8)), 256, 0, st>>>(
+        static_cast<const float*>(src), sb, sc, sh, sw, static_cast<__nv_bfloat16*>(col), ldcol, P, C, H, W, T, flip, act,
+        static_cast<float>(slope));
+  } else if (out_bf16)
     conv::im2col_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, st>>>(
         static_cast<const float*>(src), sb, sc, sh, sw, static_cast<__nv_bfloat16*>(col), ldcol, total, C, H, W, T, Kp,
         flip, act, static_cast<float>(slope));
@@ -620,6 +768,32 @@ int vcnf_col2im(const void* gcol, int64_t ldcol, const void* src, void* gsrc, in
   return launch_status();
 }
 
+int64_t vcnf_convnet3_pack_elems(int C0, int Hd, int C3, int with_bwd) {
+  if (C0 <= 0 || Hd <= 0 || C3 <= 0) return 0;
+  const int64_t K1p = (9 * C0 + 63) / 64 * 64, Np3 = (C3 + 15) / 16 * 16, K3p = (9 * C3 + 63) / 64 * 64,
+                Np1 = (C0 + 15) / 16 * 16;
+  int64_t n = static_cast<int64_t>(Hd) * K1p + static_cast<int64_t>(Hd) * Hd + 9 * Np3 * Hd;
+  if (with_bwd) n += static_cast<int64_t>(Hd) * K3p + static_cast<int64_t>(Hd) * Hd + 9 * Np1 * Hd;
+  return n;
+}
+
+int vcnf_convnet3_pack(const void* w1, const void* w2, const void* w3, const void* b3, int C0, int Hd, int C3,
+                       int with_bwd, void* out_bf16, void* b3p, void* stream) {
+  if (!w1 || !w2 || !w3 || !out_bf16 || !b3p || C0 <= 0 || Hd <= 0 || C3 <= 0) return VCNF_E_BADARG;
+  conv::PackArgs a{};
+  a.w1 = static_cast<const float*>(w1); a.w2 = static_cast<const float*>(w2); a.w3 = static_cast<const float*>(w3);
+  a.b3 = static_cast<const float*>(b3);
+  a.out = static_cast<__nv_bfloat16*>(out_bf16); a.b3p = static_cast<float*>(b3p);
+  a.C0 = C0; a.Hd = Hd; a.C3 = C3;
+  a.K1p = (9 * C0 + 63) / 64 * 64; a.Np3 = (C3 + 15) / 16 * 16; a.K3p = (9 * C3 + 63) / 64 * 64; a.Np1 = (C0 + 15) / 16 * 16;
+  a.with_bwd = with_bwd ? 1 : 0;
+  const int64_t total = vcnf_convnet3_pack_elems(C0, Hd, C3, with_bwd);
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > 1184) blocks = 1184;
+  conv::convnet3_pack_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  return launch_status();
+}
+
 int64_t vcnf_colsum_workspace(int C) { return static_cast<int64_t>(conv::kSumChunks) * C * 4; }
 
 int vcnf_colsum(const void* X, int layout, int64_t rows, int C, int64_t ld_or_S, void* out, void* workspace,
@@ -635,8 +809,12 @@ int vcnf_colsum(const void* X, int layout, int64_t rows, int C, int64_t ld_or_S,
   chunks = (rows + rpc - 1) / rpc;
   if (layout == 0) {
     if (ld_or_S < C) return VCNF_E_BADARG;
-    conv::colsum_bf16_kernel<<<static_cast<unsigned>(chunks), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(X), ld_or_S,
-                                                                            rows, C, rpc, static_cast<float*>(workspace));
+    if (C % 8 == 0 && C <= 256 && ld_or_S % 8 == 0 && reinterpret_cast<uintptr_t>(X) % 16 == 0)
+      conv::colsum_bf16_vec_kernel<<<static_cast<unsigned>(chunks), 256, 0, st>>>(
+          static_cast<const __nv_bfloat16*>(X), ld_or_S, rows, C, rpc, static_cast<float*>(workspace));
+    else
+      conv::colsum_bf16_kernel<<<static_cast<unsigned>(chunks), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(X), ld_or_S,
+                                                                              rows, C, rpc, static_cast<float*>(workspace));
   } else {
     if (ld_or_S <= 0 || C > 65535) return VCNF_E_BADARG;
     conv::chansum_nchw_kernel<<<dim3(static_cast<unsigned>(chunks), C), 256, 0, st>>>(

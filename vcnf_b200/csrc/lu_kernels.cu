@@ -155,6 +155,109 @@ __global__ void __launch_bounds__(kLuThreads) lu_compose_bwd_kernel(const T* low
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// Glow's LU-parametrised 1x1 convolution weight (normflow/flows/mixing.py:83-102,117-118):
+//   W = P (tril(L, -1) + I) (triu(U, 1) + diag(sign_S exp(log_S))),  log|det W| = sum log_S,
+// with P, L, U full C x C matrices (the reference masks them with tril / triu on every call).  As library ops the
+// assembly and its autograd are ~30 launches per GlowBlock and step (tril, triu, diag, exp, two matmuls, sum and their
+// adjoints): 1 700 of the 5 100 launches of a cfg-5 step.  One CTA each way, C <= 64.
+template <typename T>
+__device__ __forceinline__ void glow_load(const T* L, const T* U, const T* sign_s, const T* log_s, int C, T* Ls, T* Us) {
+  const int ld = C + 1;
+#pragma unroll 4
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
+    const int i = e / C, j = e - i * C;
+    Ls[i * ld + j] = j < i ? L[e] : (j == i ? T(1) : T(0));
+    Us[i * ld + j] = j > i ? U[e] : (j == i ? sign_s[i] * lu_exp(log_s[i]) : T(0));
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kLuThreads) glow_w_fwd_kernel(const T* P, const T* L, const T* U, const T* sign_s,
+                                                                const T* log_s, int C, T ld_scale, T* W, T* logdet) {
+  extern __shared__ __align__(16) unsigned char lu_smem[];
+  const int ld = C + 1;
+  T* Ls = reinterpret_cast<T*>(lu_smem);
+  T* Us = Ls + C * ld;
+  T* Ms = Us + C * ld;
+  T* Ps = Ms + C * ld;
+  glow_load(L, U, sign_s, log_s, C, Ls, Us);
+#pragma unroll 4
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) Ps[(e / C) * ld + e % C] = P[e];   // coalesced, loads in flight
+  __syncthreads();
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
+    const int i = e / C, j = e - i * C;
+    const int kmax = i < j ? i : j;
+    T acc = T(0);
+#pragma unroll 8
+    for (int k = 0; k <= kmax; ++k) acc += Ls[i * ld + k] * Us[k * ld + j];
+    Ms[i * ld + j] = acc;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
+    const int i = e / C, j = e - i * C;
+    T acc = T(0);
+#pragma unroll 8
+    for (int k = 0; k < C; ++k) acc += Ps[i * ld + k] * Ms[k * ld + j];
+    W[e] = acc;
+  }
+  if (threadIdx.x < 32) {
+    T acc = T(0);
+    for (int i = threadIdx.x; i < C; i += 32) acc += log_s[i];
+    acc = warp_sum(acc);
+    if (threadIdx.x == 0) *logdet = ld_scale * acc;
+  }
+}
+
+// A = P^T gW;  gL = strict lower part of A Us^T;  gU = strict upper part of Ls^T A;
+// g_log_s[k] = (Ls^T A)[k][k] sign_k exp(log_s_k) + ld_scale g_logdet.  gL / gU are full matrices (zeros elsewhere).
+template <typename T>
+__global__ void __launch_bounds__(kLuThreads) glow_w_bwd_kernel(const T* P, const T* L, const T* U, const T* sign_s,
+                                                                const T* log_s, int C, T ld_scale, const T* gW,
+                                                                const T* g_logdet, T* gL, T* gU, T* g_log_s) {
+  extern __shared__ __align__(16) unsigned char lu_smem[];
+  const int ld = C + 1;
+  T* Ls = reinterpret_cast<T*>(lu_smem);
+  T* Us = Ls + C * ld;
+  T* As = Us + C * ld;
+  T* Ps = As + C * ld;
+  T* Gs = Ps + C * ld;
+  glow_load(L, U, sign_s, log_s, C, Ls, Us);
+#pragma unroll 4
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) {            // staged first: a dot product over global memory
+    Ps[(e / C) * ld + e % C] = P[e];                                 // is one L2 round trip per term (26 us at C = 48)
+    Gs[(e / C) * ld + e % C] = gW ? gW[e] : T(0);
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
+    const int k = e / C, j = e - k * C;
+    T acc = T(0);
+#pragma unroll 8
+    for (int i = 0; i < C; ++i) acc += Ps[i * ld + k] * Gs[i * ld + j];
+    As[k * ld + j] = acc;
+  }
+  __syncthreads();
+  const T glv = g_logdet ? *g_logdet * ld_scale : T(0);
+  for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
+    const int i = e / C, j = e - i * C;
+    T gl = T(0), gu = T(0);
+    if (j < i) {
+#pragma unroll 8
+      for (int c = j; c < C; ++c) gl += As[i * ld + c] * Us[j * ld + c];
+    } else {
+#pragma unroll 8
+      for (int r = i; r < C; ++r) gu += Ls[r * ld + i] * As[r * ld + j];
+      if (j == i) {
+        g_log_s[i] = gu * Us[i * ld + i] + glv;
+        gu = T(0);
+      }
+    }
+    gL[e] = gl;
+    gU[e] = gu;
+  }
+}
+
 }  // namespace vcnf
 
 using namespace vcnf;
@@ -229,5 +332,56 @@ extern "C" int vcnf_lu_inverse(const void* lower, const void* upper, const void*
     lu_inverse_kernel<double><<<D, kLuInvThreads, smem, st>>>(static_cast<const double*>(lower), static_cast<const double*>(upper),
                                                            static_cast<const double*>(diag_raw), eps, D,
                                                            static_cast<double*>(Winv), static_cast<double*>(logabsdet));
+  return launch_status();
+}
+
+extern "C" int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, const void* sign_s, const void* log_s, int C,
+                               double ld_scale, void* W, void* logdet, int dtype, void* stream) {
+  if (!P || !L || !U || !sign_s || !log_s || !W || !logdet || C <= 0 || (dtype != VCNF_F32 && dtype != VCNF_F64))
+    return VCNF_E_BADARG;
+  if (C > kLuMaxD) return VCNF_E_UNSUPPORTED;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = 4 * static_cast<size_t>(C) * (C + 1) * (dtype == VCNF_F32 ? 4 : 8);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(glow_w_fwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
+    cudaFuncSetAttribute(glow_w_fwd_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
+    attr_set = true;
+  }
+  if (dtype == VCNF_F32)
+    glow_w_fwd_kernel<float><<<1, kLuThreads, smem, st>>>((const float*)P, (const float*)L, (const float*)U,
+                                                       (const float*)sign_s, (const float*)log_s, C, (float)ld_scale,
+                                                       (float*)W, (float*)logdet);
+  else
+    glow_w_fwd_kernel<double><<<1, kLuThreads, smem, st>>>((const double*)P, (const double*)L, (const double*)U,
+                                                        (const double*)sign_s, (const double*)log_s, C, ld_scale,
+                                                        (double*)W, (double*)logdet);
+  return launch_status();
+}
+
+extern "C" int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, const void* sign_s, const void* log_s, int C,
+                               double ld_scale, const void* gW, const void* g_logdet, void* gL, void* gU, void* g_log_s,
+                               int dtype, void* stream) {
+  if (!P || !L || !U || !sign_s || !log_s || !gL || !gU || !g_log_s || C <= 0 || (dtype != VCNF_F32 && dtype != VCNF_F64))
+    return VCNF_E_BADARG;
+  if (C > kLuMaxD) return VCNF_E_UNSUPPORTED;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = 5 * static_cast<size_t>(C) * (C + 1) * (dtype == VCNF_F32 ? 4 : 8);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(glow_w_bwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 170 * 1024);
+    cudaFuncSetAttribute(glow_w_bwd_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 170 * 1024);
+    attr_set = true;
+  }
+  if (dtype == VCNF_F32)
+    glow_w_bwd_kernel<float><<<1, kLuThreads, smem, st>>>((const float*)P, (const float*)L, (const float*)U,
+                                                       (const float*)sign_s, (const float*)log_s, C, (float)ld_scale,
+                                                       (const float*)gW, (const float*)g_logdet, (float*)gL, (float*)gU,
+                                                       (float*)g_log_s);
+  else
+    glow_w_bwd_kernel<double><<<1, kLuThreads, smem, st>>>((const double*)P, (const double*)L, (const double*)U,
+                                                        (const double*)sign_s, (const double*)log_s, C, ld_scale,
+                                                        (const double*)gW, (const double*)g_logdet, (double*)gL,
+                                                        (double*)gU, (double*)g_log_s);
   return launch_status();
 }

@@ -33,16 +33,33 @@ class GlowBlock(Flow):
             self.flows += [Invertible1x1Conv(channels, use_lu)]
         self.flows += [ActNorm((channels,) + (1, 1))]
 
+    @staticmethod
+    def _total(log_dets, z):
+        """Sum of the sub-layers' log-dets: per-sample vectors and 0-dim constants are added separately and combined once
+        (same value as the reference's running `log_det_tot += log_det` up to summation order; one broadcast add and one
+        batch reduction in the backward instead of one per constant)."""
+        vec = [ld for ld in log_dets if torch.is_tensor(ld) and ld.dim() > 0]
+        const = [ld for ld in log_dets if not (torch.is_tensor(ld) and ld.dim() > 0)]
+        tot = None
+        for ld in vec:
+            tot = ld if tot is None else tot + ld
+        c = None
+        for ld in const:
+            c = ld if c is None else c + ld
+        if tot is None:
+            tot = torch.zeros(z.shape[0], dtype=z.dtype, device=z.device)
+        return tot if c is None else tot + c
+
     def forward(self, z):
-        log_det_tot = torch.zeros(z.shape[0], dtype=z.dtype, device=z.device)
+        lds = []
         for flow in self.flows:
             z, log_det = flow(z)
-            log_det_tot = log_det_tot + log_det
-        return z, log_det_tot
+            lds.append(log_det)
+        return z, self._total(lds, z)
 
     def inverse(self, z):
-        log_det_tot = torch.zeros(z.shape[0], dtype=z.dtype, device=z.device)
+        lds = []
         for i in range(len(self.flows) - 1, -1, -1):
             z, log_det = self.flows[i].inverse(z)
-            log_det_tot = log_det_tot + log_det
-        return z, log_det_tot
+            lds.append(log_det)
+        return z, self._total(lds, z)

@@ -113,6 +113,10 @@ class Invertible1x1Conv(Flow):
         return z_, log_det * z.size(2) * z.size(3)
 
     def inverse(self, z):
+        if self.use_lu and z.is_cuda and self.num_channels <= ops.GLOW_W_MAX and self.L.dtype == self.P.dtype:
+            # density direction (the training path): W and H W sum(log_S) in one launch each way
+            W, log_det = ops.glow_w(self.L, self.U, self.log_S, self.P, self.sign_S, z.size(2) * z.size(3))
+            return ops.small_linear(z, W), log_det
         if self.use_lu:
             W = self._assemble_W()
             log_det = torch.sum(self.log_S)

@@ -359,6 +359,14 @@ class _SmallLinear(torch.autograd.Function):
         # D x D parameter gradients: a plain [D, rows] x [rows, D] library GEMM (not on the hot path's
         # byte budget; SURVEY.md 8d "LULinearPermute ... + D^2 param grads")
         if ctx.needs_input_grad[1] or (bias is not None and ctx.needs_input_grad[2]):
+            if S != 1 and not sub and bias is None and rows > 0:
+                # image tensors: both operands read in place by vcnf_small_linear_wgrad_img (no transposed copies)
+                gW = torch.empty((D, D), dtype=x.dtype, device=x.device)
+                ws = torch.empty(_lib.query("vcnf_small_linear_wgrad_img_workspace", D, dtype_code(x)), dtype=torch.uint8,
+                                 device=x.device)
+                _launch("vcnf_small_linear_wgrad_img", ptr(x), ptr(gy), ptr(in_idx), ptr(out_idx), ptr(gW), None, ptr(ws),
+                        x.shape[0], D, S, dtype_code(x), stream(), n=2)
+                return gx, gW, None, None, None, None
             if S == 1:
                 xg = x if in_idx is None else x.index_select(1, in_idx.long())
                 gg = gy if out_idx is None else gy.index_select(1, out_idx.long())
@@ -459,6 +467,43 @@ def lu_compose(lower_entries, upper_entries, unconstrained_upper_diag, eps):
     """W = L U and log|det W| of the LU-parametrised linear flow (D <= 64)."""
     lower_entries, upper_entries, unconstrained_upper_diag = _promote(lower_entries, upper_entries, unconstrained_upper_diag)
     return _LuCompose.apply(lower_entries, upper_entries, unconstrained_upper_diag, eps)
+
+
+class _GlowW(torch.autograd.Function):
+    """W = P (tril(L,-1) + I) (triu(U,1) + diag(sign_S exp(log_S))) and ld_scale * sum(log_S) (mixing.py:92-102,117-118)
+    in one launch each way (vcnf_glow_w_fwd / _bwd)."""
+
+    @staticmethod
+    def forward(ctx, L, U, log_S, P, sign_S, ld_scale):
+        L, U, log_S, P, sign_S = (t.contiguous() for t in (L, U, log_S, P, sign_S))
+        C = L.shape[0]
+        W = torch.empty((C, C), dtype=L.dtype, device=L.device)
+        ld = torch.empty((), dtype=L.dtype, device=L.device)
+        _launch("vcnf_glow_w_fwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), C, float(ld_scale), ptr(W), ptr(ld),
+                dtype_code(L), stream())
+        ctx.ld_scale = float(ld_scale)
+        ctx.save_for_backward(L, U, log_S, P, sign_S)
+        return W, ld
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gW, gld):
+        L, U, log_S, P, sign_S = ctx.saved_tensors
+        C = L.shape[0]
+        gW = gW.contiguous() if gW is not None else None
+        gld = gld.contiguous() if gld is not None else None
+        gL, gU, gS = torch.empty_like(L), torch.empty_like(U), torch.empty_like(log_S)
+        _launch("vcnf_glow_w_bwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), C, ctx.ld_scale, ptr(gW), ptr(gld),
+                ptr(gL), ptr(gU), ptr(gS), dtype_code(L), stream())
+        return gL, gU, gS, None, None, None
+
+
+GLOW_W_MAX = 64
+
+
+def glow_w(L, U, log_S, P, sign_S, ld_scale):
+    """(W [C, C], ld_scale * sum(log_S)) of Glow's LU-parametrised 1x1 convolution; C <= GLOW_W_MAX, one dtype."""
+    return _GlowW.apply(L, U, log_S, P, sign_S, float(ld_scale))
 
 
 def lu_inverse(lower_entries, upper_entries, unconstrained_upper_diag, eps):
@@ -837,20 +882,25 @@ class _ConvNet3Bf16(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w1, b1, w2, b2, w3, b3, slope):
-        x = x.contiguous()
-        B, C0, H, W = x.shape
+        B, C0, H, W = x.shape                                      # any NCHW strides (a channel slice is read in place)
         Hd, C3 = w1.shape[0], w3.shape[0]
         bf = torch.bfloat16
-        K1p = _ceil_to(9 * C0, 64)
+        K1p, Np3, K3p, Np1 = _ceil_to(9 * C0, 64), _ceil_to(C3, 16), _ceil_to(9 * C3, 64), _ceil_to(C0, 16)
         a1 = im2col_raw(x, "nchw", B, C0, H, W, 3, K1p, bf16=True)
-        w1p = torch.nn.functional.pad(w1.detach().permute(0, 2, 3, 1).reshape(Hd, 9 * C0), (0, K1p - 9 * C0)).to(bf)
-        h1 = conv_gemm_bf16(a1, B, H, W, 1, w1p.view(1, Hd, K1p), b1.detach().float().contiguous(), slope=slope, epi=1)
-        w2p = w2.detach().reshape(Hd, Hd).to(bf).contiguous()
-        h2 = conv_gemm_bf16(h1, B, H, W, 1, w2p.view(1, Hd, Hd), b2.detach().float().contiguous(), slope=slope, epi=1)
-        Np3 = _ceil_to(C3, 16)
-        w3p = torch.nn.functional.pad(w3.detach().permute(2, 3, 0, 1).reshape(9, C3, Hd), (0, 0, 0, Np3 - C3)).to(bf)
-        b3p = torch.nn.functional.pad(b3.detach().float(), (0, Np3 - C3))
-        out = conv_gemm_bf16(h2, B, H, W, 9, w3p.contiguous(), b3p, out_nchw_channels=C3)
+        # every bf16 weight layout of the three convolutions (forward and input-gradient operands) in one launch
+        with_bwd = any(ctx.needs_input_grad[:7])
+        f32 = lambda t: t.detach().float().contiguous()                # noqa: E731  (no-op for fp32 parameters)
+        pack = torch.empty(_lib.query("vcnf_convnet3_pack_elems", C0, Hd, C3, int(with_bwd)), dtype=bf, device=x.device)
+        b3p = torch.empty(Np3, dtype=torch.float32, device=x.device)
+        _launch("vcnf_convnet3_pack", ptr(f32(w1)), ptr(f32(w2)), ptr(f32(w3)), ptr(f32(b3)) if b3 is not None else None,
+                C0, Hd, C3, int(with_bwd), ptr(pack), ptr(b3p), stream())
+        sizes = [Hd * K1p, Hd * Hd, 9 * Np3 * Hd] + ([Hd * K3p, Hd * Hd, 9 * Np1 * Hd] if with_bwd else [])
+        segs = torch.split(pack, sizes)
+        w1p, w2p, w3p = segs[0].view(1, Hd, K1p), segs[1].view(1, Hd, Hd), segs[2].view(9, Np3, Hd)
+        h1 = conv_gemm_bf16(a1, B, H, W, 1, w1p, f32(b1), slope=slope, epi=1)
+        h2 = conv_gemm_bf16(h1, B, H, W, 1, w2p, f32(b2), slope=slope, epi=1)
+        out = conv_gemm_bf16(h2, B, H, W, 9, w3p, b3p, out_nchw_channels=C3)
+        ctx.packs = (segs[3].view(1, Hd, K3p), segs[4].view(1, Hd, Hd), segs[5].view(9, Np1, Hd)) if with_bwd else None
         ctx.slope = float(slope)
         ctx.dims = (B, C0, H, W, Hd, C3, K1p)
         ctx.save_for_backward(a1, h1, h2, w1, w2, w3)
@@ -867,15 +917,12 @@ class _ConvNet3Bf16(torch.autograd.Function):
         need = ctx.needs_input_grad
         pad = torch.nn.functional.pad
         K3p = _ceil_to(9 * C3, 64)
+        wd3, wd2, wd1 = ctx.packs
         a3g = im2col_raw(g, "nchw", B, C3, H, W, 3, K3p, flip=True, bf16=True)
-        wd3 = pad(w3.permute(1, 2, 3, 0).reshape(Hd, 9 * C3), (0, K3p - 9 * C3)).to(bf)
-        gh2 = conv_gemm_bf16(a3g, B, H, W, 1, wd3.view(1, Hd, K3p), mask=h2, slope=slope, epi=2)
-        wd2 = w2.reshape(Hd, Hd).t().contiguous().to(bf)
-        gh1 = conv_gemm_bf16(gh2, B, H, W, 1, wd2.view(1, Hd, Hd), mask=h1, slope=slope, epi=2)
+        gh2 = conv_gemm_bf16(a3g, B, H, W, 1, wd3, mask=h2, slope=slope, epi=2)
+        gh1 = conv_gemm_bf16(gh2, B, H, W, 1, wd2, mask=h1, slope=slope, epi=2)
         gx = gw1 = gb1 = gw2 = gb2 = gw3 = gb3 = None
         if need[0]:
-            Np1 = _ceil_to(C0, 16)
-            wd1 = pad(w1.flip(2, 3).permute(2, 3, 1, 0).reshape(9, C0, Hd), (0, 0, 0, Np1 - C0)).to(bf).contiguous()
             gx = conv_gemm_bf16(gh1, B, H, W, 9, wd1, out_nchw_channels=C0)
         if need[5]:
             G3 = conv_wgrad_bf16(a3g, h2)
