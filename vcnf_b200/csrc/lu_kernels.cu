@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(kLuThreads) lu_compose_fwd_kernel(const T* low
     const int i = e / D, j = e - i * D;
     const int kmax = i < j ? i : j;                       // L[i][k] = 0 for k > i, U[k][j] = 0 for k > j
     T acc = T(0);
+#pragma unroll 8
     for (int k = 0; k <= kmax; ++k) acc += Ls[i * ld + k] * Us[k * ld + j];
     W[e] = acc;
   }
@@ -144,10 +145,12 @@ __global__ void __launch_bounds__(kLuThreads) lu_compose_bwd_kernel(const T* low
     const int i = e / D, j = e - i * D;
     if (j < i) {                                          // gL[i][j] = sum_c gW[i][c] U[j][c], c >= j
       T acc = T(0);
+#pragma unroll 8
       for (int c = j; c < D; ++c) acc += Gs[i * ld + c] * Us[j * ld + c];
       g_lower[i * (i - 1) / 2 + j] = acc;
     } else {                                              // gU[i][j] = sum_r L[r][i] gW[r][j], r >= i
       T acc = T(0);
+#pragma unroll 8
       for (int r = i; r < D; ++r) acc += Ls[r * ld + i] * Gs[r * ld + j];
       if (j > i) g_upper[i * D - i * (i + 1) / 2 + j - i - 1] = acc;
       else g_diag[i] = (acc + glv / Us[i * ld + i]) * lu_softplus_grad(diag_raw[i]);

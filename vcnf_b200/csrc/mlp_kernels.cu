@@ -34,34 +34,75 @@ struct MlpArgs {
 // Weights of layer l in shared memory: Ws[l][o][i] (i padded to 32 with zeros), biases bs[l][o].
 template <typename T>
 __device__ __forceinline__ void mlp_load_weights(const MlpArgs<T>& a, T* Ws, T* bs, T* WsT) {
-  for (int l = 0; l < a.nl; ++l) {
-    const int din = a.dims[l], dout = a.dims[l + 1];
-    for (int e = threadIdx.x; e < kMlpW * kMlpW; e += blockDim.x) {
-      const int o = e / kMlpW, i = e - o * kMlpW;
-      const T w = (o < dout && i < din) ? a.W[l][o * din + i] : T(0);
-      Ws[(l * kMlpW + o) * kMlpW + i] = w;
-      if (WsT) WsT[(l * kMlpW + i) * kMlpW + o] = w;
+  // Every global load of every layer is issued before the first store (blockDim.x == kMlpThreads): with a load -> store
+  // pair per loop iteration the prologue was 8 x nl serialised L2 round trips -- 15 of the 15.6 us of a 1 024-row
+  // forward launch, and the same again in the backward (cfg 1 / cfg 4 steps are chains of such launches).
+  constexpr int kPer = kMlpW * kMlpW / kMlpThreads;
+  T w[kMlpMaxLayers][kPer];
+  T bv[kMlpMaxLayers];
+#pragma unroll
+  for (int l = 0; l < kMlpMaxLayers; ++l) {
+    bv[l] = T(0);
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) w[l][k] = T(0);
+    if (l < a.nl) {
+      const int din = a.dims[l], dout = a.dims[l + 1];
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        const int e = threadIdx.x + k * kMlpThreads, o = e / kMlpW, i = e - o * kMlpW;
+        if (o < dout && i < din) w[l][k] = __ldg(a.W[l] + o * din + i);
+      }
+      if (static_cast<int>(threadIdx.x) < dout && a.b[l]) bv[l] = __ldg(a.b[l] + threadIdx.x);
     }
-    for (int o = threadIdx.x; o < kMlpW; o += blockDim.x) bs[l * kMlpW + o] = (o < dout && a.b[l]) ? a.b[l][o] : T(0);
+  }
+#pragma unroll
+  for (int l = 0; l < kMlpMaxLayers; ++l) {
+    if (l < a.nl) {
+#pragma unroll
+      for (int k = 0; k < kPer; ++k) {
+        const int e = threadIdx.x + k * kMlpThreads, o = e / kMlpW, i = e - o * kMlpW;
+        Ws[(l * kMlpW + o) * kMlpW + i] = w[l][k];
+        if (WsT) WsT[(l * kMlpW + i) * kMlpW + o] = w[l][k];
+      }
+      if (threadIdx.x < kMlpW) bs[l * kMlpW + threadIdx.x] = bv[l];
+    }
   }
 }
 
 // out[o] = act(bias[o] + sum_i W[o][i] h[i]) for o < dout (zeros above); fully unrolled so that the vectors
 // stay in registers.
 template <typename T>
-__device__ __forceinline__ void mlp_layer(const T* W, const T* bias, int dout, const T* h, T* out, bool act, T slope) {
+__device__ __forceinline__ void mlp_layer(const T* W, const T* bias, int din, int dout, const T* h, T* out, bool act,
+                                          T slope) {
+  // Two outputs at a time, two accumulator chains each (four independent FMA chains), inputs in groups of 8 up to
+  // din: a launch on a few thousand rows is one serial pass per thread, so chain length and padded work are what it
+  // costs (13.7 us for [1, 32, 32, 2] on 1 024 rows with 32-wide loops and two chains).
 #pragma unroll
-  for (int o = 0; o < kMlpW; ++o) {
-    T acc = T(0);
+  for (int o = 0; o < kMlpW; o += 2) {
+    T r0 = T(0), r1 = T(0);
     if (o < dout) {
-      const T* w = W + o * kMlpW;
-      T a0 = bias[o], a1 = T(0);
+      const T* w0 = W + o * kMlpW;
+      const T* w1 = w0 + kMlpW;
+      T a0 = bias[o], a1 = T(0), c0 = bias[o + 1], c1 = T(0);
 #pragma unroll
-      for (int i = 0; i < kMlpW; i += 2) { a0 += w[i] * h[i]; a1 += w[i + 1] * h[i + 1]; }
-      acc = a0 + a1;
-      if (act) acc = acc > T(0) ? acc : acc * slope;
+      for (int ib = 0; ib < kMlpW; ib += 8) {
+        if (ib < din) {
+#pragma unroll
+          for (int i = ib; i < ib + 8; i += 2) {
+            a0 += w0[i] * h[i]; a1 += w0[i + 1] * h[i + 1];
+            c0 += w1[i] * h[i]; c1 += w1[i + 1] * h[i + 1];
+          }
+        }
+      }
+      r0 = a0 + a1;
+      r1 = c0 + c1;                                    // row o + 1 >= dout is all zeros (weights and bias): r1 = 0
+      if (act) {
+        r0 = r0 > T(0) ? r0 : r0 * slope;
+        r1 = r1 > T(0) ? r1 : r1 * slope;
+      }
     }
-    out[o] = acc;
+    out[o] = r0;
+    out[o + 1] = r1;
   }
 }
 
@@ -70,22 +111,25 @@ __global__ void __launch_bounds__(kMlpThreads) mlp_fwd_kernel(const MlpArgs<T> a
   extern __shared__ __align__(16) unsigned char mlp_smem[];
   T* Ws = reinterpret_cast<T*>(mlp_smem);
   T* bs = Ws + kMlpMaxLayers * kMlpW * kMlpW;
+  __shared__ int sdims[kMlpMaxLayers + 1];
+  if (threadIdx.x <= kMlpMaxLayers) sdims[threadIdx.x] = a.dims[threadIdx.x];
   mlp_load_weights(a, Ws, bs, static_cast<T*>(nullptr));
   __syncthreads();
-  const int din = a.dims[0], dlast = a.dims[a.nl];
+  const int nl = a.nl, din = sdims[0], dlast = sdims[nl];
   for (int64_t r = blockIdx.x * static_cast<int64_t>(kMlpThreads) + threadIdx.x; r < a.B;
        r += static_cast<int64_t>(gridDim.x) * kMlpThreads) {
     T h[kMlpW], t[kMlpW];
     const T* xr = a.x + r * a.ldx;
 #pragma unroll
     for (int i = 0; i < kMlpW; ++i) h[i] = i < din ? xr[i] : T(0);
+    // ONE copy of the layer code, looped: unrolled over the layers the kernel was 13 700 instructions that every warp
+    // executes once -- instruction fetch (ncu: no_instruction 10.6 of 13 stall cycles per issue), not the FMA pipe,
+    // set its time (26 us for 1 024 rows).
+#pragma unroll 1
+    for (int l = 0; l < nl; ++l) {
+      mlp_layer(Ws + l * kMlpW * kMlpW, bs + l * kMlpW, sdims[l], sdims[l + 1], h, t, l + 1 < nl, a.slope);
 #pragma unroll
-    for (int l = 0; l < kMlpMaxLayers; ++l) {
-      if (l < a.nl) {
-        mlp_layer(Ws + l * kMlpW * kMlpW, bs + l * kMlpW, a.dims[l + 1], h, t, l + 1 < a.nl, a.slope);
-#pragma unroll
-        for (int i = 0; i < kMlpW; ++i) h[i] = t[i];
-      }
+      for (int i = 0; i < kMlpW; ++i) h[i] = t[i];
     }
     T* yr = a.y + r * a.ldy;
 #pragma unroll
@@ -101,46 +145,57 @@ __host__ __device__ inline int mlp_psize(const int* dims, int nl) {
   return p;
 }
 
+// Shared-memory elements of the backward kernel (host and device agree through this function).
+__host__ __device__ inline size_t mlp_bwd_elems(int nl, int psize) {
+  constexpr int kWarps = kMlpThreads / 32;
+  return 2 * static_cast<size_t>(nl) * kMlpW * kMlpW + static_cast<size_t>(nl) * kMlpW +
+         kWarps * (kMlpW * kMlpW + kMlpW * (kMlpW + 1)) + static_cast<size_t>(kWarps) * psize +
+         static_cast<size_t>(nl > 1 ? nl - 1 : 0) * kMlpW * kMlpThreads;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kMlpThreads) mlp_bwd_kernel(const MlpArgs<T> a) {
   extern __shared__ __align__(16) unsigned char mlp_smem[];
   constexpr int kWarps = kMlpThreads / 32;
-  T* Ws = reinterpret_cast<T*>(mlp_smem);
-  T* bs = Ws + kMlpMaxLayers * kMlpW * kMlpW;
-  T* WsT = bs + kMlpMaxLayers * kMlpW;
-  T* tiles = WsT + kMlpMaxLayers * kMlpW * kMlpW;                 // per warp: gT[32][32] | at[32][33]
+  const int nl = a.nl;
+  T* Ws = reinterpret_cast<T*>(mlp_smem);                         // [nl][32][32]
+  T* WsT = Ws + nl * kMlpW * kMlpW;                               // [nl][32][32]
+  T* bs = WsT + nl * kMlpW * kMlpW;                               // [nl][32]
+  T* tiles = bs + nl * kMlpW;                                     // per warp: gT[32][32] | at[32][33]
   T* accs = tiles + kWarps * (kMlpW * kMlpW + kMlpW * (kMlpW + 1));   // per warp: psize accumulators
+  T* acts = accs + kWarps * a.psize;                              // [nl - 1][32][threads]: inputs of layers 1 .. nl-1
+  __shared__ int sdims[kMlpMaxLayers + 1], soff[kMlpMaxLayers];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   T* gT = tiles + warp * (kMlpW * kMlpW + kMlpW * (kMlpW + 1));
   T* at = gT + kMlpW * kMlpW;
   T* acc = accs + warp * a.psize;
+  if (tid == 0) {
+    int p = 0;
+    for (int l = 0; l <= kMlpMaxLayers; ++l) sdims[l] = a.dims[l];
+    for (int l = 0; l < kMlpMaxLayers; ++l) { soff[l] = p; if (l < nl) p += a.dims[l + 1] * a.dims[l] + a.dims[l + 1]; }
+  }
   mlp_load_weights(a, Ws, bs, WsT);
   for (int p = tid; p < kWarps * a.psize; p += kMlpThreads) accs[p] = T(0);
   __syncthreads();
-  const int nl = a.nl, din0 = a.dims[0], dlast = a.dims[nl];
-  int off[kMlpMaxLayers];
-  {
-    int p = 0;
-    for (int l = 0; l < kMlpMaxLayers; ++l) { off[l] = p; if (l < nl) p += a.dims[l + 1] * a.dims[l] + a.dims[l + 1]; }
-  }
+  const int din0 = sdims[0], dlast = sdims[nl];
   const int64_t n_tiles = (a.B + kMlpThreads - 1) / kMlpThreads;
+  // The layer loops are real loops over ONE copy of the layer code (see mlp_fwd_kernel: unrolled, the kernel was
+  // instruction-fetch bound); the hidden activations therefore live in shared memory ([layer][unit][thread]:
+  // conflict-free), not in a register array indexed by the layer.
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const int64_t r = tile * kMlpThreads + tid;
     const bool valid = r < a.B;
-    // forward recompute: act[l] = input of layer l (act[0] = x is re-read when layer 0 needs it)
-    T act[kMlpMaxLayers][kMlpW];
+    const T* xr = a.x + (valid ? r : 0) * a.ldx;
     {
-      const T* xr = a.x + (valid ? r : 0) * a.ldx;
+      T h[kMlpW], t[kMlpW];
 #pragma unroll
-      for (int i = 0; i < kMlpW; ++i) act[1][i] = (valid && i < din0) ? xr[i] : T(0);      // staged in act[1]
-    }
+      for (int i = 0; i < kMlpW; ++i) h[i] = (valid && i < din0) ? xr[i] : T(0);
+#pragma unroll 1
+      for (int l = 0; l + 1 < nl; ++l) {                          // forward recompute up to the last layer's input
+        mlp_layer(Ws + l * kMlpW * kMlpW, bs + l * kMlpW, sdims[l], sdims[l + 1], h, t, true, a.slope);
+        T* al = acts + (static_cast<size_t>(l) * kMlpW) * kMlpThreads + tid;
 #pragma unroll
-    for (int l = 0; l < kMlpMaxLayers - 1; ++l) {
-      if (l + 1 < nl) {
-        T t[kMlpW];
-        mlp_layer(Ws + l * kMlpW * kMlpW, bs + l * kMlpW, a.dims[l + 1], l == 0 ? act[1] : act[l], t, true, a.slope);
-#pragma unroll
-        for (int i = 0; i < kMlpW; ++i) act[l + 1][i] = t[i];
+        for (int i = 0; i < kMlpW; ++i) { h[i] = t[i]; al[i * kMlpThreads] = t[i]; }
       }
     }
     T g[kMlpW];
@@ -149,62 +204,73 @@ __global__ void __launch_bounds__(kMlpThreads) mlp_bwd_kernel(const MlpArgs<T> a
 #pragma unroll
       for (int o = 0; o < kMlpW; ++o) g[o] = (valid && o < dlast) ? gr[o] : T(0);
     }
+#pragma unroll 1
+    for (int l = nl - 1; l >= 0; --l) {
+      const int din = sdims[l], dout = sdims[l + 1];
+      const T* al = acts + (static_cast<size_t>(l > 0 ? l - 1 : 0) * kMlpW) * kMlpThreads + tid;   // input of layer l (l > 0)
+      // park this warp's (g, a_l) pairs: gT[o][s], at[s][i]
 #pragma unroll
-    for (int ll = 0; ll < kMlpMaxLayers; ++ll) {
-      const int l = kMlpMaxLayers - 1 - ll;
-      if (l < nl) {
-        const int din = a.dims[l], dout = a.dims[l + 1];
-        // park this warp's (g, a_l) pairs: gT[o][s], at[s][i]
+      for (int o = 0; o < kMlpW; ++o) if (o < dout) gT[o * kMlpW + lane] = g[o];
+      if (l == 0) {
+        for (int i = 0; i < din; ++i) at[lane * (kMlpW + 1) + i] = valid ? xr[i] : T(0);
+      } else {
 #pragma unroll
-        for (int o = 0; o < kMlpW; ++o) if (o < dout) gT[o * kMlpW + lane] = g[o];
-        if (l == 0) {
-          const T* xr = a.x + (valid ? r : 0) * a.ldx;
-          for (int i = 0; i < din; ++i) at[lane * (kMlpW + 1) + i] = valid ? xr[i] : T(0);
-        } else {
+        for (int i = 0; i < kMlpW; ++i) if (i < din) at[lane * (kMlpW + 1) + i] = al[i * kMlpThreads];
+      }
+      __syncwarp();
+      if (lane < din) {                                    // column `lane` of gW_l = g^T a over the warp's 32 samples
+        T col[kMlpW];
 #pragma unroll
-          for (int i = 0; i < kMlpW; ++i) if (i < din) at[lane * (kMlpW + 1) + i] = act[l][i];
+        for (int s = 0; s < kMlpW; ++s) col[s] = at[s * (kMlpW + 1) + lane];
+        T* aw = acc + soff[l];
+        for (int o = 0; o < dout; ++o) {
+          const T* grow = gT + o * kMlpW;
+          T d0 = T(0), d1 = T(0);
+#pragma unroll
+          for (int s = 0; s < kMlpW; s += 2) { d0 += grow[s] * col[s]; d1 += grow[s + 1] * col[s + 1]; }
+          aw[o * din + lane] += d0 + d1;
         }
-        __syncwarp();
-        if (lane < din) {                                  // column `lane` of gW_l = g^T a over the warp's 32 samples
-          T col[kMlpW];
+      }
+      if (lane < dout) {
+        const T* grow = gT + lane * kMlpW;
+        T d0 = T(0);
 #pragma unroll
-          for (int s = 0; s < kMlpW; ++s) col[s] = at[s * (kMlpW + 1) + lane];
-          T* aw = acc + off[l];
-          for (int o = 0; o < dout; ++o) {
-            const T* grow = gT + o * kMlpW;
-            T d0 = T(0), d1 = T(0);
+        for (int s = 0; s < kMlpW; ++s) d0 += grow[s];
+        acc[soff[l] + dout * din + lane] += d0;
+      }
+      __syncwarp();
+      if (l > 0 || a.gx) {                                 // input gradient of the layer, then the activation's slope
+        T gp[kMlpW];
+        const T* wt = WsT + l * kMlpW * kMlpW;
 #pragma unroll
-            for (int s = 0; s < kMlpW; s += 2) { d0 += grow[s] * col[s]; d1 += grow[s + 1] * col[s + 1]; }
-            aw[o * din + lane] += d0 + d1;
-          }
-        }
-        if (lane < dout) {
-          const T* grow = gT + lane * kMlpW;
-          T d0 = T(0);
+        for (int i = 0; i < kMlpW; i += 2) {
+          T v0 = T(0), v1 = T(0);
+          if (i < din) {
+            const T* w0 = wt + i * kMlpW;
+            const T* w1 = w0 + kMlpW;                      // row i + 1 >= din of WsT is zero
+            T a0 = T(0), a1 = T(0), c0 = T(0), c1 = T(0);
 #pragma unroll
-          for (int s = 0; s < kMlpW; ++s) d0 += grow[s];
-          acc[off[l] + dout * din + lane] += d0;
-        }
-        __syncwarp();
-        if (l > 0 || a.gx) {                               // input gradient of the layer, then the activation's slope
-          T gp[kMlpW];
-          const T* wt = WsT + l * kMlpW * kMlpW;
+            for (int ob = 0; ob < kMlpW; ob += 8) {
+              if (ob < dout) {
 #pragma unroll
-          for (int i = 0; i < kMlpW; ++i) {
-            T v = T(0);
-            if (i < din) {
-              const T* w = wt + i * kMlpW;
-              T a0 = T(0), a1 = T(0);
-#pragma unroll
-              for (int o = 0; o < kMlpW; o += 2) { a0 += w[o] * g[o]; a1 += w[o + 1] * g[o + 1]; }
-              v = a0 + a1;
-              if (l > 0) v *= act[l][i] > T(0) ? T(1) : a.slope;
+                for (int o = ob; o < ob + 8; o += 2) {
+                  a0 += w0[o] * g[o]; a1 += w0[o + 1] * g[o + 1];
+                  c0 += w1[o] * g[o]; c1 += w1[o + 1] * g[o + 1];
+                }
+              }
             }
-            gp[i] = v;
+            v0 = a0 + a1;
+            v1 = c0 + c1;
+            if (l > 0) {
+              v0 *= al[i * kMlpThreads] > T(0) ? T(1) : a.slope;
+              v1 *= al[(i + 1) * kMlpThreads] > T(0) ? T(1) : a.slope;
+            }
           }
-#pragma unroll
-          for (int i = 0; i < kMlpW; ++i) g[i] = gp[i];
+          gp[i] = v0;
+          gp[i + 1] = v1;
         }
+#pragma unroll
+        for (int i = 0; i < kMlpW; ++i) g[i] = gp[i];
       }
     }
     if (a.gx && valid) {
@@ -263,10 +329,7 @@ static int launch_mlp_fwd(MlpArgs<T>& a, cudaStream_t st) {
 
 template <typename T>
 static int launch_mlp_bwd(MlpArgs<T>& a, T* gparams, cudaStream_t st) {
-  constexpr int kWarps = kMlpThreads / 32;
-  const size_t elems = 2 * static_cast<size_t>(kMlpMaxLayers) * kMlpW * kMlpW + kMlpMaxLayers * kMlpW +
-                       kWarps * (kMlpW * kMlpW + kMlpW * (kMlpW + 1)) + static_cast<size_t>(kWarps) * a.psize;
-  const size_t smem = elems * sizeof(T);
+  const size_t smem = mlp_bwd_elems(a.nl, a.psize) * sizeof(T);
   if (smem > 200 * 1024) return VCNF_E_UNSUPPORTED;
   auto kern = mlp_bwd_kernel<T>;
   static bool attr_set = false;

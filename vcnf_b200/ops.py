@@ -553,8 +553,10 @@ def mlp_small_supported(x, weights, slope):
             and 1 <= len(weights) <= MLP_MAX_LAYERS and all(w.dtype == x.dtype and w.dim() == 2 for w in weights)
             and x.shape[1] == weights[0].shape[1]
             and all(max(w.shape) <= MLP_MAX_WIDTH for w in weights)
-            # the backward keeps 4 per-warp copies of the parameter gradient in shared memory (200 KB limit)
-            and (16640 + 4 * sum(w.numel() + w.shape[0] for w in weights)) * x.element_size() <= 200 * 1024)
+            # shared memory of the backward (200 KB limit; csrc/mlp_kernels.cu mlp_bwd_elems): both weight layouts,
+            # per-warp staging tiles, 4 per-warp copies of the parameter gradient, the hidden activations of a tile
+            and (2080 * len(weights) + 8320 + 4096 * (len(weights) - 1)
+                 + 4 * sum(w.numel() + w.shape[0] for w in weights)) * x.element_size() <= 200 * 1024)
 
 
 def _ptr_array(tensors):
