@@ -212,7 +212,10 @@ int vcnf_lu_inverse(const void* lower_entries, const void* upper_entries, const 
  * Input gradient: A = grad-output [M, out], W = weight [out, in] read as [n = in, k = out]:
  * sw_n = 1, sw_k = in; mask = the saved pre-activation input.  K <= 128.  C must not alias A.
  * relu_in bit 1 (value 2): W / bias were written by the preceding kernel on this stream (MADE's W * mask) -- the
- * kernel then orders its W fetch after the programmatic-dependent-launch wait instead of overlapping it. */
+ * kernel then orders its W fetch after the programmatic-dependent-launch wait instead of overlapping it.
+ * relu_in bit 2 (value 4): C = [mask > 0] (act(A) W^T + bias + residual) -- the mask applies after the residual (last
+ * slice of an input gradient whose contraction runs over more than 128 output features: residual = C of the earlier
+ * slices). */
 int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int64_t sw_n, int64_t sw_k,
                        const void* bias, const void* residual, int64_t ldr, const void* mask, int64_t ldm,
                        void* C, int64_t ldc, int64_t M, int N, int K, int relu_in, void* stream);

@@ -667,6 +667,7 @@ struct Args2 {
   int ctas_per_ntile; // persistent CTAs sharing one column slice
   int use_tma;        // A is 16 B aligned with a 16 B multiple row pitch: stages arrive by tensor-map TMA
   int e_mode;         // elementwise operand staged by TMA: 0 none, 1 residual, 2 mask
+  int mask_last;      // C = [mask > 0] (A W^T + bias + residual) instead of [mask > 0] (A W^T + bias) + residual
   int c_tma;          // output leaves by TMA tensor stores
 };
 
@@ -1019,6 +1020,18 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
 #pragma unroll
       for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]) + bv;
       if (staged) mbar_wait(&e_full[tc % kEBufs], static_cast<uint32_t>(tc / kEBufs) & 1u);
+      if (a.mask_last) {
+        // last slice of a sliced contraction: the running sum (residual == C of the earlier slices) comes first, the
+        // ReLU mask applies to the total
+        if (a.e_mode == 1) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[j] += et[j * 128];
+        }
+        if (res_reg) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[j] += res[j];
+        }
+      }
       if (a.e_mode == 2) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) acc[j] = et[j * 128] > 0.f ? acc[j] : 0.f;
@@ -1030,13 +1043,15 @@ __global__ void __launch_bounds__(kThreads, 1) linear_ts_kernel(const Args2 a, c
 #pragma unroll
         for (int j = 0; j < 32; ++j) acc[j] = mk[j] > 0.f ? acc[j] : 0.f;
       }
-      if (a.e_mode == 1) {
+      if (!a.mask_last) {
+        if (a.e_mode == 1) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) acc[j] += et[j * 128];
-      }
-      if (res_reg) {
+          for (int j = 0; j < 32; ++j) acc[j] += et[j * 128];
+        }
+        if (res_reg) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) acc[j] += res[j];
+          for (int j = 0; j < 32; ++j) acc[j] += res[j];
+        }
       }
       if (a.c_tma) {
 #ifndef VCNF_EXP_SKIP_EPI
@@ -1647,6 +1662,7 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
   const int sms = sm_count();
   if (sms <= 0) return static_cast<int>(cudaErrorNoDevice);
   static const bool use_v1 = [] { const char* e = getenv("VCNF_GEMM_V1"); return e && atoi(e) != 0; }();
+  if (use_v1 && (relu_in & 4)) return VCNF_E_UNSUPPORTED;
   if (!use_v1) {
     gemm::v2::Args2 b{};
     b.A = static_cast<const float*>(A); b.lda = lda;
@@ -1655,7 +1671,7 @@ extern "C" int vcnf_linear_tf32x3(const void* A, int64_t lda, const void* W, int
     b.residual = static_cast<const float*>(residual); b.ldr = ldr;
     b.mask = static_cast<const float*>(mask); b.ldm = ldm;
     b.C = static_cast<float*>(C); b.ldc = ldc;
-    b.M = M; b.N = N; b.K = K; b.relu_in = relu_in & 1; b.w_dynamic = (relu_in >> 1) & 1;
+    b.M = M; b.N = N; b.K = K; b.relu_in = relu_in & 1; b.w_dynamic = (relu_in >> 1) & 1; b.mask_last = (relu_in >> 2) & 1;
     b.n_tiles = (N + 127) / 128;
     const int64_t m_tiles2 = (M + gemm::v2::kTN - 1) / gemm::v2::kTN;
     int cpt2 = sms / b.n_tiles;

@@ -330,11 +330,11 @@ static int launch_mlp_fwd(MlpArgs<T>& a, cudaStream_t st) {
 template <typename T>
 static int launch_mlp_bwd(MlpArgs<T>& a, T* gparams, cudaStream_t st) {
   const size_t smem = mlp_bwd_elems(a.nl, a.psize) * sizeof(T);
-  if (smem > 200 * 1024) return VCNF_E_UNSUPPORTED;
+  if (smem > 224 * 1024) return VCNF_E_UNSUPPORTED;
   auto kern = mlp_bwd_kernel<T>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
     attr_set = true;
   }
   const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;

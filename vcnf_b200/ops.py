@@ -553,10 +553,10 @@ def mlp_small_supported(x, weights, slope):
             and 1 <= len(weights) <= MLP_MAX_LAYERS and all(w.dtype == x.dtype and w.dim() == 2 for w in weights)
             and x.shape[1] == weights[0].shape[1]
             and all(max(w.shape) <= MLP_MAX_WIDTH for w in weights)
-            # shared memory of the backward (200 KB limit; csrc/mlp_kernels.cu mlp_bwd_elems): both weight layouts,
+            # shared memory of the backward (224 KB limit; csrc/mlp_kernels.cu mlp_bwd_elems): both weight layouts,
             # per-warp staging tiles, 4 per-warp copies of the parameter gradient, the hidden activations of a tile
             and (2080 * len(weights) + 8320 + 4096 * (len(weights) - 1)
-                 + 4 * sum(w.numel() + w.shape[0] for w in weights)) * x.element_size() <= 200 * 1024)
+                 + 4 * sum(w.numel() + w.shape[0] for w in weights)) * x.element_size() <= 224 * 1024)
 
 
 def _ptr_array(tensors):
@@ -680,16 +680,15 @@ class _Linear(torch.autograd.Function):
                         ptr(x) if ctx.relu_in else None, ldx, ptr(gx), ldo, M, K, N, ctx.w_dyn, stream())
             else:
                 # out_features > 128 (the 3K-1 wide head): reduce over column slices of <= 128
+                # (the ReLU mask rides on the LAST slice: flag 4 = mask after the running sum)
                 first = True
                 for n0 in range(0, N, 128):
                     n1 = min(N, n0 + 128)
                     last = n1 == N
                     _launch("vcnf_linear_tf32x3", ptr(gy) + 4 * n0, ldg, ptr(weight) + 4 * n0 * K, 1, K, None,
-                            None if first else ptr(gx), ldo, ptr(x) if (ctx.relu_in and last and first) else None, ldx,
-                            ptr(gx), ldo, M, K, n1 - n0, ctx.w_dyn, stream())
+                            None if first else ptr(gx), ldo, ptr(x) if (ctx.relu_in and last) else None, ldx,
+                            ptr(gx), ldo, M, K, n1 - n0, ctx.w_dyn | (4 if (ctx.relu_in and last) else 0), stream())
                     first = False
-                if ctx.relu_in and N > 128:
-                    gx = gx * (x > 0)
         want_w = ctx.needs_input_grad[1]
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         if want_w or want_b:
