@@ -372,13 +372,20 @@ int vcnf_checkerboard(void* z, void* z1, void* z2, const uint8_t* mid_parity, in
 /* ---- Glow's LU-parametrised 1x1 convolution weight (normflow/flows/mixing.py:83-102 `_assemble_W`, :117-118) ----
  * W[C, C] = P (tril(L, -1) + I) (triu(U, 1) + diag(sign_S exp(log_S))) and *logdet = ld_scale * sum(log_S) in one
  * launch (ld_scale = +-H W of the call site, mixing.py:123).  P, L, U are the module's full C x C tensors, sign_S /
- * log_S [C].  C <= 64.  Replaces tril, triu, diag, exp, two matmuls, sum and the scalar multiply. */
-int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, const void* sign_S, const void* log_S, int C,
-                    double ld_scale, void* W, void* logdet, int dtype, void* stream);
+ * log_S [C].  C <= 64.  Replaces tril, triu, diag, exp, two matmuls, sum and the scalar multiply.
+ * With an_s != NULL (the ActNorm that precedes the convolution in a GlowBlock's density direction,
+ * flows/affine/glow.py:59-75 + flows/normalization.py:30-38: z -> (z - t) e^-s) the two per-pixel maps are folded:
+ * W[o][i] is multiplied by e^{-an_s[i]} (apply it as vcnf_small_linear(..., bias = t, sub_bias_first = 1)) and
+ * *logdet = ld_scale (sum(log_S) - sum(an_s)).  Wt (may be NULL) receives the transpose (input-gradient operand). */
+int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, const void* sign_S, const void* log_S, const void* an_s,
+                    int C, double ld_scale, void* W, void* Wt, void* logdet, int dtype, void* stream);
 /* Adjoint: gW [C, C] (may be NULL) and g_logdet [1] (may be NULL) -> gL, gU [C, C] (zero outside the strict triangles,
- * like autograd through tril / triu) and g_log_S [C]. */
-int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, const void* sign_S, const void* log_S, int C,
-                    double ld_scale, const void* gW, const void* g_logdet, void* gL, void* gU, void* g_log_S, int dtype,
+ * like autograd through tril / triu) and g_log_S [C].  Folded form (an_s != NULL): gW is the raw product
+ * sum_pixels gy[o] z[i] and gb[o] = sum_pixels gy[o] of vcnf_small_linear_wgrad_img, W2 the forward's folded weight,
+ * an_t the ActNorm shift; g_an_s / g_an_t [C] receive the ActNorm parameter gradients. */
+int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, const void* sign_S, const void* log_S, const void* an_s,
+                    const void* an_t, const void* W2, const void* gb, int C, double ld_scale, const void* gW,
+                    const void* g_logdet, void* gL, void* gU, void* g_log_S, void* g_an_s, void* g_an_t, int dtype,
                     void* stream);
 
 /* ---- K7: autoregressive layers in the sampling direction, all D passes in one launch ----------------------------

@@ -30,10 +30,13 @@ def _both(layer, z, fused=False):
     return x_ref, ld_ref, x, ld, launches
 
 
-@pytest.mark.parametrize("kind,D,H,permute,bins", [("spline", 8, 32, False, 8), ("spline", 8, 32, True, 8),
-                                                   ("spline", 64, 256, False, 8), ("spline", 16, 64, True, 10),
-                                                   ("maf", 16, 64, False, 0), ("maf", 64, 256, False, 0)])
-def test_fused_inverse_kernel_equals_the_full_loop(kind, D, H, permute, bins):
+@pytest.mark.parametrize("kind,D,H,permute,bins,rows", [
+    ("spline", 8, 32, False, 8, 1003), ("spline", 8, 32, True, 8, 1003), ("spline", 64, 256, False, 8, 1003),
+    ("spline", 16, 64, True, 10, 1003), ("maf", 16, 64, False, 0, 1003), ("maf", 64, 256, False, 0, 1003),
+    # several 16-row tiles per CTA (148 CTAs x 16 rows per wave): the weight hand-over between tiles and between the
+    # two sample groups of a CTA
+    ("maf", 64, 256, False, 0, 20011), ("spline", 64, 256, False, 8, 20011), ("maf", 16, 64, False, 0, 50000)])
+def test_fused_inverse_kernel_equals_the_full_loop(kind, D, H, permute, bins, rows):
     """vcnf_made_inverse (all D passes in one launch, one MADE evaluation in total) against the reference's D-pass
     loop on the same weights: same dot products in a different summation order -> 1e-5 of the scale for the values,
     1e-4 for the log-det (a sum of D per-feature terms); ragged batch (not a multiple of the 32-row tile)."""
@@ -44,7 +47,7 @@ def test_fused_inverse_kernel_equals_the_full_loop(kind, D, H, permute, bins):
     else:
         layer = nf.flows.MaskedAffineAutoregressive(D, H).cuda()
     _randomize(layer, 0.05)
-    z = 1.5 * torch.randn(1003, D, device="cuda")
+    z = 1.5 * torch.randn(rows, D, device="cuda")
     x_ref, ld_ref, x, ld, launches = _both(layer, z, fused=True)
     if D % 16 == 0:
         assert launches == 1, launches       # the single-launch kernel splits D and H over 16 warps

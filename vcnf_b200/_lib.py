@@ -68,8 +68,9 @@ _SIGNATURES = {
                                _vp],
     "vcnf_small_linear_wgrad_img": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp],
     "vcnf_convnet3_pack": [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp],
-    "vcnf_glow_w_fwd": [_vp, _vp, _vp, _vp, _vp, _i32, _dbl, _vp, _vp, _i32, _vp],
-    "vcnf_glow_w_bwd": [_vp, _vp, _vp, _vp, _vp, _i32, _dbl, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
+    "vcnf_glow_w_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _dbl, _vp, _vp, _vp, _i32, _vp],
+    "vcnf_glow_w_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _dbl, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32,
+                        _vp],
     "vcnf_made_inverse": [_vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32,
                           _i32, _vp, _vp],
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],

@@ -176,9 +176,14 @@ __device__ __forceinline__ void glow_load(const T* L, const T* U, const T* sign_
   }
 }
 
+// With an ActNorm in front (s, t != NULL; the density direction of a GlowBlock runs ActNorm.inverse then the 1x1
+// convolution, flows/affine/glow.py:59-75) the two per-pixel affine maps are one:  W ((z - t) e^-s) = W'' (z - t) with
+// W''[o][i] = W[o][i] e^{-s_i}; the kernel then writes W'' (and its transpose, for the input gradient) and
+// logdet = ld_scale (sum log_S - sum s).
 template <typename T>
 __global__ void __launch_bounds__(kLuThreads) glow_w_fwd_kernel(const T* P, const T* L, const T* U, const T* sign_s,
-                                                                const T* log_s, int C, T ld_scale, T* W, T* logdet) {
+                                                                const T* log_s, const T* an_s, int C, T ld_scale, T* W,
+                                                                T* Wt, T* logdet) {
   extern __shared__ __align__(16) unsigned char lu_smem[];
   const int ld = C + 1;
   T* Ls = reinterpret_cast<T*>(lu_smem);
@@ -203,11 +208,13 @@ __global__ void __launch_bounds__(kLuThreads) glow_w_fwd_kernel(const T* P, cons
     T acc = T(0);
 #pragma unroll 8
     for (int k = 0; k < C; ++k) acc += Ps[i * ld + k] * Ms[k * ld + j];
+    if (an_s) acc *= lu_exp(-an_s[j]);
     W[e] = acc;
+    if (Wt) Wt[j * C + i] = acc;
   }
   if (threadIdx.x < 32) {
     T acc = T(0);
-    for (int i = threadIdx.x; i < C; i += 32) acc += log_s[i];
+    for (int i = threadIdx.x; i < C; i += 32) acc += log_s[i] - (an_s ? an_s[i] : T(0));
     acc = warp_sum(acc);
     if (threadIdx.x == 0) *logdet = ld_scale * acc;
   }
@@ -215,10 +222,16 @@ __global__ void __launch_bounds__(kLuThreads) glow_w_fwd_kernel(const T* P, cons
 
 // A = P^T gW;  gL = strict lower part of A Us^T;  gU = strict upper part of Ls^T A;
 // g_log_s[k] = (Ls^T A)[k][k] sign_k exp(log_s_k) + ld_scale g_logdet.  gL / gU are full matrices (zeros elsewhere).
+// With the ActNorm folded in (an_s, an_t, W2 = the forward's W'', gb != NULL) `gW` is the RAW product
+// G[o][i] = sum gy[o] z[i] of the per-pixel map's gradient kernel and gb[o] = sum gy[o]; the map was W'' (z - t), so
+//   gW''[o][i] = G[o][i] - t_i gb[o],   g_t[i] = - sum_o W''[o][i] gb[o],
+//   g_s[i] = - sum_o gW''[o][i] W''[o][i] - ld_scale g_logdet,   gW[o][i] = gW''[o][i] e^{-s_i}.
 template <typename T>
 __global__ void __launch_bounds__(kLuThreads) glow_w_bwd_kernel(const T* P, const T* L, const T* U, const T* sign_s,
-                                                                const T* log_s, int C, T ld_scale, const T* gW,
-                                                                const T* g_logdet, T* gL, T* gU, T* g_log_s) {
+                                                                const T* log_s, const T* an_s, const T* an_t, const T* W2,
+                                                                const T* gb, int C, T ld_scale, const T* gW,
+                                                                const T* g_logdet, T* gL, T* gU, T* g_log_s, T* g_an_s,
+                                                                T* g_an_t) {
   extern __shared__ __align__(16) unsigned char lu_smem[];
   const int ld = C + 1;
   T* Ls = reinterpret_cast<T*>(lu_smem);
@@ -227,12 +240,31 @@ __global__ void __launch_bounds__(kLuThreads) glow_w_bwd_kernel(const T* P, cons
   T* Ps = As + C * ld;
   T* Gs = Ps + C * ld;
   glow_load(L, U, sign_s, log_s, C, Ls, Us);
+  const T glv = g_logdet ? *g_logdet * ld_scale : T(0);
 #pragma unroll 4
   for (int e = threadIdx.x; e < C * C; e += kLuThreads) {            // staged first: a dot product over global memory
     Ps[(e / C) * ld + e % C] = P[e];                                 // is one L2 round trip per term (26 us at C = 48)
-    Gs[(e / C) * ld + e % C] = gW ? gW[e] : T(0);
+    T g = gW ? gW[e] : T(0);
+    if (an_s) g -= an_t[e % C] * gb[e / C];                          // gW''
+    Gs[(e / C) * ld + e % C] = g;
   }
   __syncthreads();
+  if (an_s) {
+    for (int i = threadIdx.x; i < C; i += kLuThreads) {               // column sums for the ActNorm parameters
+      T gs = T(0), gt = T(0);
+#pragma unroll 8
+      for (int o = 0; o < C; ++o) {
+        const T w2 = __ldg(W2 + o * C + i);
+        gs -= Gs[o * ld + i] * w2;
+        gt -= w2 * gb[o];
+      }
+      g_an_s[i] = gs - glv;
+      g_an_t[i] = gt;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < C * C; e += kLuThreads) Gs[(e / C) * ld + e % C] *= lu_exp(-an_s[e % C]);   // gW
+    __syncthreads();
+  }
   for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
     const int k = e / C, j = e - k * C;
     T acc = T(0);
@@ -241,7 +273,6 @@ __global__ void __launch_bounds__(kLuThreads) glow_w_bwd_kernel(const T* P, cons
     As[k * ld + j] = acc;
   }
   __syncthreads();
-  const T glv = g_logdet ? *g_logdet * ld_scale : T(0);
   for (int e = threadIdx.x; e < C * C; e += kLuThreads) {
     const int i = e / C, j = e - i * C;
     T gl = T(0), gu = T(0);
@@ -338,8 +369,9 @@ extern "C" int vcnf_lu_inverse(const void* lower, const void* upper, const void*
   return launch_status();
 }
 
-extern "C" int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, const void* sign_s, const void* log_s, int C,
-                               double ld_scale, void* W, void* logdet, int dtype, void* stream) {
+extern "C" int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, const void* sign_s, const void* log_s,
+                               const void* an_s, int C, double ld_scale, void* W, void* Wt, void* logdet, int dtype,
+                               void* stream) {
   if (!P || !L || !U || !sign_s || !log_s || !W || !logdet || C <= 0 || (dtype != VCNF_F32 && dtype != VCNF_F64))
     return VCNF_E_BADARG;
   if (C > kLuMaxD) return VCNF_E_UNSUPPORTED;
@@ -353,19 +385,21 @@ extern "C" int vcnf_glow_w_fwd(const void* P, const void* L, const void* U, cons
   }
   if (dtype == VCNF_F32)
     glow_w_fwd_kernel<float><<<1, kLuThreads, smem, st>>>((const float*)P, (const float*)L, (const float*)U,
-                                                       (const float*)sign_s, (const float*)log_s, C, (float)ld_scale,
-                                                       (float*)W, (float*)logdet);
+                                                       (const float*)sign_s, (const float*)log_s, (const float*)an_s, C,
+                                                       (float)ld_scale, (float*)W, (float*)Wt, (float*)logdet);
   else
     glow_w_fwd_kernel<double><<<1, kLuThreads, smem, st>>>((const double*)P, (const double*)L, (const double*)U,
-                                                        (const double*)sign_s, (const double*)log_s, C, ld_scale,
-                                                        (double*)W, (double*)logdet);
+                                                        (const double*)sign_s, (const double*)log_s, (const double*)an_s,
+                                                        C, ld_scale, (double*)W, (double*)Wt, (double*)logdet);
   return launch_status();
 }
 
-extern "C" int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, const void* sign_s, const void* log_s, int C,
-                               double ld_scale, const void* gW, const void* g_logdet, void* gL, void* gU, void* g_log_s,
-                               int dtype, void* stream) {
-  if (!P || !L || !U || !sign_s || !log_s || !gL || !gU || !g_log_s || C <= 0 || (dtype != VCNF_F32 && dtype != VCNF_F64))
+extern "C" int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, const void* sign_s, const void* log_s,
+                               const void* an_s, const void* an_t, const void* W2, const void* gb, int C, double ld_scale,
+                               const void* gW, const void* g_logdet, void* gL, void* gU, void* g_log_s, void* g_an_s,
+                               void* g_an_t, int dtype, void* stream) {
+  if (!P || !L || !U || !sign_s || !log_s || !gL || !gU || !g_log_s || C <= 0 || (dtype != VCNF_F32 && dtype != VCNF_F64) ||
+      (an_s && (!an_t || !W2 || !gb || !g_an_s || !g_an_t)))
     return VCNF_E_BADARG;
   if (C > kLuMaxD) return VCNF_E_UNSUPPORTED;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -377,14 +411,14 @@ extern "C" int vcnf_glow_w_bwd(const void* P, const void* L, const void* U, cons
     attr_set = true;
   }
   if (dtype == VCNF_F32)
-    glow_w_bwd_kernel<float><<<1, kLuThreads, smem, st>>>((const float*)P, (const float*)L, (const float*)U,
-                                                       (const float*)sign_s, (const float*)log_s, C, (float)ld_scale,
-                                                       (const float*)gW, (const float*)g_logdet, (float*)gL, (float*)gU,
-                                                       (float*)g_log_s);
+    glow_w_bwd_kernel<float><<<1, kLuThreads, smem, st>>>(
+        (const float*)P, (const float*)L, (const float*)U, (const float*)sign_s, (const float*)log_s, (const float*)an_s,
+        (const float*)an_t, (const float*)W2, (const float*)gb, C, (float)ld_scale, (const float*)gW,
+        (const float*)g_logdet, (float*)gL, (float*)gU, (float*)g_log_s, (float*)g_an_s, (float*)g_an_t);
   else
-    glow_w_bwd_kernel<double><<<1, kLuThreads, smem, st>>>((const double*)P, (const double*)L, (const double*)U,
-                                                        (const double*)sign_s, (const double*)log_s, C, ld_scale,
-                                                        (const double*)gW, (const double*)g_logdet, (double*)gL,
-                                                        (double*)gU, (double*)g_log_s);
+    glow_w_bwd_kernel<double><<<1, kLuThreads, smem, st>>>(
+        (const double*)P, (const double*)L, (const double*)U, (const double*)sign_s, (const double*)log_s,
+        (const double*)an_s, (const double*)an_t, (const double*)W2, (const double*)gb, C, ld_scale, (const double*)gW,
+        (const double*)g_logdet, (double*)gL, (double*)gU, (double*)g_log_s, (double*)g_an_s, (double*)g_an_t);
   return launch_status();
 }

@@ -6,7 +6,7 @@ from ..base import Flow
 from .coupling import AffineCouplingBlock
 from ..mixing import Invertible1x1Conv
 from ..normalization import ActNorm
-from ... import nets
+from ... import nets, ops
 
 
 class GlowBlock(Flow):
@@ -57,8 +57,29 @@ class GlowBlock(Flow):
             lds.append(log_det)
         return z, self._total(lds, z)
 
+    def _fused_tail(self, z):
+        """ActNorm.inverse + Invertible1x1Conv.inverse as one node (ops.glow_actnorm_conv) when the block has the
+        LU-parametrised convolution, the ActNorm is initialised and everything is one CUDA dtype; None otherwise."""
+        if len(self.flows) != 3:
+            return None
+        conv, an = self.flows[1], self.flows[2]
+        if not (isinstance(conv, Invertible1x1Conv) and conv.use_lu and isinstance(an, ActNorm)):
+            return None
+        if not (z.is_cuda and z.dim() == 4 and conv.num_channels <= ops.GLOW_W_MAX and an.initialised()):
+            return None
+        if not (z.dtype == conv.L.dtype == conv.P.dtype == an.s.dtype == an.t.dtype) or an.s.numel() != z.shape[1]:
+            return None
+        if not (isinstance(an.s, nn.Parameter) and isinstance(an.t, nn.Parameter)):
+            return None
+        return ops.glow_actnorm_conv(z, conv.L, conv.U, conv.log_S, an.s, an.t, conv.P, conv.sign_S)
+
     def inverse(self, z):
         lds = []
+        fused = self._fused_tail(z)
+        if fused is not None:
+            z, ld = fused
+            z, ld_c = self.flows[0].inverse(z)
+            return z, self._total([ld, ld_c], z)
         for i in range(len(self.flows) - 1, -1, -1):
             z, log_det = self.flows[i].inverse(z)
             lds.append(log_det)

@@ -479,8 +479,8 @@ class _GlowW(torch.autograd.Function):
         C = L.shape[0]
         W = torch.empty((C, C), dtype=L.dtype, device=L.device)
         ld = torch.empty((), dtype=L.dtype, device=L.device)
-        _launch("vcnf_glow_w_fwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), C, float(ld_scale), ptr(W), ptr(ld),
-                dtype_code(L), stream())
+        _launch("vcnf_glow_w_fwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), None, C, float(ld_scale), ptr(W), None,
+                ptr(ld), dtype_code(L), stream())
         ctx.ld_scale = float(ld_scale)
         ctx.save_for_backward(L, U, log_S, P, sign_S)
         return W, ld
@@ -493,8 +493,8 @@ class _GlowW(torch.autograd.Function):
         gW = gW.contiguous() if gW is not None else None
         gld = gld.contiguous() if gld is not None else None
         gL, gU, gS = torch.empty_like(L), torch.empty_like(U), torch.empty_like(log_S)
-        _launch("vcnf_glow_w_bwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), C, ctx.ld_scale, ptr(gW), ptr(gld),
-                ptr(gL), ptr(gU), ptr(gS), dtype_code(L), stream())
+        _launch("vcnf_glow_w_bwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), None, None, None, None, C, ctx.ld_scale,
+                ptr(gW), ptr(gld), ptr(gL), ptr(gU), ptr(gS), None, None, dtype_code(L), stream())
         return gL, gU, gS, None, None, None
 
 
@@ -504,6 +504,62 @@ GLOW_W_MAX = 64
 def glow_w(L, U, log_S, P, sign_S, ld_scale):
     """(W [C, C], ld_scale * sum(log_S)) of Glow's LU-parametrised 1x1 convolution; C <= GLOW_W_MAX, one dtype."""
     return _GlowW.apply(L, U, log_S, P, sign_S, float(ld_scale))
+
+
+class _GlowActNormConv(torch.autograd.Function):
+    """ActNorm.inverse followed by Invertible1x1Conv.inverse (the density direction of a GlowBlock,
+    flows/affine/glow.py:59-75): y = W ((z - t) e^-s) per pixel and the 0-dim log-det H W (sum log_S - sum s).
+    The two per-pixel affine maps are folded into one weight by vcnf_glow_w_fwd, applied by vcnf_small_linear; the
+    backward is the transposed map, vcnf_small_linear_wgrad_img and vcnf_glow_w_bwd (all parameter gradients of both
+    layers): 2 + 5 launches instead of 5 + 10, one pass over z each way instead of two."""
+
+    @staticmethod
+    def forward(ctx, z, L, U, log_S, s, t, P, sign_S):
+        z = z.contiguous()
+        L, U, log_S, P, sign_S = (x.contiguous() for x in (L, U, log_S, P, sign_S))
+        s1, t1 = s.reshape(-1).contiguous(), t.reshape(-1).contiguous()
+        B, C = z.shape[0], z.shape[1]
+        S = math.prod(z.shape[2:])
+        W2 = torch.empty((C, C), dtype=L.dtype, device=L.device)
+        W2t = torch.empty((C, C), dtype=L.dtype, device=L.device)
+        ld = torch.empty((), dtype=L.dtype, device=L.device)
+        _launch("vcnf_glow_w_fwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), ptr(s1), C, float(S), ptr(W2), ptr(W2t),
+                ptr(ld), dtype_code(L), stream())
+        y = torch.empty_like(z)
+        _launch("vcnf_small_linear", ptr(z), ptr(y), ptr(W2), ptr(t1), None, None, B * S, C, S, 1, dtype_code(z), stream())
+        ctx.dims = (B, C, S)
+        ctx.pshape = (s.shape, t.shape)
+        ctx.save_for_backward(z, L, U, log_S, s1, t1, P, sign_S, W2, W2t)
+        return y, ld
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy, gld):
+        z, L, U, log_S, s1, t1, P, sign_S, W2, W2t = ctx.saved_tensors
+        B, C, S = ctx.dims
+        gy = gy.contiguous()
+        gld = gld.contiguous() if gld is not None else None
+        gz = None
+        if ctx.needs_input_grad[0]:
+            gz = torch.empty_like(z)
+            _launch("vcnf_small_linear", ptr(gy), ptr(gz), ptr(W2t), None, None, None, B * S, C, S, 0, dtype_code(z),
+                    stream())
+        G = torch.empty((C, C), dtype=z.dtype, device=z.device)
+        gb = torch.empty(C, dtype=z.dtype, device=z.device)
+        ws = torch.empty(_lib.query("vcnf_small_linear_wgrad_img_workspace", C, dtype_code(z)), dtype=torch.uint8,
+                         device=z.device)
+        _launch("vcnf_small_linear_wgrad_img", ptr(z), ptr(gy), None, None, ptr(G), ptr(gb), ptr(ws), B, C, S,
+                dtype_code(z), stream(), n=3)
+        gL, gU, gS = torch.empty_like(L), torch.empty_like(U), torch.empty_like(log_S)
+        gs, gt = torch.empty_like(s1), torch.empty_like(t1)
+        _launch("vcnf_glow_w_bwd", ptr(P), ptr(L), ptr(U), ptr(sign_S), ptr(log_S), ptr(s1), ptr(t1), ptr(W2), ptr(gb), C,
+                float(S), ptr(G), ptr(gld), ptr(gL), ptr(gU), ptr(gS), ptr(gs), ptr(gt), dtype_code(L), stream())
+        return gz, gL, gU, gS, gs.view(ctx.pshape[0]), gt.view(ctx.pshape[1]), None, None
+
+
+def glow_actnorm_conv(z, L, U, log_S, s, t, P, sign_S):
+    """(W ((z - t) e^-s) per pixel, H W (sum log_S - sum s)): ActNorm.inverse + Invertible1x1Conv.inverse in one node."""
+    return _GlowActNormConv.apply(z, L, U, log_S, s, t, P, sign_S)
 
 
 def lu_inverse(lower_entries, upper_entries, unconstrained_upper_diag, eps):
