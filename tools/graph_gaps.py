@@ -73,3 +73,9 @@ print("# kernel durations inside the replayed step (a dependent-launch kernel's 
 print("#   ms/step  share  launches  us/launch  kernel")
 for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:45]:
     print("%9.3f %5.1f%%  %6d  %8.1f  %s" % (t / 1e3, 100 * t / busy, c, t / c, k))
+if len(sys.argv) > 2:
+    lo, hi = int(sys.argv[2]), int(sys.argv[3])
+    print("# kernel sequence [%d, %d) of the replayed step: start us (relative), duration us, name" % (lo, hi))
+    t0 = ev[lo].time_range.start
+    for e in ev[lo:hi]:
+        print("%9.1f %7.1f  %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:100]))
