@@ -196,6 +196,17 @@ int vcnf_lu_compose_bwd(const void* lower_entries, const void* upper_entries, co
                         const void* gW, const void* glogabsdet, void* g_lower, void* g_upper, void* g_diag, int dtype,
                         void* stream);
 
+/* The same for n <= 32 layers of equal D in one launch each way (one CTA per layer; arrays of n device pointers, read
+ * on the host at call time): the LU weights of a model do not depend on its activations, so a training step forms all
+ * of them before the first layer and back-propagates all of them after the last (mixing.py:352-396 x n). */
+int vcnf_lu_compose_fwd_batched(const void* const* lower_entries, const void* const* upper_entries,
+                                const void* const* diag_raw, double eps, int D, int n, void* const* W,
+                                void* const* logabsdet, int dtype, void* stream);
+int vcnf_lu_compose_bwd_batched(const void* const* lower_entries, const void* const* upper_entries,
+                                const void* const* diag_raw, double eps, int D, int n, const void* const* gW,
+                                const void* const* glogabsdet, void* const* g_lower, void* const* g_upper,
+                                void* const* g_diag, int dtype, void* stream);
+
 /* Sampling direction of the same layer (mixing.py:412-429, two triangular solves per call): Winv[D, D] =
  * U^-1 L^-1 and *logabsdet = log|det W| from the parameter vectors, one launch; substitutions in fp64 for
  * either dtype.  No gradient (callers that differentiate through the sampling direction keep the solves). */

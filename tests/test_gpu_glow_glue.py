@@ -174,3 +174,37 @@ def test_glow_block_folded_actnorm_conv_equals_the_separate_layers(C, H, dtype, 
     for (n, pa), pb in zip(blk.named_parameters(), ref.parameters()):
         assert pa.grad is not None and pb.grad is not None, n
         assert rel(pa.grad, pb.grad) <= 10 * tol, (n, rel(pa.grad, pb.grad))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_batched_lu_weights_equal_the_per_layer_launches(dtype, monkeypatch):
+    """forward_kld / log_prob with the LU weights of all layers formed by one launch and their log-dets absorbed into one
+    model-level sum (flows/mixing.py precompute_lu_weights) against the same model forming them layer by layer."""
+    torch.manual_seed(5)
+    flows = []
+    for _ in range(4):
+        flows += [nf.flows.CoupledRationalQuadraticSpline(7, 1, 16), nf.flows.LULinearPermute(7, identity_init=False)]
+    a = nf.NormalizingFlow(nf.distributions.DiagGaussian(7, trainable=False), flows).to(dtype).cuda()
+    b = copy.deepcopy(a)
+    monkeypatch.setattr(b, "_lu_prepare", lambda absorb=False: ([], None))
+    x = torch.randn(777, 7, generator=_g(21)).to(dtype).cuda()
+    before = ops.LAUNCHES
+    la = a.forward_kld(x.clone())
+    la.backward()
+    na = ops.LAUNCHES - before
+    before = ops.LAUNCHES
+    lb = b.forward_kld(x.clone())
+    lb.backward()
+    nb = ops.LAUNCHES - before
+    assert na == nb - 2 * (4 - 1)                              # 4 + 4 single-CTA launches became 1 + 1
+    tol = 1e-5 if dtype == torch.float32 else 1e-12
+    assert abs(float(la) - float(lb)) <= tol * max(1.0, abs(float(lb)))
+    for (n, pa), pb in zip(a.named_parameters(), b.parameters()):
+        if pb.grad is None:
+            assert pa.grad is None, n
+            continue
+        d = float((pa.grad - pb.grad).abs().max())
+        assert d <= 20 * tol * max(1.0, float(pb.grad.abs().max())), (n, d)
+    with torch.no_grad():
+        assert float((a.log_prob(x) - b.log_prob(x)).abs().max()) <= 10 * tol * 50
+    assert all("_pre" not in m.__dict__ for m in a.modules())

@@ -11,6 +11,7 @@ import torch
 import torch.nn as nn
 
 from . import ops, utils
+from .flows import mixing
 
 
 class NormalizingFlow(nn.Module):
@@ -65,6 +66,18 @@ class NormalizingFlow(nn.Module):
             cache[key] = torch.tensor(list(self.categoricals), dtype=torch.long, device=device)
         return cache[key]
 
+    def _lu_prepare(self, absorb=False):
+        """Density direction: the weights of all LULinearPermute layers of the model in one launch
+        (flows/mixing.py precompute_lu_weights) -- they do not depend on the activations.  Returns (layers served,
+        the 0-dim sum of their log-dets when `absorb`, else None)."""
+        lus = self.__dict__.get("_lu_cache")
+        if lus is None or lus[0] != len(self.flows):
+            lus = (len(self.flows), [f.linear for f in self.flows if isinstance(f, mixing.LULinearPermute)])
+            self.__dict__["_lu_cache"] = lus
+        if len(lus[1]) < 2:
+            return [], None
+        return mixing.precompute_lu_weights(lus[1], absorb=absorb)
+
     def forward_kld(self, x, extended=False):
         """core.py:33-66."""
         log_qt = torch.zeros(len(x), device=x.device)
@@ -93,12 +106,19 @@ class NormalizingFlow(nn.Module):
                     log_qt += log_det
             z[:, idx] = zc.float()
         log_q = log_qt
-        for i in range(len(self.flows) - 1, -1, -1):
-            z, log_det = self.flows[i].inverse(z)
-            if extended:
-                zarr.append(z.cpu().detach().numpy())
-                zparr.append(log_det.cpu().detach().numpy())
-            log_q += log_det
+        lus, ld_lu = self._lu_prepare(absorb=not extended)
+        try:
+            for i in range(len(self.flows) - 1, -1, -1):
+                z, log_det = self.flows[i].inverse(z)
+                if extended:
+                    zarr.append(z.cpu().detach().numpy())
+                    zparr.append(log_det.cpu().detach().numpy())
+                if log_det is not mixing.ABSORBED:
+                    log_q += log_det
+        finally:
+            mixing.clear_lu_weights(lus)
+        if ld_lu is not None:
+            log_q += ops.broadcast_scalar(ld_lu.to(torch.promote_types(ld_lu.dtype, z.dtype)), len(x))
         log_q += self.q0.log_prob(z)
         if extended:
             return -torch.mean(log_q), zarr, zparr, log_q
@@ -191,9 +211,16 @@ class NormalizingFlow(nn.Module):
         """core.py:170-183."""
         log_q = torch.zeros(len(x), dtype=x.dtype, device=x.device)
         z = x
-        for i in range(len(self.flows) - 1, -1, -1):
-            z, log_det = self.flows[i].inverse(z)
-            log_q += log_det
+        lus, ld_lu = self._lu_prepare(absorb=True)
+        try:
+            for i in range(len(self.flows) - 1, -1, -1):
+                z, log_det = self.flows[i].inverse(z)
+                if log_det is not mixing.ABSORBED:
+                    log_q += log_det
+        finally:
+            mixing.clear_lu_weights(lus)
+        if ld_lu is not None:
+            log_q += ops.broadcast_scalar(ld_lu.to(torch.promote_types(ld_lu.dtype, z.dtype)), len(x))
         log_q += self.q0.log_prob(z)
         return log_q
 

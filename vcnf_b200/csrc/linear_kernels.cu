@@ -132,9 +132,10 @@ __global__ void __launch_bounds__(kRowThreads) small_linear_rows_kernel(const Li
   int* iout = iin + DP;                                // [DP]
   T* xs = reinterpret_cast<T*>(iout + DP);             // [kRowThreads * D]
   T* ys = xs + static_cast<size_t>(kRowThreads) * D;   // [kRowThreads * D]
-  for (int e = threadIdx.x; e < D * DP; e += kRowThreads) {
+#pragma unroll 8
+  for (int e = threadIdx.x; e < D * DP; e += kRowThreads) {            // (unrolled: independent loads in flight)
     const int o = e / DP, i = e - o * DP;
-    Ws[e] = i < D ? a.W[o * D + i] : T(0);
+    Ws[e] = i < D ? __ldg(a.W + o * D + i) : T(0);
   }
   for (int e = threadIdx.x; e < DP; e += kRowThreads) {
     bs[e] = (e < D && a.bias) ? a.bias[e] : T(0);
@@ -148,7 +149,32 @@ __global__ void __launch_bounds__(kRowThreads) small_linear_rows_kernel(const Li
     const int nr = static_cast<int>(a.rows - r0 < kRowThreads ? a.rows - r0 : kRowThreads);
     const int n = nr * D;
     const T* src = a.x + r0 * D;
-    for (int e = threadIdx.x; e < n; e += kRowThreads) xs[e] = src[e];
+    // the tile is one contiguous span: 16-byte loads, all of a thread's loads issued before its first store (a
+    // load -> store pair per iteration serialises one memory latency per element)
+    const bool vec = (static_cast<size_t>(n) * sizeof(T)) % 16 == 0 && reinterpret_cast<uintptr_t>(src) % 16 == 0 &&
+                     reinterpret_cast<uintptr_t>(a.y + r0 * D) % 16 == 0;
+    constexpr int kPerVec = 16 / sizeof(T);
+    if (vec) {
+      const int nv = n / kPerVec;
+      const uint4* sv = reinterpret_cast<const uint4*>(src);
+      uint4* xv = reinterpret_cast<uint4*>(xs);
+      for (int e0 = threadIdx.x; e0 < nv; e0 += 8 * kRowThreads) {
+        uint4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int e = e0 + k * kRowThreads;
+          if (e < nv) v[k] = __ldg(sv + e);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int e = e0 + k * kRowThreads;
+          if (e < nv) xv[e] = v[k];
+        }
+      }
+    } else {
+#pragma unroll 8
+      for (int e = threadIdx.x; e < n; e += kRowThreads) xs[e] = __ldg(src + e);
+    }
     __syncthreads();                                   // (also orders the W / index loads on the first tile)
     if (r < nr) {
       T xr[DP];
@@ -158,7 +184,21 @@ __global__ void __launch_bounds__(kRowThreads) small_linear_rows_kernel(const Li
         if (a.sub_bias_first) v -= bs[i];
         xr[i] = v;
       }
-      for (int o = 0; o < D; ++o) {
+      // two outputs per step: four independent FMA chains (same per-output summation order as one output per step)
+      int o = 0;
+      for (; o + 1 < D; o += 2) {
+        T a0 = a.sub_bias_first ? T(0) : bs[o], a1 = T(0), c0 = a.sub_bias_first ? T(0) : bs[o + 1], c1 = T(0);
+        const T* w0 = Ws + o * DP;
+        const T* w1 = w0 + DP;
+#pragma unroll
+        for (int i = 0; i < DP; i += 2) {
+          a0 += w0[i] * xr[i]; a1 += w0[i + 1] * xr[i + 1];
+          c0 += w1[i] * xr[i]; c1 += w1[i + 1] * xr[i + 1];
+        }
+        ys[r * D + iout[o]] = a0 + a1;
+        ys[r * D + iout[o + 1]] = c0 + c1;
+      }
+      if (o < D) {
         T acc0 = a.sub_bias_first ? T(0) : bs[o], acc1 = T(0);
         const T* w = Ws + o * DP;
 #pragma unroll
@@ -168,7 +208,14 @@ __global__ void __launch_bounds__(kRowThreads) small_linear_rows_kernel(const Li
     }
     __syncthreads();
     T* dst = a.y + r0 * D;
-    for (int e = threadIdx.x; e < n; e += kRowThreads) dst[e] = ys[e];
+    if (vec) {
+      const int nv = n / kPerVec;
+      const uint4* yv = reinterpret_cast<const uint4*>(ys);
+      uint4* dv = reinterpret_cast<uint4*>(dst);
+      for (int e = threadIdx.x; e < nv; e += kRowThreads) dv[e] = yv[e];
+    } else {
+      for (int e = threadIdx.x; e < n; e += kRowThreads) dst[e] = ys[e];
+    }
   }
 }
 

@@ -227,12 +227,17 @@ class _LULinear(Flow):
         return self.lower_entries.is_cuda and self.features <= 64
 
     def forward(self, inputs, context=None, in_idx=None):
-        if self._fused():
+        pre = self.__dict__.pop("_pre", None)                   # formed by precompute_lu_weights for this pass
+        if pre is not None:
+            weight, logabsdet = pre
+        elif self._fused():
             weight, logabsdet = ops.lu_compose(self.lower_entries, self.upper_entries, self.unconstrained_upper_diag,
                                                self.eps)
         else:
             weight, logabsdet = self.weight(), self.logabsdet()
         out = ops.small_linear(inputs, weight, self.bias, in_idx=in_idx)
+        if logabsdet is None:                                   # absorbed into the model-level sum (precompute_lu_weights)
+            return out, None
         return out, ops.broadcast_scalar(logabsdet.to(torch.promote_types(logabsdet.dtype, inputs.dtype)), out.shape[0])
 
     def inverse(self, inputs, context=None, out_idx=None):
@@ -247,6 +252,45 @@ class _LULinear(Flow):
             winv, logabsdet = self.weight_inverse(), self.logabsdet()
         out = ops.small_linear(inputs, winv, self.bias, out_idx=out_idx, sub_bias_first=True)
         return out, ops.broadcast_scalar(-logabsdet.to(torch.promote_types(logabsdet.dtype, inputs.dtype)), out.shape[0])
+
+
+ABSORBED = 0.0      # log-det placeholder of a layer whose log|det W| the caller already holds (see precompute_lu_weights)
+
+
+def precompute_lu_weights(layers, absorb=False):
+    """W = L U and log|det W| of every `_LULinear` in `layers` with ONE launch per group of equal (D, dtype, eps)
+    (ops.lu_compose_batched) instead of one single-CTA launch per layer; each layer's next density-direction call
+    (`_LULinear.forward`) picks its pair up.  The adjoint is one launch as well, after the first layer's backward.
+    Returns (layers served, total): with `absorb` the served layers return ABSORBED instead of a per-sample log-det
+    vector and `total` is the 0-dim sum of their log|det W| (one broadcast add for the model instead of a copy, an add
+    and two batch reductions in the backward per layer); otherwise total is None.  The caller clears leftovers with
+    `clear_lu_weights`."""
+    total = None
+    groups = {}
+    for m in layers:
+        if m._fused() and m.features > 0:
+            key = (m.features, m.lower_entries.dtype, float(m.eps), m.lower_entries.device)
+            groups.setdefault(key, []).append(m)
+    served = []
+    for (_, _, eps, _), ms in groups.items():
+        for k in range(0, len(ms), ops.LU_BATCH_MAX):
+            chunk = ms[k:k + ops.LU_BATCH_MAX]
+            if len(chunk) < 2:
+                continue
+            pairs = ops.lu_compose_batched([(m.lower_entries, m.upper_entries, m.unconstrained_upper_diag) for m in chunk],
+                                           eps)
+            for m, pr in zip(chunk, pairs):
+                m.__dict__["_pre"] = (pr[0], None) if absorb else pr
+            if absorb:
+                part = torch.stack([pr[1] for pr in pairs]).sum()
+                total = part if total is None else total + part
+            served += chunk
+    return served, total
+
+
+def clear_lu_weights(layers):
+    for m in layers:
+        m.__dict__.pop("_pre", None)
 
 
 class LULinearPermute(Flow):
@@ -270,4 +314,6 @@ class LULinearPermute(Flow):
     def inverse(self, z):
         perm = _i32(self.permutation._permutation)
         z, log_det = self.linear(z, in_idx=perm)
+        if log_det is None:
+            return z, ABSORBED
         return z, log_det.view(-1)

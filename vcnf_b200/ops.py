@@ -463,6 +463,53 @@ class _LuCompose(torch.autograd.Function):
         return g_lower, g_upper, g_diag, None
 
 
+class _LuComposeBatched(torch.autograd.Function):
+    """_LuCompose for n layers at once (vcnf_lu_compose_fwd/bwd_batched, one CTA per layer): inputs
+    (eps, n, lower_0..n-1, upper_0..n-1, diag_0..n-1), outputs (W_0..n-1, logabsdet_0..n-1).  The backward runs when the
+    last of the 2n output gradients has arrived, i.e. once, after the first layer's backward."""
+
+    @staticmethod
+    def forward(ctx, eps, n, *params):
+        params = [p.contiguous() for p in params]
+        lower, upper, diag = params[:n], params[n:2 * n], params[2 * n:]
+        D = diag[0].numel()
+        dt, dev = diag[0].dtype, diag[0].device
+        Ws = [torch.empty((D, D), dtype=dt, device=dev) for _ in range(n)]
+        lds = [torch.empty((), dtype=dt, device=dev) for _ in range(n)]
+        _launch("vcnf_lu_compose_fwd_batched", _ptr_array(lower), _ptr_array(upper), _ptr_array(diag), float(eps), D, n,
+                _ptr_array(Ws), _ptr_array(lds), dtype_code(diag[0]), stream())
+        ctx.cfg = (float(eps), n, D)
+        ctx.save_for_backward(*params)
+        return (*Ws, *lds)
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, *grads):
+        eps, n, D = ctx.cfg
+        params = ctx.saved_tensors
+        lower, upper, diag = params[:n], params[n:2 * n], params[2 * n:]
+        gW = [g.contiguous() if g is not None else None for g in grads[:n]]
+        gl = [g.contiguous() if g is not None else None for g in grads[n:]]
+        g_lower, g_upper = [torch.empty_like(p) for p in lower], [torch.empty_like(p) for p in upper]
+        g_diag = [torch.empty_like(p) for p in diag]
+        _launch("vcnf_lu_compose_bwd_batched", _ptr_array(lower), _ptr_array(upper), _ptr_array(diag), eps, D, n,
+                _ptr_array(gW), _ptr_array(gl), _ptr_array(g_lower), _ptr_array(g_upper), _ptr_array(g_diag),
+                dtype_code(diag[0]), stream())
+        return (None, None, *g_lower, *g_upper, *g_diag)
+
+
+LU_BATCH_MAX = 32
+
+
+def lu_compose_batched(triples, eps):
+    """[(lower_entries, upper_entries, unconstrained_upper_diag)] * n -> [(W, logabsdet)] * n; equal D, one dtype,
+    n <= LU_BATCH_MAX."""
+    n = len(triples)
+    out = _LuComposeBatched.apply(float(eps), n, *[t[0] for t in triples], *[t[1] for t in triples],
+                                  *[t[2] for t in triples])
+    return list(zip(out[:n], out[n:]))
+
+
 def lu_compose(lower_entries, upper_entries, unconstrained_upper_diag, eps):
     """W = L U and log|det W| of the LU-parametrised linear flow (D <= 64)."""
     lower_entries, upper_entries, unconstrained_upper_diag = _promote(lower_entries, upper_entries, unconstrained_upper_diag)
