@@ -957,6 +957,14 @@ template <typename T>
 __global__ void gather_cols_kernel(const T* src, int64_t lds, T* dst, int64_t ldd, int64_t B, int n,
                                    const int32_t* cols) {
   const int64_t total = B * n;
+  if (total < (1ll << 31)) {                               // 32-bit index arithmetic (a 64-bit division per element
+    const unsigned tot = static_cast<unsigned>(total), un = static_cast<unsigned>(n);   // was most of the kernel)
+    for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < tot; e += gridDim.x * blockDim.x) {
+      const unsigned b = e / un, j = e - b * un;
+      dst[static_cast<int64_t>(b) * ldd + j] = __ldg(src + static_cast<int64_t>(b) * lds + __ldg(cols + j));
+    }
+    return;
+  }
   for (int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; e < total;
        e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int64_t b = e / n;
@@ -976,6 +984,21 @@ __global__ void scatter_cols_kernel(const T* src, int64_t lds, T* dst, int64_t l
   for (int j = threadIdx.x; j < n; j += blockDim.x) inv[cols[j]] = j;
   __syncthreads();
   const int64_t total = B * D_dst;
+  if (total < (1ll << 31)) {
+    const unsigned tot = static_cast<unsigned>(total), ud = static_cast<unsigned>(D_dst);
+    for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < tot; e += gridDim.x * blockDim.x) {
+      const unsigned b = e / ud, c = e - b * ud;
+      const int j = inv[c];
+      T* d = dst + static_cast<int64_t>(b) * ldd + c;
+      if (j >= 0) {
+        const T v = __ldg(src + static_cast<int64_t>(b) * lds + j);
+        *d = accumulate ? *d + v : v;
+      } else if (!accumulate) {
+        *d = T(0);
+      }
+    }
+    return;
+  }
   for (int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; e < total;
        e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int64_t b = e / D_dst;
