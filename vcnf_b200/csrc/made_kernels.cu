@@ -18,6 +18,7 @@
 // Results equal the reference's D-pass loop up to summation order (tests: 1e-5 / 1e-4).
 #include "common.cuh"
 #include "rqs_math.cuh"
+#include "rqs_fast.cuh"
 #include "affine_math.cuh"
 #include "../../include/vcnf_b200.h"
 
@@ -219,10 +220,17 @@ __global__ void __launch_bounds__(kThreads, 1) made_inverse_kernel(const Args a)
           float p[kPP];
 #pragma unroll
           for (int m = 0; m < kPP; ++m) p[m] = m < P ? prm[m * kR + tid] : 0.f;
-          RqsElemCfg c;
-          c.K = a.K; c.mode = a.modes[f]; c.inverse = 1; c.outside_zero = a.outside_zero;
           int bin;
-          rqs_element<float, KMAX>(p, v, a.bounds[f], 1.f, c, &out, &lad, &bin, &flag);
+          if (KMAX == 8 && a.K == 8) {
+            // the packed-math element of the spline fast path (rqs_fast.cuh; what vcnf_rqs_layer_fwd runs for fp32,
+            // K = 8, i.e. what the D-pass loop evaluates): a third of the generic element's instructions, and this
+            // phase is serial -- 16 threads of the CTA while everything else waits
+            fast::element<8, true>(p, v, a.bounds[f], 1.f, a.modes[f], a.outside_zero, &out, &lad, &bin, &flag);
+          } else {
+            RqsElemCfg c;
+            c.K = a.K; c.mode = a.modes[f]; c.inverse = 1; c.outside_zero = a.outside_zero;
+            rqs_element<float, KMAX>(p, v, a.bounds[f], 1.f, c, &out, &lad, &bin, &flag);
+          }
         }
         xs[f * kR + tid] = out;
         ld_acc += lad;
