@@ -171,3 +171,27 @@ def test_two_rank_nccl_step_equals_one_rank_on_the_concatenated_batch():
     for k, v in single.state_dict().items():
         if v.dtype.is_floating_point:
             assert_close(got[k], v, rtol=1e-4, atol=1e-5, what="dp2." + k)
+
+
+def test_loaded_tail_bound_buffer_rebuilds_the_kernel_spec():
+    """A tensor `tail_bound` is a buffer; the spline layers cache it inside their kernel spec on first use, so a
+    load_state_dict that changes it must invalidate the cache."""
+    import vcnf_b200 as nf
+    from vcnf_b200.flows.neural_spline.autoregressive import MaskedPiecewiseRationalQuadraticAutoregressive as AR
+    torch.manual_seed(4)
+    x = 2.5 * torch.randn(301, 6, device="cuda")
+
+    def build(bound):
+        torch.manual_seed(9)
+        return AR(6, 32, num_bins=8, tails="linear", tail_bound=torch.tensor(bound), init_identity=False).cuda()
+    a, b = build(1.0), build(4.0)
+    with torch.no_grad():
+        ya0, _ = a.forward(x)                                   # builds a's spec with bound 1
+        a.load_state_dict(b.state_dict())
+        ya, lda = a.forward(x)
+        yb, ldb = b.forward(x)
+        assert not torch.equal(ya0, yb)
+        assert torch.equal(ya, yb) and torch.equal(lda, ldb)
+        za, _ = a.inverse(yb)
+        zb, _ = b.inverse(yb)
+        assert torch.equal(za, zb)

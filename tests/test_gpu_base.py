@@ -114,3 +114,26 @@ def test_diag_gaussian_draw_is_consistent():
     (z.sum() + lp.sum()).backward()
     assert float((q0.loc.grad - 4096).abs().max()) < 1e-2
     assert q0.log_scale.grad is not None and torch.isfinite(q0.log_scale.grad).all()
+
+
+def test_class_cond_flow_container():
+    """nf.ClassCondFlow (core.py:200-268): the loops around a class-conditional base, against the same layers applied by
+    hand; sample() and log_prob() are consistent with each other."""
+    torch.manual_seed(2)
+    flows = [nf.flows.MaskedAffineFlow(torch.tensor([1., 0., 1., 0.]), nf.nets.MLP([4, 8, 4]), nf.nets.MLP([4, 8, 4])),
+             nf.flows.Permute(4, mode="swap")]
+    model = nf.ClassCondFlow(nf.distributions.ClassCondDiagGaussian(4, 3), flows).cuda()
+    x = torch.randn(257, 4, device="cuda")
+    y = torch.randint(0, 3, (257,), device="cuda")
+    z, ld = x, torch.zeros(257, device="cuda")
+    for f in reversed(model.flows):
+        z, d = f.inverse(z)
+        ld = ld + d
+    want = ld + model.q0.log_prob(z, y)
+    got = model.log_prob(x, y)
+    assert torch.allclose(got, want, rtol=1e-6, atol=1e-6)
+    assert abs(float(model.forward_kld(x, y)) + float(want.mean())) < 1e-5
+    with torch.no_grad():
+        xs, lq = model.sample(64, y[:64])
+        assert xs.shape == (64, 4)
+        assert torch.allclose(model.log_prob(xs, y[:64]), lq, rtol=1e-4, atol=1e-4)

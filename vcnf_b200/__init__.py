@@ -6,7 +6,7 @@ as hand-written sm_100a CUDA kernels behind the reference's Python API.
 
 The kernels live in libvcnf_b200.so (C ABI: include/vcnf_b200.h); there is no CPU fallback.
 """
-from .core import NormalizingFlow, MultiscaleFlow
+from .core import NormalizingFlow, ClassCondFlow, MultiscaleFlow
 from . import flows
 from . import distributions
 from . import transforms

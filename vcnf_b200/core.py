@@ -231,6 +231,42 @@ class NormalizingFlow(nn.Module):
         self.load_state_dict(torch.load(path))
 
 
+class ClassCondFlow(nn.Module):
+    """Flow whose base distribution is conditioned on a class label (core.py:200-268): the layer loops of
+    NormalizingFlow with `q0(num_samples, y)` / `q0.log_prob(z, y)` at the latent end (ClassCondDiagGaussian:
+    distributions/base.py, one kernel per direction)."""
+
+    def __init__(self, q0, flows):
+        super().__init__()
+        self.q0 = q0
+        self.flows = nn.ModuleList(flows)
+
+    def log_prob(self, x, y):
+        log_q = torch.zeros(len(x), dtype=x.dtype, device=x.device)
+        z = x
+        for flow in reversed(self.flows):
+            z, log_det = flow.inverse(z)
+            log_q += log_det
+        log_q += self.q0.log_prob(z, y)
+        return log_q
+
+    def forward_kld(self, x, y):
+        return -torch.mean(self.log_prob(x, y))
+
+    def sample(self, num_samples=1, y=None):
+        z, log_q = self.q0(num_samples, y)
+        for flow in self.flows:
+            z, log_det = flow(z)
+            log_q -= log_det
+        return z, log_q
+
+    def save(self, path):
+        torch.save(self.state_dict(), path)
+
+    def load(self, path):
+        self.load_state_dict(torch.load(path))
+
+
 class MultiscaleFlow(nn.Module):
     """Multiscale (RealNVP / Glow) container, core.py:271-399."""
 

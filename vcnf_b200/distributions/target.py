@@ -43,3 +43,22 @@ class TwoMoons(Target):
         a = torch.abs(z[:, 0])
         return - 0.5 * ((torch.norm(z, dim=1) - 2) / 0.2) ** 2 - 0.5 * ((a - 2) / 0.3) ** 2 \
             + torch.log(1 + torch.exp(-4 * a / 0.09))
+
+
+class NealsFunnel(Target):
+    """Neal's funnel in two dimensions (target.py:65-104): v ~ N(0, 1 + v1shift), x | v ~ N(0, exp(v / 2) + v2shift).
+    The reference evaluates it on the host (`.cpu()` on every term) and so returns a CPU tensor; this returns the same
+    values on z's device."""
+
+    def __init__(self, prop_scale=torch.tensor(20.), prop_shift=torch.tensor(-10.), v1shift=0., v2shift=0.):
+        super().__init__(prop_scale, prop_shift)
+        self.n_dims = 2
+        self.max_log_prob = 0.
+        self.v1shift, self.v2shift = v1shift, v2shift
+
+    def log_prob(self, z):
+        v, x = z[:, 0], z[:, 1]
+        half_log_2pi = 0.5 * np.log(2 * np.pi)
+        sv = torch.ones_like(v) + self.v1shift
+        sx = torch.exp(0.5 * v) + self.v2shift
+        return (-0.5 * (v / sv) ** 2 - torch.log(sv) - half_log_2pi) + (-0.5 * (x / sx) ** 2 - torch.log(sx) - half_log_2pi)

@@ -55,6 +55,13 @@ class MaskedPiecewiseRationalQuadraticAutoregressive(Autoregressive):
             self.tail_bound = tail_bound
         self._spec = None
 
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        # the kernel specs cache the tail bounds: a loaded `tail_bound` buffer must rebuild them
+        super()._load_from_state_dict(*args, **kwargs)
+        self._spec = None
+        self.__dict__.pop("_fused_cache", None)
+        self.__dict__.pop("_feature_specs", None)
     def _output_dim_multiplier(self):
         return _params_per_feature(self.tails, self.num_bins)
 

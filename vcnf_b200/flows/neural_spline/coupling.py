@@ -74,6 +74,11 @@ class PiecewiseRationalQuadraticCDF(Flow):
             self.unnormalized_derivatives = nn.Parameter(torch.rand(*shape, nd))
         self._spec = None
 
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        # the kernel spec caches the tail bounds: a loaded `tail_bound` buffer must rebuild it
+        super()._load_from_state_dict(*args, **kwargs)
+        self._spec = None
     def packed_params(self):
         return torch.cat([self.unnormalized_widths, self.unnormalized_heights,
                           self.unnormalized_derivatives], dim=-1)
@@ -207,6 +212,11 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
             self.register_buffer("tail_bound", tail_bound[transform_features])
         self._specs = None
 
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        # the kernel specs cache the tail bounds: a loaded `tail_bound` buffer must rebuild them
+        super()._load_from_state_dict(*args, **kwargs)
+        self._specs = None
     def _transform_dim_multiplier(self):
         return _params_per_feature(self.tails, self.num_bins)
 
