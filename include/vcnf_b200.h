@@ -38,6 +38,7 @@ extern "C" {
 #define VCNF_TAIL_CIRCULAR 1
 #define VCNF_TAIL_LIST_LINEAR 2
 #define VCNF_TAIL_LIST_CIRCULAR 3
+#define VCNF_TAIL_NONE 4          /* tails=None: bounded spline on [0, 2 bound] (bound 0.5 = the reference's [0, 1]), K+1 free derivatives */
 
 int vcnf_version(void);
 /* Number of SMs the library sizes persistent grids for (148 on B200); 0 if no device. */

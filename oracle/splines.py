@@ -115,6 +115,13 @@ def unconstrained_rqs(x, uw, uh, ud, inverse=False, tails="linear", tail_bound=1
     those two (K+1 entries; the feature axis is the last axis of x).  tail_bound: python
     scalar or tensor broadcastable to x.shape.
     """
+    if tails is None:
+        # neural_spline/coupling.py:321-323, autoregressive.py:106-108: the bounded spline on [0, 1] is called
+        # directly (tail_bound is not passed); splines.py:105-106 refuses inputs outside the box
+        if x.numel() and (torch.min(x) < 0.0 or torch.max(x) > 1.0):
+            raise ValueError("Input outside domain")
+        return rqs(x, uw, uh, ud, inverse=inverse, min_bin_width=min_bin_width, min_bin_height=min_bin_height,
+                   min_derivative=min_derivative, return_bin=return_bin)
     const = boundary_derivative_constant(min_derivative)
     if torch.is_tensor(tail_bound):
         bound = torch.broadcast_to(tail_bound.to(x.dtype), x.shape)

@@ -133,6 +133,33 @@ LAYER_CASES_R2 = {
 }
 
 
+def _bounded_coupling(nf, uncond):
+    cpl = nf.flows.neural_spline.coupling
+    mk = lambda cin, cout: nf.nets.ResidualNet(in_features=cin, out_features=cout, hidden_features=16, num_blocks=1)
+    return cpl.PiecewiseRationalQuadraticCoupling(mask=nf.utils.masks.create_alternating_binary_mask(6, even=True),
+                                                  transform_net_create_fn=mk, num_bins=8,
+                                                  apply_unconditional_transform=uncond)       # tails=None (the default)
+
+
+# tails=None: the bounded spline on [0, 1] (utils/splines.py:88-193 called directly, neural_spline/coupling.py:321-323,
+# autoregressive.py:106-108); inputs inside the box.  layers_r3.pt, `make_golden.py --r3`.
+LAYER_CASES_R3 = {
+    "prq_coupling_bounded": dict(
+        build=lambda nf: _bounded_coupling(nf, False),
+        x=lambda: torch.rand(64, 6, generator=_g(51)), scale=0.3),
+    "prq_coupling_bounded_uncond": dict(
+        build=lambda nf: _bounded_coupling(nf, True),
+        x=lambda: torch.rand(64, 6, generator=_g(52)), scale=0.3),
+    "prq_cdf_bounded": dict(
+        build=lambda nf: nf.flows.neural_spline.coupling.PiecewiseRationalQuadraticCDF(shape=[5], num_bins=8),
+        x=lambda: torch.rand(40, 5, generator=_g(53)), scale=0.5),
+    "marqs_bounded": dict(
+        build=lambda nf: nf.flows.neural_spline.autoregressive.MaskedPiecewiseRationalQuadraticAutoregressive(
+            features=6, hidden_features=16, num_bins=8, num_blocks=1, init_identity=False),
+        x=lambda: torch.rand(48, 6, generator=_g(54)), scale=0.3),
+}
+
+
 def build_cfg2_small(nf, layers=3, d=29, hidden=32):
     flows = []
     for _ in range(layers):

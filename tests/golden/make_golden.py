@@ -18,7 +18,7 @@ import torch
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
 from ref_shim import load_reference          # noqa: E402
-from cases import LAYER_CASES, LAYER_CASES_R2, MODEL_CASES, randomize   # noqa: E402
+from cases import LAYER_CASES, LAYER_CASES_R2, LAYER_CASES_R3, MODEL_CASES, randomize   # noqa: E402
 from harness import eval_layer, eval_model   # noqa: E402
 
 warnings.filterwarnings("ignore")
@@ -49,6 +49,10 @@ def layer_records(nf, cases, full64=False):
 
 def main():
     nf = load_reference()
+    if "--r3" in sys.argv:                 # bounded-spline cases only: the earlier fixtures stay byte-identical
+        torch.save(layer_records(nf, LAYER_CASES_R3, full64=True), os.path.join(HERE, "layers_r3.pt"))
+        print("layers_r3.pt", os.path.getsize(os.path.join(HERE, "layers_r3.pt")) // 1024, "KiB")
+        return
     if "--r2" in sys.argv:                 # round-2 rows only: the round-1 fixtures stay byte-identical
         torch.save(layer_records(nf, LAYER_CASES_R2, full64=True), os.path.join(HERE, "layers_r2.pt"))
         print("layers_r2.pt", os.path.getsize(os.path.join(HERE, "layers_r2.pt")) // 1024, "KiB")

@@ -56,7 +56,7 @@ constexpr float kLn2 = 0.6931471805599453f;
 // softmax -> bin sizes -> knots of BOTH axes.  p[k] = (softmax(scale*uw)[k], softmax(scale*uh)[k]),
 // kn[k] = (X_k, Y_k), k = 0..K.
 template <int K>
-VCNF_HD void axes(const float* prm, float scale, float bound, P2* p, P2* kn) {
+VCNF_HD void axes(const float* prm, float scale, float bound, float lo, P2* p, P2* kn) {
   P2 v[K];
   const P2 sc{scale, scale};
 #pragma unroll
@@ -79,20 +79,22 @@ VCNF_HD void axes(const float* prm, float scale, float bound, P2* p, P2* kn) {
   const float mn = RqsConst<float>::min_size();
   const float span = 1.0f - mn * float(K);
   const float two_b = bound - (-bound);
-  const P2 mn2{mn, mn}, span2{span, span}, tb2{two_b, two_b}, nb2{-bound, -bound};
+  const P2 mn2{mn, mn}, span2{span, span}, tb2{two_b, two_b}, nb2{lo, lo};
+  const float hi = lo + two_b;
   P2 run{0.f, 0.f};
   kn[0] = nb2;
 #pragma unroll
   for (int k = 0; k < K; ++k) {
     p[k] = p2mul(p[k], r);
     run = p2add(run, p2fma(span2, p[k], mn2));
-    kn[k + 1] = (k + 1 == K) ? P2{bound, bound} : p2fma(tb2, run, nb2);   // end knot pinned (splines.py:118)
+    kn[k + 1] = (k + 1 == K) ? P2{hi, hi} : p2fma(tb2, run, nb2);         // end knot pinned (splines.py:118)
   }
 }
 
 // Storage indices of the raw derivative parameters of knots i and i+1 (-1: the boundary constant);
 // same table as rqs_raw_deriv.
 VCNF_HD void deriv_slots(int i, int K, int mode, int* s0, int* s1) {
+  if (mode == DERIV_FREE) { *s0 = i; *s1 = i + 1; return; }
   const bool lin = (mode == DERIV_LINEAR) || (mode == DERIV_LIST_LINEAR);
   const int off = (mode == DERIV_LINEAR) ? -1 : 0;
   *s0 = (lin && i == 0) ? -1 : i + off;
@@ -134,7 +136,7 @@ template <int K, bool INV>
 VCNF_HD void locate(const float* prm, float v, float bound, float scale, int mode, P2* p, RqsBin<float>* b,
                     P2* e01) {
   P2 kn[K + 1];
-  axes<K>(prm, scale, bound, p, kn);
+  axes<K>(prm, scale, bound, rqs_lo(bound, mode), p, kn);
   P2 lo = kn[0], hi = kn[1];
   int idx = 0;
 #pragma unroll
@@ -204,7 +206,8 @@ VCNF_HD void element(const float* prm, float v, float bound, float scale, int mo
   float o, l;
   int ok = 1;
   if (INV) rq_inverse(v, b, &o, &l, &ok); else rq_forward(v, b, &o, &l);
-  const bool inside = (v >= -bound) && (v <= bound);
+  const float left = rqs_lo(bound, mode);
+  const bool inside = (v >= left) && (v <= left + (bound - (-bound)));
   *out = inside ? o : (outside_zero ? 0.f : v);
   *lad = inside ? l : 0.f;
   *bin = inside ? b.idx : -1;
@@ -216,7 +219,7 @@ VCNF_HD void element(const float* prm, float v, float bound, float scale, int mo
 template <int K>
 VCNF_HD void build_records(const float* prm, int mode, float bound, Knot4* rec) {
   P2 p[K], kn[K + 1];
-  axes<K>(prm, 1.f, bound, p, kn);
+  axes<K>(prm, 1.f, bound, rqs_lo(bound, mode), p, kn);
   const float edge = RqsConst<float>::edge();
   for (int k = 0; k <= K; k += 2) {
     int s;
@@ -257,7 +260,8 @@ VCNF_HD void table_element(const Knot4* rec, float v, float bound, int outside_z
   float o, l;
   int ok = 1;
   if (INV) rq_inverse(v, b, &o, &l, &ok); else rq_forward(v, b, &o, &l);
-  const bool inside = (v >= -bound) && (v <= bound);
+  // the end records ARE the interval (-bound / bound for the tail modes, 0 / 2 bound for the bounded spline)
+  const bool inside = (v >= (INV ? rec[0].y : rec[0].x)) && (v <= (INV ? rec[K].y : rec[K].x));
   *out = inside ? o : (outside_zero ? 0.f : v);
   *lad = inside ? l : 0.f;
   *bin = inside ? b.idx : -1;
@@ -343,7 +347,8 @@ template <int K, bool INV>
 VCNF_HD void element_bwd(const float* prm, float v, float bound, float scale, int mode, int outside_zero,
                          float gout, float glad, float* gv, float* gprm) {
   const int nd = rqs_num_derivs(K, mode);
-  if (!((v >= -bound) && (v <= bound))) {
+  const float left = rqs_lo(bound, mode);
+  if (!((v >= left) && (v <= left + (bound - (-bound))))) {
     *gv = outside_zero ? 0.f : gout;                 // identity tail: d out / d v = 1
     for (int j = 0; j < 2 * K + nd; ++j) gprm[j] = 0.f;
     return;
@@ -386,7 +391,7 @@ VCNF_HD void element_bwd(const float* prm, float v, float bound, float scale, in
 template <int K, bool INV>
 VCNF_HD void table_element_bwd(const Knot4* rec, float v, float bound, int outside_zero, float gout, float glad,
                                float* gv, float* gtab) {
-  if (!((v >= -bound) && (v <= bound))) {
+  if (!((v >= (INV ? rec[0].y : rec[0].x)) && (v <= (INV ? rec[K].y : rec[K].x)))) {
     *gv = outside_zero ? 0.f : gout;
     return;
   }

@@ -533,7 +533,7 @@ __device__ __forceinline__ RqsMeta<float> fast_setup(const RqsLayerArgs<float>& 
     if (part == 0) {
       m.smode[j] = mode; m.sbound[j] = bound; m.shared_col[j] = -1;
       fast::P2 p[K], kn[K + 1];
-      fast::axes<K>(prm, 1.f, bound, p, kn);
+      fast::axes<K>(prm, 1.f, bound, rqs_lo(bound, mode), p, kn);
 #pragma unroll
       for (int k = 0; k <= K; ++k) { rj[k].x = kn[k].x; rj[k].y = kn[k].y; }
     } else {

@@ -26,8 +26,15 @@ enum DerivMode : int {
   DERIV_LINEAR = 0,         // 'linear'  : K-1 stored, both ends = const       (splines.py:36-40)
   DERIV_CIRCULAR = 1,       // 'circular': K   stored, last = first           (splines.py:44-46)
   DERIV_LIST_LINEAR = 2,    // tails list, this feature linear  : K+1 stored, ends overwritten
-  DERIV_LIST_CIRCULAR = 3   // tails list, this feature circular: K+1 stored, last = first
+  DERIV_LIST_CIRCULAR = 3,  // tails list, this feature circular: K+1 stored, last = first
+  DERIV_FREE = 4            // tails=None (splines.py:88-193 called directly): K+1 stored and used as they are; the
+                            // spline lives on [0, 2 bound] (bound = 0.5: the reference's default box [0, 1])
 };
+
+// Left end of the spline's interval: -bound for every tail mode, 0 for the bounded spline (tails=None).  The right end is
+// lo + 2 bound in both cases, so everything downstream works on knot DIFFERENCES and is unchanged.
+template <typename T>
+VCNF_HD T rqs_lo(T bound, int mode) { return mode == DERIV_FREE ? T(0) : -bound; }
 
 VCNF_HD int rqs_num_derivs(int K, int mode) {
   return mode == DERIV_LINEAR ? K - 1 : (mode == DERIV_CIRCULAR ? K : K + 1);
@@ -79,6 +86,7 @@ VCNF_HD T rqs_raw_deriv(const T* ud, int j, int K, int mode, T edge, int* src) {
   if (mode == DERIV_LINEAR) s = (j == 0 || j == K) ? -1 : j - 1;
   else if (mode == DERIV_CIRCULAR) s = (j == K) ? 0 : j;
   else if (mode == DERIV_LIST_LINEAR) s = (j == 0 || j == K) ? -1 : j;
+  else if (mode == DERIV_FREE) s = j;
   else s = (j == K) ? 0 : j;
   *src = s;
   return s < 0 ? edge : ud[s];
@@ -96,7 +104,7 @@ template <typename T> struct RqsBin {
 
 // Normalised bin sizes of one axis: p[k] = softmax(scale*u)[k]; returns knots[0..K].
 template <typename T, int KMAX>
-VCNF_HD void rqs_axis(const T* u, T scale, int K, T bound, T* p, T* knots) {
+VCNF_HD void rqs_axis(const T* u, T scale, int K, T bound, T lo, T* p, T* knots) {
   T m = u[0] * scale;
 #pragma unroll
   for (int k = 1; k < KMAX; ++k) if (k < K) { T v = u[k] * scale; m = v > m ? v : m; }
@@ -108,12 +116,12 @@ VCNF_HD void rqs_axis(const T* u, T scale, int K, T bound, T* p, T* knots) {
   const T span = T(1) - mn * T(K);
   const T two_b = bound - (-bound);
   T run = T(0);
-  knots[0] = -bound;
+  knots[0] = lo;
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) if (k < K) {
     p[k] *= inv;
     run += mn + span * p[k];
-    knots[k + 1] = (k + 1 == K) ? bound : two_b * run + (-bound);   // end knot pinned (splines.py:118)
+    knots[k + 1] = (k + 1 == K) ? lo + two_b : two_b * run + lo;    // end knot pinned (splines.py:118)
   }
 }
 
@@ -241,11 +249,12 @@ struct RqsElemCfg {
 template <typename T, int KMAX>
 VCNF_HD bool rqs_locate(const T* prm, T v, T bound, T wh_scale, const RqsElemCfg& c,
                         T* pw, T* ph, RqsBin<T>* b) {
-  if (!(v >= -bound && v <= bound)) return false;
+  const T lo = rqs_lo(bound, c.mode);
+  if (!(v >= lo && v <= lo + (bound - (-bound)))) return false;
   const int K = c.K;
   T X[KMAX + 1], Y[KMAX + 1];
-  rqs_axis<T, KMAX>(prm, wh_scale, K, bound, pw, X);
-  rqs_axis<T, KMAX>(prm + K, wh_scale, K, bound, ph, Y);
+  rqs_axis<T, KMAX>(prm, wh_scale, K, bound, lo, pw, X);
+  rqs_axis<T, KMAX>(prm + K, wh_scale, K, bound, lo, ph, Y);
   const int i = c.inverse ? rqs_search<T, KMAX>(Y, K, v) : rqs_search<T, KMAX>(X, K, v);
   b->idx = i;
   b->x0 = rqs_pick<T, KMAX>(X, K + 1, i);
@@ -365,9 +374,10 @@ template <typename T, int KMAX>
 VCNF_HD void rqs_build_table(const T* prm, int K, int mode, T bound, T* tab) {
   T p[KMAX], kn[KMAX + 1];
   const int KT = K + 1;
-  rqs_axis<T, KMAX>(prm, T(1), K, bound, p, kn);
+  const T lo = rqs_lo(bound, mode);
+  rqs_axis<T, KMAX>(prm, T(1), K, bound, lo, p, kn);
   for (int k = 0; k <= K; ++k) tab[k] = kn[k];
-  rqs_axis<T, KMAX>(prm + K, T(1), K, bound, p, kn);
+  rqs_axis<T, KMAX>(prm + K, T(1), K, bound, lo, p, kn);
   for (int k = 0; k <= K; ++k) tab[KT + k] = kn[k];
   const T edge = RqsConst<T>::edge();
   for (int k = 0; k <= K; ++k) {
@@ -379,10 +389,11 @@ VCNF_HD void rqs_build_table(const T* prm, int K, int mode, T bound, T* tab) {
 
 template <typename T, int KMAX>
 VCNF_HD bool rqs_table_locate(const T* tab, int K, T v, T bound, int inverse, RqsBin<T>* b) {
-  if (!(v >= -bound && v <= bound)) return false;
   const int KT = K + 1;
   const T* X = tab;
   const T* Y = tab + KT;
+  // (the end knots ARE the interval: -bound / bound for the tail modes, 0 / 2 bound for the bounded spline)
+  if (!(v >= (inverse ? Y[0] : X[0]) && v <= (inverse ? Y[K] : X[K]))) return false;
   const T* Dv = tab + 2 * KT;
   const int i = rqs_search<T, KMAX>(inverse ? Y : X, K, v);
   b->idx = i;
@@ -448,7 +459,7 @@ VCNF_HD void rqs_table_to_raw_grad(const T* prm, int K, int mode, T bound, const
   const T kk = (bound - (-bound)) * span;
   T p[KMAX], kn[KMAX + 1];
   for (int axis = 0; axis < 2; ++axis) {
-    rqs_axis<T, KMAX>(prm + axis * K, T(1), K, bound, p, kn);
+    rqs_axis<T, KMAX>(prm + axis * K, T(1), K, bound, rqs_lo(bound, mode), p, kn);
     const T* gk = gtab + axis * KT;
     // knot_k (1 <= k <= K-1) depends on p_j for j < k
     T suffix = T(0), dot = T(0);

@@ -5,7 +5,7 @@ import torch
 from torch.nn import functional as F
 
 from ..affine.autoregressive import Autoregressive
-from .coupling import _modes_and_bounds, _params_per_feature
+from .coupling import _modes_and_bounds, _params_per_feature, check_unit_box
 from ... import ops
 from ...nets import made as made_module
 from ...utils import splines
@@ -24,8 +24,6 @@ class MaskedPiecewiseRationalQuadraticAutoregressive(Autoregressive):
                  min_bin_height=splines.DEFAULT_MIN_BIN_HEIGHT,
                  min_derivative=splines.DEFAULT_MIN_DERIVATIVE):
         splines.check_minimums(num_bins, min_bin_width, min_bin_height, min_derivative)
-        if tails is None:
-            raise NotImplementedError("tails=None (bounded spline) is not on the B200 path")
         self.num_bins = num_bins
         self.tails = tails
         self.features = features
@@ -64,6 +62,16 @@ class MaskedPiecewiseRationalQuadraticAutoregressive(Autoregressive):
         self.__dict__.pop("_feature_specs", None)
     def _output_dim_multiplier(self):
         return _params_per_feature(self.tails, self.num_bins)
+
+    def forward(self, inputs, context=None):
+        if self.tails is None:
+            check_unit_box(inputs)                               # bounded spline: [0, 1] only (utils/splines.py:105-106)
+        return super().forward(inputs, context)
+
+    def inverse(self, inputs, context=None):
+        if self.tails is None:
+            check_unit_box(inputs)
+        return super().inverse(inputs, context)
 
     def _elementwise(self, inputs, autoregressive_params, inverse=False):
         if self._spec is None:

@@ -25,8 +25,19 @@ def _params_per_feature(tails, num_bins):
     return num_bins * 3 + 1
 
 
+def check_unit_box(values):
+    """tails=None: the spline is defined on [0, 1] only and the reference refuses anything else
+    (utils/splines.py:105-106, a host-side min / max like there)."""
+    if values.numel() and (float(values.min()) < 0.0 or float(values.max()) > 1.0):
+        raise ValueError("Input outside domain")
+
+
 def _modes_and_bounds(tails, tail_bound, n):
     """Per-feature (tail mode, bound) lists for a segment of n features."""
+    if tails is None:
+        # bounded spline (neural_spline/coupling.py:321-323): `rational_quadratic_spline` is called with its default
+        # box [0, 1] and `tail_bound` is not passed on; the kernels' TAIL_NONE interval is [0, 2 bound]
+        return [ops.TAIL_NONE] * n, [0.5] * n
     if isinstance(tails, (list, tuple)):
         modes = [ops.TAIL_LIST_LINEAR if t == "linear" else ops.TAIL_LIST_CIRCULAR for t in tails]
     elif tails in _TAIL_CODE:
@@ -51,8 +62,6 @@ class PiecewiseRationalQuadraticCDF(Flow):
                  min_derivative=splines.DEFAULT_MIN_DERIVATIVE):
         super().__init__()
         splines.check_minimums(num_bins, min_bin_width, min_bin_height, min_derivative)
-        if tails is None:
-            raise NotImplementedError("tails=None (bounded spline) is not on the B200 path")
         if len(shape) not in (1, 3):
             raise NotImplementedError("spline parameters must be per feature [D] or per pixel [C, H, W]")
         self._img = len(shape) == 3
@@ -79,6 +88,7 @@ class PiecewiseRationalQuadraticCDF(Flow):
         # the kernel spec caches the tail bounds: a loaded `tail_bound` buffer must rebuild it
         super()._load_from_state_dict(*args, **kwargs)
         self._spec = None
+
     def packed_params(self):
         return torch.cat([self.unnormalized_widths, self.unnormalized_heights,
                           self.unnormalized_derivatives], dim=-1)
@@ -108,6 +118,8 @@ class PiecewiseRationalQuadraticCDF(Flow):
         return y.reshape(B, H, W, C).permute(0, 3, 1, 2).contiguous(), ld.reshape(B, H * W).sum(1)
 
     def _spline(self, inputs, inverse=False):
+        if self.tails is None:
+            check_unit_box(inputs)
         if self._img:
             return self._spline_image(inputs, inverse)
         if self._spec is None:
@@ -182,8 +194,6 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
                  min_bin_height=splines.DEFAULT_MIN_BIN_HEIGHT,
                  min_derivative=splines.DEFAULT_MIN_DERIVATIVE):
         splines.check_minimums(num_bins, min_bin_width, min_bin_height, min_derivative)
-        if tails is None:
-            raise NotImplementedError("tails=None (bounded spline) is not on the B200 path")
         self.num_bins = num_bins
         mask = torch.as_tensor(mask)
         features_vector = torch.arange(len(mask))
@@ -217,8 +227,20 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         # the kernel specs cache the tail bounds: a loaded `tail_bound` buffer must rebuild them
         super()._load_from_state_dict(*args, **kwargs)
         self._specs = None
+
     def _transform_dim_multiplier(self):
         return _params_per_feature(self.tails, self.num_bins)
+
+    def _check_domain(self, inputs):
+        """tails=None: the values that reach a bounded spline must lie in [0, 1] (utils/splines.py:105-106)."""
+        ut = self.unconditional_transform
+        both = self.tails is None and ut is not None and ut.tails is None
+        if both:
+            check_unit_box(inputs)
+        elif self.tails is None:
+            check_unit_box(inputs.index_select(1, self.transform_features.to(inputs.device)))
+        elif ut is not None and ut.tails is None:
+            check_unit_box(inputs.index_select(1, self.identity_features.to(inputs.device)))
 
     def _wh_scale(self):
         net = self.transform_net
@@ -318,6 +340,7 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
 
     def forward(self, inputs, context=None, want_bins=False):
         self._check(inputs)
+        self._check_domain(inputs)
         if inputs.dim() == 4:
             return self._image(inputs, context, False)
         if self._specs is None:
@@ -329,6 +352,7 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
 
     def inverse(self, inputs, context=None):
         self._check(inputs)
+        self._check_domain(inputs)
         if inputs.dim() == 4:
             return self._image(inputs, context, True)
         if self._specs is None:

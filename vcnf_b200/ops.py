@@ -13,7 +13,7 @@ from ._lib import call, ptr, stream, dtype_code
 LAUNCHES = 0
 
 COL_PASS, COL_COND, COL_SHARED = 0, 1, 2
-TAIL_LINEAR, TAIL_CIRCULAR, TAIL_LIST_LINEAR, TAIL_LIST_CIRCULAR = 0, 1, 2, 3
+TAIL_LINEAR, TAIL_CIRCULAR, TAIL_LIST_LINEAR, TAIL_LIST_CIRCULAR, TAIL_NONE = 0, 1, 2, 3, 4
 SCALE_MAPS = {"exp": 0, "sigmoid": 1, "sigmoid_inv": 2, "none": 3, "maf": 4}
 
 
