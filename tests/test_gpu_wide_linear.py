@@ -82,7 +82,10 @@ def test_made_runs_on_the_tensor_core_kernels():
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
 @pytest.mark.parametrize("layers,leaky,B", [([1, 32, 32, 2], 0.0, 1000), ([15, 30, 15], 0.1, 333), ([1, 4, 1], 0.0, 65),
-                                            ([7, 32, 32, 32, 5], 0.2, 4099), ([3, 16], 0.0, 17)])
+                                            ([7, 32, 32, 32, 5], 0.2, 4099), ([3, 16], 0.0, 17),
+                                            # above kMlpQuadMaxRows (8192): one thread per sample instead of four lanes
+                                            ([1, 32, 32, 2], 0.0, 20011), ([7, 32, 32, 32, 5], 0.2, 16385),
+                                            ([15, 30, 15], 0.1, 8193), ([15, 30, 15], 0.1, 8192)])
 def test_register_mlp_matches_torch(layers, leaky, B, dtype):
     """vcnf_mlp_fwd / vcnf_mlp_bwd (whole MLP in registers) against the oracle net in the same dtype: values, input
     gradient and every parameter gradient; ragged batches, 1-4 linear layers, leaky slopes."""

@@ -20,6 +20,7 @@ constexpr int kMlpThreads = 128;
 constexpr int kMlpW = 32;            // maximum layer width
 constexpr int kMlpMaxLayers = 4;     // linear layers
 constexpr int kMlpMaxGrid = 148 * 4;
+constexpr int64_t kMlpQuadMaxRows = 8192;   // at or below: the four-lanes-per-sample kernels (see mlp_fwd_quad_kernel)
 
 template <typename T>
 struct MlpArgs {
@@ -61,7 +62,7 @@ __device__ __forceinline__ void mlp_load_weights(const MlpArgs<T>& a, T* Ws, T* 
 #pragma unroll
       for (int k = 0; k < kPer; ++k) {
         const int e = threadIdx.x + k * kMlpThreads, o = e / kMlpW, i = e - o * kMlpW;
-        Ws[(l * kMlpW + o) * kMlpW + i] = w[l][k];
+        if (Ws) Ws[(l * kMlpW + o) * kMlpW + i] = w[l][k];
         if (WsT) WsT[(l * kMlpW + i) * kMlpW + o] = w[l][k];
       }
       if (threadIdx.x < kMlpW) bs[l * kMlpW + threadIdx.x] = bv[l];
@@ -299,6 +300,214 @@ __global__ void mlp_partial_reduce_kernel(const T* partial, int nblocks, int n, 
   if (lane == 0) out[j] = acc;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Small batches (cfg 1 trains on 1 024 rows, cfg 4 on 2 048): with one thread per sample a launch is ONE serial pass
+// of ~4 000 dependent instructions per thread on a handful of SMs (9 us forward, 27 us backward whatever the batch).
+// The quad kernels give every sample FOUR lanes: lane q of a quad owns outputs 8q .. 8q+7 of every layer (a quarter
+// of the FMAs and weight loads) and the full activation vector is re-assembled inside the quad with shuffles.
+// Same per-output summation order as mlp_layer, so both families agree bit for bit.
+constexpr int kQuadSamples = kMlpThreads / 4;          // samples per CTA tile
+
+// out8[j] = act(bias[8q + j] + sum_i Wt[i][8q + j] h[i]), j = 0..7, i < din rounded up to 8.  Wt is the TRANSPOSED
+// weight ([input][output], 32 x 32): the four lanes of a quad read 32 consecutive elements of row i (conflict-free, the
+// eight quads of the warp read the same words), where rows of the untransposed matrix 8 apart share their banks.
+template <typename T>
+__device__ __forceinline__ void quad_layer(const T* Wt, const T* bias, int din, int dout, int q, const T* h, T* out8,
+                                           bool act, T slope) {
+  T a0[8], a1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a0[j] = T(0); a1[j] = T(0); }
+  if (q * 8 < dout) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a0[j] = bias[q * 8 + j];
+#pragma unroll
+    for (int ib = 0; ib < kMlpW; ib += 8) {
+      if (ib < din) {
+#pragma unroll
+        for (int i = ib; i < ib + 8; i += 2) {
+          const T* r0 = Wt + i * kMlpW + q * 8;
+          const T* r1 = r0 + kMlpW;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { a0[j] += r0[j] * h[i]; a1[j] += r1[j] * h[i + 1]; }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    T r = a0[j] + a1[j];
+    if (act) r = r > T(0) ? r : r * slope;
+    out8[j] = r;
+  }
+}
+
+// full[8 qq + j] = the value out8[j] of lane qq of this quad (all four lanes end with the same 32-vector).
+template <typename T>
+__device__ __forceinline__ void quad_gather(const T* out8, T* full, int lane) {
+  const int base = lane & ~3;
+#pragma unroll
+  for (int qq = 0; qq < 4; ++qq) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) full[qq * 8 + j] = __shfl_sync(0xffffffffu, out8[j], base + qq);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kMlpThreads) mlp_fwd_quad_kernel(const MlpArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char mlp_smem[];
+  T* WsT = reinterpret_cast<T*>(mlp_smem);              // [layer][input][output]
+  T* bs = WsT + kMlpMaxLayers * kMlpW * kMlpW;
+  __shared__ int sdims[kMlpMaxLayers + 1];
+  if (threadIdx.x <= kMlpMaxLayers) sdims[threadIdx.x] = a.dims[threadIdx.x];
+  mlp_load_weights(a, static_cast<T*>(nullptr), bs, WsT);
+  __syncthreads();
+  const int nl = a.nl, din = sdims[0], dlast = sdims[nl];
+  const int lane = threadIdx.x & 31, q = lane & 3;
+  const int64_t n_tiles = (a.B + kQuadSamples - 1) / kQuadSamples;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t r = tile * kQuadSamples + (threadIdx.x >> 2);
+    const bool valid = r < a.B;
+    T h[kMlpW], o8[8];
+    const T* xr = a.x + (valid ? r : 0) * a.ldx;
+#pragma unroll
+    for (int i = 0; i < kMlpW; ++i) h[i] = (valid && i < din) ? xr[i] : T(0);
+#pragma unroll 1
+    for (int l = 0; l < nl; ++l) {
+      quad_layer(WsT + l * kMlpW * kMlpW, bs + l * kMlpW, sdims[l], sdims[l + 1], q, h, o8, l + 1 < nl, a.slope);
+      quad_gather(o8, h, lane);
+    }
+    if (valid) {
+      T* yr = a.y + r * a.ldy;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (q * 8 + j < dlast) yr[q * 8 + j] = o8[j];
+    }
+  }
+}
+
+// Backward with four lanes per sample (see mlp_fwd_quad_kernel).  A warp holds 8 samples: the forward is recomputed
+// (hidden activations of the tile in shared memory, [layer][unit][sample]), the input gradient of a layer is the same
+// quad_layer on the transposed weights, and the weight gradients are formed per warp from the parked (g, a) pairs of
+// its 8 samples (lane i accumulates column i of g^T a).  Per-warp sums are combined per CTA, per-CTA partials by
+// mlp_partial_reduce_kernel: fixed order, bit-reproducible.
+__host__ __device__ inline size_t mlp_bwd_quad_elems(int nl, int psize) {
+  constexpr int kWarps = kMlpThreads / 32;
+  return 2 * static_cast<size_t>(nl) * kMlpW * kMlpW + static_cast<size_t>(nl) * kMlpW + kMlpW +
+         kWarps * (kMlpW * 9 + 8 * (kMlpW + 1)) + static_cast<size_t>(kWarps) * psize +
+         static_cast<size_t>(nl > 1 ? nl - 1 : 0) * kQuadSamples * (kMlpW + 1);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kMlpThreads) mlp_bwd_quad_kernel(const MlpArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char mlp_smem[];
+  constexpr int kWarps = kMlpThreads / 32;
+  constexpr int kTile = kMlpW * 9 + 8 * (kMlpW + 1);   // gT[32][9] | at[8][33]: odd strides keep the quad's stores apart
+  constexpr int kAct = kMlpW + 1;                      // acts[layer][sample][33]
+  const int nl = a.nl;
+  T* Ws = reinterpret_cast<T*>(mlp_smem);                         // [nl][32][32]
+  T* WsT = Ws + nl * kMlpW * kMlpW;                               // [nl][32][32]
+  T* bs = WsT + nl * kMlpW * kMlpW;                               // [nl][32]
+  T* zb = bs + nl * kMlpW;                                        // [32] zeros (bias of the transposed products)
+  T* tiles = zb + kMlpW;                                          // per warp: gT[32][9] | at[8][33]
+  T* accs = tiles + kWarps * kTile;                               // per warp: psize accumulators
+  T* acts = accs + kWarps * a.psize;                              // [nl - 1][kQuadSamples][33]
+  __shared__ int sdims[kMlpMaxLayers + 1], soff[kMlpMaxLayers];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = lane & 3, s8 = lane >> 2;
+  const int sc = tid >> 2;                                        // sample within the CTA tile
+  T* gT = tiles + warp * kTile;
+  T* at = gT + kMlpW * 9;
+  T* acc = accs + warp * a.psize;
+  if (tid == 0) {
+    int p = 0;
+    for (int l = 0; l <= kMlpMaxLayers; ++l) sdims[l] = a.dims[l];
+    for (int l = 0; l < kMlpMaxLayers; ++l) { soff[l] = p; if (l < nl) p += a.dims[l + 1] * a.dims[l] + a.dims[l + 1]; }
+  }
+  if (tid < kMlpW) zb[tid] = T(0);
+  mlp_load_weights(a, Ws, bs, WsT);
+  for (int p = tid; p < kWarps * a.psize; p += kMlpThreads) accs[p] = T(0);
+  __syncthreads();
+  const int din0 = sdims[0], dlast = sdims[nl];
+  const int64_t n_tiles = (a.B + kQuadSamples - 1) / kQuadSamples;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t r = tile * kQuadSamples + sc;
+    const bool valid = r < a.B;
+    const T* xr = a.x + (valid ? r : 0) * a.ldx;
+    T h[kMlpW], o8[8];
+#pragma unroll
+    for (int i = 0; i < kMlpW; ++i) h[i] = (valid && i < din0) ? xr[i] : T(0);
+#pragma unroll 1
+    for (int l = 0; l + 1 < nl; ++l) {                            // forward recompute up to the last layer's input
+      quad_layer(WsT + l * kMlpW * kMlpW, bs + l * kMlpW, sdims[l], sdims[l + 1], q, h, o8, true, a.slope);
+      T* al = acts + (static_cast<size_t>(l) * kQuadSamples + sc) * kAct + q * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) al[j] = o8[j];
+      quad_gather(o8, h, lane);
+    }
+    T g[kMlpW];
+    {
+      const T* gr = a.gy + (valid ? r : 0) * a.ldgy;
+#pragma unroll
+      for (int o = 0; o < kMlpW; ++o) g[o] = (valid && o < dlast) ? gr[o] : T(0);
+    }
+#pragma unroll 1
+    for (int l = nl - 1; l >= 0; --l) {
+      const int din = sdims[l], dout = sdims[l + 1];
+      const T* al = acts + (static_cast<size_t>(l > 0 ? l - 1 : 0) * kQuadSamples + sc) * kAct;   // input of layer l
+      // park this warp's (g, a_l) pairs: gT[o][s], at[s][i]; lane q of a quad writes entries 8q .. 8q+7
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int e = q * 8 + j;
+        gT[e * 9 + s8] = g[e];
+        T av = T(0);
+        if (e < din) av = l == 0 ? (valid ? xr[e] : T(0)) : al[e];
+        at[s8 * (kMlpW + 1) + e] = av;
+      }
+      __syncwarp();
+      if (lane < din) {                                    // column `lane` of gW_l = g^T a over the warp's 8 samples
+        T col[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) col[s] = at[s * (kMlpW + 1) + lane];
+        T* aw = acc + soff[l];
+        for (int o = 0; o < dout; ++o) {
+          const T* grow = gT + o * 9;
+          T d0 = T(0), d1 = T(0);
+#pragma unroll
+          for (int s = 0; s < 8; s += 2) { d0 += grow[s] * col[s]; d1 += grow[s + 1] * col[s + 1]; }
+          aw[o * din + lane] += d0 + d1;
+        }
+      }
+      if (lane < dout) {
+        const T* grow = gT + lane * 9;
+        T d0 = T(0);
+#pragma unroll
+        for (int s = 0; s < 8; ++s) d0 += grow[s];
+        acc[soff[l] + dout * din + lane] += d0;
+      }
+      __syncwarp();
+      if (l > 0 || a.gx) {                                 // input gradient of the layer, then the activation's slope
+        quad_layer(Ws + l * kMlpW * kMlpW, zb, dout, din, q, g, o8, false, a.slope);   // W is the transpose of W^T
+        if (l > 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o8[j] *= al[q * 8 + j] > T(0) ? T(1) : a.slope;
+        }
+        quad_gather(o8, g, lane);
+      }
+    }
+    if (a.gx && valid) {
+      T* gxr = a.gx + r * a.ldgx;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (q * 8 + j < din0) gxr[q * 8 + j] = g[q * 8 + j];
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  T* mine = a.partial + static_cast<size_t>(blockIdx.x) * a.psize;
+  for (int p = tid; p < a.psize; p += kMlpThreads) {
+    T s = T(0);
+    for (int w = 0; w < kWarps; ++w) s += accs[w * a.psize + p];
+    mine[p] = s;
+  }
+}
+
 template <typename T>
 static bool mlp_fill(MlpArgs<T>& a, const void* const* W, const void* const* b, const int32_t* dims, int nl, double slope) {
   if (nl < 1 || nl > kMlpMaxLayers || !W || !dims || slope < 0.0) return false;
@@ -321,14 +530,37 @@ template <typename T>
 static int launch_mlp_fwd(MlpArgs<T>& a, cudaStream_t st) {
   const size_t smem = (static_cast<size_t>(kMlpMaxLayers) * kMlpW * kMlpW + kMlpMaxLayers * kMlpW) * sizeof(T);
   const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
-  const int64_t tiles = (a.B + kMlpThreads - 1) / kMlpThreads;
   const int64_t cap = static_cast<int64_t>(sms) * 8;
+  if (a.B <= kMlpQuadMaxRows) {                        // few rows: four lanes per sample (latency, not throughput)
+    const int64_t qt = (a.B + kQuadSamples - 1) / kQuadSamples;
+    mlp_fwd_quad_kernel<T><<<static_cast<unsigned>(qt < cap ? qt : cap), kMlpThreads, smem, st>>>(a);
+    return launch_status();
+  }
+  const int64_t tiles = (a.B + kMlpThreads - 1) / kMlpThreads;
   mlp_fwd_kernel<T><<<static_cast<unsigned>(tiles < cap ? tiles : cap), kMlpThreads, smem, st>>>(a);
   return launch_status();
 }
 
 template <typename T>
 static int launch_mlp_bwd(MlpArgs<T>& a, T* gparams, cudaStream_t st) {
+  if (a.B <= kMlpQuadMaxRows) {                        // few rows: four lanes per sample
+    const size_t qs = mlp_bwd_quad_elems(a.nl, a.psize) * sizeof(T);
+    if (qs <= 224 * 1024) {
+      auto qk = mlp_bwd_quad_kernel<T>;
+      static bool qattr = false;
+      if (!qattr) {
+        cudaFuncSetAttribute(qk, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+        qattr = true;
+      }
+      const int64_t qt = (a.B + kQuadSamples - 1) / kQuadSamples;
+      const int64_t qg = qt < kMlpMaxGrid ? qt : kMlpMaxGrid;
+      qk<<<static_cast<unsigned>(qg), kMlpThreads, qs, st>>>(a);
+      int qrc = launch_status();
+      if (qrc) return qrc;
+      mlp_partial_reduce_kernel<T><<<(a.psize + 3) / 4, 128, 0, st>>>(a.partial, static_cast<int>(qg), a.psize, gparams);
+      return launch_status();
+    }
+  }
   const size_t smem = mlp_bwd_elems(a.nl, a.psize) * sizeof(T);
   if (smem > 224 * 1024) return VCNF_E_UNSUPPORTED;
   auto kern = mlp_bwd_kernel<T>;
