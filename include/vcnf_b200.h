@@ -448,6 +448,41 @@ int vcnf_adamax_flat_guarded(void* p, const void* g, void* m, void* u, void* ste
                              const void* lr_dev, double beta1, double beta2, double eps, double weight_decay,
                              double grad_scale, const void* guard, int guard_dtype, int dtype, void* stream);
 
+/* ---- fused conditioner + spline (no-grad directions of a spline coupling layer) -----------------------------------
+ * Replaces, for `sample` / `log_prob` / evaluation, the whole chain normflow/nets/resnet.py:76-106 (ResidualNet.forward:
+ * initial layer, num_blocks pre-activation residual blocks, final layer) -> flows/neural_spline/coupling.py:70-96,309-343
+ * (parameter reshape, 1/sqrt(hidden) scaling, utils/splines.py:88-193) with ONE launch per layer: a 128-row tile goes
+ * from x to (y, log|det|) without the hidden activations or the [B, Tc * Pc] parameters touching HBM.  3xTF32 on
+ * tcgen05 (fp32-faithful, see vcnf_linear_tf32x3).  Supported: fp32, hidden = 128, ReLU, no context / dropout /
+ * batch norm, num_blocks <= 4, 8 bins, D <= 32, n_in <= 32, Tc <= 32 with ceil(Tc / (128 / Pc')) <= 4 (Pc' = 24 or 32);
+ * anything else returns VCNF_E_UNSUPPORTED (callers keep the layer-by-layer kernels).
+ *
+ * vcnf_resnet_spline_pack re-tiles the net's parameters for the kernel (TF32 hi / lo planes in the tensor-core operand
+ * layout, 16 KB stages): W / b are HOST arrays of 2 + 2 num_blocks DEVICE pointers in forward order
+ * (initial [128, n_in]; per block the two [128, 128] layers; final [Tc * Pc, 128]), b entries may be null.
+ * `packed` holds vcnf_resnet_spline_pack_bytes(...) bytes (16 B aligned) and must be re-packed when parameters change. */
+int64_t vcnf_resnet_spline_pack_bytes(int n_in, int hidden, int num_blocks, int Tc, int Pc);
+int vcnf_resnet_spline_pack(const void* const* W, const void* const* b, int n_in, int hidden, int num_blocks, int Tc,
+                            int Pc, void* packed, void* stream);
+/*   x, y [B, D] fp32 (ldx, ldy), y may not alias x; logdet [B] overwritten or added to (accumulate)
+ *   id_cols [n_in], tr_cols [Tc]: HOST arrays, the columns feeding the net (in the net's input order) and the
+ *     transformed columns (feature f of the parameters acts on column tr_cols[f]); every other column and the id
+ *     columns are copied; modes (VCNF_TAIL_*) / bounds: HOST arrays per transformed feature
+ *   wh_scale, inverse, outside_zero, err_flag: as vcnf_rqs_layer_fwd
+ *   shared_params [Ts, Ps] (device; Ts = 0 or n_in): the unconditional spline of id column j (coupling.py:165-246,
+ *     `apply_unconditional_transform`), shared_modes / shared_bounds HOST arrays; density direction: the net sees the
+ *     raw id columns and the output carries their CDF; sampling direction: the id columns are inverted first and the
+ *     net sees the result (coupling.py:98-125)
+ *   params (optional, [B, Tc * Pc] with row pitch ldp) receives the spline parameters, acts (optional,
+ *     [1 + 2 num_blocks][B, 128] contiguous) the pre-activation output of every linear layer. */
+int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64_t ldy, void* logdet, int accumulate,
+                           int64_t B, int D, int K, const int32_t* id_cols, int n_in, const int32_t* tr_cols,
+                           int Tc, int Pc, int hidden, int num_blocks, const void* packed,
+                           const uint8_t* modes, const float* bounds, double wh_scale, int inverse,
+                           int outside_zero, int32_t* err_flag, const void* shared_params, int Ts, int Ps,
+                           const uint8_t* shared_modes, const float* shared_bounds, void* params, int64_t ldp,
+                           void* acts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,104 @@
+"""vcnf_resnet_spline_fwd (the whole ResidualNet conditioner + the coupling spline in ONE launch, used by the no-grad
+directions) against the layer-by-layer kernels of the same layer (which the parity suites pin to the oracle) and against
+the oracle itself: both directions, ragged / multi-tile batches, every tail mode, with and without the unconditional
+spline on the identity columns, 0-3 residual blocks."""
+import pytest
+import torch
+
+import oracle
+import vcnf_b200 as nf
+from vcnf_b200 import ops
+from vcnf_b200.flows.neural_spline.coupling import PiecewiseRationalQuadraticCoupling
+from vcnf_b200.nets.resnet import ResidualNet
+from vcnf_b200.utils.masks import create_alternating_binary_mask
+from cases import randomize
+from parity import assert_close, SPLINE
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _both_paths(layer, x, inverse):
+    fn = layer.inverse if inverse else layer.forward
+    y_ref, ld_ref = fn(x)                       # parameters require grad: layer-by-layer kernels
+    assert y_ref.requires_grad
+    before = ops.LAUNCHES
+    with torch.no_grad():
+        y, ld = fn(x)
+    assert ops.LAUNCHES - before == 2           # pack + the fused kernel
+    return y, ld, y_ref.detach(), ld_ref.detach()
+
+
+@pytest.mark.parametrize("B", [1, 127, 128, 300, 20011])
+@pytest.mark.parametrize("inverse", [False, True])
+def test_cfg2_layer_fused_matches_layerwise(B, inverse):
+    torch.manual_seed(B)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(layer, scale=0.05)
+    layer = layer.to(DEV)
+    x = 2.0 * torch.randn(B, 29, device=DEV)    # tail bound 3: a few per cent of the elements fall in the tails
+    y, ld, y_ref, ld_ref = _both_paths(layer, x, inverse)
+    assert_close(y, y_ref, **SPLINE, what="fused cfg2 layer y")
+    assert_close(ld, ld_ref, rtol=SPLINE["rtol"], atol=29 * SPLINE["atol"], what="fused cfg2 layer logdet")
+
+
+@pytest.mark.parametrize("tails,uncond,blocks,D", [("linear", False, 1, 6), ("circular", True, 2, 9), (None, False, 0, 5),
+                                                   (["linear", "circular"] * 8, True, 3, 16), ("linear", True, 2, 32)])
+def test_fused_variants(tails, uncond, blocks, D):
+    torch.manual_seed(D)
+    mask = create_alternating_binary_mask(D, even=False)
+    layer = PiecewiseRationalQuadraticCoupling(
+        mask, lambda i, o: ResidualNet(i, o, hidden_features=128, num_blocks=blocks), num_bins=8, tails=tails,
+        tail_bound=2.5, apply_unconditional_transform=uncond)
+    randomize(layer, scale=0.05)
+    layer = layer.to(DEV)
+    x = torch.rand(777, D, device=DEV) if tails is None else 1.5 * torch.randn(777, D, device=DEV)
+    for inverse in (False, True):
+        y, ld, y_ref, ld_ref = _both_paths(layer, x, inverse)
+        assert_close(y, y_ref, **SPLINE, what="fused variant y")
+        assert_close(ld, ld_ref, rtol=SPLINE["rtol"], atol=D * SPLINE["atol"], what="fused variant logdet")
+
+
+def test_fused_outputs_params_and_activations():
+    """The optional outputs: spline parameters and the pre-activation output of every linear layer."""
+    torch.manual_seed(5)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(layer, scale=0.05)
+    layer = layer.to(DEV)
+    c = layer.prqct
+    x = torch.randn(1000, 29, device=DEV)
+    with torch.no_grad():
+        fused = c._fused_route(x, None)
+        assert fused is not None
+        y, ld, params, acts = ops.resnet_spline(x, fused, *c.transform_net.fused_params(), inverse=False,
+                                                shared=c._shared_params(), want_params=True, want_acts=True)
+        net = c.transform_net
+        xin = x[:, c.identity_features.to(DEV)]
+        h = torch.nn.functional.linear(xin.double(), net.initial_layer.weight.double(), net.initial_layer.bias.double())
+        ref = [h]
+        for blk in net.blocks:
+            l0, l1 = blk.linear_layers
+            t = torch.nn.functional.linear(torch.relu(h), l0.weight.double(), l0.bias.double())
+            h = h + torch.nn.functional.linear(torch.relu(t), l1.weight.double(), l1.bias.double())
+            ref += [t, h]
+        theta = torch.nn.functional.linear(h, net.final_layer.weight.double(), net.final_layer.bias.double())
+    for i, r in enumerate(ref):
+        assert_close(acts[i], r.float(), rtol=1e-5, atol=1e-5 * float(r.abs().max()), what="fused acts")
+    assert_close(params, theta.float(), rtol=1e-5, atol=1e-5 * float(theta.abs().max()), what="fused params")
+
+
+def test_fused_layer_against_oracle():
+    torch.manual_seed(11)
+    ref = oracle.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(ref, scale=0.05)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    layer.load_state_dict(ref.state_dict())
+    layer = layer.to(DEV)
+    x = 1.5 * torch.randn(513, 29)
+    ref = ref.double()
+    with torch.no_grad():
+        for inverse in (False, True):
+            yr, lr = (ref.inverse if inverse else ref.forward)(x.double())
+            y, ld = (layer.inverse if inverse else layer.forward)(x.to(DEV))
+            assert_close(y.cpu(), yr.float(), **SPLINE, what="fused vs oracle y")
+            assert_close(ld.cpu(), lr.float(), rtol=SPLINE["rtol"], atol=29 * SPLINE["atol"], what="fused vs oracle logdet")

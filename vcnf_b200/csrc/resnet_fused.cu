@@ -1,0 +1,608 @@
+// The whole conditioner of a spline coupling layer and the spline itself as ONE kernel (the no-grad directions:
+// `sample`, `log_prob`, evaluation):
+//
+//   h0 = W0 x_id + b0;  h_{i+1} = h_i + Wb_i relu(Wa_i relu(h_i) + ba_i) + bb_i   (normflow/nets/resnet.py:38-106)
+//   theta = Wf h_nb + bf                                                           ([B, Tc * Pc], resnet.py:104)
+//   y[:, tr] = RQS^{+-1}(x[:, tr]; theta),  y[:, id] = x[:, id],  logdet = sum_f log|dy/dx|
+//                                                   (flows/neural_spline/coupling.py:70-96,309-343; utils/splines.py:88-193)
+//
+// The layer-by-layer path moves the [B, 128] hidden activations through HBM ten times and the [B, 322] spline
+// parameters twice (1 524 B per sample-layer); here a 128-row tile stays on the SM from the gathered
+// inputs to the transformed outputs (2 * 4 D + 4 B per sample-layer):
+//
+//   * the activation operand of the next layer is written by the epilogue warps straight into shared memory in the
+//     tcgen05 K-major canonical layout, already split into TF32 hi / lo planes (3xTF32, see gemm_tf32x3.cu);
+//   * the weights (pre-split and pre-tiled by vcnf_resnet_spline_pack, 16-column stages of 16 KB) stream from L2
+//     through a ring of bulk copies issued by one thread;
+//   * accumulators (hi*hi and the cross terms, two buffers) live in tensor memory; the residual stream of the tile
+//     lives in the epilogue threads' registers;
+//   * the head runs in slices of whole features (each padded to a multiple of 8 columns), and the spline of a slice is
+//     evaluated from the accumulator registers while the tensor core works on the next slice.
+//
+// Warp roles (384 threads, one CTA per SM, persistent over tiles): warp 0 weight copies, warp 1 MMA issue, warp 2 TMEM
+// allocation, warps 4-11 epilogue (TMEM lane quarter = warp % 4, two warps per quarter split the columns / features).
+#include <cuda.h>
+#include "common.cuh"
+#include "rqs_fast.cuh"
+#include "../../include/vcnf_b200.h"
+
+namespace vcnf {
+namespace fusednet {
+
+constexpr int kH = 128;                 // hidden width = UMMA N of the hidden layers (and rows per tile = UMMA M)
+constexpr int kRows = 128;
+constexpr int kMaxBlocks = 4;
+constexpr int kMaxUnits = 1 + 2 * kMaxBlocks + 4;      // layers + head slices
+constexpr int kMaxSlices = 4;
+constexpr int kWK = 16;                 // columns of the contraction per weight stage
+constexpr int kWStages = 4;
+constexpr uint32_t kWPlane = kH * kWK * 4;             // 8 KB: hi (or lo) plane of a weight stage
+constexpr uint32_t kWStage = 2 * kWPlane;
+constexpr uint32_t kWSbo = kWK * 32;                   // byte stride between 8-row groups of a weight stage
+constexpr int kAChunk = 32;             // activation columns per chunk (readiness granularity)
+constexpr uint32_t kAPlane = kRows * kAChunk * 4;      // 16 KB
+constexpr uint32_t kAChunkBytes = 2 * kAPlane;         // hi | lo
+constexpr uint32_t kASbo = kAChunk * 32;
+constexpr int kThreads = 384;
+constexpr int kEpiWarp0 = 4, kEpiWarps = 8, kEpiThreads = kEpiWarps * 32;
+constexpr int kMaxD = 32;
+constexpr uint32_t kTmemCols = 512;     // 2 buffers x (main 128 | cross terms 128)
+
+struct Args {
+  const float* x; int64_t ldx;
+  float* y; int64_t ldy;
+  float* logdet; int accumulate;
+  int64_t B; int D;
+  const unsigned char* packed;          // weight stages, then biases (see pack kernel)
+  int n_in, nb, Tc, Pc, PcP, fs, n_slices;
+  int id_cols[kMaxD], tr_cols[kMaxD];
+  unsigned char modes[kMaxD];
+  float bounds[kMaxD];
+  float wh_scale;
+  int outside_zero;
+  int* err_flag;
+  const float* shared; int Ts, Ps;      // optional: batch-shared spline on the id columns (unconditional transform)
+  unsigned char smodes[kMaxD];
+  float sbounds[kMaxD];
+  float* params; int64_t ldp;           // optional: theta [B, Tc * Pc]
+  float* acts; int64_t act_stride;      // optional: pre-activation outputs of every layer, [1 + 2 nb][B, 128]
+};
+
+// ---- raw PTX wrappers (same conventions as gemm_tf32x3.cu) ------------------------------------------------------
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); }
+
+// K-major, no swizzle: 8 rows x 16 B core matrices, LBO = distance between the two 16 B k-chunks of one MMA (K = 8
+// tf32), SBO = distance between 8-row groups (cute/arch/mma_sm100_desc.hpp bit layout, version 1).
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr >> 4) & 0x3fffu);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fffu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  return d;
+}
+__host__ __device__ constexpr uint32_t instr_desc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(N >> 3) << 17) |
+         (static_cast<uint32_t>(M >> 4) << 24);
+}
+__host__ __device__ __forceinline__ float rn_tf32(float a) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float((__float_as_uint(a) + 0x1000u) & 0xffffe000u);
+#else
+  return a;
+#endif
+}
+__device__ __forceinline__ void split_tf32(float a, float& hi, float& lo) {
+  hi = rn_tf32(a);
+  lo = rn_tf32(a - hi);
+}
+
+// ---- packed parameter buffer -------------------------------------------------------------------------------------
+// Units u = 0 .. L + S - 1: the L = 1 + 2 nb linear layers, then the S head slices.  Unit 0 has ceil(n_in / 16)
+// weight stages, every other unit 8 (K = 128).  A stage is [hi plane | lo plane], each 128 rows x 16 k in the
+// canonical layout (row = output feature of the unit).  Head slice s, row fi * PcP + i = parameter i of feature
+// s * fs + fi (zero rows pad).  After the stages: (L + S) x 128 biases in the same row order.
+__host__ __device__ inline int n_layers(int nb) { return 1 + 2 * nb; }
+__host__ __device__ inline int stages0(int n_in) { return (n_in + kWK - 1) / kWK; }
+__host__ __device__ inline int total_stages(int n_in, int nb, int S) { return stages0(n_in) + 8 * (2 * nb + S); }
+__host__ __device__ inline size_t packed_bytes(int n_in, int nb, int S) {
+  return static_cast<size_t>(total_stages(n_in, nb, S)) * kWStage + static_cast<size_t>(n_layers(nb) + S) * kH * 4;
+}
+
+struct PackArgs {
+  const float* W[kMaxUnits];     // [0]: initial [128, n_in]; [1 .. 2 nb]: hidden [128, 128]; [2 nb + 1]: head [Tc*Pc, 128]
+  const float* b[kMaxUnits];
+  int n_in, nb, Tc, Pc, PcP, fs, S;
+  unsigned char* out;
+};
+
+__global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
+  const int L = n_layers(a.nb), S = a.S;
+  const int st0 = stages0(a.n_in);
+  const int n_st = total_stages(a.n_in, a.nb, S);
+  const int64_t n_w = static_cast<int64_t>(n_st) * kH * kWK;
+  const int64_t n_b = static_cast<int64_t>(L + S) * kH;
+  for (int64_t e = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < n_w + n_b;
+       e += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    if (e < n_w) {
+      const int st = static_cast<int>(e / (kH * kWK));
+      const int rem = static_cast<int>(e - static_cast<int64_t>(st) * (kH * kWK));
+      const int n = rem / kWK, kk = rem - n * kWK;
+      int u, t;
+      if (st < st0) { u = 0; t = st; } else { u = 1 + (st - st0) / 8; t = (st - st0) % 8; }
+      const int k = t * kWK + kk;
+      float v = 0.f;
+      if (u == 0) {
+        if (k < a.n_in) v = a.W[0][n * a.n_in + k];
+      } else if (u < L) {
+        v = a.W[u][n * kH + k];
+      } else {
+        const int s = u - L, fi = n / a.PcP, i = n - fi * a.PcP, f = s * a.fs + fi;
+        if (fi < a.fs && i < a.Pc && f < a.Tc) v = a.W[L][static_cast<int64_t>(f * a.Pc + i) * kH + k];
+      }
+      float hi, lo;
+      split_tf32(v, hi, lo);
+      unsigned char* base = a.out + static_cast<size_t>(st) * kWStage;
+      const uint32_t off = static_cast<uint32_t>(n >> 3) * kWSbo + (kk >> 2) * 128 + (n & 7) * 16 + (kk & 3) * 4;
+      *reinterpret_cast<float*>(base + off) = hi;
+      *reinterpret_cast<float*>(base + kWPlane + off) = lo;
+    } else {
+      const int eb = static_cast<int>(e - n_w);
+      const int u = eb / kH, n = eb - u * kH;
+      float v = 0.f;
+      if (u < L) {
+        v = a.b[u] ? a.b[u][n] : 0.f;
+      } else {
+        const int s = u - L, fi = n / a.PcP, i = n - fi * a.PcP, f = s * a.fs + fi;
+        if (fi < a.fs && i < a.Pc && f < a.Tc && a.b[L]) v = a.b[L][f * a.Pc + i];
+      }
+      reinterpret_cast<float*>(a.out + static_cast<size_t>(n_st) * kWStage)[eb] = v;
+    }
+  }
+}
+
+// One spline element whose parameter vector sits in REGISTERS: fast::locate with the two derivative parameters picked
+// by selects instead of a dynamically indexed load (same values, same arithmetic).
+template <int K, bool INV, int PCP>
+__device__ __forceinline__ void element_regs(const float (&prm)[PCP], float v, float bound, float scale, int mode,
+                                             int outside_zero, float* out, float* lad, int* flag) {
+  using namespace fast;
+  P2 p[K], kn[K + 1];
+  const float left = rqs_lo(bound, mode);
+  axes<K>(prm, scale, bound, left, p, kn);
+  P2 lo = kn[0], hi = kn[1];
+  int idx = 0;
+#pragma unroll
+  for (int k = 1; k < K; ++k) {
+    const bool ge = v >= (INV ? kn[k].y : kn[k].x);
+    lo.x = ge ? kn[k].x : lo.x;  lo.y = ge ? kn[k].y : lo.y;
+    hi.x = ge ? kn[k + 1].x : hi.x;  hi.y = ge ? kn[k + 1].y : hi.y;
+    idx = ge ? k : idx;
+  }
+  RqsBin<float> b;
+  b.idx = idx;
+  const P2 wh = p2add(hi, P2{-lo.x, -lo.y});
+  b.x0 = lo.x; b.w = wh.x; b.y0 = lo.y; b.h = wh.y;
+  deriv_slots(idx, K, mode, &b.s0, &b.s1);
+  const float edge = RqsConst<float>::edge();
+  float r0 = edge, r1 = edge;
+#pragma unroll
+  for (int k = 0; k < PCP - 2 * K; ++k) {
+    r0 = (b.s0 == k) ? prm[2 * K + k] : r0;
+    r1 = (b.s1 == k) ? prm[2 * K + k] : r1;
+  }
+  b.r0 = r0; b.r1 = r1;
+  P2 e01;
+  const P2 sp = softplus2(P2{r0, r1}, &e01);
+  b.d0 = RqsConst<float>::min_deriv() + sp.x;
+  b.d1 = RqsConst<float>::min_deriv() + sp.y;
+  float o, l;
+  int ok = 1;
+  if (INV) rq_inverse(v, b, &o, &l, &ok); else rq_forward(v, b, &o, &l);
+  const bool inside = (v >= left) && (v <= left + (bound - (-bound)));
+  *out = inside ? o : (outside_zero ? 0.f : v);
+  *lad = inside ? l : 0.f;
+  if (inside && !ok) *flag |= 1;
+}
+
+template <bool INV, int PCP>
+__global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid_constant__ Args a) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  uint64_t* w_full = reinterpret_cast<uint64_t*>(smem);           // [kWStages] copy engine -> MMA
+  uint64_t* w_empty = w_full + kWStages;                          // [kWStages] MMA -> copy issuer
+  uint64_t* a_ready = w_empty + kWStages;                         // [4] epilogue -> MMA: activation chunk j written
+  uint64_t* acc_full = a_ready + 4;                               // [2] MMA -> epilogue
+  uint64_t* acc_empty = acc_full + 2;                             // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  int* s_id = reinterpret_cast<int*>(smem + 256);                 // [32]
+  int* s_tr = s_id + kMaxD;                                       // [32]
+  int* s_mode = s_tr + kMaxD;                                     // [32]
+  float* s_bound = reinterpret_cast<float*>(s_mode + kMaxD);      // [32]
+  unsigned char* A = smem + 1024;                                 // 4 chunks x [hi 16 KB | lo 16 KB]
+  unsigned char* Wst = A + 4 * kAChunkBytes;                      // kWStages x [hi 8 KB | lo 8 KB]
+  float* bias = reinterpret_cast<float*>(Wst + kWStages * kWStage);   // [(L + S)][128]
+  const int L = n_layers(a.nb), S = a.n_slices, D = a.D;
+  float* lds = bias + (L + S) * kH;                               // [128]
+  fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(lds + kRows); // [Ts][9] knot records of the batch-shared splines
+  float* xs = reinterpret_cast<float*>(rec + a.Ts * 9);           // [128][D]
+  float* s_sbound = reinterpret_cast<float*>(smem + 768);         // [32]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int st0 = stages0(a.n_in);
+  const int n_st = total_stages(a.n_in, a.nb, S);
+  const int64_t n_tiles = (a.B + kRows - 1) / kRows;
+
+  if (tid == 0) {
+    for (int s = 0; s < kWStages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+    for (int j = 0; j < 4; ++j) mbar_init(&a_ready[j], kEpiWarps);
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps); }
+    mbar_init_fence();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+  if (tid < kMaxD) {
+    s_id[tid] = a.id_cols[tid];
+    s_tr[tid] = a.tr_cols[tid];
+    s_mode[tid] = a.modes[tid];
+    s_bound[tid] = a.bounds[tid];
+    s_sbound[tid] = a.sbounds[tid];
+    if (tid < a.Ts) fast::build_records<8>(a.shared + tid * a.Ps, a.smodes[tid], a.sbounds[tid], rec + tid * 9);
+  }
+  {
+    const float* bsrc = reinterpret_cast<const float*>(a.packed + static_cast<size_t>(n_st) * kWStage);
+    for (int i = tid; i < (L + S) * kH; i += kThreads) bias[i] = __ldg(bsrc + i);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================== weight stages: bulk copies from L2 =====================================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int st = 0; st < n_st; ++st, ++it) {
+          const int s = it % kWStages;
+          mbar_wait(&w_empty[s], ((it / kWStages) & 1u) ^ 1u);
+          mbar_expect_tx(&w_full[s], kWStage);
+          bulk_g2s(Wst + s * kWStage, a.packed + static_cast<size_t>(st) * kWStage, kWStage, &w_full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issue =====================================
+    const uint32_t idesc = instr_desc_tf32(kRows, kH);
+    uint32_t it = 0, uc = 0, aph = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      for (int u = 0; u < L + S; ++u, ++uc) {
+        const uint32_t buf = uc & 1u;
+        mbar_wait(&acc_empty[buf], ((uc >> 1) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t d_main = tmem_base + buf * 256u, d_small = d_main + 128u;
+        const int nst = u == 0 ? st0 : 8;
+        for (int t = 0; t < nst; ++t, ++it) {
+          const int j = t >> 1;
+          if (u <= L && (t & 1) == 0) {               // chunk j of this unit's activation operand (head slices share one)
+            mbar_wait(&a_ready[j], (aph >> j) & 1u);
+            aph ^= 1u << j;
+          }
+          const int s = it % kWStages;
+          mbar_wait(&w_full[s], (it / kWStages) & 1u);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t a_hi = smem_u32(A) + static_cast<uint32_t>(j) * kAChunkBytes + static_cast<uint32_t>(t & 1) * 512u;
+            const uint32_t a_lo = a_hi + kAPlane;
+            const uint32_t b_hi = smem_u32(Wst) + static_cast<uint32_t>(s) * kWStage;
+            const uint32_t b_lo = b_hi + kWPlane;
+#pragma unroll
+            for (int combo = 0; combo < 3; ++combo) {          // small terms first: lo*hi, hi*lo, then hi*hi
+              const uint32_t ab = combo == 0 ? a_lo : a_hi;
+              const uint32_t bb = combo == 1 ? b_lo : b_hi;
+#pragma unroll
+              for (int kk = 0; kk < 2; ++kk) {
+                const uint64_t ad = smem_desc(ab + kk * 256, 128, kASbo);
+                const uint64_t bd = smem_desc(bb + kk * 256, 128, kWSbo);
+                if (combo == 2) mma_tf32(d_main, ad, bd, idesc, (t > 0 || kk > 0) ? 1u : 0u);
+                else mma_tf32(d_small, ad, bd, idesc, (t > 0 || combo > 0 || kk > 0) ? 1u : 0u);
+              }
+            }
+            tc_commit(&w_empty[s]);
+            if (t == nst - 1) tc_commit(&acc_full[buf]);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // ===================================== epilogue / spline =====================================
+    const int ew = warp - kEpiWarp0, q = warp & 3, g = ew >> 2;
+    const int et = ew * 32 + lane, row = q * 32 + lane;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    unsigned char* a_row = A + static_cast<uint32_t>(row >> 3) * kASbo + (row & 7) * 16;
+    uint32_t uc = 0;
+    int flag = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int64_t m0 = tile * kRows;
+      for (int e = et; e < kRows * D; e += kEpiThreads) {
+        const int r = e / D, c = e - r * D;
+        xs[e] = (m0 + r < a.B) ? __ldg(a.x + (m0 + r) * a.ldx + c) : 0.f;
+      }
+      epi_bar();
+      float ldsum = 0.f;
+      if (INV && a.Ts > 0) {            // sampling direction: the id columns go through their own spline FIRST
+        for (int j = g; j < a.Ts; j += 2) {
+          float o, l;
+          int bin;
+          fast::table_element<8, true>(rec + j * 9, xs[row * D + s_id[j]], s_sbound[j], a.outside_zero, &o, &l, &bin, &flag);
+          xs[row * D + s_id[j]] = o;
+          ldsum += l;
+        }
+        epi_bar();
+      }
+      // gathered inputs of the net -> chunk 0 of the activation operand (this thread: 16 columns of its row)
+#pragma unroll
+      for (int kq = 0; kq < 4; ++kq) {
+        const int k0 = g * 16 + kq * 4;
+        if (k0 < st0 * kWK) {
+          float h4[4], l4[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float v = (k0 + c < a.n_in) ? xs[row * D + s_id[k0 + c]] : 0.f;
+            split_tf32(v, h4[c], l4[c]);
+          }
+          *reinterpret_cast<float4*>(a_row + (k0 >> 2) * 128) = make_float4(h4[0], h4[1], h4[2], h4[3]);
+          *reinterpret_cast<float4*>(a_row + kAPlane + (k0 >> 2) * 128) = make_float4(l4[0], l4[1], l4[2], l4[3]);
+        }
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_ready[0]);
+      if (!INV && a.Ts > 0) {           // density direction: the net saw the raw id columns, the output gets their CDF
+        epi_bar();
+        for (int j = g; j < a.Ts; j += 2) {
+          float o, l;
+          int bin;
+          fast::table_element<8, false>(rec + j * 9, xs[row * D + s_id[j]], s_sbound[j], a.outside_zero, &o, &l, &bin, &flag);
+          xs[row * D + s_id[j]] = o;
+          ldsum += l;
+        }
+      }
+
+      float res[64];                                   // residual stream of this thread's 4 x 16 columns
+#pragma unroll
+      for (int i = 0; i < 64; ++i) res[i] = 0.f;
+      for (int u = 0; u < L; ++u, ++uc) {
+        const uint32_t buf = uc & 1u;
+        mbar_wait(&acc_full[buf], (uc >> 1) & 1u);
+        tc_fence_after();
+        const bool add_res = u >= 2 && (u & 1) == 0, write_res = (u & 1) == 0, relu_next = u != L - 1;
+        const float* bu = bias + u * kH;
+        float* act_row = a.acts ? a.acts + static_cast<int64_t>(u) * a.act_stride + (m0 + row) * kH : nullptr;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int c0 = j * 32 + g * 16;
+          uint32_t r[16], r2[16];
+          tmem_ld16(t_lane + buf * 256u + c0, r);
+          tmem_ld16(t_lane + buf * 256u + 128u + c0, r2);
+          tmem_ld_wait();
+          float v[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            v[i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bu[c0 + i];
+            if (add_res) v[i] += res[j * 16 + i];
+            if (write_res) res[j * 16 + i] = v[i];
+          }
+          if (act_row && m0 + row < a.B) {
+#pragma unroll
+            for (int i = 0; i < 16; i += 4)
+              *reinterpret_cast<float4*>(act_row + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          }
+          unsigned char* dst = a_row + static_cast<uint32_t>(j) * kAChunkBytes + (g * 4) * 128;
+#pragma unroll
+          for (int i = 0; i < 16; i += 4) {
+            float h4[4], l4[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) split_tf32(relu_next ? fmaxf(v[i + c], 0.f) : v[i + c], h4[c], l4[c]);
+            *reinterpret_cast<float4*>(dst + (i >> 2) * 128) = make_float4(h4[0], h4[1], h4[2], h4[3]);
+            *reinterpret_cast<float4*>(dst + kAPlane + (i >> 2) * 128) = make_float4(l4[0], l4[1], l4[2], l4[3]);
+          }
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&a_ready[j]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      }
+
+      for (int s = 0; s < S; ++s, ++uc) {
+        const uint32_t buf = uc & 1u;
+        mbar_wait(&acc_full[buf], (uc >> 1) & 1u);
+        tc_fence_after();
+        const int nf = (a.Tc - s * a.fs) < a.fs ? (a.Tc - s * a.fs) : a.fs;
+        const float* bu = bias + (L + s) * kH;
+        for (int fi = g; fi < nf; fi += 2) {
+          const int f = s * a.fs + fi, col0 = fi * PCP;
+          uint32_t r[PCP], r2[PCP];
+#pragma unroll
+          for (int c8 = 0; c8 < PCP; c8 += 8) {
+            tmem_ld8(t_lane + buf * 256u + col0 + c8, r + c8);
+            tmem_ld8(t_lane + buf * 256u + 128u + col0 + c8, r2 + c8);
+          }
+          tmem_ld_wait();
+          float prm[PCP];
+#pragma unroll
+          for (int i = 0; i < PCP; ++i) prm[i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bu[col0 + i];
+          if (a.params && m0 + row < a.B) {
+            float* pr = a.params + (m0 + row) * a.ldp + f * a.Pc;
+#pragma unroll
+            for (int i = 0; i < PCP; ++i) if (i < a.Pc) pr[i] = prm[i];
+          }
+          const int col = s_tr[f];
+          const float v = xs[row * D + col];
+          float o, l;
+          element_regs<8, INV, PCP>(prm, v, s_bound[f], a.wh_scale, s_mode[f], a.outside_zero, &o, &l, &flag);
+          xs[row * D + col] = o;
+          ldsum += l;
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      }
+      if (g == 1) lds[row] = ldsum;
+      epi_bar();
+      if (g == 0 && m0 + row < a.B) {
+        const float t = ldsum + lds[row];
+        a.logdet[m0 + row] = a.accumulate ? a.logdet[m0 + row] + t : t;
+      }
+      for (int e = et; e < kRows * D; e += kEpiThreads) {
+        const int r = e / D, c = e - r * D;
+        if (m0 + r < a.B) a.y[(m0 + r) * a.ldy + c] = xs[e];
+      }
+      epi_bar();
+    }
+    if (flag && a.err_flag) atomicOr(a.err_flag, 1);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+inline size_t smem_bytes(int nb, int S, int D) {
+  return 1024 + 4 * static_cast<size_t>(kAChunkBytes) + kWStages * static_cast<size_t>(kWStage) +
+         (static_cast<size_t>(n_layers(nb) + S) * kH + kRows + static_cast<size_t>(kRows) * D) * 4 + kMaxD * 9 * 16;
+}
+
+}  // namespace fusednet
+}  // namespace vcnf
+
+using namespace vcnf;
+using namespace vcnf::fusednet;
+
+static bool shape_ok(int n_in, int hidden, int nb, int Tc, int Pc, int* PcP, int* fs, int* S) {
+  if (hidden != kH || n_in < 1 || n_in > kMaxD || nb < 0 || nb > kMaxBlocks || Tc < 1 || Tc > kMaxD || Pc < 1 || Pc > 32)
+    return false;
+  *PcP = Pc <= 24 ? 24 : 32;
+  *fs = kH / *PcP;
+  *S = (Tc + *fs - 1) / *fs;
+  return *S <= kMaxSlices;
+}
+
+extern "C" int64_t vcnf_resnet_spline_pack_bytes(int n_in, int hidden, int num_blocks, int Tc, int Pc) {
+  int PcP, fs, S;
+  if (!shape_ok(n_in, hidden, num_blocks, Tc, Pc, &PcP, &fs, &S)) return VCNF_E_UNSUPPORTED;
+  return static_cast<int64_t>(packed_bytes(n_in, num_blocks, S));
+}
+
+extern "C" int vcnf_resnet_spline_pack(const void* const* W, const void* const* b, int n_in, int hidden, int num_blocks,
+                                       int Tc, int Pc, void* packed, void* stream) {
+  if (!W || !b || !packed) return VCNF_E_BADARG;
+  PackArgs p = {};
+  if (!shape_ok(n_in, hidden, num_blocks, Tc, Pc, &p.PcP, &p.fs, &p.S)) return VCNF_E_UNSUPPORTED;
+  const int L = n_layers(num_blocks);
+  for (int u = 0; u <= L; ++u) {
+    if (!W[u]) return VCNF_E_BADARG;
+    p.W[u] = static_cast<const float*>(W[u]);
+    p.b[u] = static_cast<const float*>(b[u]);
+  }
+  p.n_in = n_in; p.nb = num_blocks; p.Tc = Tc; p.Pc = Pc;
+  p.out = static_cast<unsigned char*>(packed);
+  const int64_t n = static_cast<int64_t>(total_stages(n_in, num_blocks, p.S)) * kH * kWK + static_cast<int64_t>(L + p.S) * kH;
+  const int64_t blocks = (n + 255) / 256;
+  pack_kernel<<<static_cast<unsigned>(blocks < 1184 ? blocks : 1184), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  return launch_status();
+}
+
+extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64_t ldy, void* logdet, int accumulate,
+                                      int64_t B, int D, int K, const int32_t* id_cols, int n_in, const int32_t* tr_cols,
+                                      int Tc, int Pc, int hidden, int num_blocks, const void* packed,
+                                      const uint8_t* modes, const float* bounds, double wh_scale, int inverse,
+                                      int outside_zero, int32_t* err_flag, const void* shared_params, int Ts, int Ps,
+                                      const uint8_t* shared_modes, const float* shared_bounds, void* params,
+                                      int64_t ldp, void* acts, void* stream) {
+  if (Ts < 0 || (Ts > 0 && (!shared_params || !shared_modes || !shared_bounds))) return VCNF_E_BADARG;
+  if (Ts != 0 && Ts != n_in) return VCNF_E_UNSUPPORTED;   // the shared splines act on the net's input columns
+  if (!x || !y || !logdet || !id_cols || !tr_cols || !packed || !modes || !bounds || B < 0 || D < 1) return VCNF_E_BADARG;
+  Args a = {};
+  if (K != 8 || D > kMaxD || !shape_ok(n_in, hidden, num_blocks, Tc, Pc, &a.PcP, &a.fs, &a.n_slices)) return VCNF_E_UNSUPPORTED;
+  if (B == 0) return 0;
+  for (int i = 0; i < n_in; ++i) { if (id_cols[i] < 0 || id_cols[i] >= D) return VCNF_E_BADARG; a.id_cols[i] = id_cols[i]; }
+  for (int i = 0; i < Tc; ++i) {
+    if (tr_cols[i] < 0 || tr_cols[i] >= D) return VCNF_E_BADARG;
+    a.tr_cols[i] = tr_cols[i]; a.modes[i] = modes[i]; a.bounds[i] = bounds[i];
+  }
+  a.x = static_cast<const float*>(x); a.ldx = ldx;
+  a.y = static_cast<float*>(y); a.ldy = ldy;
+  a.logdet = static_cast<float*>(logdet); a.accumulate = accumulate;
+  a.B = B; a.D = D;
+  a.packed = static_cast<const unsigned char*>(packed);
+  a.n_in = n_in; a.nb = num_blocks; a.Tc = Tc; a.Pc = Pc;
+  a.wh_scale = static_cast<float>(wh_scale);
+  a.outside_zero = outside_zero;
+  a.err_flag = err_flag;
+  a.shared = static_cast<const float*>(shared_params); a.Ts = Ts; a.Ps = Ps;
+  for (int i = 0; i < Ts; ++i) { a.smodes[i] = shared_modes[i]; a.sbounds[i] = shared_bounds[i]; }
+  a.params = static_cast<float*>(params); a.ldp = ldp;
+  a.acts = static_cast<float*>(acts); a.act_stride = B * kH;
+  const size_t smem = smem_bytes(num_blocks, a.n_slices, D);
+  const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
+  const int64_t tiles = (B + kRows - 1) / kRows;
+  const unsigned grid = static_cast<unsigned>(tiles < sms ? tiles : sms);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define VCNF_FUSED_LAUNCH(INV, PCP)                                                                         \
+  do {                                                                                                      \
+    auto k = resnet_spline_kernel<INV, PCP>;                                                                \
+    static bool attr = false;                                                                               \
+    if (!attr) { cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr = true; } \
+    k<<<grid, kThreads, smem, st>>>(a);                                                                     \
+  } while (0)
+  if (a.PcP == 24) { if (inverse) VCNF_FUSED_LAUNCH(true, 24); else VCNF_FUSED_LAUNCH(false, 24); }
+  else { if (inverse) VCNF_FUSED_LAUNCH(true, 32); else VCNF_FUSED_LAUNCH(false, 32); }
+#undef VCNF_FUSED_LAUNCH
+  return launch_status();
+}

@@ -221,15 +221,47 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         if torch.is_tensor(tail_bound):
             self.register_buffer("tail_bound", tail_bound[transform_features])
         self._specs = None
+        self._fused = None
 
 
     def _load_from_state_dict(self, *args, **kwargs):
         # the kernel specs cache the tail bounds: a loaded `tail_bound` buffer must rebuild them
         super()._load_from_state_dict(*args, **kwargs)
         self._specs = None
+        self._fused = None
 
     def _transform_dim_multiplier(self):
         return _params_per_feature(self.tails, self.num_bins)
+
+    def _shared_params(self):
+        ut = self.unconditional_transform
+        return ut.packed_params() if ut is not None else None
+
+    def _fused_route(self, inputs, context):
+        """The no-grad directions of a dense ResidualNet conditioner run as ONE kernel per layer
+        (vcnf_resnet_spline_fwd: net + spline, nothing but x and y touches HBM).  Returns the ops.FusedNetSpec or None
+        (gradients needed, or a configuration the kernel does not cover: the layer-by-layer kernels then run)."""
+        net = self.transform_net
+        ut = self.unconditional_transform
+        if (context is not None or (ut is not None and getattr(ut, "_img", False)) or inputs.dim() != 2
+                or not inputs.is_cuda or inputs.dtype != torch.float32 or not hasattr(net, "fusable") or not net.fusable()):
+            return None
+        if torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters())):
+            return None
+        if self._fused is None:
+            if self._specs is None:
+                self._build_specs()
+            trans = self.transform_features.tolist()
+            cmodes, cbounds = _modes_and_bounds(self.tails, self.tail_bound, len(trans))
+            smodes, sbounds = ut.segment() if ut is not None else ((), ())
+            Ps = _params_per_feature(ut.tails, self.num_bins) if ut is not None else 0
+            spec = ops.FusedNetSpec(self.identity_features.tolist(), trans, cmodes, cbounds, self.num_bins,
+                                    self._transform_dim_multiplier(), self._wh_scale(),
+                                    isinstance(self.tails, (list, tuple)), net.hidden_features, len(net.blocks),
+                                    smodes, sbounds, Ps) \
+                if self.features <= 32 and len(trans) <= 32 and len(self.identity_features) <= 32 else None
+            self._fused = spec if spec is not None and spec.supported else False
+        return self._fused or None
 
     def _check_domain(self, inputs):
         """tails=None: the values that reach a bounded spline must lie in [0, 1] (utils/splines.py:105-106)."""
@@ -345,6 +377,10 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
             return self._image(inputs, context, False)
         if self._specs is None:
             self._build_specs()
+        fused = None if want_bins else self._fused_route(inputs, context)
+        if fused is not None:
+            return ops.resnet_spline(inputs, fused, *self.transform_net.fused_params(), inverse=False,
+                                     shared=self._shared_params())
         identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
         params = self.transform_net(identity_split, context)
         shared = self.unconditional_transform.packed_params() if self.unconditional_transform is not None else None
@@ -357,6 +393,10 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
             return self._image(inputs, context, True)
         if self._specs is None:
             self._build_specs()
+        fused = self._fused_route(inputs, context)
+        if fused is not None:
+            return ops.resnet_spline(inputs, fused, *self.transform_net.fused_params(), inverse=True,
+                                     shared=self._shared_params())
         logabsdet = 0.0
         if self.unconditional_transform is not None:
             inputs, logabsdet = ops.rqs_layer(inputs, None, self.unconditional_transform.packed_params(),

@@ -73,6 +73,24 @@ class ResidualNet(nn.Module):
 
     accepts_padded_rows = True   # inputs may be [B, n] views of wider storage (unit column stride)
 
+    def fusable(self):
+        """True when the whole net fits vcnf_resnet_spline_fwd (ops.resnet_spline): plain ReLU residual blocks of width
+        128 on fp32 CUDA parameters, nothing stochastic."""
+        if self.context_features is not None or self.preprocessing is not None or self.hidden_features != 128:
+            return False
+        if not (0 <= len(self.blocks) <= 4):
+            return False
+        for blk in self.blocks:
+            if blk.use_batch_norm or not _is_relu(blk.activation) or (blk.dropout.p != 0. and blk.training):
+                return False
+        w = self.initial_layer.weight
+        return w.is_cuda and w.dtype == torch.float32
+
+    def fused_params(self):
+        layers = [self.initial_layer] + [l for blk in self.blocks for l in blk.linear_layers] + [self.final_layer]
+        return ([l.weight.detach().contiguous() for l in layers],
+                [None if l.bias is None else l.bias.detach().contiguous() for l in layers])
+
     def forward(self, inputs, context=None):
         h = inputs if self.preprocessing is None else self.preprocessing(inputs)
         h = h if context is None else torch.cat((h, context), dim=1)

@@ -1317,3 +1317,70 @@ def made_inverse(y, packed, map_code, K=0, modes=None, bounds=None, outside_zero
             ptr(packed["band"]), ptr(packed["fin"]), ptr(packed["band_idx"]), ptr(packed["order"]),
             packed["band_units"], ptr(bounds), ptr(modes), int(K), int(map_code), int(outside_zero), None, stream())
     return x, ld
+
+
+# ------------------------------------------------------------------ fused conditioner + spline (no-grad directions)
+class FusedNetSpec:
+    """Host-side constants of vcnf_resnet_spline_fwd for one coupling layer: column lists, tail modes / bounds (ctypes
+    arrays: the kernel takes them as launch arguments) and the packed-parameter buffer."""
+
+    def __init__(self, id_cols, tr_cols, modes, bounds, K, Pc, wh_scale, outside_zero, hidden, num_blocks,
+                 shared_modes=(), shared_bounds=(), Ps=0):
+        import ctypes
+        self.Ts, self.Ps = len(shared_modes), int(Ps)
+        self.smodes = (ctypes.c_uint8 * max(self.Ts, 1))(*[int(m) for m in shared_modes])
+        self.sbounds = (ctypes.c_float * max(self.Ts, 1))(*[float(b) for b in shared_bounds])
+        self.n_in, self.Tc, self.K, self.Pc = len(id_cols), len(tr_cols), int(K), int(Pc)
+        self.hidden, self.num_blocks = int(hidden), int(num_blocks)
+        self.id_cols = (ctypes.c_int32 * self.n_in)(*[int(c) for c in id_cols])
+        self.tr_cols = (ctypes.c_int32 * self.Tc)(*[int(c) for c in tr_cols])
+        self.modes = (ctypes.c_uint8 * self.Tc)(*[int(m) for m in modes])
+        self.bounds = (ctypes.c_float * self.Tc)(*[float(b) for b in bounds])
+        self.wh_scale, self.outside_zero = float(wh_scale), int(outside_zero)
+        self.nbytes = _lib.query("vcnf_resnet_spline_pack_bytes", self.n_in, self.hidden, self.num_blocks, self.Tc, self.Pc)
+        self.packed = {}
+
+    @property
+    def supported(self):
+        return self.nbytes > 0 and self.K == 8 and self.Ts in (0, self.n_in)
+
+    def pack(self, weights, biases):
+        import ctypes
+        dev = weights[0].device
+        buf = self.packed.get(str(dev))
+        if buf is None:
+            buf = self.packed[str(dev)] = torch.empty(self.nbytes, dtype=torch.uint8, device=dev)
+        n = len(weights)
+        W = (ctypes.c_void_p * n)(*[w.data_ptr() for w in weights])
+        b = (ctypes.c_void_p * n)(*[(v.data_ptr() if v is not None else None) for v in biases])
+        _launch("vcnf_resnet_spline_pack", W, b, self.n_in, self.hidden, self.num_blocks, self.Tc, self.Pc, ptr(buf),
+                stream())
+        return buf
+
+
+def resnet_spline(x, fspec, weights, biases, inverse, shared=None, want_params=False, want_acts=False):
+    """The whole ResidualNet conditioner + the coupling spline in one launch (vcnf_resnet_spline_fwd), no gradient.
+    weights / biases: contiguous fp32 parameters in forward order; shared: [Ts, Ps] parameters of the unconditional
+    spline on the identity columns (or None).  Returns (y, logabsdet[, params][, acts])."""
+    x = x.contiguous()
+    if (shared is None) != (fspec.Ts == 0):
+        raise ValueError("resnet_spline: shared parameters do not match the layer's specification")
+    shared = shared.detach().contiguous() if shared is not None else None
+    B, D = x.shape
+    packed = fspec.pack(weights, biases)
+    y = torch.empty_like(x)
+    ld = torch.empty(B, dtype=x.dtype, device=x.device)
+    params = torch.empty((B, fspec.Tc * fspec.Pc), dtype=x.dtype, device=x.device) if want_params else None
+    acts = (torch.empty((1 + 2 * fspec.num_blocks, B, fspec.hidden), dtype=x.dtype, device=x.device)
+            if want_acts else None)
+    _launch("vcnf_resnet_spline_fwd", ptr(x), D, ptr(y), D, ptr(ld), 0, B, D, fspec.K, fspec.id_cols, fspec.n_in,
+            fspec.tr_cols, fspec.Tc, fspec.Pc, fspec.hidden, fspec.num_blocks, ptr(packed), fspec.modes, fspec.bounds,
+            fspec.wh_scale, int(inverse), fspec.outside_zero, None, ptr(shared), fspec.Ts, fspec.Ps, fspec.smodes,
+            fspec.sbounds, ptr(params),
+            params.stride(0) if params is not None else 0, ptr(acts), stream())
+    out = (y, ld)
+    if want_params:
+        out += (params,)
+    if want_acts:
+        out += (acts,)
+    return out
