@@ -21,6 +21,7 @@
 //
 // Warp roles (384 threads, one CTA per SM, persistent over tiles): warp 0 weight copies, warp 1 MMA issue, warp 2 TMEM
 // allocation, warps 4-11 epilogue (TMEM lane quarter = warp % 4, two warps per quarter split the columns / features).
+#include <cstdlib>
 #include <cuda.h>
 #include "common.cuh"
 #include "rqs_fast.cuh"
@@ -35,7 +36,7 @@ constexpr int kMaxBlocks = 4;
 constexpr int kMaxUnits = 1 + 2 * kMaxBlocks + 4;      // layers + head slices
 constexpr int kMaxSlices = 4;
 constexpr int kWK = 16;                 // columns of the contraction per weight stage
-constexpr int kWStages = 4;
+constexpr int kWStages = 7;
 constexpr uint32_t kWPlane = kH * kWK * 4;             // 8 KB: hi (or lo) plane of a weight stage
 constexpr uint32_t kWStage = 2 * kWPlane;
 constexpr uint32_t kWSbo = kWK * 32;                   // byte stride between 8-row groups of a weight stage
@@ -54,6 +55,8 @@ struct Args {
   float* logdet; int accumulate;
   int64_t B; int D;
   const unsigned char* packed;          // weight stages, then biases (see pack kernel)
+  int dbg;
+  int copies; int64_t copy_stride;      // replicas of the packed block; CTA i streams replica i % copies
   int n_in, nb, Tc, Pc, PcP, fs, n_slices;
   int id_cols[kMaxD], tr_cols[kMaxD];
   unsigned char modes[kMaxD];
@@ -96,6 +99,56 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
       "}\n" ::"r"(d_tmem),
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t leader;
+  asm volatile("{.reg .b32 rx; .reg .pred px; elect.sync rx|px, 0xffffffff; selp.b32 %0, 1, 0, px;}" : "=r"(leader));
+  return leader != 0;
+}
+// One weight stage (16 columns of the contraction = two K = 8 steps) of the split product, activations from tensor
+// memory: A_lo*W_hi and A_hi*W_lo into d_small, A_hi*W_hi into d_main.  acc = 0 starts both accumulators.
+#define VCNF_MMA_TS "tcgen05.mma.cta_group::1.kind::tf32 "
+__device__ __forceinline__ void mma_stage2(uint32_t d_main, uint32_t d_small, uint32_t a_hi, uint32_t a_lo, uint64_t b_hi,
+                                           uint64_t b_lo, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred pa, pt;\n\t"
+      ".reg .b32 ah1, al1;\n\t"
+      ".reg .b64 bh1, bl1;\n\t"
+      "setp.ne.b32 pa, %7, 0;\n\t"
+      "setp.eq.b32 pt, %6, %6;\n\t"
+      "add.u32 ah1, %2, 8;\n\t add.u32 al1, %3, 8;\n\t add.u64 bh1, %4, 16;\n\t add.u64 bl1, %5, 16;\n\t"
+      VCNF_MMA_TS "[%1], [%3], %4, %6, pa;\n\t"
+      VCNF_MMA_TS "[%1], [%2], %5, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [%2], %4, %6, pa;\n\t"
+      VCNF_MMA_TS "[%1], [al1], bh1, %6, pt;\n\t"
+      VCNF_MMA_TS "[%1], [ah1], bl1, %6, pt;\n\t"
+      VCNF_MMA_TS "[%0], [ah1], bh1, %6, pt;\n\t"
+      "}\n" ::"r"(d_main), "r"(d_small), "r"(a_hi), "r"(a_lo), "l"(b_hi), "l"(b_lo), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
   asm volatile(
@@ -158,6 +211,7 @@ struct PackArgs {
   const float* b[kMaxUnits];
   int n_in, nb, Tc, Pc, PcP, fs, S;
   unsigned char* out;
+  int copies; int64_t copy_stride;
 };
 
 __global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
@@ -186,10 +240,12 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
       }
       float hi, lo;
       split_tf32(v, hi, lo);
-      unsigned char* base = a.out + static_cast<size_t>(st) * kWStage;
       const uint32_t off = static_cast<uint32_t>(n >> 3) * kWSbo + (kk >> 2) * 128 + (n & 7) * 16 + (kk & 3) * 4;
-      *reinterpret_cast<float*>(base + off) = hi;
-      *reinterpret_cast<float*>(base + kWPlane + off) = lo;
+      for (int c = 0; c < a.copies; ++c) {
+        unsigned char* base = a.out + c * a.copy_stride + static_cast<size_t>(st) * kWStage;
+        *reinterpret_cast<float*>(base + off) = hi;
+        *reinterpret_cast<float*>(base + kWPlane + off) = lo;
+      }
     } else {
       const int eb = static_cast<int>(e - n_w);
       const int u = eb / kH, n = eb - u * kH;
@@ -200,7 +256,8 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
         const int s = u - L, fi = n / a.PcP, i = n - fi * a.PcP, f = s * a.fs + fi;
         if (fi < a.fs && i < a.Pc && f < a.Tc && a.b[L]) v = a.b[L][f * a.Pc + i];
       }
-      reinterpret_cast<float*>(a.out + static_cast<size_t>(n_st) * kWStage)[eb] = v;
+      for (int c = 0; c < a.copies; ++c)
+        reinterpret_cast<float*>(a.out + c * a.copy_stride + static_cast<size_t>(n_st) * kWStage)[eb] = v;
     }
   }
 }
@@ -249,27 +306,33 @@ __device__ __forceinline__ void element_regs(const float (&prm)[PCP], float v, f
   if (inside && !ok) *flag |= 1;
 }
 
+__device__ long long g_ftrace[2][128];
+#define FTRACE(role, idx) do { if (blockIdx.x == 0 && lane == 0 && (idx) < 128) g_ftrace[role][idx] = clock64(); } while (0)
+
 template <bool INV, int PCP>
 __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid_constant__ Args a) {
   extern __shared__ __align__(1024) unsigned char smem[];
   uint64_t* w_full = reinterpret_cast<uint64_t*>(smem);           // [kWStages] copy engine -> MMA
   uint64_t* w_empty = w_full + kWStages;                          // [kWStages] MMA -> copy issuer
-  uint64_t* a_ready = w_empty + kWStages;                         // [4] epilogue -> MMA: activation chunk j written
-  uint64_t* acc_full = a_ready + 4;                               // [2] MMA -> epilogue
-  uint64_t* acc_empty = acc_full + 2;                             // [2] epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* a_ready = reinterpret_cast<uint64_t*>(smem + 128);    // [4] epilogue -> MMA: activation chunk j written
+  uint64_t* acc_full = a_ready + 4;                               // MMA -> epilogue
+  uint64_t* acc_empty = acc_full + 1;                             // epilogue -> MMA: accumulator read out
+  uint64_t* x_full = acc_empty + 1;                               // [2] prefetch warps -> epilogue
+  uint64_t* x_empty = x_full + 2;                                 // [2] epilogue -> prefetch warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_empty + 2);
   int* s_id = reinterpret_cast<int*>(smem + 256);                 // [32]
   int* s_tr = s_id + kMaxD;                                       // [32]
   int* s_mode = s_tr + kMaxD;                                     // [32]
   float* s_bound = reinterpret_cast<float*>(s_mode + kMaxD);      // [32]
-  unsigned char* A = smem + 1024;                                 // 4 chunks x [hi 16 KB | lo 16 KB]
-  unsigned char* Wst = A + 4 * kAChunkBytes;                      // kWStages x [hi 8 KB | lo 8 KB]
-  float* bias = reinterpret_cast<float*>(Wst + kWStages * kWStage);   // [(L + S)][128]
+  float* s_sbound = reinterpret_cast<float*>(smem + 768);         // [32]
+  unsigned char* Wst = smem + 1024;                               // kWStages x [hi 8 KB | lo 8 KB]
+  float* res = reinterpret_cast<float*>(Wst + kWStages * kWStage);    // [128 columns][128 rows]: residual stream, then
+                                                                      // the staged spline parameters of a head slice
+  float* bias = res + kH * kRows;                                 // [(L + S)][128]
   const int L = n_layers(a.nb), S = a.n_slices, D = a.D;
   float* lds = bias + (L + S) * kH;                               // [128]
   fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(lds + kRows); // [Ts][9] knot records of the batch-shared splines
-  float* xs = reinterpret_cast<float*>(rec + a.Ts * 9);           // [128][D]
-  float* s_sbound = reinterpret_cast<float*>(smem + 768);         // [32]
+  float* xs0 = reinterpret_cast<float*>(rec + a.Ts * 9);          // 2 x [128][D]: x tile in, y tile out
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int st0 = stages0(a.n_in);
@@ -279,7 +342,9 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
   if (tid == 0) {
     for (int s = 0; s < kWStages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int j = 0; j < 4; ++j) mbar_init(&a_ready[j], kEpiWarps);
-    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], kEpiWarps); }
+    mbar_init(acc_full, 1);
+    mbar_init(acc_empty, kEpiWarps);
+    for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 2); mbar_init(&x_empty[b], kEpiWarps); }
     mbar_init_fence();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
@@ -299,79 +364,113 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t col_alo = 128, col_main = 256, col_cross = 384;   // A hi at column 0
 
   if (warp == 0) {
     // ===================================== weight stages: bulk copies from L2 =====================================
-    if (lane == 0) {
-      uint32_t it = 0;
+    if (lane == 0 && !(a.dbg & 1)) {
+      // All CTAs walk the same 0.9 MB of weights in lockstep: with ONE copy every SM asks the same few L2 slices for the
+      // same 16 KB at the same time (measured 0.37 us per stage, 44 GB/s per SM); replicas spread the requests.
+      const unsigned char* wsrc = a.packed + (blockIdx.x % a.copies) * a.copy_stride;
+      uint32_t s = 0, ph = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        for (int st = 0; st < n_st; ++st, ++it) {
-          const int s = it % kWStages;
-          mbar_wait(&w_empty[s], ((it / kWStages) & 1u) ^ 1u);
+        for (int st = 0; st < n_st; ++st) {
+          mbar_wait(&w_empty[s], ph ^ 1u);
           mbar_expect_tx(&w_full[s], kWStage);
-          bulk_g2s(Wst + s * kWStage, a.packed + static_cast<size_t>(st) * kWStage, kWStage, &w_full[s]);
+          bulk_g2s(Wst + s * kWStage, wsrc + static_cast<size_t>(st) * kWStage, kWStage, &w_full[s]);
+          if (++s == kWStages) { s = 0; ph ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================================== MMA issue =====================================
+    // ===================================== MMA issue (activations from tensor memory) =====================================
     const uint32_t idesc = instr_desc_tf32(kRows, kH);
-    uint32_t it = 0, uc = 0, aph = 0;
+    uint32_t s = 0, ph = 0, uc = 0, aph = 0;
+    int ti = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       for (int u = 0; u < L + S; ++u, ++uc) {
-        const uint32_t buf = uc & 1u;
-        mbar_wait(&acc_empty[buf], ((uc >> 1) & 1u) ^ 1u);
+        FTRACE(0, ti); ++ti;
+        mbar_wait(acc_empty, (uc & 1u) ^ 1u);
         tc_fence_after();
-        const uint32_t d_main = tmem_base + buf * 256u, d_small = d_main + 128u;
+        FTRACE(0, ti); ++ti;
         const int nst = u == 0 ? st0 : 8;
-        for (int t = 0; t < nst; ++t, ++it) {
+        for (int t = 0; t < nst; ++t) {
           const int j = t >> 1;
           if (u <= L && (t & 1) == 0) {               // chunk j of this unit's activation operand (head slices share one)
             mbar_wait(&a_ready[j], (aph >> j) & 1u);
             aph ^= 1u << j;
           }
-          const int s = it % kWStages;
-          mbar_wait(&w_full[s], (it / kWStages) & 1u);
+          if (!(a.dbg & 1)) mbar_wait(&w_full[s], ph);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t a_hi = smem_u32(A) + static_cast<uint32_t>(j) * kAChunkBytes + static_cast<uint32_t>(t & 1) * 512u;
-            const uint32_t a_lo = a_hi + kAPlane;
-            const uint32_t b_hi = smem_u32(Wst) + static_cast<uint32_t>(s) * kWStage;
-            const uint32_t b_lo = b_hi + kWPlane;
-#pragma unroll
-            for (int combo = 0; combo < 3; ++combo) {          // small terms first: lo*hi, hi*lo, then hi*hi
-              const uint32_t ab = combo == 0 ? a_lo : a_hi;
-              const uint32_t bb = combo == 1 ? b_lo : b_hi;
-#pragma unroll
-              for (int kk = 0; kk < 2; ++kk) {
-                const uint64_t ad = smem_desc(ab + kk * 256, 128, kASbo);
-                const uint64_t bd = smem_desc(bb + kk * 256, 128, kWSbo);
-                if (combo == 2) mma_tf32(d_main, ad, bd, idesc, (t > 0 || kk > 0) ? 1u : 0u);
-                else mma_tf32(d_small, ad, bd, idesc, (t > 0 || combo > 0 || kk > 0) ? 1u : 0u);
-              }
-            }
-            tc_commit(&w_empty[s]);
-            if (t == nst - 1) tc_commit(&acc_full[buf]);
+          // Operands are computed by the WHOLE warp in convergent code and the six MMAs of a stage leave from one asm
+          // block: inside a divergent `if (lane == 0)` every tcgen05.mma is wrapped in an ELECT / broadcast loop
+          // (measured here: 117 clk per MMA issued that way against the 64 clk the shape needs).
+          const uint32_t a_hi = tmem_base + static_cast<uint32_t>(t) * kWK;
+          const uint32_t b_hi = smem_u32(Wst) + s * kWStage;
+          const uint64_t bh = smem_desc(b_hi, 128, kWSbo);
+          const uint64_t bl = smem_desc(b_hi + kWPlane, 128, kWSbo);
+          const uint32_t acc0 = t > 0 ? 1u : 0u;
+          const bool last = t == nst - 1, dbg_w = (a.dbg & 1) != 0;
+          if (elect_one()) {
+            mma_stage2(tmem_base + col_main, tmem_base + col_cross, a_hi, a_hi + col_alo, bh, bl, idesc, acc0);
+            if (!dbg_w) tc_commit(&w_empty[s]);
+            if (last) tc_commit(acc_full);
           }
           __syncwarp();
+          if (t == 0 || t == nst - 1) { FTRACE(0, ti); ++ti; }
+          if (++s == kWStages) { s = 0; ph ^= 1u; }
         }
       }
     }
-  } else if (warp >= kEpiWarp0) {
+  } else if (warp < kEpiWarp0) {
+    // ===================================== x tiles: prefetched one tile ahead =====================================
+    const int pt = tid - 64;
+    const bool fast_copy = a.ldx == D && reinterpret_cast<uintptr_t>(a.x) % 16 == 0;
+    uint32_t k = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++k) {
+      const uint32_t b = k & 1u;
+      float* xs = xs0 + b * (kRows * D);
+      const int64_t m0 = tile * kRows;
+      mbar_wait(&x_empty[b], ((k >> 1) & 1u) ^ 1u);
+      if (fast_copy) {
+        const int64_t valid = (a.B - m0 < kRows ? a.B - m0 : kRows) * D * 4;       // bytes of the tile that exist
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(a.x + m0 * D);
+        for (int c = pt; c < kRows * D / 4; c += 64) {
+          const int64_t left = valid - static_cast<int64_t>(c) * 16;
+          const uint32_t nbytes = left >= 16 ? 16u : (left > 0 ? static_cast<uint32_t>(left) : 0u);
+          cp_async16(smem_u32(xs) + c * 16, nbytes ? src + c * 16 : src, nbytes);
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
+      } else {
+        for (int e0 = pt; e0 < kRows * D; e0 += 64 * 8) {
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int e = e0 + i * 64, r = e / D, c = e - r * D;
+            v[i] = (e < kRows * D && m0 + r < a.B) ? __ldg(a.x + (m0 + r) * a.ldx + c) : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) if (e0 + i * 64 < kRows * D) xs[e0 + i * 64] = v[i];
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&x_full[b]);
+    }
+  } else {
     // ===================================== epilogue / spline =====================================
     const int ew = warp - kEpiWarp0, q = warp & 3, g = ew >> 2;
     const int et = ew * 32 + lane, row = q * 32 + lane;
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    unsigned char* a_row = A + static_cast<uint32_t>(row >> 3) * kASbo + (row & 7) * 16;
-    uint32_t uc = 0;
+    uint32_t uc = 0, k = 0;
     int flag = 0;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    int ei = warp == kEpiWarp0 ? 0 : 1000;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++k) {
       const int64_t m0 = tile * kRows;
-      for (int e = et; e < kRows * D; e += kEpiThreads) {
-        const int r = e / D, c = e - r * D;
-        xs[e] = (m0 + r < a.B) ? __ldg(a.x + (m0 + r) * a.ldx + c) : 0.f;
-      }
-      epi_bar();
+      const uint32_t xb = k & 1u;
+      float* xs = xs0 + xb * (kRows * D);
+      FTRACE(1, ei); ++ei;
+      mbar_wait(&x_full[xb], (k >> 1) & 1u);
+      FTRACE(1, ei); ++ei;
       float ldsum = 0.f;
       if (INV && a.Ts > 0) {            // sampling direction: the id columns go through their own spline FIRST
         for (int j = g; j < a.Ts; j += 2) {
@@ -383,22 +482,22 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         }
         epi_bar();
       }
-      // gathered inputs of the net -> chunk 0 of the activation operand (this thread: 16 columns of its row)
+      // gathered inputs of the net -> columns [16 g, 16 g + 16) of the activation operand (tensor memory, hi | lo)
+      if (g * 16 < st0 * kWK) {
+        uint32_t h16[16], l16[16];
 #pragma unroll
-      for (int kq = 0; kq < 4; ++kq) {
-        const int k0 = g * 16 + kq * 4;
-        if (k0 < st0 * kWK) {
-          float h4[4], l4[4];
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const float v = (k0 + c < a.n_in) ? xs[row * D + s_id[k0 + c]] : 0.f;
-            split_tf32(v, h4[c], l4[c]);
-          }
-          *reinterpret_cast<float4*>(a_row + (k0 >> 2) * 128) = make_float4(h4[0], h4[1], h4[2], h4[3]);
-          *reinterpret_cast<float4*>(a_row + kAPlane + (k0 >> 2) * 128) = make_float4(l4[0], l4[1], l4[2], l4[3]);
+        for (int c = 0; c < 16; ++c) {
+          const int kcol = g * 16 + c;
+          const float v = (kcol < a.n_in) ? xs[row * D + s_id[kcol < a.n_in ? kcol : 0]] : 0.f;
+          float hi, lo;
+          split_tf32(v, hi, lo);
+          h16[c] = __float_as_uint(hi); l16[c] = __float_as_uint(lo);
         }
+        tmem_st16(t_lane + g * 16, h16);
+        tmem_st16(t_lane + col_alo + g * 16, l16);
+        tmem_st_wait();
       }
-      fence_async_smem();
+      tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&a_ready[0]);
       if (!INV && a.Ts > 0) {           // density direction: the net saw the raw id columns, the output gets their CDF
@@ -412,86 +511,117 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         }
       }
 
-      float res[64];                                   // residual stream of this thread's 4 x 16 columns
-#pragma unroll
-      for (int i = 0; i < 64; ++i) res[i] = 0.f;
+      FTRACE(1, ei); ++ei;
       for (int u = 0; u < L; ++u, ++uc) {
-        const uint32_t buf = uc & 1u;
-        mbar_wait(&acc_full[buf], (uc >> 1) & 1u);
+        mbar_wait(acc_full, uc & 1u);
         tc_fence_after();
+        FTRACE(1, ei); ++ei;
+        float v[64];                                   // this thread's 4 x 16 accumulator columns, read out at once
+#pragma unroll
+        for (int jj = 0; jj < 4; jj += 2) {
+          uint32_t r[32], r2[32];
+          tmem_ld16(t_lane + col_main + jj * 32 + g * 16, r);
+          tmem_ld16(t_lane + col_cross + jj * 32 + g * 16, r2);
+          tmem_ld16(t_lane + col_main + (jj + 1) * 32 + g * 16, r + 16);
+          tmem_ld16(t_lane + col_cross + (jj + 1) * 32 + g * 16, r2 + 16);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[jj * 16 + i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty);         // the next unit may start accumulating
+        FTRACE(1, ei); ++ei;
         const bool add_res = u >= 2 && (u & 1) == 0, write_res = (u & 1) == 0, relu_next = u != L - 1;
         const float* bu = bias + u * kH;
         float* act_row = a.acts ? a.acts + static_cast<int64_t>(u) * a.act_stride + (m0 + row) * kH : nullptr;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int c0 = j * 32 + g * 16;
-          uint32_t r[16], r2[16];
-          tmem_ld16(t_lane + buf * 256u + c0, r);
-          tmem_ld16(t_lane + buf * 256u + 128u + c0, r2);
-          tmem_ld_wait();
-          float v[16];
+          uint32_t h16[16], l16[16];
+          float bb[16], rr[16];                          // all loads of the chunk first: two warps per scheduler
+#pragma unroll                                           // cannot hide a load -> add -> store chain per element
+          for (int i = 0; i < 16; i += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bu + c0 + i);
+            bb[i] = b4.x; bb[i + 1] = b4.y; bb[i + 2] = b4.z; bb[i + 3] = b4.w;
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) rr[i] = add_res ? res[(c0 + i) * kRows + row] : 0.f;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            v[i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bu[c0 + i];
-            if (add_res) v[i] += res[j * 16 + i];
-            if (write_res) res[j * 16 + i] = v[i];
+            const float t = (v[j * 16 + i] + bb[i]) + rr[i];
+            if (write_res) res[(c0 + i) * kRows + row] = t;
+            v[j * 16 + i] = t;
+            float hi, lo;
+            split_tf32(relu_next ? fmaxf(t, 0.f) : t, hi, lo);
+            h16[i] = __float_as_uint(hi); l16[i] = __float_as_uint(lo);
           }
+          tmem_st16(t_lane + c0, h16);
+          tmem_st16(t_lane + col_alo + c0, l16);
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&a_ready[j]);
           if (act_row && m0 + row < a.B) {
 #pragma unroll
             for (int i = 0; i < 16; i += 4)
-              *reinterpret_cast<float4*>(act_row + c0 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+              *reinterpret_cast<float4*>(act_row + c0 + i) =
+                  make_float4(v[j * 16 + i], v[j * 16 + i + 1], v[j * 16 + i + 2], v[j * 16 + i + 3]);
           }
-          unsigned char* dst = a_row + static_cast<uint32_t>(j) * kAChunkBytes + (g * 4) * 128;
-#pragma unroll
-          for (int i = 0; i < 16; i += 4) {
-            float h4[4], l4[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) split_tf32(relu_next ? fmaxf(v[i + c], 0.f) : v[i + c], h4[c], l4[c]);
-            *reinterpret_cast<float4*>(dst + (i >> 2) * 128) = make_float4(h4[0], h4[1], h4[2], h4[3]);
-            *reinterpret_cast<float4*>(dst + kAPlane + (i >> 2) * 128) = make_float4(l4[0], l4[1], l4[2], l4[3]);
-          }
-          fence_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&a_ready[j]);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        FTRACE(1, ei); ++ei;
       }
 
       for (int s = 0; s < S; ++s, ++uc) {
-        const uint32_t buf = uc & 1u;
-        mbar_wait(&acc_full[buf], (uc >> 1) & 1u);
+        mbar_wait(acc_full, uc & 1u);
         tc_fence_after();
-        const int nf = (a.Tc - s * a.fs) < a.fs ? (a.Tc - s * a.fs) : a.fs;
+        FTRACE(1, ei); ++ei;
         const float* bu = bias + (L + s) * kH;
-        for (int fi = g; fi < nf; fi += 2) {
-          const int f = s * a.fs + fi, col0 = fi * PCP;
-          uint32_t r[PCP], r2[PCP];
+        if (s > 0) epi_bar();                          // every thread has read the previous slice's staged parameters
 #pragma unroll
-          for (int c8 = 0; c8 < PCP; c8 += 8) {
-            tmem_ld8(t_lane + buf * 256u + col0 + c8, r + c8);
-            tmem_ld8(t_lane + buf * 256u + 128u + col0 + c8, r2 + c8);
+        for (int jj = 0; jj < 4; jj += 2) {            // accumulator -> [column][row] staging (the residual buffer is free)
+          uint32_t r[32], r2[32];
+          tmem_ld16(t_lane + col_main + jj * 32 + g * 16, r);
+          tmem_ld16(t_lane + col_cross + jj * 32 + g * 16, r2);
+          tmem_ld16(t_lane + col_main + (jj + 1) * 32 + g * 16, r + 16);
+          tmem_ld16(t_lane + col_cross + (jj + 1) * 32 + g * 16, r2 + 16);
+          float bb[32];
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bu + (jj + (i >> 4)) * 32 + g * 16 + (i & 15));
+            bb[i] = b4.x; bb[i + 1] = b4.y; bb[i + 2] = b4.z; bb[i + 3] = b4.w;
           }
           tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int c = (jj + (i >> 4)) * 32 + g * 16 + (i & 15);
+            res[c * kRows + row] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bb[i];
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty);
+        FTRACE(1, ei); ++ei;
+        epi_bar();
+        const int nf = (a.Tc - s * a.fs) < a.fs ? (a.Tc - s * a.fs) : a.fs;
+        for (int fi = g; fi < nf; fi += 2) {
+          const int f = s * a.fs + fi;
           float prm[PCP];
 #pragma unroll
-          for (int i = 0; i < PCP; ++i) prm[i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bu[col0 + i];
+          for (int i = 0; i < PCP; ++i) prm[i] = res[(fi * PCP + i) * kRows + row];
           if (a.params && m0 + row < a.B) {
             float* pr = a.params + (m0 + row) * a.ldp + f * a.Pc;
 #pragma unroll
             for (int i = 0; i < PCP; ++i) if (i < a.Pc) pr[i] = prm[i];
           }
           const int col = s_tr[f];
-          const float v = xs[row * D + col];
+          const float xv = xs[row * D + col];
           float o, l;
-          element_regs<8, INV, PCP>(prm, v, s_bound[f], a.wh_scale, s_mode[f], a.outside_zero, &o, &l, &flag);
+          element_regs<8, INV, PCP>(prm, xv, s_bound[f], a.wh_scale, s_mode[f], a.outside_zero, &o, &l, &flag);
           xs[row * D + col] = o;
           ldsum += l;
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        FTRACE(1, ei); ++ei;
       }
       if (g == 1) lds[row] = ldsum;
       epi_bar();
@@ -499,11 +629,28 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         const float t = ldsum + lds[row];
         a.logdet[m0 + row] = a.accumulate ? a.logdet[m0 + row] + t : t;
       }
-      for (int e = et; e < kRows * D; e += kEpiThreads) {
-        const int r = e / D, c = e - r * D;
-        if (m0 + r < a.B) a.y[(m0 + r) * a.ldy + c] = xs[e];
+      if (a.ldy == D && reinterpret_cast<uintptr_t>(a.y) % 16 == 0) {      // the tile is one contiguous block of y
+        const int64_t n_valid = (a.B - m0 < kRows ? a.B - m0 : kRows) * D;   // floats
+        float* yt = a.y + m0 * D;
+        for (int e = et * 4; e < kRows * D; e += kEpiThreads * 4) {
+          const float4 v4 = *reinterpret_cast<const float4*>(xs + e);
+          if (e + 3 < n_valid) {
+            *reinterpret_cast<float4*>(yt + e) = v4;
+          } else {
+            if (e < n_valid) yt[e] = v4.x;
+            if (e + 1 < n_valid) yt[e + 1] = v4.y;
+            if (e + 2 < n_valid) yt[e + 2] = v4.z;
+          }
+        }
+      } else {
+        for (int e = et; e < kRows * D; e += kEpiThreads) {
+          const int r = e / D, c = e - r * D;
+          if (m0 + r < a.B) a.y[(m0 + r) * a.ldy + c] = xs[e];
+        }
       }
-      epi_bar();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&x_empty[xb]);
+      FTRACE(1, ei); ++ei;
     }
     if (flag && a.err_flag) atomicOr(a.err_flag, 1);
   }
@@ -514,8 +661,8 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
 }
 
 inline size_t smem_bytes(int nb, int S, int D) {
-  return 1024 + 4 * static_cast<size_t>(kAChunkBytes) + kWStages * static_cast<size_t>(kWStage) +
-         (static_cast<size_t>(n_layers(nb) + S) * kH + kRows + static_cast<size_t>(kRows) * D) * 4 + kMaxD * 9 * 16;
+  return 1024 + kWStages * static_cast<size_t>(kWStage) + static_cast<size_t>(kH) * kRows * 4 +
+         (static_cast<size_t>(n_layers(nb) + S) * kH + kRows + 2 * static_cast<size_t>(kRows) * D) * 4 + kMaxD * 9 * 16;
 }
 
 }  // namespace fusednet
@@ -523,6 +670,20 @@ inline size_t smem_bytes(int nb, int S, int D) {
 
 using namespace vcnf;
 using namespace vcnf::fusednet;
+
+static int fused_copies() {
+  static int n = 0;
+  if (n == 0) {
+    const char* e = getenv("VCNF_FUSED_COPIES");
+    n = e ? atoi(e) : 8;
+    if (n < 1) n = 1;
+    if (n > 64) n = 64;
+  }
+  return n;
+}
+static int64_t copy_stride_bytes(int n_in, int nb, int S) {
+  return static_cast<int64_t>((packed_bytes(n_in, nb, S) + 1023) / 1024 * 1024);
+}
 
 static bool shape_ok(int n_in, int hidden, int nb, int Tc, int Pc, int* PcP, int* fs, int* S) {
   if (hidden != kH || n_in < 1 || n_in > kMaxD || nb < 0 || nb > kMaxBlocks || Tc < 1 || Tc > kMaxD || Pc < 1 || Pc > 32)
@@ -536,7 +697,7 @@ static bool shape_ok(int n_in, int hidden, int nb, int Tc, int Pc, int* PcP, int
 extern "C" int64_t vcnf_resnet_spline_pack_bytes(int n_in, int hidden, int num_blocks, int Tc, int Pc) {
   int PcP, fs, S;
   if (!shape_ok(n_in, hidden, num_blocks, Tc, Pc, &PcP, &fs, &S)) return VCNF_E_UNSUPPORTED;
-  return static_cast<int64_t>(packed_bytes(n_in, num_blocks, S));
+  return copy_stride_bytes(n_in, num_blocks, S) * fused_copies();
 }
 
 extern "C" int vcnf_resnet_spline_pack(const void* const* W, const void* const* b, int n_in, int hidden, int num_blocks,
@@ -552,6 +713,8 @@ extern "C" int vcnf_resnet_spline_pack(const void* const* W, const void* const* 
   }
   p.n_in = n_in; p.nb = num_blocks; p.Tc = Tc; p.Pc = Pc;
   p.out = static_cast<unsigned char*>(packed);
+  p.copies = fused_copies();
+  p.copy_stride = copy_stride_bytes(n_in, num_blocks, p.S);
   const int64_t n = static_cast<int64_t>(total_stages(n_in, num_blocks, p.S)) * kH * kWK + static_cast<int64_t>(L + p.S) * kH;
   const int64_t blocks = (n + 255) / 256;
   pack_kernel<<<static_cast<unsigned>(blocks < 1184 ? blocks : 1184), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
@@ -581,6 +744,9 @@ extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64
   a.logdet = static_cast<float*>(logdet); a.accumulate = accumulate;
   a.B = B; a.D = D;
   a.packed = static_cast<const unsigned char*>(packed);
+  a.copies = fused_copies();
+  a.copy_stride = copy_stride_bytes(n_in, num_blocks, a.n_slices);
+  { const char* e = getenv("VCNF_FUSED_DBG"); a.dbg = e ? atoi(e) : 0; }
   a.n_in = n_in; a.nb = num_blocks; a.Tc = Tc; a.Pc = Pc;
   a.wh_scale = static_cast<float>(wh_scale);
   a.outside_zero = outside_zero;
@@ -605,4 +771,8 @@ extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64
   else { if (inverse) VCNF_FUSED_LAUNCH(true, 32); else VCNF_FUSED_LAUNCH(false, 32); }
 #undef VCNF_FUSED_LAUNCH
   return launch_status();
+}
+
+extern "C" int vcnf_debug_fused_trace(long long* out) {
+  return static_cast<int>(cudaMemcpyFromSymbol(out, vcnf::fusednet::g_ftrace, sizeof(long long) * 256));
 }
