@@ -18,15 +18,22 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
+def _layerwise(fn, *args):
+    ops.FUSED_NET = False
+    try:
+        return fn(*args)
+    finally:
+        ops.FUSED_NET = True
+
+
 def _both_paths(layer, x, inverse):
     fn = layer.inverse if inverse else layer.forward
-    y_ref, ld_ref = fn(x)                       # parameters require grad: layer-by-layer kernels
-    assert y_ref.requires_grad
-    before = ops.LAUNCHES
     with torch.no_grad():
+        y_ref, ld_ref = _layerwise(fn, x)       # layer-by-layer kernels
+        before = ops.LAUNCHES
         y, ld = fn(x)
     assert ops.LAUNCHES - before == 2           # pack + the fused kernel
-    return y, ld, y_ref.detach(), ld_ref.detach()
+    return y, ld, y_ref, ld_ref
 
 
 @pytest.mark.parametrize("B", [1, 127, 128, 300, 20011])
@@ -102,3 +109,35 @@ def test_fused_layer_against_oracle():
             y, ld = (layer.inverse if inverse else layer.forward)(x.to(DEV))
             assert_close(y.cpu(), yr.float(), **SPLINE, what="fused vs oracle y")
             assert_close(ld.cpu(), lr.float(), rtol=SPLINE["rtol"], atol=29 * SPLINE["atol"], what="fused vs oracle logdet")
+
+
+@pytest.mark.parametrize("B", [300, 4099])
+def test_training_route_values_and_gradients(B):
+    """With gradients the density direction takes its VALUES from the fused launch and builds the layer-by-layer autograd
+    nodes around them: outputs and every gradient against the layer-by-layer path."""
+    torch.manual_seed(B)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(layer, scale=0.05)
+    layer = layer.to(DEV)
+    x = 1.5 * torch.randn(B, 29, device=DEV)
+    gz = torch.randn(B, 29, device=DEV)
+    gl = torch.randn(B, device=DEV)
+
+    def run():
+        xi = x.clone().requires_grad_(True)
+        layer.zero_grad(set_to_none=True)
+        z, ld = layer.inverse(xi)               # density direction (prqct.forward)
+        ((z * gz).sum() + (ld * gl).sum()).backward()
+        return z.detach(), ld.detach(), xi.grad, {n: p.grad.clone() for n, p in layer.named_parameters()}
+
+    before = ops.LAUNCHES
+    z, ld, gx, gp = run()
+    fused_launches = ops.LAUNCHES - before
+    before = ops.LAUNCHES
+    zr, lr, gxr, gpr = _layerwise(run)
+    assert fused_launches < ops.LAUNCHES - before
+    assert_close(z, zr, **SPLINE, what="fused train z")
+    assert_close(ld, lr, rtol=SPLINE["rtol"], atol=29 * SPLINE["atol"], what="fused train logdet")
+    assert_close(gx, gxr, rtol=1e-4, atol=1e-4 * float(gxr.abs().max()), what="fused train gx")
+    for n, r in gpr.items():
+        assert_close(gp[n], r, rtol=1e-4, atol=1e-4 * float(r.abs().max()), what="fused train grad " + n)

@@ -32,6 +32,7 @@ namespace fusednet {
 
 constexpr int kH = 128;                 // hidden width = UMMA N of the hidden layers (and rows per tile = UMMA M)
 constexpr int kRows = 128;
+constexpr int kRS = kRows + 1;           // row stride of the [column][row] staging buffer: conflict-free both ways
 constexpr int kMaxBlocks = 4;
 constexpr int kMaxUnits = 1 + 2 * kMaxBlocks + 4;      // layers + head slices
 constexpr int kMaxSlices = 4;
@@ -44,8 +45,10 @@ constexpr int kAChunk = 32;             // activation columns per chunk (readine
 constexpr uint32_t kAPlane = kRows * kAChunk * 4;      // 16 KB
 constexpr uint32_t kAChunkBytes = 2 * kAPlane;         // hi | lo
 constexpr uint32_t kASbo = kAChunk * 32;
-constexpr int kThreads = 384;
-constexpr int kEpiWarp0 = 4, kEpiWarps = 8, kEpiThreads = kEpiWarps * 32;
+constexpr int kEpiWarp0 = 4, kEpiWarps = 16, kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = (kEpiWarp0 + kEpiWarps) * 32;
+constexpr int kG = kEpiWarps / 4;       // column groups: epilogue threads per row
+constexpr int kCW = 32 / kG;            // columns of a 32-column chunk per thread
 constexpr int kMaxD = 32;
 constexpr uint32_t kTmemCols = 512;     // 2 buffers x (main 128 | cross terms 128)
 
@@ -164,6 +167,17 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* r) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                : "r"(taddr)
                : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+template <int N> __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t* r) {
+  if (N == 16) tmem_ld16(taddr, r); else tmem_ld8(taddr, r);
+}
+template <int N> __device__ __forceinline__ void tmem_st(uint32_t taddr, const uint32_t* r) {
+  if (N == 16) tmem_st16(taddr, r); else tmem_st8(taddr, r);
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); }
@@ -328,10 +342,10 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
   unsigned char* Wst = smem + 1024;                               // kWStages x [hi 8 KB | lo 8 KB]
   float* res = reinterpret_cast<float*>(Wst + kWStages * kWStage);    // [128 columns][128 rows]: residual stream, then
                                                                       // the staged spline parameters of a head slice
-  float* bias = res + kH * kRows;                                 // [(L + S)][128]
+  float* bias = res + kH * kRS + 32;                              // (+32 floats keeps 16-byte alignment)                                 // [(L + S)][128]
   const int L = n_layers(a.nb), S = a.n_slices, D = a.D;
   float* lds = bias + (L + S) * kH;                               // [128]
-  fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(lds + kRows); // [Ts][9] knot records of the batch-shared splines
+  fast::Knot4* rec = reinterpret_cast<fast::Knot4*>(lds + (kG - 1) * kRows); // [Ts][9] knot records of the batch-shared splines
   float* xs0 = reinterpret_cast<float*>(rec + a.Ts * 9);          // 2 x [128][D]: x tile in, y tile out
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -424,7 +438,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
     }
   } else if (warp < kEpiWarp0) {
     // ===================================== x tiles: prefetched one tile ahead =====================================
-    const int pt = tid - 64;
+    const int pt = tid - 64;   // warps 2 and 3
     const bool fast_copy = a.ldx == D && reinterpret_cast<uintptr_t>(a.x) % 16 == 0;
     uint32_t k = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++k) {
@@ -458,6 +472,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
     }
   } else {
     // ===================================== epilogue / spline =====================================
+    // thread = (row, g): TMEM lane quarter q = warp % 4, column group g = kCW columns of every 32-column chunk
     const int ew = warp - kEpiWarp0, q = warp & 3, g = ew >> 2;
     const int et = ew * 32 + lane, row = q * 32 + lane;
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
@@ -473,7 +488,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
       FTRACE(1, ei); ++ei;
       float ldsum = 0.f;
       if (INV && a.Ts > 0) {            // sampling direction: the id columns go through their own spline FIRST
-        for (int j = g; j < a.Ts; j += 2) {
+        for (int j = g; j < a.Ts; j += kG) {
           float o, l;
           int bin;
           fast::table_element<8, true>(rec + j * 9, xs[row * D + s_id[j]], s_sbound[j], a.outside_zero, &o, &l, &bin, &flag);
@@ -482,19 +497,19 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         }
         epi_bar();
       }
-      // gathered inputs of the net -> columns [16 g, 16 g + 16) of the activation operand (tensor memory, hi | lo)
-      if (g * 16 < st0 * kWK) {
-        uint32_t h16[16], l16[16];
+      // gathered inputs of the net -> columns [kCW g, kCW g + kCW) of the activation operand (tensor memory, hi | lo)
+      if (g * kCW < st0 * kWK) {
+        uint32_t hh[kCW], ll[kCW];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          const int kcol = g * 16 + c;
+        for (int c = 0; c < kCW; ++c) {
+          const int kcol = g * kCW + c;
           const float v = (kcol < a.n_in) ? xs[row * D + s_id[kcol < a.n_in ? kcol : 0]] : 0.f;
           float hi, lo;
           split_tf32(v, hi, lo);
-          h16[c] = __float_as_uint(hi); l16[c] = __float_as_uint(lo);
+          hh[c] = __float_as_uint(hi); ll[c] = __float_as_uint(lo);
         }
-        tmem_st16(t_lane + g * 16, h16);
-        tmem_st16(t_lane + col_alo + g * 16, l16);
+        tmem_st<kCW>(t_lane + g * kCW, hh);
+        tmem_st<kCW>(t_lane + col_alo + g * kCW, ll);
         tmem_st_wait();
       }
       tc_fence_before();
@@ -502,7 +517,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
       if (lane == 0) mbar_arrive(&a_ready[0]);
       if (!INV && a.Ts > 0) {           // density direction: the net saw the raw id columns, the output gets their CDF
         epi_bar();
-        for (int j = g; j < a.Ts; j += 2) {
+        for (int j = g; j < a.Ts; j += kG) {
           float o, l;
           int bin;
           fast::table_element<8, false>(rec + j * 9, xs[row * D + s_id[j]], s_sbound[j], a.outside_zero, &o, &l, &bin, &flag);
@@ -516,17 +531,17 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         mbar_wait(acc_full, uc & 1u);
         tc_fence_after();
         FTRACE(1, ei); ++ei;
-        float v[64];                                   // this thread's 4 x 16 accumulator columns, read out at once
+        float v[4 * kCW];                              // this thread's 4 x kCW accumulator columns, read out at once
+        {
+          uint32_t r[4 * kCW], r2[4 * kCW];
 #pragma unroll
-        for (int jj = 0; jj < 4; jj += 2) {
-          uint32_t r[32], r2[32];
-          tmem_ld16(t_lane + col_main + jj * 32 + g * 16, r);
-          tmem_ld16(t_lane + col_cross + jj * 32 + g * 16, r2);
-          tmem_ld16(t_lane + col_main + (jj + 1) * 32 + g * 16, r + 16);
-          tmem_ld16(t_lane + col_cross + (jj + 1) * 32 + g * 16, r2 + 16);
+          for (int j = 0; j < 4; ++j) {
+            tmem_ld<kCW>(t_lane + col_main + j * 32 + g * kCW, r + j * kCW);
+            tmem_ld<kCW>(t_lane + col_cross + j * 32 + g * kCW, r2 + j * kCW);
+          }
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[jj * 16 + i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]);
+          for (int i = 0; i < 4 * kCW; ++i) v[i] = __uint_as_float(r[i]) + __uint_as_float(r2[i]);
         }
         tc_fence_before();
         __syncwarp();
@@ -537,36 +552,36 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         float* act_row = a.acts ? a.acts + static_cast<int64_t>(u) * a.act_stride + (m0 + row) * kH : nullptr;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const int c0 = j * 32 + g * 16;
-          uint32_t h16[16], l16[16];
-          float bb[16], rr[16];                          // all loads of the chunk first: two warps per scheduler
+          const int c0 = j * 32 + g * kCW;
+          uint32_t hh[kCW], ll[kCW];
+          float bb[kCW], rr[kCW];                        // all loads of the chunk first: few warps per scheduler
 #pragma unroll                                           // cannot hide a load -> add -> store chain per element
-          for (int i = 0; i < 16; i += 4) {
+          for (int i = 0; i < kCW; i += 4) {
             const float4 b4 = *reinterpret_cast<const float4*>(bu + c0 + i);
             bb[i] = b4.x; bb[i + 1] = b4.y; bb[i + 2] = b4.z; bb[i + 3] = b4.w;
           }
 #pragma unroll
-          for (int i = 0; i < 16; ++i) rr[i] = add_res ? res[(c0 + i) * kRows + row] : 0.f;
+          for (int i = 0; i < kCW; ++i) rr[i] = add_res ? res[(c0 + i) * kRS + row] : 0.f;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float t = (v[j * 16 + i] + bb[i]) + rr[i];
-            if (write_res) res[(c0 + i) * kRows + row] = t;
-            v[j * 16 + i] = t;
+          for (int i = 0; i < kCW; ++i) {
+            const float t = (v[j * kCW + i] + bb[i]) + rr[i];
+            if (write_res) res[(c0 + i) * kRS + row] = t;
+            v[j * kCW + i] = t;
             float hi, lo;
             split_tf32(relu_next ? fmaxf(t, 0.f) : t, hi, lo);
-            h16[i] = __float_as_uint(hi); l16[i] = __float_as_uint(lo);
+            hh[i] = __float_as_uint(hi); ll[i] = __float_as_uint(lo);
           }
-          tmem_st16(t_lane + c0, h16);
-          tmem_st16(t_lane + col_alo + c0, l16);
+          tmem_st<kCW>(t_lane + c0, hh);
+          tmem_st<kCW>(t_lane + col_alo + c0, ll);
           tmem_st_wait();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&a_ready[j]);
           if (act_row && m0 + row < a.B) {
 #pragma unroll
-            for (int i = 0; i < 16; i += 4)
+            for (int i = 0; i < kCW; i += 4)
               *reinterpret_cast<float4*>(act_row + c0 + i) =
-                  make_float4(v[j * 16 + i], v[j * 16 + i + 1], v[j * 16 + i + 2], v[j * 16 + i + 3]);
+                  make_float4(v[j * kCW + i], v[j * kCW + i + 1], v[j * kCW + i + 2], v[j * kCW + i + 3]);
           }
         }
         FTRACE(1, ei); ++ei;
@@ -578,24 +593,24 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         FTRACE(1, ei); ++ei;
         const float* bu = bias + (L + s) * kH;
         if (s > 0) epi_bar();                          // every thread has read the previous slice's staged parameters
+        {                                              // accumulator -> [column][row] staging (the residual buffer is free)
+          uint32_t r[4 * kCW], r2[4 * kCW];
 #pragma unroll
-        for (int jj = 0; jj < 4; jj += 2) {            // accumulator -> [column][row] staging (the residual buffer is free)
-          uint32_t r[32], r2[32];
-          tmem_ld16(t_lane + col_main + jj * 32 + g * 16, r);
-          tmem_ld16(t_lane + col_cross + jj * 32 + g * 16, r2);
-          tmem_ld16(t_lane + col_main + (jj + 1) * 32 + g * 16, r + 16);
-          tmem_ld16(t_lane + col_cross + (jj + 1) * 32 + g * 16, r2 + 16);
-          float bb[32];
+          for (int j = 0; j < 4; ++j) {
+            tmem_ld<kCW>(t_lane + col_main + j * 32 + g * kCW, r + j * kCW);
+            tmem_ld<kCW>(t_lane + col_cross + j * 32 + g * kCW, r2 + j * kCW);
+          }
+          float bb[4 * kCW];
 #pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            const float4 b4 = *reinterpret_cast<const float4*>(bu + (jj + (i >> 4)) * 32 + g * 16 + (i & 15));
+          for (int i = 0; i < 4 * kCW; i += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bu + (i / kCW) * 32 + g * kCW + (i % kCW));
             bb[i] = b4.x; bb[i + 1] = b4.y; bb[i + 2] = b4.z; bb[i + 3] = b4.w;
           }
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int c = (jj + (i >> 4)) * 32 + g * 16 + (i & 15);
-            res[c * kRows + row] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bb[i];
+          for (int i = 0; i < 4 * kCW; ++i) {
+            const int c = (i / kCW) * 32 + g * kCW + (i % kCW);
+            res[c * kRS + row] = __uint_as_float(r[i]) + __uint_as_float(r2[i]) + bb[i];
           }
         }
         tc_fence_before();
@@ -604,16 +619,19 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         FTRACE(1, ei); ++ei;
         epi_bar();
         const int nf = (a.Tc - s * a.fs) < a.fs ? (a.Tc - s * a.fs) : a.fs;
-        for (int fi = g; fi < nf; fi += 2) {
+        if (a.params) {                                // the slice's parameters, one row per warp pass: coalesced
+          for (int rr = ew; rr < kRows; rr += kEpiWarps) {
+            if (m0 + rr < a.B && lane < a.Pc) {
+              float* pr = a.params + (m0 + rr) * a.ldp + (s * a.fs) * a.Pc + lane;
+              for (int fi = 0; fi < nf; ++fi) pr[fi * a.Pc] = res[(fi * PCP + lane) * kRS + rr];
+            }
+          }
+        }
+        for (int fi = g; fi < nf; fi += kG) {
           const int f = s * a.fs + fi;
           float prm[PCP];
 #pragma unroll
-          for (int i = 0; i < PCP; ++i) prm[i] = res[(fi * PCP + i) * kRows + row];
-          if (a.params && m0 + row < a.B) {
-            float* pr = a.params + (m0 + row) * a.ldp + f * a.Pc;
-#pragma unroll
-            for (int i = 0; i < PCP; ++i) if (i < a.Pc) pr[i] = prm[i];
-          }
+          for (int i = 0; i < PCP; ++i) prm[i] = res[(fi * PCP + i) * kRS + row];
           const int col = s_tr[f];
           const float xv = xs[row * D + col];
           float o, l;
@@ -623,10 +641,12 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         }
         FTRACE(1, ei); ++ei;
       }
-      if (g == 1) lds[row] = ldsum;
+      if (g > 0) lds[(g - 1) * kRows + row] = ldsum;
       epi_bar();
       if (g == 0 && m0 + row < a.B) {
-        const float t = ldsum + lds[row];
+        float t = ldsum;
+#pragma unroll
+        for (int gg = 1; gg < kG; ++gg) t += lds[(gg - 1) * kRows + row];
         a.logdet[m0 + row] = a.accumulate ? a.logdet[m0 + row] + t : t;
       }
       if (a.ldy == D && reinterpret_cast<uintptr_t>(a.y) % 16 == 0) {      // the tile is one contiguous block of y
@@ -661,8 +681,8 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
 }
 
 inline size_t smem_bytes(int nb, int S, int D) {
-  return 1024 + kWStages * static_cast<size_t>(kWStage) + static_cast<size_t>(kH) * kRows * 4 +
-         (static_cast<size_t>(n_layers(nb) + S) * kH + kRows + 2 * static_cast<size_t>(kRows) * D) * 4 + kMaxD * 9 * 16;
+  return 1024 + kWStages * static_cast<size_t>(kWStage) + (static_cast<size_t>(kH) * kRS + 32) * 4 +
+         (static_cast<size_t>(n_layers(nb) + S) * kH + (kG - 1) * kRows + 2 * static_cast<size_t>(kRows) * D) * 4 + kMaxD * 9 * 16;
 }
 
 }  // namespace fusednet

@@ -237,16 +237,20 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         ut = self.unconditional_transform
         return ut.packed_params() if ut is not None else None
 
+    def _needs_grad(self, inputs):
+        return torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters()))
+
     def _fused_route(self, inputs, context):
-        """The no-grad directions of a dense ResidualNet conditioner run as ONE kernel per layer
-        (vcnf_resnet_spline_fwd: net + spline, nothing but x and y touches HBM).  Returns the ops.FusedNetSpec or None
-        (gradients needed, or a configuration the kernel does not cover: the layer-by-layer kernels then run)."""
+        """A dense ResidualNet conditioner and the spline run as ONE kernel per layer (vcnf_resnet_spline_fwd).  Without
+        gradients nothing but x and y touches HBM; with gradients (density direction) the same launch also writes what
+        the backward kernels need (layer outputs, spline parameters) and the layer-by-layer autograd nodes are built
+        around those values.  Returns the ops.FusedNetSpec, or None for a configuration the kernel does not cover."""
         net = self.transform_net
         ut = self.unconditional_transform
+        if not ops.FUSED_NET:
+            return None
         if (context is not None or (ut is not None and getattr(ut, "_img", False)) or inputs.dim() != 2
                 or not inputs.is_cuda or inputs.dtype != torch.float32 or not hasattr(net, "fusable") or not net.fusable()):
-            return None
-        if torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters())):
             return None
         if self._fused is None:
             if self._specs is None:
@@ -378,9 +382,18 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         if self._specs is None:
             self._build_specs()
         fused = None if want_bins else self._fused_route(inputs, context)
-        if fused is not None:
+        if fused is not None and not self._needs_grad(inputs):
             return ops.resnet_spline(inputs, fused, *self.transform_net.fused_params(), inverse=False,
                                      shared=self._shared_params())
+        if fused is not None and self.transform_net.hidden_features <= ops.KSLICE:
+            # training: values from the one fused launch, graph (and backward kernels) of the layer-by-layer path
+            shared = self._shared_params()
+            y, ld, params, acts = ops.resnet_spline(
+                inputs.detach(), fused, *self.transform_net.fused_params(), inverse=False, shared=shared,
+                want_params="padded" if self.transform_net.padded_out else True, want_acts=True)
+            identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
+            params = self.transform_net(identity_split, None, pre=(acts, params))
+            return ops.rqs_layer(inputs, params, shared, self._specs["both"], False, pre=(y, ld))
         identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
         params = self.transform_net(identity_split, context)
         shared = self.unconditional_transform.packed_params() if self.unconditional_transform is not None else None
@@ -394,7 +407,7 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         if self._specs is None:
             self._build_specs()
         fused = self._fused_route(inputs, context)
-        if fused is not None:
+        if fused is not None and not self._needs_grad(inputs):
             return ops.resnet_spline(inputs, fused, *self.transform_net.fused_params(), inverse=True,
                                      shared=self._shared_params())
         logabsdet = 0.0

@@ -33,13 +33,16 @@ class ResidualBlock(nn.Module):
                 and (self.dropout.p == 0. or not self.training)
                 and ops.linear_supported(inputs, self.linear_layers[0].weight))
 
-    def forward(self, inputs, context=None):
+    def forward(self, inputs, context=None, pre=None):
+        """pre = (t, out) already computed by the fused net + spline kernel: only the autograd nodes are built."""
         if self._fast(inputs, context):
             l0, l1 = self.linear_layers
             if l0.bias is not None and l1.bias is not None and ops.resblock_supported(inputs, l0.weight):
-                return ops.residual_block(inputs, l0.weight, l0.bias, l1.weight, l1.bias)
-            t = ops.linear(inputs, l0.weight, l0.bias, relu_in=True)
-            return ops.linear(t, l1.weight, l1.bias, residual=inputs, relu_in=True)
+                return ops.residual_block(inputs, l0.weight, l0.bias, l1.weight, l1.bias, pre=pre)
+            t = ops.linear(inputs, l0.weight, l0.bias, relu_in=True, pre=None if pre is None else pre[0])
+            return ops.linear(t, l1.weight, l1.bias, residual=inputs, relu_in=True, pre=None if pre is None else pre[1])
+        if pre is not None:
+            raise RuntimeError("ResidualBlock: precomputed outputs need the kernel route")
         h = inputs
         if self.use_batch_norm:
             h = self.batch_norm_layers[0](h)
@@ -91,11 +94,21 @@ class ResidualNet(nn.Module):
         return ([l.weight.detach().contiguous() for l in layers],
                 [None if l.bias is None else l.bias.detach().contiguous() for l in layers])
 
-    def forward(self, inputs, context=None):
+    def forward(self, inputs, context=None, pre=None):
+        """pre = (acts [1 + 2 blocks, B, hidden], params) from ops.resnet_spline: the values are taken from there and only
+        the autograd nodes of the layer-by-layer path are built (their backward kernels run as usual)."""
         h = inputs if self.preprocessing is None else self.preprocessing(inputs)
         h = h if context is None else torch.cat((h, context), dim=1)
         fast = (ops.linear_supported(h, self.initial_layer.weight)
                 and (self.hidden_features <= ops.KSLICE or self.hidden_features % 4 == 0))
+        if pre is not None:
+            if not fast:
+                raise RuntimeError("ResidualNet: precomputed outputs need the kernel route")
+            acts, params = pre
+            h = ops.linear(h, self.initial_layer.weight, self.initial_layer.bias, pre=acts[0])
+            for i, block in enumerate(self.blocks):
+                h = block(h, context=context, pre=(acts[2 * i + 1], acts[2 * i + 2]))
+            return ops.linear(h, self.final_layer.weight, self.final_layer.bias, pad_out=self.padded_out, pre=params)
         h = ops.linear(h, self.initial_layer.weight, self.initial_layer.bias) if fast else self.initial_layer(h)
         for block in self.blocks:
             h = block(h, context=context)

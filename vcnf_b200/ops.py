@@ -82,7 +82,7 @@ class SplineSpec:
 
 class _RqsLayer(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, cond, shared, spec, inverse, want_bins):
+    def forward(ctx, x, cond, shared, spec, inverse, want_bins, pre=None):
         x = x.contiguous()
         B, D = x.shape
         if D != spec.D:
@@ -90,6 +90,10 @@ class _RqsLayer(torch.autograd.Function):
         cmap, cm, cb, sm, sb = spec.on(x.device, x.dtype)
         cond = _rows(cond) if cond is not None else None
         shared = shared.contiguous() if shared is not None else None
+        if pre is not None:            # (y, logdet) already computed by the fused net + spline kernel: only the graph node
+            ctx.spec, ctx.inverse = spec, int(inverse)
+            ctx.save_for_backward(x, cond, shared)
+            return pre[0], pre[1]
         y = torch.empty_like(x)
         logdet = torch.empty(B, dtype=x.dtype, device=x.device)
         bins = torch.empty((B, D), dtype=torch.int8, device=x.device) if want_bins else None
@@ -128,13 +132,14 @@ class _RqsLayer(torch.autograd.Function):
                 ptr(gcond), gcond.stride(0) if gcond is not None else 0, ptr(shared), spec.Ts, spec.Ps, ptr(sm), ptr(sb),
                 ptr(gshared), ptr(ws), ctx.inverse, spec.outside_zero, dtype_code(x), stream(),
                 n=2 if spec.Ts > 0 else 1)
-        return gx, gcond, gshared, None, None, None
+        return gx, gcond, gshared, None, None, None, None
 
 
-def rqs_layer(x, cond, shared, spec, inverse, want_bins=False):
-    """Spline layer: returns (y, logdet[, bin_idx])."""
+def rqs_layer(x, cond, shared, spec, inverse, want_bins=False, pre=None):
+    """Spline layer: returns (y, logdet[, bin_idx]).  pre = (y, logdet) computed elsewhere (ops.resnet_spline): only the
+    autograd node is built."""
     x, cond, shared = _promote(x, cond, shared)
-    return _RqsLayer.apply(x, cond, shared, spec, inverse, want_bins)
+    return _RqsLayer.apply(x, cond, shared, spec, inverse, want_bins, pre)
 
 
 class _GatherCols(torch.autograd.Function):
@@ -741,7 +746,7 @@ class _Linear(torch.autograd.Function):
     the ReLU, the bias, the residual add and the ReLU-backward mask are fused into the kernels."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, relu_in, pad_out):
+    def forward(ctx, x, weight, bias, residual, relu_in, pad_out, pre=None):
         # anything but the Parameter objects themselves may have been written by a kernel earlier on this stream
         # (MADE's W * mask, a re-laid convolution weight): the GEMM then fetches W after its dependency wait
         is_param = lambda t: t is None or isinstance(t, torch.nn.Parameter)
@@ -751,6 +756,11 @@ class _Linear(torch.autograd.Function):
         N = weight.shape[0]
         bias_ = bias.contiguous() if bias is not None else None
         res_ = _rows(residual) if residual is not None else None
+        if pre is not None:            # output already computed by the fused net + spline kernel: only the graph node
+            ctx.relu_in, ctx.w_dyn = bool(relu_in), w_dyn
+            ctx.has_bias, ctx.has_res = bias is not None, residual is not None
+            ctx.save_for_backward(x, weight)
+            return pre
         y = _padded_empty(M, N, x.dtype, x.device) if pad_out else torch.empty((M, N), dtype=x.dtype, device=x.device)
         for k0 in range(0, K, KSLICE):
             # in_features > 128: slices of the contraction accumulate in place (`residual` = y)
@@ -817,12 +827,12 @@ class _Linear(torch.autograd.Function):
                 gw = None
         if ctx.has_res and ctx.needs_input_grad[3]:
             gres = gy
-        return gx, gw, gb, gres, None, None
+        return gx, gw, gb, gres, None, None, None
 
 
-def linear(x, weight, bias=None, residual=None, relu_in=False, pad_out=False):
+def linear(x, weight, bias=None, residual=None, relu_in=False, pad_out=False, pre=None):
     """pad_out=True: the result is a view with a 16-byte-multiple row pitch (see _padded_empty)."""
-    return _Linear.apply(x, weight, bias, residual, relu_in, pad_out)
+    return _Linear.apply(x, weight, bias, residual, relu_in, pad_out, pre)
 
 
 class _ResBlock(torch.autograd.Function):
@@ -832,9 +842,12 @@ class _ResBlock(torch.autograd.Function):
     GEMM instead of a separate [B, features] add kernel (32 such adds per cfg-2 step)."""
 
     @staticmethod
-    def forward(ctx, x, w0, b0, w1, b1):
+    def forward(ctx, x, w0, b0, w1, b1, pre=None):
         x, w0, w1 = _rows(x), w0.contiguous(), w1.contiguous()
         M, F_ = x.shape
+        if pre is not None:            # (t, out) already computed by the fused net + spline kernel
+            ctx.save_for_backward(x, pre[0], w0, w1)
+            return pre[1]
         t = torch.empty((M, F_), dtype=x.dtype, device=x.device)
         out = torch.empty((M, F_), dtype=x.dtype, device=x.device)
         _launch("vcnf_linear_tf32x3", ptr(x), x.stride(0), ptr(w0), F_, 1, ptr(b0), None, 0, None, 0,
@@ -851,7 +864,7 @@ class _ResBlock(torch.autograd.Function):
         g = _rows(g)
         M, F_ = x.shape
         ldg, ldx = g.stride(0), x.stride(0)
-        need_x, need_w0, need_b0, need_w1, need_b1 = ctx.needs_input_grad
+        need_x, need_w0, need_b0, need_w1, need_b1 = ctx.needs_input_grad[:5]
         gx = gw0 = gb0 = gw1 = gb1 = None
         # g_t = [t > 0] * (g W1)
         gt = torch.empty((M, F_), dtype=x.dtype, device=x.device)
@@ -874,12 +887,13 @@ class _ResBlock(torch.autograd.Function):
             ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
             _launch("vcnf_linear_wgrad_tf32x3", ptr(gt), F_, ptr(x), ldx, ptr(gw0), ptr(gb0), ptr(ws), M, F_, F_, 1,
                     stream(), n=2)
-        return gx, gw0 if need_w0 else None, gb0 if need_b0 else None, gw1 if need_w1 else None, gb1 if need_b1 else None
+        return (gx, gw0 if need_w0 else None, gb0 if need_b0 else None, gw1 if need_w1 else None,
+                gb1 if need_b1 else None, None)
 
 
-def residual_block(x, w0, b0, w1, b1):
+def residual_block(x, w0, b0, w1, b1, pre=None):
     """x + Linear1(relu(Linear0(relu(x)))) with square weights [F, F], F <= 128, biases required."""
-    return _ResBlock.apply(x, w0, b0, w1, b1)
+    return _ResBlock.apply(x, w0, b0, w1, b1, pre)
 
 
 # ------------------------------------------------------------------ convolutional conditioner (Glow, K9)
@@ -1319,7 +1333,10 @@ def made_inverse(y, packed, map_code, K=0, modes=None, bounds=None, outside_zero
     return x, ld
 
 
-# ------------------------------------------------------------------ fused conditioner + spline (no-grad directions)
+# ------------------------------------------------------------------ fused conditioner + spline
+FUSED_NET = True      # False: spline coupling layers keep the layer-by-layer kernels (the tests' reference path)
+
+
 class FusedNetSpec:
     """Host-side constants of vcnf_resnet_spline_fwd for one coupling layer: column lists, tail modes / bounds (ctypes
     arrays: the kernel takes them as launch arguments) and the packed-parameter buffer."""
@@ -1370,7 +1387,10 @@ def resnet_spline(x, fspec, weights, biases, inverse, shared=None, want_params=F
     packed = fspec.pack(weights, biases)
     y = torch.empty_like(x)
     ld = torch.empty(B, dtype=x.dtype, device=x.device)
-    params = torch.empty((B, fspec.Tc * fspec.Pc), dtype=x.dtype, device=x.device) if want_params else None
+    params = None
+    if want_params:       # "padded": row pitch a multiple of 16 bytes, like ResidualNet's own output for the spline layer
+        params = (_padded_empty(B, fspec.Tc * fspec.Pc, x.dtype, x.device) if want_params == "padded"
+                  else torch.empty((B, fspec.Tc * fspec.Pc), dtype=x.dtype, device=x.device))
     acts = (torch.empty((1 + 2 * fspec.num_blocks, B, fspec.hidden), dtype=x.dtype, device=x.device)
             if want_acts else None)
     _launch("vcnf_resnet_spline_fwd", ptr(x), D, ptr(y), D, ptr(ld), 0, B, D, fspec.K, fspec.id_cols, fspec.n_in,
