@@ -481,6 +481,35 @@ def extra_kernel_rooflines(dev, flush):
         "ms": ms, "achieved": 12 * B / (ms * 1e-3) / 1e9, "frac": 12 * B / (ms * 1e-3) / 1e9 / peak, "unit": "GB/s",
         "bytes_per_launch": 12 * B, "tflops_fp32_fma": flops / (ms * 1e-3) / 1e12,
         "note": "FP32 FMA-pipe bound (~100 flop / B, SURVEY.md K6): the TFLOP/s figure is the relevant one"}
+    # fused conditioner + spline (vcnf_resnet_spline_fwd), one cfg-2 layer in the no-grad direction on the bench batch:
+    # tensor-bound -- 3 TF32 MMAs per product; peak = half the measured bf16 rate (TF32 runs at half the bf16 rate)
+    try:
+        import vcnf_b200 as nf
+        layer = nf.flows.CoupledRationalQuadraticSpline(D, BLOCKS, HIDDEN, num_bins=BINS).to(dev)
+        c = layer.prqct
+        xb = torch.randn(BATCH, D, device=dev)
+        with torch.no_grad():
+            fused = c._fused_route(xb, None)
+            w, bs = c.transform_net.fused_params()
+            shared = c._shared_params()
+            packed = fused.pack(w, bs)
+            fused.pack = lambda *_: packed                     # time the kernel, not the 4 us re-tiling launch
+            ms = _time_launches(lambda: ops.resnet_spline(xb, fused, w, bs, inverse=False, shared=shared), flush, reps=10)
+        n_id = len(c.identity_features)
+        macs = n_id * HIDDEN + 2 * BLOCKS * HIDDEN * HIDDEN + HIDDEN * fused.Tc * fused.Pc      # per row, unpadded
+        try:
+            tpeak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) / 2
+            tsrc = "MEASURED_PEAKS.json bf16_tflops / 2 (TF32 = half the bf16 rate)"
+        except Exception:
+            tpeak, tsrc = 1100.0, "fallback (B200_PROFILING.md: 1.1 PFLOP/s dense TF32)"
+        tf = 3 * 2.0 * macs * BATCH / (ms * 1e-3) / 1e12
+        out["resnet_spline_kernel (vcnf_resnet_spline_fwd, cfg 2 layer, no-grad direction)"] = {
+            "ms": ms, "bound": "tensor", "achieved": tf, "unit": "TFLOP/s", "peak": tpeak, "peak_source": tsrc,
+            "frac": tf / tpeak, "flops_per_launch": 3 * 2.0 * macs * BATCH,
+            "bytes_per_launch": (2 * 4 * D + 4) * BATCH,
+            "note": "executed TF32 flops (3 MMAs per fp32 product, unpadded shapes); HBM traffic is x in, y and log|det| out"}
+    except Exception as exc:                                   # noqa: BLE001
+        out["resnet_spline_kernel"] = {"error": repr(exc)[:200]}
     return out
 
 

@@ -1,3 +1,4 @@
+"""Timeline of one tile of the fused net + spline kernel (needs a library built with -DVCNF_FUSED_TRACE)."""
 import os, sys, ctypes
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)

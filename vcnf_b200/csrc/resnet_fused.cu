@@ -1,26 +1,34 @@
-// The whole conditioner of a spline coupling layer and the spline itself as ONE kernel (the no-grad directions:
-// `sample`, `log_prob`, evaluation):
+// The whole conditioner of a spline coupling layer and the spline itself as ONE kernel:
 //
 //   h0 = W0 x_id + b0;  h_{i+1} = h_i + Wb_i relu(Wa_i relu(h_i) + ba_i) + bb_i   (normflow/nets/resnet.py:38-106)
 //   theta = Wf h_nb + bf                                                           ([B, Tc * Pc], resnet.py:104)
-//   y[:, tr] = RQS^{+-1}(x[:, tr]; theta),  y[:, id] = x[:, id],  logdet = sum_f log|dy/dx|
-//                                                   (flows/neural_spline/coupling.py:70-96,309-343; utils/splines.py:88-193)
+//   y[:, tr] = RQS^{+-1}(x[:, tr]; theta),  y[:, id] = CDF^{+-1}(x[:, id]) or x[:, id],  logdet = sum log|dy/dx|
+//                                           (flows/neural_spline/coupling.py:70-125,309-343; utils/splines.py:88-193)
 //
 // The layer-by-layer path moves the [B, 128] hidden activations through HBM ten times and the [B, 322] spline
 // parameters twice (1 524 B per sample-layer); here a 128-row tile stays on the SM from the gathered
-// inputs to the transformed outputs (2 * 4 D + 4 B per sample-layer):
+// inputs to the transformed outputs (2 * 4 D + 4 B per sample-layer in the no-grad directions; with gradients the
+// same launch additionally writes what the backward kernels read: layer outputs and theta):
 //
-//   * the activation operand of the next layer is written by the epilogue warps straight into shared memory in the
-//     tcgen05 K-major canonical layout, already split into TF32 hi / lo planes (3xTF32, see gemm_tf32x3.cu);
-//   * the weights (pre-split and pre-tiled by vcnf_resnet_spline_pack, 16-column stages of 16 KB) stream from L2
-//     through a ring of bulk copies issued by one thread;
-//   * accumulators (hi*hi and the cross terms, two buffers) live in tensor memory; the residual stream of the tile
-//     lives in the epilogue threads' registers;
-//   * the head runs in slices of whole features (each padded to a multiple of 8 columns), and the spline of a slice is
-//     evaluated from the accumulator registers while the tensor core works on the next slice.
+//   * the activation operand of the next layer is written by the epilogue warps straight into TENSOR MEMORY (TF32
+//     hi / lo planes, columns [0, 256)) and read from there by tcgen05.mma (3xTF32, see gemm_tf32x3.cu); the
+//     accumulators (hi*hi and the cross terms) take the other 256 columns, and are read out whole and released before
+//     the epilogue starts converting, so the next layer's MMAs start as soon as its first 32 input columns exist;
+//   * the weights (pre-split and pre-tiled by vcnf_resnet_spline_pack: 16-column stages of 16 KB) stream from L2
+//     through a 7-stage ring of bulk copies issued by one thread;
+//   * the residual stream of the tile lives in shared memory ([column][row], conflict-free both ways); during the head
+//     the same buffer stages the parameters of a slice (whole features, each padded to a multiple of 8 columns), the
+//     accumulator is released, and the splines are evaluated from there while the tensor core works on the next slice;
+//   * x tiles are prefetched one tile ahead with cp.async by two otherwise idle warps, y tiles leave as 16-byte stores.
 //
-// Warp roles (384 threads, one CTA per SM, persistent over tiles): warp 0 weight copies, warp 1 MMA issue, warp 2 TMEM
-// allocation, warps 4-11 epilogue (TMEM lane quarter = warp % 4, two warps per quarter split the columns / features).
+// Warp roles (640 threads, one CTA per SM, persistent over tiles): warp 0 weight copies, warp 1 MMA issue (operands in
+// convergent code, one asm block per stage), warps 2-3 x prefetch (warp 2 also allocates TMEM), warps 4-19 epilogue
+// (TMEM lane quarter = warp % 4, four warps per quarter split the columns / features).
+//
+// Measured (B200, cfg 2 layer, 65 536 rows): 122 us against 153 us of GEMM launches + 27 us spline layer by layer;
+// one tile takes 28 us of which 16.5 us are MMAs (a 128 x 128 x 8 TF32 MMA with the A operand in tensor memory retires
+// every 91 clocks here, 64-column MMAs every 61: splitting a layer into column halves to overlap its epilogue was
+// measured and does not pay), the rest are the hand-offs between the MMA stream and the epilogue of the SAME tile.
 #include <cstdlib>
 #include <cuda.h>
 #include "common.cuh"
@@ -58,8 +66,6 @@ struct Args {
   float* logdet; int accumulate;
   int64_t B; int D;
   const unsigned char* packed;          // weight stages, then biases (see pack kernel)
-  int dbg;
-  int copies; int64_t copy_stride;      // replicas of the packed block; CTA i streams replica i % copies
   int n_in, nb, Tc, Pc, PcP, fs, n_slices;
   int id_cols[kMaxD], tr_cols[kMaxD];
   unsigned char modes[kMaxD];
@@ -225,7 +231,6 @@ struct PackArgs {
   const float* b[kMaxUnits];
   int n_in, nb, Tc, Pc, PcP, fs, S;
   unsigned char* out;
-  int copies; int64_t copy_stride;
 };
 
 __global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
@@ -255,11 +260,9 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
       float hi, lo;
       split_tf32(v, hi, lo);
       const uint32_t off = static_cast<uint32_t>(n >> 3) * kWSbo + (kk >> 2) * 128 + (n & 7) * 16 + (kk & 3) * 4;
-      for (int c = 0; c < a.copies; ++c) {
-        unsigned char* base = a.out + c * a.copy_stride + static_cast<size_t>(st) * kWStage;
-        *reinterpret_cast<float*>(base + off) = hi;
-        *reinterpret_cast<float*>(base + kWPlane + off) = lo;
-      }
+      unsigned char* base = a.out + static_cast<size_t>(st) * kWStage;
+      *reinterpret_cast<float*>(base + off) = hi;
+      *reinterpret_cast<float*>(base + kWPlane + off) = lo;
     } else {
       const int eb = static_cast<int>(e - n_w);
       const int u = eb / kH, n = eb - u * kH;
@@ -270,8 +273,7 @@ __global__ void __launch_bounds__(256) pack_kernel(const PackArgs a) {
         const int s = u - L, fi = n / a.PcP, i = n - fi * a.PcP, f = s * a.fs + fi;
         if (fi < a.fs && i < a.Pc && f < a.Tc && a.b[L]) v = a.b[L][f * a.Pc + i];
       }
-      for (int c = 0; c < a.copies; ++c)
-        reinterpret_cast<float*>(a.out + c * a.copy_stride + static_cast<size_t>(n_st) * kWStage)[eb] = v;
+      reinterpret_cast<float*>(a.out + static_cast<size_t>(n_st) * kWStage)[eb] = v;
     }
   }
 }
@@ -320,8 +322,14 @@ __device__ __forceinline__ void element_regs(const float (&prm)[PCP], float v, f
   if (inside && !ok) *flag |= 1;
 }
 
+// Timeline of CTA 0 (clock64 at the hand-offs of the MMA warp and of the first epilogue warp), read back with
+// vcnf_debug_fused_trace by tools/fused_trace.py; compiled in with -DVCNF_FUSED_TRACE only.
+#ifdef VCNF_FUSED_TRACE
 __device__ long long g_ftrace[2][128];
 #define FTRACE(role, idx) do { if (blockIdx.x == 0 && lane == 0 && (idx) < 128) g_ftrace[role][idx] = clock64(); } while (0)
+#else
+#define FTRACE(role, idx) do { } while (0)
+#endif
 
 template <bool INV, int PCP>
 __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid_constant__ Args a) {
@@ -382,10 +390,10 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
 
   if (warp == 0) {
     // ===================================== weight stages: bulk copies from L2 =====================================
-    if (lane == 0 && !(a.dbg & 1)) {
-      // All CTAs walk the same 0.9 MB of weights in lockstep: with ONE copy every SM asks the same few L2 slices for the
-      // same 16 KB at the same time (measured 0.37 us per stage, 44 GB/s per SM); replicas spread the requests.
-      const unsigned char* wsrc = a.packed + (blockIdx.x % a.copies) * a.copy_stride;
+    if (lane == 0) {
+      // Every CTA walks the same 0.9 MB of weights: they stay in L2 (replicating the block per CTA group changed
+      // nothing measurable, so one copy it is).
+      const unsigned char* wsrc = a.packed;
       uint32_t s = 0, ph = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         for (int st = 0; st < n_st; ++st) {
@@ -414,7 +422,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
             mbar_wait(&a_ready[j], (aph >> j) & 1u);
             aph ^= 1u << j;
           }
-          if (!(a.dbg & 1)) mbar_wait(&w_full[s], ph);
+          mbar_wait(&w_full[s], ph);
           tc_fence_after();
           // Operands are computed by the WHOLE warp in convergent code and the six MMAs of a stage leave from one asm
           // block: inside a divergent `if (lane == 0)` every tcgen05.mma is wrapped in an ELECT / broadcast loop
@@ -424,10 +432,10 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
           const uint64_t bh = smem_desc(b_hi, 128, kWSbo);
           const uint64_t bl = smem_desc(b_hi + kWPlane, 128, kWSbo);
           const uint32_t acc0 = t > 0 ? 1u : 0u;
-          const bool last = t == nst - 1, dbg_w = (a.dbg & 1) != 0;
+          const bool last = t == nst - 1;
           if (elect_one()) {
             mma_stage2(tmem_base + col_main, tmem_base + col_cross, a_hi, a_hi + col_alo, bh, bl, idesc, acc0);
-            if (!dbg_w) tc_commit(&w_empty[s]);
+            tc_commit(&w_empty[s]);
             if (last) tc_commit(acc_full);
           }
           __syncwarp();
@@ -691,20 +699,6 @@ inline size_t smem_bytes(int nb, int S, int D) {
 using namespace vcnf;
 using namespace vcnf::fusednet;
 
-static int fused_copies() {
-  static int n = 0;
-  if (n == 0) {
-    const char* e = getenv("VCNF_FUSED_COPIES");
-    n = e ? atoi(e) : 8;
-    if (n < 1) n = 1;
-    if (n > 64) n = 64;
-  }
-  return n;
-}
-static int64_t copy_stride_bytes(int n_in, int nb, int S) {
-  return static_cast<int64_t>((packed_bytes(n_in, nb, S) + 1023) / 1024 * 1024);
-}
-
 static bool shape_ok(int n_in, int hidden, int nb, int Tc, int Pc, int* PcP, int* fs, int* S) {
   if (hidden != kH || n_in < 1 || n_in > kMaxD || nb < 0 || nb > kMaxBlocks || Tc < 1 || Tc > kMaxD || Pc < 1 || Pc > 32)
     return false;
@@ -717,7 +711,7 @@ static bool shape_ok(int n_in, int hidden, int nb, int Tc, int Pc, int* PcP, int
 extern "C" int64_t vcnf_resnet_spline_pack_bytes(int n_in, int hidden, int num_blocks, int Tc, int Pc) {
   int PcP, fs, S;
   if (!shape_ok(n_in, hidden, num_blocks, Tc, Pc, &PcP, &fs, &S)) return VCNF_E_UNSUPPORTED;
-  return copy_stride_bytes(n_in, num_blocks, S) * fused_copies();
+  return static_cast<int64_t>(packed_bytes(n_in, num_blocks, S));
 }
 
 extern "C" int vcnf_resnet_spline_pack(const void* const* W, const void* const* b, int n_in, int hidden, int num_blocks,
@@ -733,8 +727,6 @@ extern "C" int vcnf_resnet_spline_pack(const void* const* W, const void* const* 
   }
   p.n_in = n_in; p.nb = num_blocks; p.Tc = Tc; p.Pc = Pc;
   p.out = static_cast<unsigned char*>(packed);
-  p.copies = fused_copies();
-  p.copy_stride = copy_stride_bytes(n_in, num_blocks, p.S);
   const int64_t n = static_cast<int64_t>(total_stages(n_in, num_blocks, p.S)) * kH * kWK + static_cast<int64_t>(L + p.S) * kH;
   const int64_t blocks = (n + 255) / 256;
   pack_kernel<<<static_cast<unsigned>(blocks < 1184 ? blocks : 1184), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
@@ -764,9 +756,6 @@ extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64
   a.logdet = static_cast<float*>(logdet); a.accumulate = accumulate;
   a.B = B; a.D = D;
   a.packed = static_cast<const unsigned char*>(packed);
-  a.copies = fused_copies();
-  a.copy_stride = copy_stride_bytes(n_in, num_blocks, a.n_slices);
-  { const char* e = getenv("VCNF_FUSED_DBG"); a.dbg = e ? atoi(e) : 0; }
   a.n_in = n_in; a.nb = num_blocks; a.Tc = Tc; a.Pc = Pc;
   a.wh_scale = static_cast<float>(wh_scale);
   a.outside_zero = outside_zero;
@@ -793,6 +782,8 @@ extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64
   return launch_status();
 }
 
+#ifdef VCNF_FUSED_TRACE
 extern "C" int vcnf_debug_fused_trace(long long* out) {
   return static_cast<int>(cudaMemcpyFromSymbol(out, vcnf::fusednet::g_ftrace, sizeof(long long) * 256));
 }
+#endif
