@@ -78,3 +78,12 @@ def test_product_does_not_import_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+def test_fused_net_shape_queries_run_without_a_gpu():
+    """vcnf_resnet_spline_pack_bytes is pure host code: supported shapes give a size, unsupported ones VCNF_E_UNSUPPORTED."""
+    from vcnf_b200 import _lib
+    assert _lib.query("vcnf_resnet_spline_pack_bytes", 15, 128, 2, 14, 23) == (1 + 8 * 7) * 16384 + 8 * 128 * 4
+    assert _lib.query("vcnf_resnet_spline_pack_bytes", 15, 64, 2, 14, 23) == -2       # hidden must be 128
+    assert _lib.query("vcnf_resnet_spline_pack_bytes", 40, 128, 2, 14, 23) == -2      # more than 32 net inputs
+    assert _lib.query("vcnf_resnet_spline_pack_bytes", 15, 128, 2, 32, 25) == -2      # 32 features x 32 columns > 4 slices

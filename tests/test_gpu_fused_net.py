@@ -141,3 +141,52 @@ def test_training_route_values_and_gradients(B):
     assert_close(gx, gxr, rtol=1e-4, atol=1e-4 * float(gxr.abs().max()), what="fused train gx")
     for n, r in gpr.items():
         assert_close(gp[n], r, rtol=1e-4, atol=1e-4 * float(r.abs().max()), what="fused train grad " + n)
+
+
+def test_c_abi_padded_rows_and_accumulate():
+    """Straight through the C ABI: x and y as [B, 29] views of wider storage (row pitch 32: the element-wise tile copies),
+    log-det accumulated onto an existing vector, and an empty batch."""
+    import ctypes
+    from vcnf_b200 import _lib
+    from vcnf_b200._lib import ptr, stream
+    torch.manual_seed(3)
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    randomize(layer, scale=0.05)
+    layer = layer.to(DEV)
+    c = layer.prqct
+    B = 1000
+    x = 1.5 * torch.randn(B, 29, device=DEV)
+    with torch.no_grad():
+        y_ref, ld_ref = c.forward(x)
+        f = c._fused_route(x, None)
+        w, b = c.transform_net.fused_params()
+        packed = f.pack(w, b)
+        shared = c._shared_params().contiguous()
+        xp = torch.zeros(B, 32, device=DEV)
+        xp[:, :29] = x
+        yp = torch.full((B, 32), 7.0, device=DEV)
+        ld = torch.full((B,), 2.0, device=DEV)
+        err = torch.zeros(1, dtype=torch.int32, device=DEV)
+
+        def call(rows):
+            _lib.call("vcnf_resnet_spline_fwd", ptr(xp), 32, ptr(yp), 32, ptr(ld), 1, rows, 29, 8, f.id_cols, f.n_in,
+                      f.tr_cols, f.Tc, f.Pc, f.hidden, f.num_blocks, ptr(packed), f.modes, f.bounds, f.wh_scale, 0,
+                      f.outside_zero, ptr(err), ptr(shared), f.Ts, f.Ps, f.smodes, f.sbounds, None, 0, None, stream())
+        call(0)                                    # nothing is touched
+        assert float(yp.min()) == 7.0 and float(ld.min()) == 2.0
+        call(B)
+    assert torch.equal(yp[:, :29], y_ref) and float(yp[:, 29:].min()) == 7.0     # same kernel, same tile arithmetic
+    assert_close(ld, ld_ref + 2.0, rtol=1e-6, atol=1e-5, what="fused accumulate logdet")
+    assert int(err) == 0
+
+
+def test_unsupported_shapes_keep_the_layerwise_kernels():
+    """hidden != 128 is not covered: the layer runs layer by layer, with the same results API."""
+    torch.manual_seed(4)
+    layer = nf.flows.CoupledRationalQuadraticSpline(8, 1, 64).to(DEV)
+    x = torch.randn(100, 8, device=DEV)
+    with torch.no_grad():
+        assert layer.prqct._fused_route(x, None) is None
+        before = ops.LAUNCHES
+        layer.forward(x)
+        assert ops.LAUNCHES - before > 3
