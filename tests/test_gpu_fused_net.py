@@ -190,3 +190,32 @@ def test_unsupported_shapes_keep_the_layerwise_kernels():
         before = ops.LAUNCHES
         layer.forward(x)
         assert ops.LAUNCHES - before > 3
+
+
+def test_fused_training_step_against_oracle_gradients():
+    """forward_kld of a two-layer cfg-2-shaped model (hidden 128: the fused forward with saved outputs + the
+    layer-by-layer backward kernels) against the oracle evaluated in fp64: loss and every parameter gradient."""
+    from cases import build_cfg2_small
+    from parity import assert_grads_close
+    torch.manual_seed(21)
+    ref = build_cfg2_small(oracle, layers=2, d=29, hidden=128)
+    randomize(ref, scale=0.05)
+    model = build_cfg2_small(nf, layers=2, d=29, hidden=128)
+    model.load_state_dict(ref.state_dict())
+    model = model.to(DEV)
+    ref = ref.double()
+    x = 1.2 * torch.randn(512, 29)
+    before = ops.LAUNCHES
+    loss = model.forward_kld(x.to(DEV))
+    loss.backward()
+    fused_launches = ops.LAUNCHES - before
+    lr = -torch.mean(ref.log_prob(x.double()))          # = forward_kld without categorical columns (core.py:36-67)
+    lr.backward()
+    assert_close(loss.detach().cpu(), lr.detach().float(), rtol=1e-4, atol=2e-4, what="fused train loss vs oracle")
+    got = {n: p.grad.detach().cpu() for n, p in model.named_parameters()}
+    want = {n: (p.grad.float() if p.grad is not None else None) for n, p in ref.named_parameters()}
+    assert_grads_close(got, want, rtol=1e-4, what="fused train vs oracle")
+    model.zero_grad(set_to_none=True)
+    before = ops.LAUNCHES
+    _layerwise(lambda: model.forward_kld(x.to(DEV)).backward())
+    assert fused_launches < ops.LAUNCHES - before          # the fused route really ran
