@@ -474,14 +474,15 @@ int vcnf_resnet_spline_pack(const void* const* W, const void* const* b, int n_in
  *     raw id columns and the output carries their CDF; sampling direction: the id columns are inverted first and the
  *     net sees the result (coupling.py:98-125)
  *   params (optional, [B, Tc * Pc] with row pitch ldp) receives the spline parameters, acts (optional,
- *     [1 + 2 num_blocks][B, 128] contiguous) the pre-activation output of every linear layer. */
+ *     [1 + 2 num_blocks][B, 128] contiguous) the pre-activation output of every linear layer, xid (optional,
+ *     [B, n_in] with row pitch ldxid) the gathered net inputs x[:, id_cols] (density direction: the raw columns). */
 int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64_t ldy, void* logdet, int accumulate,
                            int64_t B, int D, int K, const int32_t* id_cols, int n_in, const int32_t* tr_cols,
                            int Tc, int Pc, int hidden, int num_blocks, const void* packed,
                            const uint8_t* modes, const float* bounds, double wh_scale, int inverse,
                            int outside_zero, int32_t* err_flag, const void* shared_params, int Ts, int Ps,
                            const uint8_t* shared_modes, const float* shared_bounds, void* params, int64_t ldp,
-                           void* acts, void* stream);
+                           void* acts, void* xid, int64_t ldxid, void* stream);
 
 #ifdef __cplusplus
 }

@@ -171,7 +171,8 @@ def test_c_abi_padded_rows_and_accumulate():
         def call(rows):
             _lib.call("vcnf_resnet_spline_fwd", ptr(xp), 32, ptr(yp), 32, ptr(ld), 1, rows, 29, 8, f.id_cols, f.n_in,
                       f.tr_cols, f.Tc, f.Pc, f.hidden, f.num_blocks, ptr(packed), f.modes, f.bounds, f.wh_scale, 0,
-                      f.outside_zero, ptr(err), ptr(shared), f.Ts, f.Ps, f.smodes, f.sbounds, None, 0, None, stream())
+                      f.outside_zero, ptr(err), ptr(shared), f.Ts, f.Ps, f.smodes, f.sbounds, None, 0, None, None, 0,
+                      stream())
         call(0)                                    # nothing is touched
         assert float(yp.min()) == 7.0 and float(ld.min()) == 2.0
         call(B)

@@ -78,7 +78,8 @@ _SIGNATURES = {
     "vcnf_adam_flat": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _dbl, _dbl, _dbl, _dbl, _dbl, _i32, _vp],
     "vcnf_resnet_spline_pack": [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp],
     "vcnf_resnet_spline_fwd": [_vp, _i64, _vp, _i64, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32,
-                               _vp, _vp, _vp, _dbl, _i32, _i32, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _i64, _vp, _vp],
+                               _vp, _vp, _vp, _dbl, _i32, _i32, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _i64, _vp, _vp, _i64,
+                               _vp],
 }
 _I64_RETURN = {
     "vcnf_rqs_layer_bwd_workspace": [_i32, _i32, _i32],

@@ -78,6 +78,7 @@ struct Args {
   float sbounds[kMaxD];
   float* params; int64_t ldp;           // optional: theta [B, Tc * Pc]
   float* acts; int64_t act_stride;      // optional: pre-activation outputs of every layer, [1 + 2 nb][B, 128]
+  float* xid; int64_t ldxid;            // optional: the gathered net inputs x[:, id_cols], [B, n_in]
 };
 
 // ---- raw PTX wrappers (same conventions as gemm_tf32x3.cu) ------------------------------------------------------
@@ -512,6 +513,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         for (int c = 0; c < kCW; ++c) {
           const int kcol = g * kCW + c;
           const float v = (kcol < a.n_in) ? xs[row * D + s_id[kcol < a.n_in ? kcol : 0]] : 0.f;
+          if (a.xid && kcol < a.n_in && m0 + row < a.B) a.xid[(m0 + row) * a.ldxid + kcol] = v;
           float hi, lo;
           split_tf32(v, hi, lo);
           hh[c] = __float_as_uint(hi); ll[c] = __float_as_uint(lo);
@@ -739,7 +741,7 @@ extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64
                                       const uint8_t* modes, const float* bounds, double wh_scale, int inverse,
                                       int outside_zero, int32_t* err_flag, const void* shared_params, int Ts, int Ps,
                                       const uint8_t* shared_modes, const float* shared_bounds, void* params,
-                                      int64_t ldp, void* acts, void* stream) {
+                                      int64_t ldp, void* acts, void* xid, int64_t ldxid, void* stream) {
   if (Ts < 0 || (Ts > 0 && (!shared_params || !shared_modes || !shared_bounds))) return VCNF_E_BADARG;
   if (Ts != 0 && Ts != n_in) return VCNF_E_UNSUPPORTED;   // the shared splines act on the net's input columns
   if (!x || !y || !logdet || !id_cols || !tr_cols || !packed || !modes || !bounds || B < 0 || D < 1) return VCNF_E_BADARG;
@@ -764,6 +766,7 @@ extern "C" int vcnf_resnet_spline_fwd(const void* x, int64_t ldx, void* y, int64
   for (int i = 0; i < Ts; ++i) { a.smodes[i] = shared_modes[i]; a.sbounds[i] = shared_bounds[i]; }
   a.params = static_cast<float*>(params); a.ldp = ldp;
   a.acts = static_cast<float*>(acts); a.act_stride = B * kH;
+  a.xid = static_cast<float*>(xid); a.ldxid = ldxid;
   const size_t smem = smem_bytes(num_blocks, a.n_slices, D);
   const int sms = sm_count() > 0 ? sm_count() : VCNF_SM_COUNT_DEFAULT;
   const int64_t tiles = (B + kRows - 1) / kRows;

@@ -388,10 +388,11 @@ class PiecewiseRationalQuadraticCoupling(Coupling):
         if fused is not None and self.transform_net.hidden_features <= ops.KSLICE:
             # training: values from the one fused launch, graph (and backward kernels) of the layer-by-layer path
             shared = self._shared_params()
-            y, ld, params, acts = ops.resnet_spline(
+            y, ld, params, acts, xid = ops.resnet_spline(
                 inputs.detach(), fused, *self.transform_net.fused_params(), inverse=False, shared=shared,
-                want_params="padded" if self.transform_net.padded_out else True, want_acts=True)
-            identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)
+                want_params="padded" if self.transform_net.padded_out else True, want_acts=True,
+                want_xid="padded" if self._pad_rows else True)
+            identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows, pre=xid)
             params = self.transform_net(identity_split, None, pre=(acts, params))
             return ops.rqs_layer(inputs, params, shared, self._specs["both"], False, pre=(y, ld))
         identity_split = ops.gather_cols(inputs, self._cols(inputs.device), self._pad_rows)

@@ -144,10 +144,14 @@ def rqs_layer(x, cond, shared, spec, inverse, want_bins=False, pre=None):
 
 class _GatherCols(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, cols, pad):
+    def forward(ctx, x, cols, pad, pre=None):
         x = x.contiguous()
         B, D = x.shape
         n = cols.numel()
+        if pre is not None:            # already gathered by the fused net + spline kernel: only the graph node
+            ctx.save_for_backward(cols)
+            ctx.D = D
+            return pre
         out = _padded_empty(B, n, x.dtype, x.device) if pad else torch.empty((B, n), dtype=x.dtype, device=x.device)
         _launch("vcnf_gather_cols", ptr(x), D, ptr(out), out.stride(0), B, n, ptr(cols), dtype_code(x), stream())
         ctx.save_for_backward(cols)
@@ -162,13 +166,13 @@ class _GatherCols(torch.autograd.Function):
         B, n = g.shape
         gx = torch.empty((B, ctx.D), dtype=g.dtype, device=g.device)
         _launch("vcnf_scatter_cols", ptr(g), g.stride(0), ptr(gx), ctx.D, B, n, ctx.D, ptr(cols), 0, dtype_code(g), stream())
-        return gx, None, None
+        return gx, None, None, None
 
 
-def gather_cols(x, cols_i32, pad=False):
+def gather_cols(x, cols_i32, pad=False, pre=None):
     """x[:, cols].  pad=True returns a view whose row pitch is a 16-byte multiple (for consumers that
     take a leading dimension, i.e. ops.linear)."""
-    return _GatherCols.apply(x, cols_i32, pad)
+    return _GatherCols.apply(x, cols_i32, pad, pre)
 
 
 class _AffineCoupling(torch.autograd.Function):
@@ -1375,7 +1379,7 @@ class FusedNetSpec:
         return buf
 
 
-def resnet_spline(x, fspec, weights, biases, inverse, shared=None, want_params=False, want_acts=False):
+def resnet_spline(x, fspec, weights, biases, inverse, shared=None, want_params=False, want_acts=False, want_xid=False):
     """The whole ResidualNet conditioner + the coupling spline in one launch (vcnf_resnet_spline_fwd), no gradient.
     weights / biases: contiguous fp32 parameters in forward order; shared: [Ts, Ps] parameters of the unconditional
     spline on the identity columns (or None).  Returns (y, logabsdet[, params][, acts])."""
@@ -1393,14 +1397,21 @@ def resnet_spline(x, fspec, weights, biases, inverse, shared=None, want_params=F
                   else torch.empty((B, fspec.Tc * fspec.Pc), dtype=x.dtype, device=x.device))
     acts = (torch.empty((1 + 2 * fspec.num_blocks, B, fspec.hidden), dtype=x.dtype, device=x.device)
             if want_acts else None)
+    xid = None
+    if want_xid:          # x[:, id_cols]: what gather_cols would return ("padded": 16-byte-multiple row pitch)
+        xid = (_padded_empty(B, fspec.n_in, x.dtype, x.device) if want_xid == "padded"
+               else torch.empty((B, fspec.n_in), dtype=x.dtype, device=x.device))
     _launch("vcnf_resnet_spline_fwd", ptr(x), D, ptr(y), D, ptr(ld), 0, B, D, fspec.K, fspec.id_cols, fspec.n_in,
             fspec.tr_cols, fspec.Tc, fspec.Pc, fspec.hidden, fspec.num_blocks, ptr(packed), fspec.modes, fspec.bounds,
             fspec.wh_scale, int(inverse), fspec.outside_zero, None, ptr(shared), fspec.Ts, fspec.Ps, fspec.smodes,
             fspec.sbounds, ptr(params),
-            params.stride(0) if params is not None else 0, ptr(acts), stream())
+            params.stride(0) if params is not None else 0, ptr(acts), ptr(xid), xid.stride(0) if xid is not None else 0,
+            stream())
     out = (y, ld)
     if want_params:
         out += (params,)
     if want_acts:
         out += (acts,)
+    if want_xid:
+        out += (xid,)
     return out
