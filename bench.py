@@ -209,9 +209,11 @@ def kernel_roofline(model, dev, flush):
                   gbv.data_ptr(), wws.data_ptr(), B, HIDDEN, HIDDEN, 1, torch.cuda.current_stream().cuda_stream)
 
     kernels = (("linear_ts_kernel (vcnf_linear_tf32x3 fwd/dgrad: hidden 128x128, relu+bias+residual fused)", lin_fwd,
-                4 * (3 * HIDDEN), 224),                       # read h (A and residual), write y
+                4 * (3 * HIDDEN), 128),                       # read h (A and residual), write y; 128 per step = the
+                                                              # input-gradient GEMMs (the forward ones are inside
+                                                              # resnet_spline_kernel since round 2, see other_kernels)
                ("linear_wgrad_tma_kernel (vcnf_linear_wgrad_tf32x3, + reduce)", lin_wgrad, 4 * (2 * HIDDEN), 96),
-               ("rqs_layer_fwd_fast_kernel (vcnf_rqs_layer_fwd)", fwd, 4 * (P + 2 * D + 1), 16),
+               ("rqs_layer_fwd_fast_kernel (vcnf_rqs_layer_fwd)", fwd, 4 * (P + 2 * D + 1), 0),   # not in the cfg-2 step any more
                ("rqs_layer_bwd_fast_kernel (vcnf_rqs_layer_bwd, + shared-grad reduce)", bwd, 4 * (2 * P + 3 * D + 1), 16))
     for name, fn, bytes_per_sample, per_step in kernels:
         ms = _time_launches(fn, flush)
