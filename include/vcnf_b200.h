@@ -203,6 +203,11 @@ int vcnf_lu_compose_bwd(const void* lower_entries, const void* upper_entries, co
 int vcnf_lu_compose_fwd_batched(const void* const* lower_entries, const void* const* upper_entries,
                                 const void* const* diag_raw, double eps, int D, int n, void* const* W,
                                 void* const* logabsdet, int dtype, void* stream);
+/* (L U)^-1 and log|det L U| of n <= 32 layers of equal D in one launch (grid D x n): a sampling pass of a model inverts
+ * every LU layer once, and none of them depends on the samples (mixing.py:412-429 x n; vcnf_lu_inverse per layer). */
+int vcnf_lu_inverse_batched(const void* const* lower_entries, const void* const* upper_entries,
+                            const void* const* diag_raw, double eps, int D, int n, void* const* Winv,
+                            void* const* logabsdet, int dtype, void* stream);
 int vcnf_lu_compose_bwd_batched(const void* const* lower_entries, const void* const* upper_entries,
                                 const void* const* diag_raw, double eps, int D, int n, const void* const* gW,
                                 const void* const* glogabsdet, void* const* g_lower, void* const* g_upper,

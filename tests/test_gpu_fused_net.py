@@ -220,3 +220,27 @@ def test_fused_training_step_against_oracle_gradients():
     before = ops.LAUNCHES
     _layerwise(lambda: model.forward_kld(x.to(DEV)).backward())
     assert fused_launches < ops.LAUNCHES - before          # the fused route really ran
+
+
+def test_sample_with_batched_lu_inverses_matches_the_per_layer_path():
+    """sample() without gradients inverts all LU layers in one launch and folds their log-dets into one term; with
+    gradients enabled every layer forms its own inverse (and the coupling layers run layer by layer)."""
+    from cases import build_cfg2_small
+    torch.manual_seed(31)
+    model = build_cfg2_small(nf, layers=3, d=29, hidden=128)
+    randomize(model, scale=0.05)
+    model = model.to(DEV)
+    torch.manual_seed(5)
+    with torch.no_grad():
+        before = ops.LAUNCHES
+        z, lq = model.sample(777)
+        fast = ops.LAUNCHES - before
+    torch.manual_seed(5)
+    before = ops.LAUNCHES
+    zr, lqr = _layerwise(model.sample, 777)     # grad mode: per-layer inverses, layer-by-layer coupling kernels
+    assert fast < ops.LAUNCHES - before
+    assert_close(z, zr.detach(), **SPLINE, what="sample z, batched LU inverses")
+    assert_close(lq, lqr.detach(), rtol=SPLINE["rtol"], atol=3 * 29 * SPLINE["atol"], what="sample log_q, batched LU inverses")
+    for f in model.flows:                       # nothing is left behind for a later call
+        if hasattr(f, "linear"):
+            assert "_pre_inv" not in f.linear.__dict__

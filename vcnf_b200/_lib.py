@@ -45,6 +45,7 @@ _SIGNATURES = {
     "vcnf_lu_inverse": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd": [_vp, _vp, _vp, _dbl, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_fwd_batched": [_vp, _vp, _vp, _dbl, _i32, _i32, _vp, _vp, _i32, _vp],
+    "vcnf_lu_inverse_batched": [_vp, _vp, _vp, _dbl, _i32, _i32, _vp, _vp, _i32, _vp],
     "vcnf_lu_compose_bwd_batched": [_vp, _vp, _vp, _dbl, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _vp],
     "vcnf_im2col": [_vp, _i64, _i64, _i64, _i64, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _dbl, _i32, _vp],
     "vcnf_col2im": [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _dbl, _vp],

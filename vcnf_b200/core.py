@@ -185,9 +185,25 @@ class NormalizingFlow(nn.Module):
     def sample(self, num_samples=1):
         """core.py:144-168."""
         z, log_q = self.q0(num_samples)
-        for flow in self.flows:
-            z, log_det = flow(z)
-            log_q -= log_det
+        lus, ld_lu = [], None
+        if not torch.is_grad_enabled():
+            # every LU layer is inverted once per pass and none depends on the samples: one launch for all of them, their
+            # log-dets as one model-level term (flows/mixing.py precompute_lu_inverses)
+            cache = self.__dict__.get("_lu_cache")
+            if cache is None or cache[0] != len(self.flows):
+                cache = (len(self.flows), [f.linear for f in self.flows if isinstance(f, mixing.LULinearPermute)])
+                self.__dict__["_lu_cache"] = cache
+            if len(cache[1]) >= 2:
+                lus, ld_lu = mixing.precompute_lu_inverses(cache[1], absorb=True)
+        try:
+            for flow in self.flows:
+                z, log_det = flow(z)
+                if log_det is not mixing.ABSORBED:
+                    log_q -= log_det
+        finally:
+            mixing.clear_lu_weights(lus)
+        if ld_lu is not None:       # sampling direction: log|det| of each layer is -log|det L U|, and log_q -= log_det
+            log_q += ops.broadcast_scalar(ld_lu.to(torch.promote_types(ld_lu.dtype, z.dtype)), len(z))
         if self.categoricals is not None and len(self.categoricals) > 0:
             idx = self._cat_index(z.device)
             zc = z[:, idx]

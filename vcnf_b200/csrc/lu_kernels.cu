@@ -104,8 +104,8 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kLuInvThreads) lu_inverse_kernel(const T* lower, const T* upper, const T* diag_raw, T eps,
-                                                                   int D, T* Winv, T* logabsdet) {
+__device__ __forceinline__ void lu_inverse_body(const T* lower, const T* upper, const T* diag_raw, T eps, int D, T* Winv,
+                                                T* logabsdet) {
   extern __shared__ __align__(16) unsigned char lu_smem[];
   const int ld = D + 1;
   T* Ls = reinterpret_cast<T*>(lu_smem);
@@ -144,6 +144,20 @@ __global__ void __launch_bounds__(kLuInvThreads) lu_inverse_kernel(const T* lowe
     acc = warp_sum(acc);
     if (lane == 0) *logabsdet = acc;
   }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kLuInvThreads) lu_inverse_kernel(const T* lower, const T* upper, const T* diag_raw, T eps,
+                                                                   int D, T* Winv, T* logabsdet) {
+  lu_inverse_body(lower, upper, diag_raw, eps, D, Winv, logabsdet);
+}
+
+// n layers in one launch: grid (D, n), blockIdx.y = layer (a sampling pass inverts every LU layer of the model once).
+template <typename T>
+__global__ void __launch_bounds__(kLuInvThreads) lu_inverse_batched_kernel(const LuBatch b, T eps, int D) {
+  const int l = blockIdx.y;
+  lu_inverse_body(static_cast<const T*>(b.lower[l]), static_cast<const T*>(b.upper[l]), static_cast<const T*>(b.diag[l]), eps,
+                  D, static_cast<T*>(b.out0[l]), static_cast<T*>(b.out1[l]));
 }
 
 // Given gW = dLoss/dW and gl = dLoss/d log|det|:  gL = gW U^T (strictly lower part), gU = L^T gW (upper part),
@@ -403,6 +417,34 @@ extern "C" int vcnf_lu_inverse(const void* lower, const void* upper, const void*
     lu_inverse_kernel<double><<<D, kLuInvThreads, smem, st>>>(static_cast<const double*>(lower), static_cast<const double*>(upper),
                                                            static_cast<const double*>(diag_raw), eps, D,
                                                            static_cast<double*>(Winv), static_cast<double*>(logabsdet));
+  return launch_status();
+}
+
+extern "C" int vcnf_lu_inverse_batched(const void* const* lower, const void* const* upper, const void* const* diag_raw,
+                                       double eps, int D, int n, void* const* Winv, void* const* logabsdet, int dtype,
+                                       void* stream) {
+  if (n == 0) return 0;
+  if (!diag_raw || !Winv || !logabsdet || D <= 0 || n < 0 || (D > 1 && (!lower || !upper)) ||
+      (dtype != VCNF_F32 && dtype != VCNF_F64))
+    return VCNF_E_BADARG;
+  if (D > kLuMaxD || n > kLuBatchMax) return VCNF_E_UNSUPPORTED;
+  LuBatch b{};
+  for (int l = 0; l < n; ++l) {
+    b.lower[l] = lower ? lower[l] : nullptr; b.upper[l] = upper ? upper[l] : nullptr; b.diag[l] = diag_raw[l];
+    b.out0[l] = Winv[l]; b.out1[l] = logabsdet[l];
+    if (!b.diag[l] || !b.out0[l] || !b.out1[l] || (D > 1 && (!b.lower[l] || !b.upper[l]))) return VCNF_E_BADARG;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = 2 * static_cast<size_t>(D) * (D + 1) * (dtype == VCNF_F32 ? 4 : 8);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(lu_inverse_batched_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(lu_inverse_batched_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    attr_set = true;
+  }
+  const dim3 grid(static_cast<unsigned>(D), static_cast<unsigned>(n));
+  if (dtype == VCNF_F32) lu_inverse_batched_kernel<float><<<grid, kLuInvThreads, smem, st>>>(b, static_cast<float>(eps), D);
+  else lu_inverse_batched_kernel<double><<<grid, kLuInvThreads, smem, st>>>(b, eps, D);
   return launch_status();
 }
 

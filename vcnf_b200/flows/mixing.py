@@ -242,6 +242,12 @@ class _LULinear(Flow):
 
     def inverse(self, inputs, context=None, out_idx=None):
         needs_grad = torch.is_grad_enabled() and (inputs.requires_grad or self.lower_entries.requires_grad)
+        pre = self.__dict__.pop("_pre_inv", None)               # formed by precompute_lu_inverses for this pass
+        if pre is not None and not needs_grad and pre[0].dtype == inputs.dtype:
+            out = ops.small_linear(inputs, pre[0], self.bias, out_idx=out_idx, sub_bias_first=True)
+            if pre[1] is None:                                  # -log|det| absorbed into the model-level sum
+                return out, None
+            return out, ops.broadcast_scalar(-pre[1].to(torch.promote_types(pre[1].dtype, inputs.dtype)), out.shape[0])
         if self._fused() and not needs_grad:
             # sampling without a gradient: (L U)^-1 and log|det| from one kernel instead of ~25 tiny launches
             winv, logabsdet = ops.lu_inverse(self.lower_entries, self.upper_entries, self.unconstrained_upper_diag,
@@ -288,9 +294,39 @@ def precompute_lu_weights(layers, absorb=False):
     return served, total
 
 
+def precompute_lu_inverses(layers, absorb=False):
+    """Sampling direction without gradients: (L U)^-1 and log|det| of every `_LULinear` in `layers` with ONE launch per
+    group of equal (D, dtype, eps) (ops.lu_inverse_batched) instead of one launch per layer; each layer's next
+    `_LULinear.inverse` call picks its pair up.  Returns (layers served, total) like precompute_lu_weights: with `absorb`
+    the served layers return ABSORBED and `total` is the 0-dim sum of their log|det W| (the sampling direction's log-det
+    is its negative)."""
+    total = None
+    groups = {}
+    for m in layers:
+        if m._fused() and m.features > 0:
+            key = (m.features, m.lower_entries.dtype, float(m.eps), m.lower_entries.device)
+            groups.setdefault(key, []).append(m)
+    served = []
+    for (_, _, eps, _), ms in groups.items():
+        for k in range(0, len(ms), ops.LU_BATCH_MAX):
+            chunk = ms[k:k + ops.LU_BATCH_MAX]
+            if len(chunk) < 2:
+                continue
+            pairs, lds = ops.lu_inverse_batched([(m.lower_entries, m.upper_entries, m.unconstrained_upper_diag)
+                                                 for m in chunk], eps)
+            for m, pr in zip(chunk, pairs):
+                m.__dict__["_pre_inv"] = (pr[0], None) if absorb else pr
+            if absorb:
+                part = lds.sum()
+                total = part if total is None else total + part
+            served += chunk
+    return served, total
+
+
 def clear_lu_weights(layers):
     for m in layers:
         m.__dict__.pop("_pre", None)
+        m.__dict__.pop("_pre_inv", None)
 
 
 class LULinearPermute(Flow):
@@ -309,6 +345,8 @@ class LULinearPermute(Flow):
         perm = _i32(self.permutation._permutation)
         # out[:, perm[o]] = v[o]  ==  v[:, argsort(perm)]
         z, log_det = self.linear.inverse(z, out_idx=perm)
+        if log_det is None:
+            return z, ABSORBED
         return z, log_det.view(-1)
 
     def inverse(self, z):

@@ -630,6 +630,23 @@ def lu_inverse(lower_entries, upper_entries, unconstrained_upper_diag, eps):
     return winv, logabsdet
 
 
+def lu_inverse_batched(triples, eps):
+    """[(lower_entries, upper_entries, unconstrained_upper_diag)] * n -> [((L U)^-1, log|det L U|)] * n in one launch
+    (no gradient; equal D, one dtype, n <= LU_BATCH_MAX)."""
+    n = len(triples)
+    flat = _promote(*[t.detach() for tr in triples for t in tr])
+    lower = [flat[3 * i].contiguous() for i in range(n)]
+    upper = [flat[3 * i + 1].contiguous() for i in range(n)]
+    diag = [flat[3 * i + 2].contiguous() for i in range(n)]
+    D = diag[0].numel()
+    dt, dev = diag[0].dtype, diag[0].device
+    winv = torch.empty((n, D, D), dtype=dt, device=dev)
+    lds = torch.empty((n,), dtype=dt, device=dev)
+    _launch("vcnf_lu_inverse_batched", _ptr_array(lower), _ptr_array(upper), _ptr_array(diag), float(eps), D, n,
+            _ptr_array([winv[i] for i in range(n)]), _ptr_array([lds[i] for i in range(n)]), dtype_code(diag[0]), stream())
+    return [(winv[i], lds[i]) for i in range(n)], lds
+
+
 class _BroadcastScalar(torch.autograd.Function):
     """A 0-dim tensor repeated over the batch (`logabsdet * inputs.new_ones(batch_size)`, mixing.py:410,429):
     one copy kernel forward instead of fill + multiply; the adjoint (sum of the n incoming gradients) as two
