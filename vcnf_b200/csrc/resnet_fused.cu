@@ -488,13 +488,15 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
     uint32_t uc = 0, k = 0;
     int flag = 0;
     int ei = warp == kEpiWarp0 ? 0 : 1000;
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++k) {
-      const int64_t m0 = tile * kRows;
-      const uint32_t xb = k & 1u;
-      float* xs = xs0 + xb * (kRows * D);
-      FTRACE(1, ei); ++ei;
-      mbar_wait(&x_full[xb], (k >> 1) & 1u);
-      FTRACE(1, ei); ++ei;
+    // Prologue of a tile: wait for its prefetched x, (sampling direction) unconditional splines of the id columns,
+    // first-layer operand -> tensor memory, (density direction) unconditional splines.  Returns the log-det collected
+    // so far.  It runs for tile t + 1 in the middle of tile t's LAST head slice (right after that slice's accumulator is
+    // staged: every MMA of tile t has retired, the operand columns are free), so the first layer of the next tile
+    // computes while the last splines of this one are evaluated and its outputs stored.
+    auto prologue = [&](int64_t tile_p, uint32_t kp) -> float {
+      const int64_t m0 = tile_p * kRows;
+      float* xs = xs0 + (kp & 1u) * (kRows * D);
+      mbar_wait(&x_full[kp & 1u], (kp >> 1) & 1u);
       float ldsum = 0.f;
       if (INV && a.Ts > 0) {            // sampling direction: the id columns go through their own spline FIRST
         for (int j = g; j < a.Ts; j += kG) {
@@ -535,6 +537,16 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
           ldsum += l;
         }
       }
+      return ldsum;
+    };
+    float ld_next = 0.f;
+    if (static_cast<int64_t>(blockIdx.x) < n_tiles) ld_next = prologue(blockIdx.x, 0);
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++k) {
+      const int64_t m0 = tile * kRows;
+      const uint32_t xb = k & 1u;
+      float* xs = xs0 + xb * (kRows * D);
+      const bool has_next = tile + gridDim.x < n_tiles;
+      float ldsum = ld_next;
 
       FTRACE(1, ei); ++ei;
       for (int u = 0; u < L; ++u, ++uc) {
@@ -627,6 +639,7 @@ __global__ void __launch_bounds__(kThreads, 1) resnet_spline_kernel(const __grid
         __syncwarp();
         if (lane == 0) mbar_arrive(acc_empty);
         FTRACE(1, ei); ++ei;
+        if (s == S - 1 && has_next) ld_next = prologue(tile + gridDim.x, k + 1);
         epi_bar();
         const int nf = (a.Tc - s * a.fs) < a.fs ? (a.Tc - s * a.fs) : a.fs;
         if (a.params) {                                // the slice's parameters, one row per warp pass: coalesced
