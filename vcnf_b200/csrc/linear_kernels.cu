@@ -350,10 +350,21 @@ __global__ void __launch_bounds__(kBwdThreads, 2) small_linear_bwd_kernel(const 
       if (st) par1 ^= 1u; else par0 ^= 1u;
       const T* rx = raw + static_cast<size_t>(st) * 2 * TR * D;
       const T* rg = rx + static_cast<size_t>(TR) * D;
-      for (int e = tid; e < n; e += kBwdThreads) {
-        const int r = e / D, c = e - r * D;
-        xs[r * PD + inv_in[c]] = rx[e];
-        gs[r * PD + inv_out[c]] = rg[e];
+      if (D <= 32) {                                   // lane = column (its permuted slots are loop invariants), warp = row:
+        const int c = tid & 31;                        // no division and no index lookup per element
+        if (c < D) {
+          const int ci = inv_in[c], co = inv_out[c];
+          for (int r = tid >> 5; r < nr; r += kBwdThreads / 32) {
+            xs[r * PD + ci] = rx[r * D + c];
+            gs[r * PD + co] = rg[r * D + c];
+          }
+        }
+      } else {
+        for (int e = tid; e < n; e += kBwdThreads) {
+          const int r = e / D, c = e - r * D;
+          xs[r * PD + inv_in[c]] = rx[e];
+          gs[r * PD + inv_out[c]] = rg[e];
+        }
       }
     } else {
       const T* sx = a.x + r0 * D;
@@ -405,9 +416,17 @@ __global__ void __launch_bounds__(kBwdThreads, 2) small_linear_bwd_kernel(const 
     if (a.gx) {
       __syncthreads();
       T* dst = a.gx + r0 * D;
-      for (int e = tid; e < n; e += kBwdThreads) {
-        const int r = e / D, c = e - r * D;
-        dst[e] = os[r * PD + inv_in[c]];
+      if (D <= 32) {
+        const int c = tid & 31;
+        if (c < D) {
+          const int ci = inv_in[c];
+          for (int r = tid >> 5; r < nr; r += kBwdThreads / 32) dst[r * D + c] = os[r * PD + ci];
+        }
+      } else {
+        for (int e = tid; e < n; e += kBwdThreads) {
+          const int r = e / D, c = e - r * D;
+          dst[e] = os[r * PD + inv_in[c]];
+        }
       }
     }
   }
