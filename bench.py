@@ -510,6 +510,12 @@ def extra_kernel_rooflines(dev, flush):
             "frac": tf / tpeak, "flops_per_launch": 3 * 2.0 * macs * BATCH,
             "bytes_per_launch": (2 * 4 * D + 4) * BATCH,
             "note": "executed TF32 flops (3 MMAs per fp32 product, unpadded shapes); HBM traffic is x in, y and log|det| out"}
+        try:        # dram bytes of one launch from the committed ncu --set full capture (profiles/r2_fused_ncu_summary.txt:
+            #         the 7.6 MB of y were still in L2 when the capture ended, so this is the read side)
+            out["resnet_spline_kernel (vcnf_resnet_spline_fwd, cfg 2 layer, no-grad direction)"]["traffic"] = json.load(
+                open(os.path.join(ROOT, "profiles", "traffic.json"))).get("resnet_spline_kernel")
+        except Exception:                                      # noqa: BLE001
+            pass
     except Exception as exc:                                   # noqa: BLE001
         out["resnet_spline_kernel"] = {"error": repr(exc)[:200]}
     return out
