@@ -87,3 +87,21 @@ def test_fused_net_shape_queries_run_without_a_gpu():
     assert _lib.query("vcnf_resnet_spline_pack_bytes", 15, 64, 2, 14, 23) == -2       # hidden must be 128
     assert _lib.query("vcnf_resnet_spline_pack_bytes", 40, 128, 2, 14, 23) == -2      # more than 32 net inputs
     assert _lib.query("vcnf_resnet_spline_pack_bytes", 15, 128, 2, 32, 25) == -2      # 32 features x 32 columns > 4 slices
+
+
+def test_fused_route_is_a_cuda_only_choice():
+    """Host logic of the fused conditioner + spline route: never taken for host tensors (the layer-by-layer ops then raise
+    the usual 'no CPU path' error), its specification is built from the layer's own column lists and tail modes."""
+    import torch
+    import vcnf_b200 as nf
+    from vcnf_b200 import ops
+    layer = nf.flows.CoupledRationalQuadraticSpline(29, 2, 128)
+    c = layer.prqct
+    x = torch.randn(4, 29)
+    assert c._fused_route(x, None) is None
+    spec = ops.FusedNetSpec(c.identity_features.tolist(), c.transform_features.tolist(), [ops.TAIL_LINEAR] * 14, [3.0] * 14,
+                            8, 23, 1.0 / 128 ** 0.5, False, 128, 2, [ops.TAIL_LINEAR] * 15, [3.0] * 15, 23)
+    assert spec.supported and spec.n_in == 15 and spec.Tc == 14 and spec.Ts == 15
+    assert list(spec.id_cols) == c.identity_features.tolist() and list(spec.tr_cols) == c.transform_features.tolist()
+    assert not ops.FusedNetSpec([0], [1], [ops.TAIL_LINEAR], [3.0], 8, 23, 1.0, False, 64, 2).supported      # hidden 64
+    assert not ops.FusedNetSpec([0], [1], [ops.TAIL_LINEAR], [3.0], 10, 29, 1.0, False, 128, 2).supported    # 10 bins
