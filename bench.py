@@ -719,17 +719,19 @@ def gpu_run(args):
         sample_rate = world * BATCH / (sample_ms * 1e-3)
         sample_ok = bool(torch.isfinite(z_s).all() and torch.isfinite(lq_s).all())
         # model.log_prob(x) on the bench batch, no gradients (evaluation): eager calls, CUDA events
+        logp = parallel.GraphedLogProb(model, x_dev) if not args.no_graph else (lambda xb: model.log_prob(xb))
         for _ in range(3):
-            model.log_prob(x_dev)
+            logp(x_dev)
         torch.cuda.synchronize()
         l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0.record()
         for _ in range(10):
-            lp = model.log_prob(x_dev)
+            lp = logp(x_dev)
         l1.record()
         torch.cuda.synchronize()
         logp_ms = l0.elapsed_time(l1) / 10
         logp_ok = bool(torch.isfinite(lp).all())
+        logp_graph = bool(getattr(logp, "graph", None) is not None)
 
     # strong-scaling point of cfg 3a (BASELINE: "batch 256K sharded over 8 GPUs"): global batch fixed at 262 144
     strong = None
@@ -798,7 +800,8 @@ def gpu_run(args):
         "sample": {"value": sample_rate, "unit": "samples/s", "batch": BATCH, "ms_per_draw": sample_ms,
                    "cuda_graph": draw_graph, "cuda_graph_error": draw_err, "finite": sample_ok},
         "log_prob": {"value": world * BATCH / (logp_ms * 1e-3), "unit": "samples/s", "batch": BATCH, "ms_per_call": logp_ms,
-                     "finite": logp_ok, "note": "model.log_prob(x) under no_grad on this rank, eager launches"},
+                     "finite": logp_ok, "cuda_graph": logp_graph,
+                     "note": "model.log_prob(x) without gradients on the bench batch (parallel.GraphedLogProb)"},
         "loss": float(loss_val),
     }
     _emit(line)

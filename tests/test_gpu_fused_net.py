@@ -244,3 +244,23 @@ def test_sample_with_batched_lu_inverses_matches_the_per_layer_path():
     for f in model.flows:                       # nothing is left behind for a later call
         if hasattr(f, "linear"):
             assert "_pre_inv" not in f.linear.__dict__
+
+
+def test_graphed_log_prob_matches_eager_and_sees_new_parameters():
+    """parallel.GraphedLogProb: the replayed evaluation equals the eager one, follows the input it is given, and
+    (weights are re-tiled inside the graph) follows parameter updates made between replays."""
+    from vcnf_b200 import parallel
+    from cases import build_cfg2_small
+    torch.manual_seed(41)
+    model = build_cfg2_small(nf, layers=2, d=29, hidden=128)
+    randomize(model, scale=0.05)
+    model = model.to(DEV)
+    x1, x2 = torch.randn(2048, 29, device=DEV), 1.3 * torch.randn(2048, 29, device=DEV)
+    lp = parallel.GraphedLogProb(model, x1)
+    assert lp.graph is not None, lp.capture_error
+    with torch.no_grad():
+        for x in (x1, x2):
+            assert torch.equal(lp(x), model.log_prob(x))
+        for p in model.parameters():
+            p.add_(0.01 * torch.randn_like(p))
+        assert torch.equal(lp(x2), model.log_prob(x2))

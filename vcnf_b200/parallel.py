@@ -291,3 +291,37 @@ class GraphedSampler:
                 return self.model.sample(self.n)
         self.graph.replay()
         return self.out
+
+
+class GraphedLogProb:
+    """`model.log_prob(x)` without gradients (evaluation; core.py:170-183) captured once for a fixed batch shape and
+    replayed: `lp = GraphedLogProb(model, x_example)(x)` -- x is copied into the static input, the result is a static
+    tensor overwritten by the next call.  Falls back to eager calls if capture is not possible."""
+
+    def __init__(self, model, x_example, warmup=3):
+        self.model = model
+        self.x = x_example.detach().clone()
+        self.graph, self.out, self.capture_error = None, None, None
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(warmup):
+                model.log_prob(self.x)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.no_grad(), torch.cuda.graph(g):
+                self.out = model.log_prob(self.x)
+            self.graph = g
+        except Exception as exc:            # noqa: BLE001 -- report and run eagerly
+            self.capture_error = _after_failed_capture(exc)
+            self.graph = None
+
+    def __call__(self, x):
+        if self.graph is None:
+            with torch.no_grad():
+                return self.model.log_prob(x)
+        self.x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        return self.out
