@@ -1,4 +1,6 @@
-"""Timeline of one tile of the fused net + spline kernel (needs a library built with -DVCNF_FUSED_TRACE)."""
+"""Timeline of one tile of the fused net + spline kernel.  Needs a library built with the trace points compiled in:
+    touch vcnf_b200/csrc/resnet_fused.cu && VCNF_NVCC_EXTRA=-DVCNF_FUSED_TRACE python -m vcnf_b200.build
+(rebuild without the variable afterwards: the trace stores cost ~7 % of the kernel)."""
 import os, sys, ctypes
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
